@@ -1,0 +1,101 @@
+"""Pins the CPU oracle (oracle/) against the hand-derived known answers and against its
+independent numpy restatement.  CPU only.  Reference: Helpers/RagIndex.cs:59-67,124-135."""
+import json
+import math
+import os
+
+import numpy as np
+import pytest
+
+from oracle import oracle_c as oc
+from oracle import oracle_np as onp
+
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+
+
+def _load(name):
+    with open(os.path.join(GOLD, name)) as f:
+        return json.load(f)
+
+
+def _rows(case):
+    rows = case["rows"]
+    if not rows:
+        return np.zeros((0, len(case["query"])), dtype=np.float32)
+    return np.asarray(rows, dtype=np.float32)
+
+
+def _check_scores(got, exp):
+    assert len(got) == len(exp)
+    for g, e in zip(got, exp):
+        if e == "nan":
+            assert math.isnan(g)
+        else:
+            assert g == e and math.copysign(1.0, g) == math.copysign(1.0, e), (g, e)
+
+
+@pytest.mark.parametrize("case", _load("kat_v1.json"), ids=lambda c: c["name"])
+@pytest.mark.parametrize("impl", ["c", "np"])
+def test_known_answers(case, impl):
+    rows, q = _rows(case), np.asarray(case["query"], dtype=np.float32)
+    mod = oc if impl == "c" else onp
+    idx, sc = mod.query(rows, q, case["top_k"])
+    assert list(idx) == case["expect_idx"]
+    _check_scores(list(sc), case["expect_score"])
+
+
+def test_kat_python_loop_agrees():
+    for case in _load("kat_v1.json"):
+        rows, q = _rows(case), np.asarray(case["query"], dtype=np.float32)
+        for r in range(rows.shape[0]):
+            a, b = onp.cosine_py(q, rows[r]), oc.cosine(q, rows[r])
+            assert (a == b) or (math.isnan(a) and math.isnan(b))
+
+
+def test_generator_pinned():
+    g = _load("synth_v1.json")
+    for key, bf in (("generator", False), ("generator_bf16", True)):
+        s = g[key]
+        want = np.asarray(s["f32_hex"], dtype=np.uint32).view(np.float32)
+        for mod in (oc, onp):
+            got = mod.synth_rows(s["row0"], s["n_rows"], s["dim"], s["seed"], round_bf16=bf)
+            assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+
+
+def _corpus(c, mod=oc):
+    corpus = mod.synth_rows(0, c["n"], c["dim"], c["corpus_seed"])
+    q = mod.synth_rows(0, 1, c["dim"], c["query_seed"])[0]
+    corpus[7] = corpus[42]
+    corpus[c["n"] - 3] = corpus[42]
+    corpus[13] = 0.0
+    corpus[21] = q
+    corpus[22] = -q
+    return corpus, q
+
+
+@pytest.mark.parametrize("ci", range(4))
+def test_seeded_queries_c_matches_fixture(ci):
+    c = _load("synth_v1.json")["queries"][ci]
+    corpus, q = _corpus(c)
+    for threads in (1, 3):
+        idx, sc = oc.query(corpus, q, c["top_k"], n_threads=threads)
+        assert [int(i) for i in idx] == c["expect_idx"]
+        assert [float(s).hex() for s in sc] == c["expect_score_hex"]
+
+
+def test_c_and_numpy_bitwise_equal_scores():
+    rng = np.random.default_rng(0)
+    rows = rng.standard_normal((513, 131)).astype(np.float32) * 3.0
+    q = rng.standard_normal(131).astype(np.float32)
+    a, b = oc.score_all(rows, q), onp.score_all(rows, q)
+    assert np.array_equal(a.view(np.uint64), b.view(np.uint64))
+    for r in (0, 17, 512):
+        assert onp.cosine_py(q, rows[r]) == a[r]
+
+
+def test_unit_rows_survive_renormalisation_exactly():
+    """Design fact the store relies on (DESIGN.md 'exact rows'): for rows that are unit-norm up to
+    fp32 rounding, fl32(1/sqrt(sum x^2)) == 1.0f, so normalising stores the row bit for bit."""
+    rows = oc.synth_rows(0, 20000, 768, 1234)
+    n2 = (rows.astype(np.float64) ** 2).sum(axis=1)
+    assert np.all((1.0 / np.sqrt(n2)).astype(np.float32) == np.float32(1.0))
