@@ -1,0 +1,164 @@
+/*
+ * ragstore.h -- C ABI of the B200-native vector store + top-k search that replaces the
+ * in-memory RAG index of johnnypax/llm-kubernetes-minikube-sharp4dev.
+ *
+ * The reference has no FFI at all: its store is `List<RagChunk>` on the managed heap and its
+ * search is a LINQ chain.  Every entry point below therefore cites the managed member whose
+ * work it takes over (paths relative to Minimal_Agent_RAG/Minimal_RAG/ in the reference):
+ *
+ *   Helpers/RagIndex.cs:8        readonly List<RagChunk> _chunks          -> the store handle
+ *   Helpers/RagIndex.cs:48       _chunks.Add(new RagChunk(.., emb))       -> ragstore_add
+ *   Helpers/RagIndex.cs:59-67    QueryAsync: Select(Cosine).OrderByDescending.Take(max(1,k))
+ *                                                                         -> ragstore_search
+ *   Helpers/RagIndex.cs:124-135  static double Cosine(float[], float[])   -> the scoring kernels
+ *   Program.cs:326-327           RagChunk(float[] Embedding) / RagHit(double Score)
+ *                                                                         -> fp32 in, fp64 score out
+ *
+ * Conventions: plain C types only; every call returns an int status (0 = RAGSTORE_OK) and never
+ * unwinds across the boundary; the caller owns every in/out buffer; the library owns device
+ * memory; handles are opaque.  INTEGRATION.md shows the P/Invoke declarations a maintainer
+ * of the reference would add.
+ */
+#ifndef RAGSTORE_H_
+#define RAGSTORE_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define RAGSTORE_API __attribute__((visibility("default")))
+#else
+#define RAGSTORE_API
+#endif
+
+typedef struct ragstore ragstore_t;
+
+/* status codes */
+enum {
+    RAGSTORE_OK = 0,
+    RAGSTORE_ERR_INVALID = 1,      /* bad argument (null pointer, dim <= 0, wrong row_dim on add, ...) */
+    RAGSTORE_ERR_CUDA = 2,         /* a CUDA call failed; ragstore_last_error has the text */
+    RAGSTORE_ERR_CAPACITY = 3,     /* add would exceed the capacity fixed at create */
+    RAGSTORE_ERR_UNSUPPORTED = 4,  /* dim / k outside what the kernels cover */
+    RAGSTORE_ERR_NO_DEVICE = 5     /* no usable sm_100 device: there is NO CPU fallback */
+};
+
+/* storage element type of the device matrix (north_star (1): fp32, optionally bf16) */
+enum { RAGSTORE_F32 = 0, RAGSTORE_BF16 = 1 };
+
+/* flags for ragstore_add */
+enum {
+    RAGSTORE_ADD_HOST = 0,           /* `rows` is host memory (pageable or pinned) */
+    RAGSTORE_ADD_DEVICE = 1,         /* `rows` is device memory on the store's device */
+    RAGSTORE_ADD_PRENORMALISED = 2   /* store the rows as given (caller asserts unit norm); the
+                                        per-row reciprocal norm is still measured and applied */
+};
+
+/* per-query result flags written by the search calls */
+enum {
+    RAGSTORE_HIT_CERTIFIED = 1,  /* the candidate margin proved that no row outside the rescored
+                                    set can belong to the top-k (DESIGN.md "certificate") */
+    RAGSTORE_HIT_EXACT_ROWS = 2  /* every returned row is stored bit-for-bit as it was added, so
+                                    its fp64 score is the reference's value, not a 1e-7 neighbour */
+};
+
+/* one rescored hit as exchanged between shards: 16 bytes, (score desc, id asc) is the total order */
+typedef struct ragstore_cand {
+    double score;   /* fp64 cosine, arithmetic of RagIndex.cs:124-135 */
+    int64_t id;     /* global row id = row_base + local row; -1 marks an empty slot */
+} ragstore_cand;
+
+/* ---- life cycle -------------------------------------------------------------------------- */
+
+/* Replaces `new RagIndex(..)` + `List<RagChunk> _chunks = new()` (RagIndex.cs:8,11).
+ * dim: embedding length (the reference takes whatever the model returns; fixed here at create).
+ * capacity_rows: rows reserved in HBM (append-only, like the reference's list).
+ * device: CUDA ordinal.  Fails with RAGSTORE_ERR_NO_DEVICE when no GPU is present. */
+RAGSTORE_API int ragstore_create(int dim, int dtype, int64_t capacity_rows, int device,
+                                 uint32_t flags, ragstore_t** out);
+
+RAGSTORE_API int ragstore_destroy(ragstore_t* s);
+
+/* ---- store side --------------------------------------------------------------------------- */
+
+/* Replaces `_chunks.Add(new RagChunk(id, file, text, emb))` (RagIndex.cs:48), batched: n_rows
+ * embeddings, row-major, row_dim floats each.  Rows are L2-normalised by the upload kernel and
+ * appended; the first new row id (== insertion order == list position, as in the reference) is
+ * returned.  The reference accepts any length at insert and scores -1 at query time
+ * (RagIndex.cs:126); a fixed-width matrix cannot, so row_dim != dim is RAGSTORE_ERR_INVALID.
+ * Returns after the rows are visible to searches.  Calls are serialised internally and may
+ * overlap with searches; a search sees a prefix of the appended rows. */
+RAGSTORE_API int ragstore_add(ragstore_t* s, const float* rows, int64_t n_rows, int row_dim,
+                              uint32_t flags, int64_t* out_first_row);
+
+/* Replaces `_chunks.Count` (RagIndex.cs:55). */
+RAGSTORE_API int ragstore_count(ragstore_t* s, int64_t* out_rows);
+
+/* Global id of local row 0 (row-sharded corpora).  Default 0. */
+RAGSTORE_API int ragstore_set_row_base(ragstore_t* s, int64_t row_base);
+
+/* ---- search side -------------------------------------------------------------------------- */
+
+/* Replaces the body of QueryAsync after the embedding call (RagIndex.cs:62-66) for n_queries
+ * queries at once: host buffers in, host buffers out, synchronous, re-entrant.
+ *   queries   n_queries x query_dim fp32, row-major (raw, not normalised)
+ *   top_k     as passed to QueryAsync; max(1, top_k) rows are requested (RagIndex.cs:65)
+ *   out_idx / out_score   n_queries x max(1,top_k); row ids best first, fp64 scores
+ *   out_found per query: min(count, max(1,top_k))    out_flags per query: RAGSTORE_HIT_* (may be NULL)
+ * Mirrors the reference's corner cases: empty store -> 0 hits; query_dim != dim -> every score is
+ * -1, so rows 0..found-1 in insertion order with score -1.0 (RagIndex.cs:126 + stable sort). */
+RAGSTORE_API int ragstore_search(ragstore_t* s, const float* queries, int n_queries, int query_dim,
+                                 int top_k, int64_t* out_idx, double* out_score,
+                                 int32_t* out_found, int32_t* out_flags);
+
+/* Same work with every buffer already in device memory and no host synchronisation: enqueues on
+ * `stream` (a cudaStream_t; NULL = the store's own stream) and returns.  query_dim must equal dim.
+ * Not re-entrant: one in-flight device search per store (it uses the store's scratch). */
+RAGSTORE_API int ragstore_search_device(ragstore_t* s, const float* d_queries, int n_queries,
+                                        int top_k, int64_t* d_idx, double* d_score,
+                                        int32_t* d_found, int32_t* d_flags, void* stream);
+
+/* Row-sharded search, step 1 (per shard): the shard's own rescored top max(1,top_k) as
+ * `ragstore_cand` records (global ids), best first, padded with {-inf, -1}.  d_out has
+ * max(1,top_k) records.  The records of all shards are then all-gathered (NCCL) by the host. */
+RAGSTORE_API int ragstore_search_shard_device(ragstore_t* s, const float* d_query, int top_k,
+                                              ragstore_cand* d_out, int32_t* d_flags, void* stream);
+
+/* Row-sharded search, step 2 (every rank, after the all-gather): merge n_shards x per_shard
+ * records into the global top max(1,top_k) under (score desc, id asc) -- the order a single
+ * RagIndex over the concatenated corpus would return (RagIndex.cs:64-65). */
+RAGSTORE_API int ragstore_merge_shards_device(const ragstore_cand* d_gathered, int n_shards,
+                                              int per_shard, int top_k, int64_t* d_idx,
+                                              double* d_score, int32_t* d_found, int device,
+                                              void* stream);
+
+/* ---- utilities ----------------------------------------------------------------------------- */
+
+/* Last error text of the calling thread (empty string if none). Returns the length written. */
+RAGSTORE_API int ragstore_last_error(char* buf, int buf_len);
+
+/* Library/ABI version (major*1000 + minor). */
+RAGSTORE_API int ragstore_version(void);
+
+/* Store facts for tests and the bench: fills up to n of
+ * [dim, ld (padded row length), dtype, count, capacity, n_inexact_rows, device, sm_count]. */
+RAGSTORE_API int ragstore_info(ragstore_t* s, int64_t* out, int n);
+
+/* Raw device views of the store (matrix, per-row reciprocal norms) for tests and benches. */
+RAGSTORE_API int ragstore_device_views(ragstore_t* s, void** d_matrix, float** d_rnorm,
+                                       uint8_t** d_exact);
+
+/* Fills a device fp32 buffer with the synthetic benchmark corpus (SURVEY.md 8(d) "Synthetic
+ * inputs"; bit-identical to oracle/ragindex_oracle.c:rag_synth_rows).  Not a reference function:
+ * benchmark plumbing so that a 30 GB corpus never crosses PCIe. */
+RAGSTORE_API int ragstore_synth_fill_device(float* d_out, int64_t row0, int64_t n_rows, int dim,
+                                            int64_t ld, uint64_t seed, int round_bf16, int device,
+                                            void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RAGSTORE_H_ */

@@ -1,0 +1,74 @@
+// normalise.cu -- K1: batched upload/normalise kernel that fills the device-resident store.
+//
+// Replaces the store call `_chunks.Add(new RagChunk(id, file, text, emb))`
+// (reference Helpers/RagIndex.cs:48) for a whole batch of embeddings, and hoists the per-row norm
+// that the reference recomputes inside every Cosine call (RagIndex.cs:132,134) to ingest time.
+//
+// One warp per row.  Pass 1: sum of squares in fp64.  scale = fl32(1/sqrt(sum)) (1 for a zero or
+// non-finite row, or when the caller asserts unit rows).  Pass 2: store x*scale as fp32 or bf16,
+// measure the norm of what was actually stored and keep its reciprocal (the scan multiplies by
+// it, so the approximate score is a true cosine of the stored row), and record whether the stored
+// row is bit-identical to the input ("exact row": scale == 1.0f and, for bf16, a lossless round).
+#include <math_constants.h>
+
+#include "common.cuh"
+#include "ragstore_internal.h"
+
+namespace rag {
+
+template <typename T>
+__global__ void __launch_bounds__(256) normalise_rows_kernel(const NormaliseArgs a) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warp0 = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = (static_cast<int64_t>(gridDim.x) * blockDim.x) >> 5;
+    for (int64_t r = warp0; r < a.n_rows; r += nwarps) {
+        const float* src = a.src + r * a.src_ld;
+        double acc = 0.0;
+        for (int i = lane; i < a.dim; i += 32) {
+            const double x = static_cast<double>(src[i]);
+            acc += x * x;
+        }
+        const double n2 = warp_sum(acc);
+        float scale = 1.0f;
+        if (!a.prenormalised && n2 > 0.0 && n2 < CUDART_INF) scale = static_cast<float>(1.0 / sqrt(n2));
+        T* dst = static_cast<T*>(a.dst) + r * static_cast<int64_t>(a.ld);
+        double acc2 = 0.0;
+        bool same = (scale == 1.0f);
+        for (int i = lane; i < a.ld; i += 32) {
+            const float x = i < a.dim ? src[i] : 0.f;  // read before the (possibly aliasing) write
+            const float y = __fmul_rn(x, scale);
+            float stored;
+            if constexpr (sizeof(T) == 4) {
+                dst[i] = y;
+                stored = y;
+            } else {
+                const uint32_t b = f32_to_bf16_bits(y);
+                dst[i] = static_cast<uint16_t>(b);
+                stored = bf16_bits_to_f32(b);
+                same = same && (__float_as_uint(stored) == __float_as_uint(x));
+            }
+            acc2 += static_cast<double>(stored) * static_cast<double>(stored);
+        }
+        const double n2s = warp_sum(acc2);
+        same = __all_sync(0xffffffffu, same);
+        if (lane == 0) {
+            a.rnorm[r] = (n2s > 0.0 && n2s < CUDART_INF) ? static_cast<float>(1.0 / sqrt(n2s)) : 0.f;
+            a.exact[r] = same ? 1 : 0;
+            if (!same && a.inexact_counter) atomicAdd(a.inexact_counter, 1ull);
+        }
+    }
+}
+
+int launch_normalise(const NormaliseArgs& a, cudaStream_t stream) {
+    if (a.n_rows <= 0) return 0;
+    const int threads = 256;
+    int64_t blocks = (a.n_rows + 7) / 8;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    if (a.dtype == RAGSTORE_F32)
+        normalise_rows_kernel<float><<<static_cast<int>(blocks), threads, 0, stream>>>(a);
+    else
+        normalise_rows_kernel<uint16_t><<<static_cast<int>(blocks), threads, 0, stream>>>(a);
+    return static_cast<int>(cudaGetLastError());
+}
+
+}  // namespace rag

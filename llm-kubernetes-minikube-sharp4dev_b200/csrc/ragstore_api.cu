@@ -1,0 +1,536 @@
+// ragstore_api.cu -- the C ABI of include/ragstore.h: store life cycle, batched ingest, search.
+//
+// Host-side replacement for the reference's `class RagIndex` internals
+// (Minimal_Agent_RAG/Minimal_RAG/Helpers/RagIndex.cs:8,48,59-67): the `List<RagChunk>` becomes a
+// device-resident row-major matrix, `Add` becomes a batched upload + normalise kernel, and the
+// LINQ search becomes one fused kernel launch per query.  There is no CPU scoring path in this
+// library: without a CUDA device every call fails with RAGSTORE_ERR_NO_DEVICE.
+#include <atomic>
+#include <condition_variable>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "ragstore_internal.h"
+
+using namespace rag;
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(int code, const char* what, const char* detail = nullptr) {
+    g_err = what;
+    if (detail) {
+        g_err += ": ";
+        g_err += detail;
+    }
+    return code;
+}
+
+#define CU_TRY(expr)                                                              \
+    do {                                                                          \
+        cudaError_t e__ = (expr);                                                 \
+        if (e__ != cudaSuccess) return fail(RAGSTORE_ERR_CUDA, #expr, cudaGetErrorString(e__)); \
+    } while (0)
+
+struct DeviceGuard {
+    int prev = -1;
+    bool ok = false;
+    explicit DeviceGuard(int dev) {
+        if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+        ok = cudaSetDevice(dev) == cudaSuccess;
+    }
+    ~DeviceGuard() {
+        if (prev >= 0) cudaSetDevice(prev);
+    }
+};
+
+constexpr int kCtxQueries = 64;  // queries per host-search context batch
+constexpr int kNumCtx = 4;       // concurrent host searches per store
+
+struct SearchCtx {
+    cudaStream_t st = nullptr;
+    ScanScratch scratch{};
+    float* d_q = nullptr;
+    int64_t* d_idx = nullptr;
+    double* d_score = nullptr;
+    int32_t* d_found = nullptr;
+    int32_t* d_flags = nullptr;
+    float* h_q = nullptr;  // pinned mirrors
+    int64_t* h_idx = nullptr;
+    double* h_score = nullptr;
+    int32_t* h_found = nullptr;
+    int32_t* h_flags = nullptr;
+};
+
+int choose_kp(int take) {
+    // candidate list = requested hits + a safety margin that the certificate can use
+    const int want = take + (take / 4 > 8 ? take / 4 : 8);
+    int kp = 32;
+    while (kp < want && kp < kMaxKp) kp <<= 1;
+    return kp;
+}
+
+float scan_eps(int dim_ld, int dtype) {
+    // |approx - reference| <= (terms per lane + butterfly + normalisation roundings) * 2^-24
+    const int per_chunk = dtype == RAGSTORE_F32 ? 4 : 8;
+    const int chunks = (dim_ld + per_chunk - 1) / per_chunk;
+    const int dv = (chunks + 31) / 32;
+    const int terms = dv * per_chunk;
+    return static_cast<float>((terms + 16) * 5.9604644775390625e-08);
+}
+
+}  // namespace
+
+struct ragstore {
+    int device = 0, dim = 0, ld = 0, dtype = 0, sm_count = 0;
+    int64_t capacity = 0;
+    std::atomic<int64_t> count{0};
+    int64_t row_base = 0;
+    void* mat = nullptr;
+    float* rnorm = nullptr;
+    uint8_t* exact = nullptr;
+    unsigned long long* d_inexact = nullptr;
+    cudaStream_t ingest_stream = nullptr;
+    cudaStream_t dev_stream = nullptr;
+    std::mutex add_mu;
+    float* d_stage = nullptr;
+    size_t stage_floats = 0;
+    ScanScratch dev_scratch{};
+    std::vector<SearchCtx> ctxs;
+    std::vector<int> free_ctx;
+    std::mutex ctx_mu;
+    std::condition_variable ctx_cv;
+    size_t elem_size() const { return dtype == RAGSTORE_F32 ? 4 : 2; }
+};
+
+namespace {
+
+int alloc_scratch(ScanScratch& s) {
+    uint8_t* p = nullptr;
+    CU_TRY(cudaMalloc(&p, kScanScratchBytes));
+    CU_TRY(cudaMemset(p, 0, kScanScratchBytes));
+    s.ticket = reinterpret_cast<unsigned int*>(p);
+    s.cta_lists = reinterpret_cast<uint64_t*>(p + 256);
+    return RAGSTORE_OK;
+}
+
+void free_scratch(ScanScratch& s) {
+    if (s.ticket) cudaFree(s.ticket);
+    s = ScanScratch{};
+}
+
+int alloc_ctx(SearchCtx& c, int ld) {
+    CU_TRY(cudaStreamCreateWithFlags(&c.st, cudaStreamNonBlocking));
+    int rc = alloc_scratch(c.scratch);
+    if (rc) return rc;
+    const size_t nq = kCtxQueries;
+    CU_TRY(cudaMalloc(&c.d_q, nq * ld * sizeof(float)));
+    CU_TRY(cudaMalloc(&c.d_idx, nq * kMaxKp * sizeof(int64_t)));
+    CU_TRY(cudaMalloc(&c.d_score, nq * kMaxKp * sizeof(double)));
+    CU_TRY(cudaMalloc(&c.d_found, nq * sizeof(int32_t)));
+    CU_TRY(cudaMalloc(&c.d_flags, nq * sizeof(int32_t)));
+    CU_TRY(cudaMallocHost(&c.h_q, nq * ld * sizeof(float)));
+    CU_TRY(cudaMallocHost(&c.h_idx, nq * kMaxKp * sizeof(int64_t)));
+    CU_TRY(cudaMallocHost(&c.h_score, nq * kMaxKp * sizeof(double)));
+    CU_TRY(cudaMallocHost(&c.h_found, nq * sizeof(int32_t)));
+    CU_TRY(cudaMallocHost(&c.h_flags, nq * sizeof(int32_t)));
+    return RAGSTORE_OK;
+}
+
+void free_ctx(SearchCtx& c) {
+    if (c.st) cudaStreamDestroy(c.st);
+    free_scratch(c.scratch);
+    cudaFree(c.d_q);
+    cudaFree(c.d_idx);
+    cudaFree(c.d_score);
+    cudaFree(c.d_found);
+    cudaFree(c.d_flags);
+    cudaFreeHost(c.h_q);
+    cudaFreeHost(c.h_idx);
+    cudaFreeHost(c.h_score);
+    cudaFreeHost(c.h_found);
+    cudaFreeHost(c.h_flags);
+    c = SearchCtx{};
+}
+
+ScanArgs base_args(const ragstore* s, int64_t n, int take, int kp) {
+    ScanArgs a{};
+    a.mat = s->mat;
+    a.rnorm = s->rnorm;
+    a.exact = s->exact;
+    a.n_rows = n;
+    a.dim = s->dim;
+    a.ld = s->ld;
+    a.dtype = s->dtype;
+    a.row_base = s->row_base;
+    a.k_take = take;
+    a.kp = kp;
+    a.eps = scan_eps(s->ld, s->dtype);
+    a.sm_count = s->sm_count;
+    return a;
+}
+
+}  // namespace
+
+extern "C" {
+
+int ragstore_version(void) { return 1000; }
+
+int ragstore_last_error(char* buf, int buf_len) {
+    if (!buf || buf_len <= 0) return 0;
+    const int n = static_cast<int>(g_err.size()) < buf_len - 1 ? static_cast<int>(g_err.size()) : buf_len - 1;
+    memcpy(buf, g_err.data(), n);
+    buf[n] = 0;
+    return n;
+}
+
+int ragstore_create(int dim, int dtype, int64_t capacity_rows, int device, uint32_t flags, ragstore_t** out) {
+    (void)flags;
+    if (!out) return fail(RAGSTORE_ERR_INVALID, "ragstore_create: out is null");
+    *out = nullptr;
+    if (dim <= 0 || capacity_rows <= 0 || (dtype != RAGSTORE_F32 && dtype != RAGSTORE_BF16))
+        return fail(RAGSTORE_ERR_INVALID, "ragstore_create: dim and capacity_rows must be positive, dtype f32|bf16");
+    if (capacity_rows >= 0xFFFFFFFFll)
+        return fail(RAGSTORE_ERR_UNSUPPORTED, "ragstore_create: at most 2^32-2 rows per store (shard the corpus)");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0 || device < 0 || device >= ndev) {
+        cudaGetLastError();
+        return fail(RAGSTORE_ERR_NO_DEVICE, "ragstore_create: no usable CUDA device (this library has no CPU path)");
+    }
+    cudaDeviceProp prop;
+    CU_TRY(cudaGetDeviceProperties(&prop, device));
+    if (prop.major < 10)
+        return fail(RAGSTORE_ERR_NO_DEVICE, "ragstore_create: kernels are built for sm_100a (B200) only");
+    DeviceGuard g(device);
+    if (!g.ok) return fail(RAGSTORE_ERR_CUDA, "cudaSetDevice failed");
+
+    ragstore* s = new ragstore();
+    s->device = device;
+    s->dim = dim;
+    s->dtype = dtype;
+    const int align = dtype == RAGSTORE_F32 ? 4 : 8;  // 16-byte rows
+    s->ld = (dim + align - 1) / align * align;
+    s->capacity = capacity_rows;
+    s->sm_count = prop.multiProcessorCount;
+    // probe the scan layout once so that an unsupported dim fails at create, not at first search
+    {
+        const size_t row_bytes = static_cast<size_t>(s->ld) * s->elem_size();
+        if (row_bytes > 24 * 1024) {
+            delete s;
+            return fail(RAGSTORE_ERR_UNSUPPORTED, "ragstore_create: rows above 24 KB are not covered by the scan kernel");
+        }
+    }
+    auto bail = [&](int rc) {
+        ragstore_destroy(s);
+        return rc;
+    };
+    const size_t mat_bytes = static_cast<size_t>(capacity_rows) * s->ld * s->elem_size();
+    const size_t cap4 = static_cast<size_t>((capacity_rows + 3) & ~3ll) + 64;
+    cudaError_t e;
+    if ((e = cudaMalloc(&s->mat, mat_bytes)) != cudaSuccess) return bail(fail(RAGSTORE_ERR_CUDA, "cudaMalloc(matrix)", cudaGetErrorString(e)));
+    if ((e = cudaMalloc(&s->rnorm, cap4 * sizeof(float))) != cudaSuccess) return bail(fail(RAGSTORE_ERR_CUDA, "cudaMalloc(rnorm)", cudaGetErrorString(e)));
+    if ((e = cudaMemset(s->rnorm, 0, cap4 * sizeof(float))) != cudaSuccess) return bail(fail(RAGSTORE_ERR_CUDA, "cudaMemset(rnorm)", cudaGetErrorString(e)));
+    if ((e = cudaMalloc(&s->exact, cap4)) != cudaSuccess) return bail(fail(RAGSTORE_ERR_CUDA, "cudaMalloc(exact)", cudaGetErrorString(e)));
+    if ((e = cudaMalloc(&s->d_inexact, sizeof(unsigned long long))) != cudaSuccess) return bail(fail(RAGSTORE_ERR_CUDA, "cudaMalloc(counter)", cudaGetErrorString(e)));
+    if ((e = cudaMemset(s->d_inexact, 0, sizeof(unsigned long long))) != cudaSuccess) return bail(fail(RAGSTORE_ERR_CUDA, "cudaMemset(counter)", cudaGetErrorString(e)));
+    if ((e = cudaStreamCreateWithFlags(&s->ingest_stream, cudaStreamNonBlocking)) != cudaSuccess) return bail(fail(RAGSTORE_ERR_CUDA, "cudaStreamCreate", cudaGetErrorString(e)));
+    if ((e = cudaStreamCreateWithFlags(&s->dev_stream, cudaStreamNonBlocking)) != cudaSuccess) return bail(fail(RAGSTORE_ERR_CUDA, "cudaStreamCreate", cudaGetErrorString(e)));
+    int rc = alloc_scratch(s->dev_scratch);
+    if (rc) return bail(rc);
+    s->ctxs.resize(kNumCtx);
+    for (int i = 0; i < kNumCtx; ++i) {
+        rc = alloc_ctx(s->ctxs[i], s->ld);
+        if (rc) return bail(rc);
+        s->free_ctx.push_back(i);
+    }
+    *out = s;
+    return RAGSTORE_OK;
+}
+
+int ragstore_destroy(ragstore_t* s) {
+    if (!s) return RAGSTORE_OK;
+    DeviceGuard g(s->device);
+    cudaDeviceSynchronize();
+    for (auto& c : s->ctxs) free_ctx(c);
+    free_scratch(s->dev_scratch);
+    if (s->ingest_stream) cudaStreamDestroy(s->ingest_stream);
+    if (s->dev_stream) cudaStreamDestroy(s->dev_stream);
+    cudaFree(s->d_stage);
+    cudaFree(s->d_inexact);
+    cudaFree(s->exact);
+    cudaFree(s->rnorm);
+    cudaFree(s->mat);
+    delete s;
+    return RAGSTORE_OK;
+}
+
+int ragstore_count(ragstore_t* s, int64_t* out_rows) {
+    if (!s || !out_rows) return fail(RAGSTORE_ERR_INVALID, "ragstore_count: null argument");
+    *out_rows = s->count.load(std::memory_order_acquire);
+    return RAGSTORE_OK;
+}
+
+int ragstore_set_row_base(ragstore_t* s, int64_t row_base) {
+    if (!s || row_base < 0) return fail(RAGSTORE_ERR_INVALID, "ragstore_set_row_base: bad argument");
+    s->row_base = row_base;
+    return RAGSTORE_OK;
+}
+
+int ragstore_add(ragstore_t* s, const float* rows, int64_t n_rows, int row_dim, uint32_t flags, int64_t* out_first_row) {
+    if (!s || (!rows && n_rows > 0) || n_rows < 0) return fail(RAGSTORE_ERR_INVALID, "ragstore_add: null/negative argument");
+    if (row_dim != s->dim) return fail(RAGSTORE_ERR_INVALID, "ragstore_add: row_dim differs from the store's dim");
+    std::lock_guard<std::mutex> lk(s->add_mu);
+    const int64_t first = s->count.load(std::memory_order_acquire);
+    if (out_first_row) *out_first_row = first;
+    if (n_rows == 0) return RAGSTORE_OK;
+    if (first + n_rows > s->capacity) return fail(RAGSTORE_ERR_CAPACITY, "ragstore_add: capacity exceeded");
+    DeviceGuard g(s->device);
+    if (!g.ok) return fail(RAGSTORE_ERR_CUDA, "cudaSetDevice failed");
+    const bool on_device = (flags & RAGSTORE_ADD_DEVICE) != 0;
+    const bool in_place = (s->dtype == RAGSTORE_F32);  // fp32: land rows in the matrix, normalise in place
+    const size_t esz = s->elem_size();
+    const int64_t chunk_rows = std::max<int64_t>(1, (int64_t(64) << 20) / (int64_t(s->dim) * 4));
+
+    for (int64_t r0 = 0; r0 < n_rows; r0 += chunk_rows) {
+        const int64_t n = std::min(chunk_rows, n_rows - r0);
+        const float* src = rows + r0 * s->dim;
+        uint8_t* dst_row = static_cast<uint8_t*>(s->mat) + static_cast<size_t>(first + r0) * s->ld * esz;
+        NormaliseArgs a{};
+        a.dst = dst_row;
+        a.rnorm = s->rnorm + first + r0;
+        a.exact = s->exact + first + r0;
+        a.n_rows = n;
+        a.dim = s->dim;
+        a.ld = s->ld;
+        a.dtype = s->dtype;
+        a.prenormalised = (flags & RAGSTORE_ADD_PRENORMALISED) ? 1 : 0;
+        a.inexact_counter = s->d_inexact;
+        if (on_device && !in_place) {
+            a.src = src;
+            a.src_ld = s->dim;
+        } else if (in_place) {
+            CU_TRY(cudaMemcpy2DAsync(dst_row, static_cast<size_t>(s->ld) * 4, src, static_cast<size_t>(s->dim) * 4,
+                                     static_cast<size_t>(s->dim) * 4, static_cast<size_t>(n),
+                                     on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, s->ingest_stream));
+            a.src = reinterpret_cast<const float*>(dst_row);
+            a.src_ld = s->ld;
+        } else {
+            const size_t need = static_cast<size_t>(chunk_rows) * s->dim;
+            if (s->stage_floats < need) {
+                cudaFree(s->d_stage);
+                s->d_stage = nullptr;
+                s->stage_floats = 0;
+                CU_TRY(cudaMalloc(&s->d_stage, need * sizeof(float)));
+                s->stage_floats = need;
+            }
+            CU_TRY(cudaMemcpyAsync(s->d_stage, src, static_cast<size_t>(n) * s->dim * 4, cudaMemcpyHostToDevice, s->ingest_stream));
+            a.src = s->d_stage;
+            a.src_ld = s->dim;
+        }
+        const int rc = launch_normalise(a, s->ingest_stream);
+        if (rc) return fail(RAGSTORE_ERR_CUDA, "normalise kernel launch", cudaGetErrorString(static_cast<cudaError_t>(rc)));
+        if (!in_place && !on_device) CU_TRY(cudaStreamSynchronize(s->ingest_stream));  // staging buffer reuse
+    }
+    CU_TRY(cudaStreamSynchronize(s->ingest_stream));
+    s->count.store(first + n_rows, std::memory_order_release);  // publish: searches see a prefix
+    return RAGSTORE_OK;
+}
+
+int ragstore_info(ragstore_t* s, int64_t* out, int n) {
+    if (!s || !out) return fail(RAGSTORE_ERR_INVALID, "ragstore_info: null argument");
+    DeviceGuard g(s->device);
+    unsigned long long inexact = 0;
+    CU_TRY(cudaMemcpy(&inexact, s->d_inexact, sizeof(inexact), cudaMemcpyDeviceToHost));
+    const int64_t v[8] = {s->dim, s->ld, s->dtype, s->count.load(), s->capacity, static_cast<int64_t>(inexact), s->device, s->sm_count};
+    for (int i = 0; i < n && i < 8; ++i) out[i] = v[i];
+    return RAGSTORE_OK;
+}
+
+int ragstore_device_views(ragstore_t* s, void** d_matrix, float** d_rnorm, uint8_t** d_exact) {
+    if (!s) return fail(RAGSTORE_ERR_INVALID, "ragstore_device_views: null store");
+    if (d_matrix) *d_matrix = s->mat;
+    if (d_rnorm) *d_rnorm = s->rnorm;
+    if (d_exact) *d_exact = s->exact;
+    return RAGSTORE_OK;
+}
+
+int ragstore_search_device(ragstore_t* s, const float* d_queries, int n_queries, int top_k, int64_t* d_idx,
+                           double* d_score, int32_t* d_found, int32_t* d_flags, void* stream) {
+    if (!s || !d_queries || n_queries < 0 || !d_idx || !d_score) return fail(RAGSTORE_ERR_INVALID, "ragstore_search_device: null argument");
+    DeviceGuard g(s->device);
+    cudaStream_t st = stream ? static_cast<cudaStream_t>(stream) : s->dev_stream;
+    const int64_t n = s->count.load(std::memory_order_acquire);
+    const int req = top_k < 1 ? 1 : top_k;
+    const int take = static_cast<int>(std::min<int64_t>(n, req));
+    if (n == 0) {
+        if (d_found) CU_TRY(cudaMemsetAsync(d_found, 0, sizeof(int32_t) * n_queries, st));
+        return RAGSTORE_OK;
+    }
+    if (take > kMaxKp) return fail(RAGSTORE_ERR_UNSUPPORTED, "top_k above 256 is not covered yet");
+    const int kp = choose_kp(take);
+    for (int q = 0; q < n_queries; ++q) {
+        ScanArgs a = base_args(s, n, take, kp);
+        a.d_query = d_queries + static_cast<size_t>(q) * s->dim;
+        a.scratch = s->dev_scratch;
+        a.out_idx = d_idx + static_cast<size_t>(q) * req;
+        a.out_score = d_score + static_cast<size_t>(q) * req;
+        a.out_found = d_found ? d_found + q : nullptr;
+        a.out_flags = d_flags ? d_flags + q : nullptr;
+        const int rc = launch_scan(a, st);
+        if (rc) return fail(RAGSTORE_ERR_CUDA, "scan kernel launch", cudaGetErrorString(static_cast<cudaError_t>(rc)));
+    }
+    return RAGSTORE_OK;
+}
+
+int ragstore_search_shard_device(ragstore_t* s, const float* d_query, int top_k, ragstore_cand* d_out,
+                                 int32_t* d_flags, void* stream) {
+    if (!s || !d_query || !d_out) return fail(RAGSTORE_ERR_INVALID, "ragstore_search_shard_device: null argument");
+    DeviceGuard g(s->device);
+    cudaStream_t st = stream ? static_cast<cudaStream_t>(stream) : s->dev_stream;
+    const int64_t n = s->count.load(std::memory_order_acquire);
+    const int req = top_k < 1 ? 1 : top_k;
+    if (req > kMaxKp) return fail(RAGSTORE_ERR_UNSUPPORTED, "top_k above 256 is not covered yet");
+    const int take = static_cast<int>(std::min<int64_t>(n, req));
+    if (n == 0) {
+        // an empty shard contributes only padding; 0xFF bytes give id = -1 and a NaN score (ranked last, skipped)
+        CU_TRY(cudaMemsetAsync(d_out, 0xFF, sizeof(ragstore_cand) * req, st));
+        if (d_flags) {
+            const int32_t f = RAGSTORE_HIT_CERTIFIED | RAGSTORE_HIT_EXACT_ROWS;
+            CU_TRY(cudaMemcpyAsync(d_flags, &f, sizeof(f), cudaMemcpyHostToDevice, st));
+        }
+        return RAGSTORE_OK;
+    }
+    ScanArgs a = base_args(s, n, take, choose_kp(take));
+    a.d_query = d_query;
+    a.scratch = s->dev_scratch;
+    a.out_flags = d_flags;
+    a.out_cand = d_out;
+    a.cand_slots = req;
+    const int rc = launch_scan(a, st);
+    if (rc) return fail(RAGSTORE_ERR_CUDA, "scan kernel launch", cudaGetErrorString(static_cast<cudaError_t>(rc)));
+    return RAGSTORE_OK;
+}
+
+int ragstore_merge_shards_device(const ragstore_cand* d_gathered, int n_shards, int per_shard, int top_k,
+                                 int64_t* d_idx, double* d_score, int32_t* d_found, int device, void* stream) {
+    if (!d_gathered || !d_idx || !d_score || !d_found || n_shards <= 0 || per_shard <= 0)
+        return fail(RAGSTORE_ERR_INVALID, "ragstore_merge_shards_device: bad argument");
+    DeviceGuard g(device);
+    if (!g.ok) return fail(RAGSTORE_ERR_NO_DEVICE, "ragstore_merge_shards_device: no such device");
+    const int req = top_k < 1 ? 1 : top_k;
+    const int rc = launch_merge_shards(d_gathered, n_shards * per_shard, req, d_idx, d_score, d_found,
+                                       static_cast<cudaStream_t>(stream));
+    if (rc) return fail(RAGSTORE_ERR_CUDA, "merge kernel launch", cudaGetErrorString(static_cast<cudaError_t>(rc)));
+    return RAGSTORE_OK;
+}
+
+int ragstore_search(ragstore_t* s, const float* queries, int n_queries, int query_dim, int top_k, int64_t* out_idx,
+                    double* out_score, int32_t* out_found, int32_t* out_flags) {
+    if (!s || n_queries < 0 || (n_queries > 0 && (!queries || !out_idx || !out_score || !out_found)))
+        return fail(RAGSTORE_ERR_INVALID, "ragstore_search: null argument");
+    const int64_t n = s->count.load(std::memory_order_acquire);  // snapshot: a prefix of the appended rows
+    const int req = top_k < 1 ? 1 : top_k;                       // Math.Max(1, topK)
+    const int take = static_cast<int>(std::min<int64_t>(n, req));
+    if (n == 0 || n_queries == 0) {
+        for (int q = 0; q < n_queries; ++q) {
+            out_found[q] = 0;
+            if (out_flags) out_flags[q] = RAGSTORE_HIT_CERTIFIED | RAGSTORE_HIT_EXACT_ROWS;
+        }
+        return RAGSTORE_OK;
+    }
+    if (query_dim != s->dim) {
+        // RagIndex.cs:126: every Cosine returns -1; the stable sort keeps insertion order
+        for (int q = 0; q < n_queries; ++q) {
+            for (int j = 0; j < take; ++j) {
+                out_idx[static_cast<size_t>(q) * req + j] = s->row_base + j;
+                out_score[static_cast<size_t>(q) * req + j] = -1.0;
+            }
+            out_found[q] = take;
+            if (out_flags) out_flags[q] = RAGSTORE_HIT_CERTIFIED | RAGSTORE_HIT_EXACT_ROWS;
+        }
+        return RAGSTORE_OK;
+    }
+    if (take > kMaxKp) return fail(RAGSTORE_ERR_UNSUPPORTED, "top_k above 256 is not covered yet");
+    DeviceGuard g(s->device);
+    if (!g.ok) return fail(RAGSTORE_ERR_CUDA, "cudaSetDevice failed");
+
+    int ci;
+    {
+        std::unique_lock<std::mutex> lk(s->ctx_mu);
+        s->ctx_cv.wait(lk, [&] { return !s->free_ctx.empty(); });
+        ci = s->free_ctx.back();
+        s->free_ctx.pop_back();
+    }
+    struct Release {
+        ragstore* s;
+        int ci;
+        ~Release() {
+            {
+                std::lock_guard<std::mutex> lk(s->ctx_mu);
+                s->free_ctx.push_back(ci);
+            }
+            s->ctx_cv.notify_one();
+        }
+    } rel{s, ci};
+    SearchCtx& c = s->ctxs[ci];
+
+    int kp0 = choose_kp(take);
+    for (int q0 = 0; q0 < n_queries; q0 += kCtxQueries) {
+        const int nq = std::min(kCtxQueries, n_queries - q0);
+        memcpy(c.h_q, queries + static_cast<size_t>(q0) * s->dim, static_cast<size_t>(nq) * s->dim * sizeof(float));
+        CU_TRY(cudaMemcpyAsync(c.d_q, c.h_q, static_cast<size_t>(nq) * s->dim * sizeof(float), cudaMemcpyHostToDevice, c.st));
+        std::vector<int> todo(nq);
+        for (int i = 0; i < nq; ++i) todo[i] = i;
+        int kp = kp0;
+        while (!todo.empty()) {
+            for (int i : todo) {
+                ScanArgs a = base_args(s, n, take, kp);
+                a.d_query = c.d_q + static_cast<size_t>(i) * s->dim;
+                a.scratch = c.scratch;
+                a.out_idx = c.d_idx + static_cast<size_t>(i) * kMaxKp;
+                a.out_score = c.d_score + static_cast<size_t>(i) * kMaxKp;
+                a.out_found = c.d_found + i;
+                a.out_flags = c.d_flags + i;
+                const int rc = launch_scan(a, c.st);
+                if (rc) return fail(RAGSTORE_ERR_CUDA, "scan kernel launch", cudaGetErrorString(static_cast<cudaError_t>(rc)));
+            }
+            CU_TRY(cudaMemcpyAsync(c.h_idx, c.d_idx, static_cast<size_t>(nq) * kMaxKp * sizeof(int64_t), cudaMemcpyDeviceToHost, c.st));
+            CU_TRY(cudaMemcpyAsync(c.h_score, c.d_score, static_cast<size_t>(nq) * kMaxKp * sizeof(double), cudaMemcpyDeviceToHost, c.st));
+            CU_TRY(cudaMemcpyAsync(c.h_found, c.d_found, static_cast<size_t>(nq) * sizeof(int32_t), cudaMemcpyDeviceToHost, c.st));
+            CU_TRY(cudaMemcpyAsync(c.h_flags, c.d_flags, static_cast<size_t>(nq) * sizeof(int32_t), cudaMemcpyDeviceToHost, c.st));
+            CU_TRY(cudaStreamSynchronize(c.st));
+            std::vector<int> again;
+            for (int i : todo) {
+                const bool cert = (c.h_flags[i] & RAGSTORE_HIT_CERTIFIED) != 0;
+                if (!cert && kp < kMaxKp) {
+                    again.push_back(i);  // widen the candidate list and rescan this query
+                    continue;
+                }
+                const size_t o = static_cast<size_t>(q0 + i) * req;
+                memcpy(out_idx + o, c.h_idx + static_cast<size_t>(i) * kMaxKp, sizeof(int64_t) * take);
+                memcpy(out_score + o, c.h_score + static_cast<size_t>(i) * kMaxKp, sizeof(double) * take);
+                out_found[q0 + i] = c.h_found[i];
+                if (out_flags) out_flags[q0 + i] = c.h_flags[i];
+            }
+            todo.swap(again);
+            kp = kMaxKp;
+        }
+    }
+    return RAGSTORE_OK;
+}
+
+int ragstore_synth_fill_device(float* d_out, int64_t row0, int64_t n_rows, int dim, int64_t ld, uint64_t seed,
+                               int round_bf16, int device, void* stream) {
+    if (!d_out || n_rows < 0 || dim <= 0 || ld < dim) return fail(RAGSTORE_ERR_INVALID, "ragstore_synth_fill_device: bad argument");
+    DeviceGuard g(device);
+    if (!g.ok) return fail(RAGSTORE_ERR_NO_DEVICE, "ragstore_synth_fill_device: no such device");
+    const int rc = launch_synth(d_out, row0, n_rows, dim, ld, seed, round_bf16, static_cast<cudaStream_t>(stream));
+    if (rc) return fail(RAGSTORE_ERR_CUDA, "synth kernel launch", cudaGetErrorString(static_cast<cudaError_t>(rc)));
+    return RAGSTORE_OK;
+}
+
+}  // extern "C"

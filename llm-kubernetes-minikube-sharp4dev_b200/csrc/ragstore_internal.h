@@ -1,0 +1,72 @@
+// ragstore_internal.h -- host-side declarations shared by the .cu files of libragstore.so.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/ragstore.h"
+
+namespace rag {
+
+constexpr int kConsumerWarps = 8;                       // warps that score rows
+constexpr int kScanThreads = (kConsumerWarps + 1) * 32; // + one producer warp (bulk-copy issue)
+constexpr int kMaxKp = 256;                             // largest candidate list kept per warp/CTA
+constexpr int kMaxCtas = 1024;                          // scratch sizing: CTAs of one scan launch
+constexpr int kMaxBatchQ = 4;                           // queries scored per corpus sweep (GEMV path)
+
+// Scratch one scan launch needs in global memory (beyond inputs/outputs).
+struct ScanScratch {
+    uint64_t* cta_lists;   // [kMaxCtas * kMaxKp] per-CTA candidate keys
+    unsigned int* ticket;  // [1] "last CTA done" counter, self-resetting
+};
+constexpr size_t kScanScratchBytes = sizeof(uint64_t) * size_t(kMaxCtas) * kMaxKp + 256;
+
+struct ScanArgs {
+    // store
+    const void* mat;        // row-major [n_rows][ld] of fp32 or bf16
+    const float* rnorm;     // [round_up(n_rows,4)] reciprocal norm of each STORED row (0 for a zero row)
+    const uint8_t* exact;   // [n_rows] 1 = stored bit-for-bit as added (may be null => treated as 1)
+    int64_t n_rows;
+    int dim, ld, dtype;
+    int64_t row_base;
+    // query + selection
+    const float* d_query;   // raw fp32 [dim]
+    int k_take;             // min(n_rows, max(1, top_k))
+    int kp;                 // candidate list length: power of two in [32, kMaxKp], >= k_take
+    float eps;              // bound on |approximate score - reference score| (DESIGN.md "certificate")
+    // scratch
+    ScanScratch scratch;
+    // outputs (device memory)
+    int64_t* out_idx;       // [k_take]  (may be null when out_cand is used)
+    double* out_score;      // [k_take]
+    int32_t* out_found;     // [1]
+    int32_t* out_flags;     // [1] RAGSTORE_HIT_*
+    ragstore_cand* out_cand;// [cand_slots] shard records, padded with {-inf,-1} (may be null)
+    int cand_slots;
+    int sm_count;
+};
+
+// Enqueues the fused scan + top-k + exact-rescore kernel.  Returns cudaError_t as int.
+int launch_scan(const ScanArgs& a, cudaStream_t stream);
+// One-time per-device kernel attribute set-up (max dynamic shared memory).
+int scan_configure_device();
+
+struct NormaliseArgs {
+    const float* src;     // [n_rows][src_ld] fp32 (may alias dst for the fp32 store)
+    int64_t src_ld;
+    void* dst;            // first destination row in the matrix
+    float* rnorm;         // destination slice of the per-row reciprocal norms
+    uint8_t* exact;       // destination slice of the per-row exact flags
+    int64_t n_rows;
+    int dim, ld, dtype;
+    int prenormalised;
+    unsigned long long* inexact_counter;  // device counter of rows stored inexactly
+};
+int launch_normalise(const NormaliseArgs& a, cudaStream_t stream);
+
+int launch_synth(float* d_out, int64_t row0, int64_t n_rows, int dim, int64_t ld, uint64_t seed,
+                 int round_bf16, cudaStream_t stream);
+
+int launch_merge_shards(const ragstore_cand* d_gathered, int n_items, int k_take, int64_t* d_idx,
+                        double* d_score, int32_t* d_found, cudaStream_t stream);
+
+}  // namespace rag

@@ -1,0 +1,176 @@
+"""ctypes binding of include/ragstore.h (the same entry points the C# P/Invoke layer binds;
+see INTEGRATION.md).  Loads the in-tree libragstore.so; never falls back to anything else."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+RAGSTORE_F32, RAGSTORE_BF16 = 0, 1
+RAGSTORE_ADD_HOST, RAGSTORE_ADD_DEVICE, RAGSTORE_ADD_PRENORMALISED = 0, 1, 2
+RAGSTORE_HIT_CERTIFIED, RAGSTORE_HIT_EXACT_ROWS = 1, 2
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+
+class RagStoreError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"ragstore error {code}: {msg}")
+        self.code = code
+
+
+class Cand(C.Structure):
+    _fields_ = [("score", C.c_double), ("id", C.c_int64)]
+
+
+def lib_path() -> str:
+    return os.path.join(_HERE, "libragstore.so")
+
+
+def lib():
+    """The loaded library.  Raises if it has not been built (python __graft_entry__.py build)."""
+    global _LIB
+    if _LIB is None:
+        p = lib_path()
+        if not os.path.exists(p):
+            raise RagStoreError(-1, f"{p} not built: run `make -C {os.path.join(_HERE, 'csrc')}`; there is no CPU fallback")
+        L = C.CDLL(p)
+        vp, i64p, f64p, i32p, f32p = C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_double), C.POINTER(C.c_int32), C.POINTER(C.c_float)
+        sig = {
+            "ragstore_version": (C.c_int, []),
+            "ragstore_last_error": (C.c_int, [C.c_char_p, C.c_int]),
+            "ragstore_create": (C.c_int, [C.c_int, C.c_int, C.c_int64, C.c_int, C.c_uint32, C.POINTER(vp)]),
+            "ragstore_destroy": (C.c_int, [vp]),
+            "ragstore_add": (C.c_int, [vp, vp, C.c_int64, C.c_int, C.c_uint32, i64p]),
+            "ragstore_count": (C.c_int, [vp, i64p]),
+            "ragstore_set_row_base": (C.c_int, [vp, C.c_int64]),
+            "ragstore_search": (C.c_int, [vp, f32p, C.c_int, C.c_int, C.c_int, i64p, f64p, i32p, i32p]),
+            "ragstore_search_device": (C.c_int, [vp, vp, C.c_int, C.c_int, vp, vp, vp, vp, vp]),
+            "ragstore_search_shard_device": (C.c_int, [vp, vp, C.c_int, vp, vp, vp]),
+            "ragstore_merge_shards_device": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, vp, vp, vp, C.c_int, vp]),
+            "ragstore_info": (C.c_int, [vp, i64p, C.c_int]),
+            "ragstore_device_views": (C.c_int, [vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]),
+            "ragstore_synth_fill_device": (C.c_int, [vp, C.c_int64, C.c_int64, C.c_int, C.c_int64, C.c_uint64, C.c_int, C.c_int, vp]),
+        }
+        for name, (res, args) in sig.items():
+            fn = getattr(L, name)
+            fn.restype, fn.argtypes = res, args
+        _LIB = L
+    return _LIB
+
+
+def last_error() -> str:
+    buf = C.create_string_buffer(1024)
+    lib().ragstore_last_error(buf, 1024)
+    return buf.value.decode("utf-8", "replace")
+
+
+def check(rc: int):
+    if rc != 0:
+        raise RagStoreError(rc, last_error())
+
+
+def _ptr(x):
+    """Device pointer of a torch tensor / int / None."""
+    if x is None:
+        return None
+    if isinstance(x, int):
+        return C.c_void_p(x)
+    return C.c_void_p(x.data_ptr())
+
+
+class RagStore:
+    """Owning wrapper of one ragstore_t (one device-resident shard)."""
+
+    def __init__(self, dim: int, capacity_rows: int, dtype: int = RAGSTORE_F32, device: int = 0):
+        self._h = C.c_void_p()
+        check(lib().ragstore_create(dim, dtype, capacity_rows, device, 0, C.byref(self._h)))
+        self.dim, self.dtype, self.device, self.capacity = dim, dtype, device, capacity_rows
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h:
+            lib().ragstore_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    # ---- store side
+    def add(self, rows: np.ndarray, prenormalised: bool = False) -> int:
+        rows = np.ascontiguousarray(rows, dtype=np.float32)
+        if rows.ndim != 2:
+            raise ValueError("rows must be [n, dim]")
+        first = C.c_int64(-1)
+        flags = RAGSTORE_ADD_HOST | (RAGSTORE_ADD_PRENORMALISED if prenormalised else 0)
+        check(lib().ragstore_add(self._h, C.c_void_p(rows.ctypes.data), rows.shape[0], rows.shape[1], flags, C.byref(first)))
+        return first.value
+
+    def add_device(self, d_rows, n_rows: int, row_dim: int, prenormalised: bool = False) -> int:
+        """d_rows: torch CUDA fp32 tensor (or raw device pointer) [n_rows, row_dim], contiguous."""
+        first = C.c_int64(-1)
+        flags = RAGSTORE_ADD_DEVICE | (RAGSTORE_ADD_PRENORMALISED if prenormalised else 0)
+        check(lib().ragstore_add(self._h, _ptr(d_rows), n_rows, row_dim, flags, C.byref(first)))
+        return first.value
+
+    def count(self) -> int:
+        n = C.c_int64(0)
+        check(lib().ragstore_count(self._h, C.byref(n)))
+        return n.value
+
+    def set_row_base(self, base: int):
+        check(lib().ragstore_set_row_base(self._h, base))
+
+    def info(self) -> dict:
+        v = (C.c_int64 * 8)()
+        check(lib().ragstore_info(self._h, v, 8))
+        keys = ["dim", "ld", "dtype", "count", "capacity", "n_inexact_rows", "device", "sm_count"]
+        return dict(zip(keys, list(v)))
+
+    def device_views(self):
+        m, r, e = C.c_void_p(), C.c_void_p(), C.c_void_p()
+        check(lib().ragstore_device_views(self._h, C.byref(m), C.byref(r), C.byref(e)))
+        return m.value, r.value, e.value
+
+    # ---- search side (host buffers: the call the C# RagIndex makes)
+    def search(self, queries: np.ndarray, top_k: int):
+        q = np.ascontiguousarray(queries, dtype=np.float32)
+        if q.ndim == 1:
+            q = q[None, :]
+        nq, qd = q.shape
+        req = max(1, int(top_k))
+        idx = np.full((nq, req), -1, dtype=np.int64)
+        score = np.full((nq, req), np.nan, dtype=np.float64)
+        found = np.zeros(nq, dtype=np.int32)
+        flags = np.zeros(nq, dtype=np.int32)
+        check(lib().ragstore_search(self._h, q.ctypes.data_as(C.POINTER(C.c_float)), nq, qd, int(top_k),
+                                    idx.ctypes.data_as(C.POINTER(C.c_int64)), score.ctypes.data_as(C.POINTER(C.c_double)),
+                                    found.ctypes.data_as(C.POINTER(C.c_int32)), flags.ctypes.data_as(C.POINTER(C.c_int32))))
+        return idx, score, found, flags
+
+    # ---- device-resident variants (torch tensors or raw pointers), asynchronous on `stream`
+    def search_device(self, d_queries, n_queries: int, top_k: int, d_idx, d_score, d_found=None, d_flags=None, stream: int = 0):
+        check(lib().ragstore_search_device(self._h, _ptr(d_queries), n_queries, int(top_k), _ptr(d_idx), _ptr(d_score),
+                                           _ptr(d_found), _ptr(d_flags), C.c_void_p(stream)))
+
+    def search_shard_device(self, d_query, top_k: int, d_cand, d_flags=None, stream: int = 0):
+        check(lib().ragstore_search_shard_device(self._h, _ptr(d_query), int(top_k), _ptr(d_cand), _ptr(d_flags), C.c_void_p(stream)))
+
+
+def merge_shards_device(d_gathered, n_shards: int, per_shard: int, top_k: int, d_idx, d_score, d_found, device: int = 0, stream: int = 0):
+    check(lib().ragstore_merge_shards_device(_ptr(d_gathered), n_shards, per_shard, int(top_k), _ptr(d_idx), _ptr(d_score),
+                                             _ptr(d_found), device, C.c_void_p(stream)))
+
+
+def synth_fill_device(d_out, row0: int, n_rows: int, dim: int, ld: int, seed: int, round_bf16: bool = False, device: int = 0, stream: int = 0):
+    check(lib().ragstore_synth_fill_device(_ptr(d_out), row0, n_rows, dim, ld, seed, int(round_bf16), device, C.c_void_p(stream)))

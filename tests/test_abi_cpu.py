@@ -1,0 +1,47 @@
+"""CPU-only checks of the boundary: the C-ABI library builds/loads, exports every symbol the header
+declares, and refuses to run without a GPU (no CPU fallback)."""
+import os
+import re
+
+import pytest
+
+import ragstore_b200 as rb
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared():
+    src = open(os.path.join(ROOT, "include", "ragstore.h")).read()
+    return sorted(set(re.findall(r"RAGSTORE_API\s+[\w\s\*]+?\b(ragstore_\w+)\s*\(", src)))
+
+
+def test_header_declares_entry_points():
+    names = _declared()
+    for must in ("ragstore_create", "ragstore_add", "ragstore_search", "ragstore_count", "ragstore_destroy"):
+        assert must in names
+
+
+def test_library_exports_every_declared_symbol():
+    L = rb.lib()
+    for name in _declared():
+        assert hasattr(L, name), f"{name} declared in include/ragstore.h but not exported"
+    assert L.ragstore_version() >= 1000
+
+
+def test_no_cpu_fallback_without_device():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    with pytest.raises(rb.RagStoreError) as ei:
+        rb.RagStore(8, 16)
+    assert ei.value.code == 5  # RAGSTORE_ERR_NO_DEVICE
+
+
+def test_product_does_not_import_oracle():
+    pkg = os.path.join(ROOT, "llm-kubernetes-minikube-sharp4dev_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h", ".cpp")):
+                txt = open(os.path.join(dirpath, f), errors="replace").read()
+                assert not re.search(r"^\s*(from|import)\s+oracle\b", txt, re.M), f
+                assert "liboracle" not in txt, f

@@ -1,0 +1,200 @@
+"""GPU parity: the CUDA path (through the C ABI) against the CPU oracle on the same inputs.
+Bar: top-k indices bit-exact (ties -> lower row); fp32-store scores bit-equal when rows are stored
+exactly, else within 1e-5 relative (north_star); certificate flag set on ordinary data."""
+import json
+import math
+import os
+
+import numpy as np
+import pytest
+
+import ragstore_b200 as rb
+from oracle import oracle_c as oc
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+REL_TOL = 1e-5   # north_star: fp32 scores within 1e-5 relative
+
+
+def _load(name):
+    with open(os.path.join(GOLD, name)) as f:
+        return json.load(f)
+
+
+def _search(rows, q, k, dtype=rb.RAGSTORE_F32, prenorm=False):
+    rows = np.ascontiguousarray(rows, dtype=np.float32)
+    with rb.RagStore(rows.shape[1], max(1, rows.shape[0]), dtype) as st:
+        if rows.shape[0]:
+            st.add(rows, prenormalised=prenorm)
+        idx, sc, found, flags = st.search(np.asarray(q, dtype=np.float32), k)
+        return idx[0, :found[0]].copy(), sc[0, :found[0]].copy(), int(flags[0]), st.info()
+
+
+def _close(got, exp):
+    for g, e in zip(got, exp):
+        if isinstance(e, str) or (isinstance(e, float) and math.isnan(e)):
+            assert math.isnan(g)
+        else:
+            assert abs(g - e) <= REL_TOL * max(abs(e), 1e-30) + 1e-12, (g, e)
+
+
+@pytest.mark.parametrize("case", _load("kat_v1.json"), ids=lambda c: c["name"])
+def test_known_answers(case):
+    rows = np.asarray(case["rows"], dtype=np.float32).reshape(len(case["rows"]), -1)
+    q = np.asarray(case["query"], dtype=np.float32)
+    if rows.shape[0] == 0:
+        with rb.RagStore(len(q), 4) as st:
+            idx, sc, found, _ = st.search(q, case["top_k"])
+            assert found[0] == 0
+        return
+    idx, sc, flags, _ = _search(rows, q, case["top_k"])
+    assert list(idx) == case["expect_idx"]
+    _close(list(sc), case["expect_score"])
+
+
+def _corpus(c):
+    corpus = oc.synth_rows(0, c["n"], c["dim"], c["corpus_seed"])
+    q = oc.synth_rows(0, 1, c["dim"], c["query_seed"])[0]
+    corpus[7] = corpus[42]
+    corpus[c["n"] - 3] = corpus[42]
+    corpus[13] = 0.0
+    corpus[21] = q
+    corpus[22] = -q
+    return corpus, q
+
+
+@pytest.mark.parametrize("ci", range(4))
+def test_golden_seeded_queries_bit_exact(ci):
+    c = _load("synth_v1.json")["queries"][ci]
+    corpus, q = _corpus(c)
+    idx, sc, flags, info = _search(corpus, q, c["top_k"])
+    assert [int(i) for i in idx] == c["expect_idx"]
+    # unit rows are stored bit for bit -> the fp64 scores ARE the reference's values
+    assert info["n_inexact_rows"] == 0
+    assert flags & rb.RAGSTORE_HIT_EXACT_ROWS
+    assert [float(s).hex() for s in sc] == c["expect_score_hex"]
+
+
+@pytest.mark.parametrize("n,d,k", [(1, 8, 5), (5, 3, 2), (31, 33, 7), (1000, 768, 5), (10000, 768, 5),
+                                   (4097, 1024, 10), (2500, 384, 6), (3000, 100, 100), (777, 2048, 10), (300, 1536, 3),
+                                   (64, 4096, 4)])
+def test_random_corpus_matches_oracle(n, d, k):
+    rng = np.random.default_rng(n * 7919 + d)
+    rows = (rng.standard_normal((n, d)) * rng.uniform(0.1, 30.0, size=(n, 1))).astype(np.float32)  # NOT unit norm
+    q = rng.standard_normal(d).astype(np.float32)
+    eidx, esc = oc.query(rows, q, k, n_threads=4)
+    idx, sc, flags, info = _search(rows, q, k)
+    assert list(idx) == list(eidx)
+    assert np.allclose(sc, esc, rtol=REL_TOL, atol=1e-12)
+    assert flags & rb.RAGSTORE_HIT_CERTIFIED
+
+
+def test_config1_minimal_rag_10k_768_top5():
+    """BASELINE.json configs[0]: 10k x 768 fp32 synthetic normalised, single query, top-5 cosine."""
+    rows = oc.synth_rows(0, 10000, 768, 1234)
+    with rb.RagStore(768, 10000) as st:
+        st.add(rows)
+        assert st.info()["n_inexact_rows"] == 0
+        for qi in range(8):
+            q = oc.synth_rows(qi, 1, 768, 5678)[0]
+            eidx, esc = oc.query(rows, q, 5, n_threads=4)
+            idx, sc, found, flags = st.search(q, 5)
+            assert list(idx[0]) == list(eidx)
+            assert np.array_equal(sc[0].view(np.uint64), esc.view(np.uint64))   # bit-exact fp64 scores
+            assert flags[0] == (rb.RAGSTORE_HIT_CERTIFIED | rb.RAGSTORE_HIT_EXACT_ROWS)
+
+
+def test_batch_of_queries_and_appends():
+    rows = oc.synth_rows(0, 6000, 256, 3)
+    qs = oc.synth_rows(0, 70, 256, 4)          # > one context batch (64)
+    with rb.RagStore(256, 8000) as st:
+        assert st.add(rows[:2500]) == 0
+        assert st.add(rows[2500:2501]) == 2500
+        assert st.add(rows[2501:]) == 2501
+        assert st.count() == 6000
+        idx, sc, found, flags = st.search(qs, 10)
+        for i in range(qs.shape[0]):
+            eidx, esc = oc.query(rows, qs[i], 10, n_threads=4)
+            assert list(idx[i]) == list(eidx)
+            assert np.array_equal(sc[i].view(np.uint64), esc.view(np.uint64))
+
+
+def test_duplicates_everywhere_lower_index_wins():
+    base = oc.synth_rows(0, 1, 128, 5)[0]
+    rows = np.tile(base, (5000, 1))
+    q = oc.synth_rows(0, 1, 128, 6)[0]
+    idx, sc, flags, _ = _search(rows, q, 10)
+    assert list(idx) == list(range(10))
+    eidx, esc = oc.query(rows, q, 10)
+    assert np.array_equal(sc.view(np.uint64), esc.view(np.uint64))
+
+
+def test_dim_mismatch_and_k_semantics():
+    rows = oc.synth_rows(0, 50, 16, 1)
+    with rb.RagStore(16, 64) as st:
+        st.add(rows)
+        idx, sc, found, _ = st.search(np.ones(15, dtype=np.float32), 3)
+        assert list(idx[0]) == [0, 1, 2] and list(sc[0]) == [-1.0, -1.0, -1.0]
+        idx, sc, found, _ = st.search(rows[9], 0)
+        assert found[0] == 1 and idx[0, 0] == 9
+        idx, sc, found, _ = st.search(rows[9], 200)
+        assert found[0] == 50
+        eidx, _ = oc.query(rows, rows[9], 200)
+        assert list(idx[0, :50]) == list(eidx)
+        with pytest.raises(rb.RagStoreError):
+            st.add(np.ones((2, 15), dtype=np.float32))
+        with pytest.raises(rb.RagStoreError):
+            st.add(np.ones((100, 16), dtype=np.float32))   # capacity
+
+
+def test_scale_invariance_and_linearity_properties():
+    """Size-independent properties: positive row scaling leaves ranking and (to 1e-5) scores unchanged;
+    searching for a stored row returns that row first with score ~1."""
+    rng = np.random.default_rng(5)
+    rows = oc.synth_rows(0, 20000, 768, 77)
+    scaled = rows * rng.uniform(0.5, 4.0, size=(rows.shape[0], 1)).astype(np.float32)
+    q = oc.synth_rows(3, 1, 768, 78)[0]
+    i1, s1, _, _ = _search(rows, q, 10)
+    i2, s2, _, _ = _search(scaled, q, 10)
+    assert list(i1) == list(i2)
+    assert np.allclose(s1, s2, rtol=REL_TOL)
+    i3, s3, _, _ = _search(rows, rows[12345], 1)
+    assert i3[0] == 12345 and abs(s3[0] - 1.0) < 1e-6
+
+
+def test_device_synth_matches_oracle_generator():
+    import torch
+    d_out = torch.empty((1000, 768), dtype=torch.float32, device="cuda")
+    from ragstore_b200 import native
+    native.synth_fill_device(d_out, 17, 1000, 768, 768, 1234)
+    torch.cuda.synchronize()
+    assert np.array_equal(d_out.cpu().numpy().view(np.uint32), oc.synth_rows(17, 1000, 768, 1234).view(np.uint32))
+    native.synth_fill_device(d_out, 0, 1000, 768, 768, 99, round_bf16=True)
+    torch.cuda.synchronize()
+    assert np.array_equal(d_out.cpu().numpy().view(np.uint32), oc.synth_rows(0, 1000, 768, 99, round_bf16=True).view(np.uint32))
+
+
+def test_bf16_store_matches_oracle_on_rounded_inputs():
+    """bf16 storage: inputs already bf16-representable and added PRENORMALISED are stored bit for bit,
+    so the oracle on the same (rounded) inputs must agree exactly; stated tolerance otherwise 1e-5 rel."""
+    rows = oc.synth_rows(0, 20000, 768, 1234, round_bf16=True)
+    q = oc.synth_rows(0, 1, 768, 5678)[0]
+    eidx, esc = oc.query(rows, q, 100, n_threads=4)
+    idx, sc, flags, info = _search(rows, q, 100, dtype=rb.RAGSTORE_BF16, prenorm=True)
+    assert info["n_inexact_rows"] == 0
+    assert list(idx) == list(eidx)
+    assert np.array_equal(sc.view(np.uint64), esc.view(np.uint64))
+
+
+def test_rag_index_mirror():
+    emb = {f"t{i}": oc.synth_rows(i, 1, 64, 42)[0] for i in range(40)}
+    ri = rb.RagIndex("nomic-embed-text", embedder=lambda model, text: emb[text], capacity_rows=128)
+    ri.AddRange([rb.RagChunk(f"doc.md#{i}", "doc.md", f"t{i}", emb[f"t{i}"]) for i in range(40)])
+    hits = ri.Query("t7", 5)
+    assert len(hits) == 5 and hits[0].Id == "doc.md#7" and hits[0].Text == "t7"
+    rows = np.stack([emb[f"t{i}"] for i in range(40)])
+    eidx, esc = oc.query(rows, emb["t7"], 5)
+    assert [h.Id for h in hits] == [f"doc.md#{i}" for i in eidx]
+    assert [h.Score for h in hits] == list(esc)
+    assert rb.RagIndex("m").QueryEmbedding(emb["t1"], 3) == []
+    ri.close()
