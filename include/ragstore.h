@@ -49,6 +49,12 @@ enum {
 /* storage element type of the device matrix (north_star (1): fp32, optionally bf16) */
 enum { RAGSTORE_F32 = 0, RAGSTORE_BF16 = 1 };
 
+/* flags for ragstore_create.  A row whose stored image differs from the floats that were added
+ * (normalising changed it, or bf16 rounding did) can keep its original fp32 values in a sidecar that
+ * only the rescoring stage reads, so returned scores are the reference's values for the row as added.
+ * Default: sidecar on for fp32 stores, off for bf16 stores. */
+enum { RAGSTORE_CREATE_DEFAULT = 0, RAGSTORE_CREATE_SIDECAR_ON = 1, RAGSTORE_CREATE_SIDECAR_OFF = 2 };
+
 /* flags for ragstore_add */
 enum {
     RAGSTORE_ADD_HOST = 0,           /* `rows` is host memory (pageable or pinned) */
@@ -61,8 +67,9 @@ enum {
 enum {
     RAGSTORE_HIT_CERTIFIED = 1,  /* the candidate margin proved that no row outside the rescored
                                     set can belong to the top-k (DESIGN.md "certificate") */
-    RAGSTORE_HIT_EXACT_ROWS = 2  /* every returned row is stored bit-for-bit as it was added, so
-                                    its fp64 score is the reference's value, not a 1e-7 neighbour */
+    RAGSTORE_HIT_EXACT_ROWS = 2  /* every returned row was rescored from the exact fp32 values that
+                                    were added (stored bit-for-bit, or kept in the sidecar), so its
+                                    fp64 score is the reference's value, not a 1e-7 neighbour */
 };
 
 /* one rescored hit as exchanged between shards: 16 bytes, (score desc, id asc) is the total order */
@@ -75,7 +82,8 @@ typedef struct ragstore_cand {
 
 /* Replaces `new RagIndex(..)` + `List<RagChunk> _chunks = new()` (RagIndex.cs:8,11).
  * dim: embedding length (the reference takes whatever the model returns; fixed here at create).
- * capacity_rows: rows reserved in HBM (append-only, like the reference's list).
+ * capacity_rows: upper bound on rows; only ADDRESS SPACE is reserved for it, physical HBM is mapped
+ *   as rows arrive (append-only, like the reference's list), so a generous bound is free.
  * device: CUDA ordinal.  Fails with RAGSTORE_ERR_NO_DEVICE when no GPU is present. */
 RAGSTORE_API int ragstore_create(int dim, int dtype, int64_t capacity_rows, int device,
                                  uint32_t flags, ragstore_t** out);
@@ -144,7 +152,8 @@ RAGSTORE_API int ragstore_last_error(char* buf, int buf_len);
 RAGSTORE_API int ragstore_version(void);
 
 /* Store facts for tests and the bench: fills up to n of
- * [dim, ld (padded row length), dtype, count, capacity, n_inexact_rows, device, sm_count]. */
+ * [dim, ld (padded row length), dtype, count, capacity, n_inexact_rows, device, sm_count,
+ *  has_sidecar, sidecar_rows, matrix_bytes_mapped, uses_vmm]. */
 RAGSTORE_API int ragstore_info(ragstore_t* s, int64_t* out, int n);
 
 /* Raw device views of the store (matrix, per-row reciprocal norms) for tests and benches. */

@@ -34,8 +34,19 @@ __global__ void __launch_bounds__(256) normalise_rows_kernel(const NormaliseArgs
         T* dst = static_cast<T*>(a.dst) + r * static_cast<int64_t>(a.ld);
         double acc2 = 0.0;
         bool same = (scale == 1.0f);
+        // fp32 store: "stored == input" is known now; keep the original values of an inexact row in
+        // the sidecar BEFORE the in-place write destroys them.
+        float* raw = nullptr;
+        if (sizeof(T) == 4 && !same && a.raw_slot) {
+            unsigned int slot = 0;
+            if (lane == 0) slot = atomicAdd(a.raw_count, 1u);
+            slot = __shfl_sync(0xffffffffu, slot, 0);
+            raw = a.raw_rows + static_cast<size_t>(slot) * a.raw_ld;
+            if (lane == 0) a.raw_slot[r] = static_cast<int32_t>(slot);
+        }
         for (int i = lane; i < a.ld; i += 32) {
             const float x = i < a.dim ? src[i] : 0.f;  // read before the (possibly aliasing) write
+            if (raw && i < a.raw_ld) raw[i] = x;
             const float y = __fmul_rn(x, scale);
             float stored;
             if constexpr (sizeof(T) == 4) {
@@ -51,6 +62,21 @@ __global__ void __launch_bounds__(256) normalise_rows_kernel(const NormaliseArgs
         }
         const double n2s = warp_sum(acc2);
         same = __all_sync(0xffffffffu, same);
+        if (sizeof(T) == 2 && a.raw_slot) {  // bf16 store: exactness is only known after rounding
+            if (!same) {
+                unsigned int slot = 0;
+                if (lane == 0) slot = atomicAdd(a.raw_count, 1u);
+                slot = __shfl_sync(0xffffffffu, slot, 0);
+                raw = a.raw_rows + static_cast<size_t>(slot) * a.raw_ld;
+                for (int i = lane; i < a.raw_ld; i += 32) raw[i] = i < a.dim ? src[i] : 0.f;
+                if (lane == 0) a.raw_slot[r] = static_cast<int32_t>(slot);
+            }
+        }
+        if (a.raw_slot && same && lane == 0) a.raw_slot[r] = -1;
+        if (lane == 0 && a.min_norm_bits && n2 > 0.0 && n2 < CUDART_INF) {
+            // positive floats order like their bit patterns; round the norm DOWN so it stays a lower bound
+            atomicMin(a.min_norm_bits, __float_as_uint(__double2float_rd(sqrt(n2))));
+        }
         if (lane == 0) {
             a.rnorm[r] = (n2s > 0.0 && n2s < CUDART_INF) ? static_cast<float>(1.0 / sqrt(n2s)) : 0.f;
             a.exact[r] = same ? 1 : 0;

@@ -14,6 +14,7 @@
 #include <vector>
 
 #include "ragstore_internal.h"
+#include "vmm_buffer.h"
 
 using namespace rag;
 
@@ -90,10 +91,17 @@ struct ragstore {
     int64_t capacity = 0;
     std::atomic<int64_t> count{0};
     int64_t row_base = 0;
+    VmmBuffer mat_buf, rnorm_buf, exact_buf, slot_buf, raw_buf;  // address-stable, grown on demand
     void* mat = nullptr;
     float* rnorm = nullptr;
     uint8_t* exact = nullptr;
-    unsigned long long* d_inexact = nullptr;
+    int32_t* raw_slot = nullptr;   // null when the store keeps no sidecar
+    float* raw_rows = nullptr;
+    int raw_ld = 0;
+    int64_t raw_used = 0;          // sidecar rows in use (host copy, refreshed after every add)
+    unsigned long long* d_inexact = nullptr;  // [0] inexact rows, then [1] raw_count (u32), [2] min_norm_bits (u32)
+    unsigned int* d_raw_count = nullptr;
+    uint32_t* d_min_norm = nullptr;
     cudaStream_t ingest_stream = nullptr;
     cudaStream_t dev_stream = nullptr;
     std::mutex add_mu;
@@ -162,6 +170,10 @@ ScanArgs base_args(const ragstore* s, int64_t n, int take, int kp) {
     a.mat = s->mat;
     a.rnorm = s->rnorm;
     a.exact = s->exact;
+    a.raw_slot = s->raw_slot;
+    a.raw_rows = s->raw_rows;
+    a.raw_ld = s->raw_ld;
+    a.min_norm_bits = s->d_min_norm;
     a.n_rows = n;
     a.dim = s->dim;
     a.ld = s->ld;
@@ -189,7 +201,6 @@ int ragstore_last_error(char* buf, int buf_len) {
 }
 
 int ragstore_create(int dim, int dtype, int64_t capacity_rows, int device, uint32_t flags, ragstore_t** out) {
-    (void)flags;
     if (!out) return fail(RAGSTORE_ERR_INVALID, "ragstore_create: out is null");
     *out = nullptr;
     if (dim <= 0 || capacity_rows <= 0 || (dtype != RAGSTORE_F32 && dtype != RAGSTORE_BF16))
@@ -228,15 +239,35 @@ int ragstore_create(int dim, int dtype, int64_t capacity_rows, int device, uint3
         ragstore_destroy(s);
         return rc;
     };
-    const size_t mat_bytes = static_cast<size_t>(capacity_rows) * s->ld * s->elem_size();
     const size_t cap4 = static_cast<size_t>((capacity_rows + 3) & ~3ll) + 64;
+    // sidecar of original fp32 rows for inexactly stored ones: on for fp32 stores, off for bf16 stores
+    // (lossy by choice) unless the caller says otherwise
+    bool sidecar = dtype == RAGSTORE_F32;
+    if (flags & RAGSTORE_CREATE_SIDECAR_ON) sidecar = true;
+    if (flags & RAGSTORE_CREATE_SIDECAR_OFF) sidecar = false;
+    s->raw_ld = (dim + 3) / 4 * 4;
     cudaError_t e;
-    if ((e = cudaMalloc(&s->mat, mat_bytes)) != cudaSuccess) return bail(fail(RAGSTORE_ERR_CUDA, "cudaMalloc(matrix)", cudaGetErrorString(e)));
-    if ((e = cudaMalloc(&s->rnorm, cap4 * sizeof(float))) != cudaSuccess) return bail(fail(RAGSTORE_ERR_CUDA, "cudaMalloc(rnorm)", cudaGetErrorString(e)));
-    if ((e = cudaMemset(s->rnorm, 0, cap4 * sizeof(float))) != cudaSuccess) return bail(fail(RAGSTORE_ERR_CUDA, "cudaMemset(rnorm)", cudaGetErrorString(e)));
-    if ((e = cudaMalloc(&s->exact, cap4)) != cudaSuccess) return bail(fail(RAGSTORE_ERR_CUDA, "cudaMalloc(exact)", cudaGetErrorString(e)));
-    if ((e = cudaMalloc(&s->d_inexact, sizeof(unsigned long long))) != cudaSuccess) return bail(fail(RAGSTORE_ERR_CUDA, "cudaMalloc(counter)", cudaGetErrorString(e)));
-    if ((e = cudaMemset(s->d_inexact, 0, sizeof(unsigned long long))) != cudaSuccess) return bail(fail(RAGSTORE_ERR_CUDA, "cudaMemset(counter)", cudaGetErrorString(e)));
+    int vr;
+    if ((vr = s->mat_buf.reserve(static_cast<size_t>(capacity_rows) * s->ld * s->elem_size(), device))) return bail(fail(RAGSTORE_ERR_CUDA, "reserve(matrix)", cudaGetErrorString(static_cast<cudaError_t>(vr))));
+    if ((vr = s->rnorm_buf.reserve(cap4 * sizeof(float), device))) return bail(fail(RAGSTORE_ERR_CUDA, "reserve(rnorm)", cudaGetErrorString(static_cast<cudaError_t>(vr))));
+    if ((vr = s->exact_buf.reserve(cap4, device))) return bail(fail(RAGSTORE_ERR_CUDA, "reserve(exact)", cudaGetErrorString(static_cast<cudaError_t>(vr))));
+    s->mat = s->mat_buf.ptr<void>();
+    s->rnorm = s->rnorm_buf.ptr<float>();
+    s->exact = s->exact_buf.ptr<uint8_t>();
+    if (sidecar) {
+        if ((vr = s->slot_buf.reserve(cap4 * sizeof(int32_t), device))) return bail(fail(RAGSTORE_ERR_CUDA, "reserve(raw_slot)", cudaGetErrorString(static_cast<cudaError_t>(vr))));
+        if ((vr = s->raw_buf.reserve(static_cast<size_t>(capacity_rows) * s->raw_ld * sizeof(float), device))) return bail(fail(RAGSTORE_ERR_CUDA, "reserve(raw_rows)", cudaGetErrorString(static_cast<cudaError_t>(vr))));
+        s->raw_slot = s->slot_buf.ptr<int32_t>();
+        s->raw_rows = s->raw_buf.ptr<float>();
+    }
+    if ((e = cudaMalloc(&s->d_inexact, 64)) != cudaSuccess) return bail(fail(RAGSTORE_ERR_CUDA, "cudaMalloc(counters)", cudaGetErrorString(e)));
+    if ((e = cudaMemset(s->d_inexact, 0, 64)) != cudaSuccess) return bail(fail(RAGSTORE_ERR_CUDA, "cudaMemset(counters)", cudaGetErrorString(e)));
+    s->d_raw_count = reinterpret_cast<unsigned int*>(s->d_inexact + 1);
+    s->d_min_norm = reinterpret_cast<uint32_t*>(s->d_inexact + 2);
+    {
+        const uint32_t inf_bits = 0x7F800000u;
+        if ((e = cudaMemcpy(s->d_min_norm, &inf_bits, 4, cudaMemcpyHostToDevice)) != cudaSuccess) return bail(fail(RAGSTORE_ERR_CUDA, "cudaMemcpy(min_norm)", cudaGetErrorString(e)));
+    }
     if ((e = cudaStreamCreateWithFlags(&s->ingest_stream, cudaStreamNonBlocking)) != cudaSuccess) return bail(fail(RAGSTORE_ERR_CUDA, "cudaStreamCreate", cudaGetErrorString(e)));
     if ((e = cudaStreamCreateWithFlags(&s->dev_stream, cudaStreamNonBlocking)) != cudaSuccess) return bail(fail(RAGSTORE_ERR_CUDA, "cudaStreamCreate", cudaGetErrorString(e)));
     int rc = alloc_scratch(s->dev_scratch);
@@ -261,9 +292,11 @@ int ragstore_destroy(ragstore_t* s) {
     if (s->dev_stream) cudaStreamDestroy(s->dev_stream);
     cudaFree(s->d_stage);
     cudaFree(s->d_inexact);
-    cudaFree(s->exact);
-    cudaFree(s->rnorm);
-    cudaFree(s->mat);
+    s->raw_buf.release();
+    s->slot_buf.release();
+    s->exact_buf.release();
+    s->rnorm_buf.release();
+    s->mat_buf.release();
     delete s;
     return RAGSTORE_OK;
 }
@@ -298,11 +331,29 @@ int ragstore_add(ragstore_t* s, const float* rows, int64_t n_rows, int row_dim, 
     for (int64_t r0 = 0; r0 < n_rows; r0 += chunk_rows) {
         const int64_t n = std::min(chunk_rows, n_rows - r0);
         const float* src = rows + r0 * s->dim;
+        {   // map physical memory behind the rows about to land (addresses of existing rows never move)
+            const size_t upto = static_cast<size_t>(first + r0 + n);
+            const size_t upto4 = ((upto + 3) & ~size_t(3)) + 64;
+            int vr = s->mat_buf.ensure(upto * s->ld * esz, false, s->ingest_stream);
+            if (!vr) vr = s->rnorm_buf.ensure(upto4 * sizeof(float), true, s->ingest_stream);
+            if (!vr) vr = s->exact_buf.ensure(upto4, true, s->ingest_stream);
+            if (!vr && s->raw_slot) vr = s->slot_buf.ensure(upto4 * sizeof(int32_t), true, s->ingest_stream);
+            if (!vr && s->raw_slot) {
+                const size_t worst = std::min<size_t>(static_cast<size_t>(s->raw_used + n), static_cast<size_t>(s->capacity));
+                vr = s->raw_buf.ensure(worst * s->raw_ld * sizeof(float), false, s->ingest_stream);
+            }
+            if (vr) return fail(RAGSTORE_ERR_CUDA, "mapping device memory for new rows", cudaGetErrorString(static_cast<cudaError_t>(vr)));
+        }
         uint8_t* dst_row = static_cast<uint8_t*>(s->mat) + static_cast<size_t>(first + r0) * s->ld * esz;
         NormaliseArgs a{};
         a.dst = dst_row;
         a.rnorm = s->rnorm + first + r0;
         a.exact = s->exact + first + r0;
+        a.raw_slot = s->raw_slot ? s->raw_slot + first + r0 : nullptr;
+        a.raw_rows = s->raw_rows;
+        a.raw_ld = s->raw_ld;
+        a.raw_count = s->d_raw_count;
+        a.min_norm_bits = s->d_min_norm;
         a.n_rows = n;
         a.dim = s->dim;
         a.ld = s->ld;
@@ -333,7 +384,11 @@ int ragstore_add(ragstore_t* s, const float* rows, int64_t n_rows, int row_dim, 
         }
         const int rc = launch_normalise(a, s->ingest_stream);
         if (rc) return fail(RAGSTORE_ERR_CUDA, "normalise kernel launch", cudaGetErrorString(static_cast<cudaError_t>(rc)));
-        if (!in_place && !on_device) CU_TRY(cudaStreamSynchronize(s->ingest_stream));  // staging buffer reuse
+        // the sidecar bound for the next chunk needs this chunk's count; this also fences staging reuse
+        unsigned int raw_now = 0;
+        CU_TRY(cudaMemcpyAsync(&raw_now, s->d_raw_count, sizeof(raw_now), cudaMemcpyDeviceToHost, s->ingest_stream));
+        CU_TRY(cudaStreamSynchronize(s->ingest_stream));
+        s->raw_used = raw_now;
     }
     CU_TRY(cudaStreamSynchronize(s->ingest_stream));
     s->count.store(first + n_rows, std::memory_order_release);  // publish: searches see a prefix
@@ -345,8 +400,9 @@ int ragstore_info(ragstore_t* s, int64_t* out, int n) {
     DeviceGuard g(s->device);
     unsigned long long inexact = 0;
     CU_TRY(cudaMemcpy(&inexact, s->d_inexact, sizeof(inexact), cudaMemcpyDeviceToHost));
-    const int64_t v[8] = {s->dim, s->ld, s->dtype, s->count.load(), s->capacity, static_cast<int64_t>(inexact), s->device, s->sm_count};
-    for (int i = 0; i < n && i < 8; ++i) out[i] = v[i];
+    const int64_t v[12] = {s->dim, s->ld, s->dtype, s->count.load(), s->capacity, static_cast<int64_t>(inexact), s->device, s->sm_count,
+                           s->raw_slot ? 1 : 0, s->raw_used, static_cast<int64_t>(s->mat_buf.mapped()), s->mat_buf.uses_vmm() ? 1 : 0};
+    for (int i = 0; i < n && i < 12; ++i) out[i] = v[i];
     return RAGSTORE_OK;
 }
 

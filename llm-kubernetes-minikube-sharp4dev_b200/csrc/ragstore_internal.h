@@ -25,6 +25,10 @@ struct ScanArgs {
     const void* mat;        // row-major [n_rows][ld] of fp32 or bf16
     const float* rnorm;     // [round_up(n_rows,4)] reciprocal norm of each STORED row (0 for a zero row)
     const uint8_t* exact;   // [n_rows] 1 = stored bit-for-bit as added (may be null => treated as 1)
+    const int32_t* raw_slot;// [n_rows] slot of the row's original fp32 values in raw_rows, -1 = stored exactly (may be null)
+    const float* raw_rows;  // [n_slots][raw_ld] original fp32 rows of the inexactly stored ones (sidecar)
+    int raw_ld;
+    const uint32_t* min_norm_bits;  // fp32 bits of the smallest non-zero original row norm (may be null)
     int64_t n_rows;
     int dim, ld, dtype;
     int64_t row_base;
@@ -56,6 +60,11 @@ struct NormaliseArgs {
     void* dst;            // first destination row in the matrix
     float* rnorm;         // destination slice of the per-row reciprocal norms
     uint8_t* exact;       // destination slice of the per-row exact flags
+    int32_t* raw_slot;    // destination slice of the sidecar slots (null = no sidecar)
+    float* raw_rows;      // sidecar base
+    int raw_ld;
+    unsigned int* raw_count;              // device counter of sidecar rows in use
+    uint32_t* min_norm_bits;              // device scalar: fp32 bits of the smallest non-zero row norm
     int64_t n_rows;
     int dim, ld, dtype;
     int prenormalised;

@@ -47,6 +47,7 @@ struct ScanMisc {  // lives in shared memory at off_misc
     double ex[kMaxKp];
     double dot[kMaxKp];
     double nb[kMaxKp];
+    uint8_t raw_fmt[kMaxKp];  // 1 = the staged row is the fp32 original from the sidecar
 };
 
 // ---------------------------------------------------------------- warp-level sorted lists in smem
@@ -304,18 +305,32 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
     // lists[0..kp) : the kp best approximate keys of the whole shard, descending
 
     const int n_cand = static_cast<int>(min(static_cast<int64_t>(kp), a.n_rows));
-    const uint32_t rs = L.row_bytes + 16;  // padded smem row stride: spreads rows over banks
+    // Rows are staged in the (now idle) tile ring.  A row that was stored inexactly (normalised with
+    // scale != 1, or rounded to bf16) is rescored from its ORIGINAL fp32 values kept in the sidecar,
+    // so the fp64 score below is the reference's value for the row as it was added.
+    const uint32_t raw_bytes = a.raw_slot ? static_cast<uint32_t>(a.raw_ld) * 4u : 0u;
+    const uint32_t rs = max(L.row_bytes, raw_bytes) + 16;  // padded smem row stride: spreads rows over banks
     const int cap = max(1, static_cast<int>((L.n_stages * L.stage_bytes) / rs));
     const int nchunks = static_cast<int>(L.nchunks);
-    uint8_t* rowbuf = smem;  // the tile ring is idle now
+    uint8_t* rowbuf = smem;
 
     for (int b0 = 0; b0 < n_cand; b0 += cap) {
         const int nb = min(cap, n_cand - b0);
         for (int c = warp; c < nb; c += kScanThreads / 32) {
             const uint32_t row = key_row(lists[b0 + c]);
-            const uint4* src = reinterpret_cast<const uint4*>(mat + static_cast<size_t>(row) * L.row_bytes);
+            const int32_t slot = a.raw_slot ? a.raw_slot[row] : -1;
+            const uint4* src;
+            int nch;
+            if (slot >= 0) {
+                src = reinterpret_cast<const uint4*>(a.raw_rows + static_cast<size_t>(slot) * a.raw_ld);
+                nch = static_cast<int>(raw_bytes / 16);
+            } else {
+                src = reinterpret_cast<const uint4*>(mat + static_cast<size_t>(row) * L.row_bytes);
+                nch = nchunks;
+            }
             uint4* dst = reinterpret_cast<uint4*>(rowbuf + static_cast<size_t>(c) * rs);
-            for (int ch = lane; ch < nchunks; ch += 32) dst[ch] = __ldg(src + ch);
+            for (int ch = lane; ch < nch; ch += 32) dst[ch] = __ldg(src + ch);
+            if (lane == 0) misc->raw_fmt[c] = slot >= 0 ? 1 : 0;
         }
         __syncthreads();
         const int nchains = 2 * nb + (b0 == 0 ? 1 : 0);
@@ -327,15 +342,16 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
             } else {
                 const int c = id >> 1;
                 const uint8_t* row = rowbuf + static_cast<size_t>(c) * rs;
+                const bool f32row = (sizeof(T) == 4) || misc->raw_fmt[c];
                 if (id & 1) {
                     for (int i = 0; i < a.dim; ++i) {
-                        const float x = elem_at<T>(row, i);
+                        const float x = f32row ? reinterpret_cast<const float*>(row)[i] : elem_at<T>(row, i);
                         acc = __dadd_rn(acc, static_cast<double>(__fmul_rn(x, x)));  // :132
                     }
                     misc->nb[c] = acc;
                 } else {
                     for (int i = 0; i < a.dim; ++i) {
-                        const float x = elem_at<T>(row, i);
+                        const float x = f32row ? reinterpret_cast<const float*>(row)[i] : elem_at<T>(row, i);
                         acc = __dadd_rn(acc, static_cast<double>(__fmul_rn(qraw[i], x)));  // :130
                     }
                     misc->dot[c] = acc;
@@ -365,7 +381,7 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
         if (rank < a.k_take) {
             if (a.out_idx) a.out_idx[rank] = gid;
             if (a.out_score) a.out_score[rank] = sc;
-            if (a.exact && a.exact[rc] == 0) atomicAdd(&misc->inexact, 1);
+            if (a.exact && a.exact[rc] == 0 && !(a.raw_slot && a.raw_slot[rc] >= 0)) atomicAdd(&misc->inexact, 1);
             if (rank == a.k_take - 1) misc->ek = sc;
         }
         if (a.out_cand && rank < a.cand_slots && rank < a.k_take) {
@@ -385,8 +401,18 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
         if (a.n_rows <= static_cast<int64_t>(kp)) {
             cert = true;  // every row was rescored
         } else {
+            // Rows outside the survivors have approximate score <= bound.  Their reference score is at
+            // most bound + eps, where eps covers the fp32 rounding of the scan AND the reference's
+            // "+1e-9" in the denominator (RagIndex.cs:134), which moves a score by at most
+            // 1e-9 / (|q| * smallest row norm) towards zero.
             const double bound = static_cast<double>(key_score(lists[kp - 1]));
-            cert = misc->ek > bound + static_cast<double>(a.eps);  // false if either side is NaN
+            double shrink = 0.0;
+            if (a.min_norm_bits) {
+                const double d = sqrt(misc->na) * static_cast<double>(__uint_as_float(*a.min_norm_bits));
+                shrink = 1e-9 / d;  // +inf when the query is zero: then only a full rescore certifies
+            }
+            cert = misc->ek > bound + static_cast<double>(a.eps) + shrink;  // false if either side is NaN
+            if (misc->na == 0.0) cert = true;  // zero query: every reference score is exactly +0.0 (or NaN, ranked last)
         }
         int32_t flags = 0;
         if (cert) flags |= RAGSTORE_HIT_CERTIFIED;
@@ -410,6 +436,7 @@ static bool make_layout(const ScanArgs& a, int dv, ScanLayout& L) {
     const uint32_t fixed_lists = sizeof(uint64_t) * 2u * kConsumerWarps * static_cast<uint32_t>(a.kp);
     const uint32_t fixed = 16u * 8u * 2u /*barriers*/ + 2u * L.qpad * 4u + fixed_lists + sizeof(ScanMisc) + 512u;
     if (fixed + 2u * (4u * L.row_bytes + 128u) > kSmemBudget) return false;
+    if (a.raw_slot && static_cast<uint32_t>(a.raw_ld) * 4u + 16u > 2u * (4u * L.row_bytes + 128u)) return false;
     const uint32_t ring = kSmemBudget - fixed;
     // rows per tile: a multiple of 4 (16-byte granularity of the reciprocal-norm slice), ~32 KB
     uint32_t R = (32u * 1024u) / L.row_bytes;

@@ -10,6 +10,7 @@ import numpy as np
 RAGSTORE_F32, RAGSTORE_BF16 = 0, 1
 RAGSTORE_ADD_HOST, RAGSTORE_ADD_DEVICE, RAGSTORE_ADD_PRENORMALISED = 0, 1, 2
 RAGSTORE_HIT_CERTIFIED, RAGSTORE_HIT_EXACT_ROWS = 1, 2
+RAGSTORE_CREATE_SIDECAR_ON, RAGSTORE_CREATE_SIDECAR_OFF = 1, 2
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB = None
@@ -84,9 +85,9 @@ def _ptr(x):
 class RagStore:
     """Owning wrapper of one ragstore_t (one device-resident shard)."""
 
-    def __init__(self, dim: int, capacity_rows: int, dtype: int = RAGSTORE_F32, device: int = 0):
+    def __init__(self, dim: int, capacity_rows: int, dtype: int = RAGSTORE_F32, device: int = 0, flags: int = 0):
         self._h = C.c_void_p()
-        check(lib().ragstore_create(dim, dtype, capacity_rows, device, 0, C.byref(self._h)))
+        check(lib().ragstore_create(dim, dtype, capacity_rows, device, flags, C.byref(self._h)))
         self.dim, self.dtype, self.device, self.capacity = dim, dtype, device, capacity_rows
 
     def close(self):
@@ -132,9 +133,10 @@ class RagStore:
         check(lib().ragstore_set_row_base(self._h, base))
 
     def info(self) -> dict:
-        v = (C.c_int64 * 8)()
-        check(lib().ragstore_info(self._h, v, 8))
-        keys = ["dim", "ld", "dtype", "count", "capacity", "n_inexact_rows", "device", "sm_count"]
+        v = (C.c_int64 * 12)()
+        check(lib().ragstore_info(self._h, v, 12))
+        keys = ["dim", "ld", "dtype", "count", "capacity", "n_inexact_rows", "device", "sm_count",
+                "has_sidecar", "sidecar_rows", "matrix_bytes_mapped", "uses_vmm"]
         return dict(zip(keys, list(v)))
 
     def device_views(self):

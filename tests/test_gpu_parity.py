@@ -40,8 +40,8 @@ def _close(got, exp):
 
 @pytest.mark.parametrize("case", _load("kat_v1.json"), ids=lambda c: c["name"])
 def test_known_answers(case):
-    rows = np.asarray(case["rows"], dtype=np.float32).reshape(len(case["rows"]), -1)
     q = np.asarray(case["query"], dtype=np.float32)
+    rows = np.asarray(case["rows"], dtype=np.float32).reshape(len(case["rows"]), -1 if case["rows"] else len(q))
     if rows.shape[0] == 0:
         with rb.RagStore(len(q), 4) as st:
             idx, sc, found, _ = st.search(q, case["top_k"])
@@ -85,8 +85,28 @@ def test_random_corpus_matches_oracle(n, d, k):
     eidx, esc = oc.query(rows, q, k, n_threads=4)
     idx, sc, flags, info = _search(rows, q, k)
     assert list(idx) == list(eidx)
-    assert np.allclose(sc, esc, rtol=REL_TOL, atol=1e-12)
-    assert flags & rb.RAGSTORE_HIT_CERTIFIED
+    # non-unit rows are stored normalised, but rescored from their original values (sidecar):
+    # the fp64 scores are the reference's, bit for bit
+    assert np.array_equal(sc.view(np.uint64), esc.view(np.uint64))
+    assert flags == (rb.RAGSTORE_HIT_CERTIFIED | rb.RAGSTORE_HIT_EXACT_ROWS)
+    assert info["sidecar_rows"] == info["n_inexact_rows"] > 0
+
+
+def test_without_sidecar_scores_within_tolerance():
+    """Sidecar off: inexactly stored rows are rescored from their normalised image; indices still match on
+    ordinary data, scores within the north_star tolerance (1e-5 relative), and the result says so."""
+    rng = np.random.default_rng(3)
+    rows = (rng.standard_normal((5000, 768)) * 7.0).astype(np.float32)
+    q = rng.standard_normal(768).astype(np.float32)
+    eidx, esc = oc.query(rows, q, 10, n_threads=4)
+    with rb.RagStore(768, 5000, rb.RAGSTORE_F32, 0, rb.RAGSTORE_CREATE_SIDECAR_OFF) as st:
+        st.add(rows)
+        idx, sc, found, flags = st.search(q, 10)
+        assert st.info()["has_sidecar"] == 0
+    assert list(idx[0]) == list(eidx)
+    assert np.allclose(sc[0], esc, rtol=REL_TOL, atol=1e-12)
+    assert not (flags[0] & rb.RAGSTORE_HIT_EXACT_ROWS)
+    assert flags[0] & rb.RAGSTORE_HIT_CERTIFIED
 
 
 def test_config1_minimal_rag_10k_768_top5():

@@ -20,7 +20,8 @@ def run(n, d, k, dtype, iters=20):
     native.synth_fill_device(q, 0, 1, d, d, 5678)
     idx = torch.zeros(max(1, k), dtype=torch.int64, device="cuda"); sc = torch.zeros(max(1, k), dtype=torch.float64, device="cuda")
     fnd = torch.zeros(1, dtype=torch.int32, device="cuda"); flg = torch.zeros(1, dtype=torch.int32, device="cuda")
-    s = torch.cuda.current_stream().cuda_stream
+    ts = torch.cuda.Stream(); torch.cuda.set_stream(ts)
+    s = ts.cuda_stream
     for _ in range(3):
         st.search_device(q, 1, k, idx, sc, fnd, flg, stream=s)
     torch.cuda.synchronize()
@@ -37,8 +38,7 @@ def run(n, d, k, dtype, iters=20):
     st.close()
 
 if __name__ == "__main__":
-    run(10000, 768, 5, rb.RAGSTORE_F32)
-    run(1000000, 768, 10, rb.RAGSTORE_F32)
-    run(4000000, 768, 10, rb.RAGSTORE_F32)
-    run(1000000, 1024, 10, rb.RAGSTORE_F32)
-    run(2000000, 768, 100, rb.RAGSTORE_BF16)
+    F, B = rb.RAGSTORE_F32, rb.RAGSTORE_BF16
+    for (n, d, k, t) in [(10000, 768, 10, F), (10000, 768, 100, F), (10000, 768, 10, B), (10000, 768, 100, B),
+                         (2000000, 768, 10, F), (2000000, 768, 100, F), (2000000, 768, 10, B), (2000000, 768, 100, B)]:
+        run(n, d, k, t)
