@@ -156,6 +156,10 @@ RAGSTORE_API int ragstore_version(void);
  *  has_sidecar, sidecar_rows, matrix_bytes_mapped, uses_vmm]. */
 RAGSTORE_API int ragstore_info(ragstore_t* s, int64_t* out, int n);
 
+/* Profiling aid: %globaltimer (ns) at the phase boundaries of the store's most recent
+ * ragstore_search_device launch: [start, scan done, lists merged, rows staged, rescored, end]. */
+RAGSTORE_API int ragstore_debug_stamps(ragstore_t* s, uint64_t* out, int n);
+
 /* Raw device views of the store (matrix, per-row reciprocal norms) for tests and benches. */
 RAGSTORE_API int ragstore_device_views(ragstore_t* s, void** d_matrix, float** d_rnorm,
                                        uint8_t** d_exact);

@@ -122,6 +122,7 @@ int alloc_scratch(ScanScratch& s) {
     CU_TRY(cudaMalloc(&p, kScanScratchBytes));
     CU_TRY(cudaMemset(p, 0, kScanScratchBytes));
     s.ticket = reinterpret_cast<unsigned int*>(p);
+    s.stamps = reinterpret_cast<unsigned long long*>(p + 64);
     s.cta_lists = reinterpret_cast<uint64_t*>(p + 256);
     return RAGSTORE_OK;
 }
@@ -403,6 +404,15 @@ int ragstore_info(ragstore_t* s, int64_t* out, int n) {
     const int64_t v[12] = {s->dim, s->ld, s->dtype, s->count.load(), s->capacity, static_cast<int64_t>(inexact), s->device, s->sm_count,
                            s->raw_slot ? 1 : 0, s->raw_used, static_cast<int64_t>(s->mat_buf.mapped()), s->mat_buf.uses_vmm() ? 1 : 0};
     for (int i = 0; i < n && i < 12; ++i) out[i] = v[i];
+    return RAGSTORE_OK;
+}
+
+int ragstore_debug_stamps(ragstore_t* s, uint64_t* out, int n) {
+    if (!s || !out) return fail(RAGSTORE_ERR_INVALID, "ragstore_debug_stamps: null argument");
+    DeviceGuard g(s->device);
+    uint64_t v[8] = {0};
+    CU_TRY(cudaMemcpy(v, s->dev_scratch.stamps, sizeof(v), cudaMemcpyDeviceToHost));
+    for (int i = 0; i < n && i < 8; ++i) out[i] = v[i];
     return RAGSTORE_OK;
 }
 

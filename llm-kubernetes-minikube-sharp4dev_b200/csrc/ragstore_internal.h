@@ -17,6 +17,7 @@ constexpr int kMaxBatchQ = 4;                           // queries scored per co
 struct ScanScratch {
     uint64_t* cta_lists;   // [kMaxCtas * kMaxKp] per-CTA candidate keys
     unsigned int* ticket;  // [1] "last CTA done" counter, self-resetting
+    unsigned long long* stamps;  // [8] %globaltimer at the phase boundaries of the last launch (profiling aid)
 };
 constexpr size_t kScanScratchBytes = sizeof(uint64_t) * size_t(kMaxCtas) * kMaxKp + 256;
 

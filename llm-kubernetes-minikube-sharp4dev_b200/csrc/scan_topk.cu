@@ -11,18 +11,19 @@
 //   * the corpus is row-major and contiguous, so a tile of R rows is ONE contiguous span: the
 //     producer lane streams tiles (plus the R reciprocal norms) into a multi-stage shared-memory
 //     ring with 1-D bulk async copies (cp.async.bulk -> TMA engine, SASS UBLKCP) that complete on
-//     mbarriers; nothing is staged through registers, ~170 KB per SM are in flight;
-//   * a consumer warp owns whole rows: 128-bit conflict-free LDS, the normalised query in
-//     registers, a fixed 4-accumulator + xor-butterfly reduction (identical tree for every row, so
-//     duplicate rows score identically and ties fall to the lower row);
+//     mbarriers; nothing is staged through registers, ~190 KB per SM are in flight;
+//   * a consumer warp owns whole tiles (tile i of the CTA goes to warp i mod 8) and scores them four
+//     rows at a time: 128-bit conflict-free LDS, the normalised query in registers, four FMA chains
+//     per row and a transposed xor-butterfly that reduces four rows with six shuffles.  Every row
+//     goes through the same reduction tree, so duplicate rows score identically and ties fall to
+//     the lower row;
 //   * the score never leaves the SM: it is packed with the row id into an order-preserving 64-bit
-//     key and offered to the warp's sorted candidate list (threshold test first; inserts are
-//     O(k log N) per warp over the whole scan);
+//     key; keys above the warp's threshold are buffered and merged (bitonic) into the warp's sorted
+//     candidate list 32 at a time;
 //   * lists are merged warp -> CTA -> (last CTA to finish, atomic ticket) grid with bitonic merges;
 //   * the last CTA then recomputes the reference's exact fp64 arithmetic for the k' >= k survivors,
 //     orders them by (fp64 score desc, row asc), emits the top k and a certificate that no row
-//     outside the survivors could have ranked (approximate score of the worst survivor + eps is
-//     below the k-th exact score).
+//     outside the survivors could have ranked.
 // HBM traffic: every stored element is read exactly once (d * sizeof(elem) + 4 bytes per row).
 #include <math_constants.h>
 
@@ -31,11 +32,14 @@
 
 namespace rag {
 
+constexpr int kGroup = 4;  // rows scored together by one warp
+
 struct ScanLayout {
     uint32_t rows_per_tile, n_stages, row_bytes, tile_bytes, stage_bytes;
     uint32_t nchunks;    // 16-byte chunks per row
     uint32_t qpad;       // floats in each query buffer (zero padded)
-    uint32_t off_bars, off_qraw, off_qhat, off_lists, off_misc, total;
+    uint32_t off_bars, off_qraw, off_qhat, off_lists, off_buf, off_misc, total;
+    uint32_t n_consumers;  // consumer warps that take tiles; divides n_stages, so a warp owns fixed stages
 };
 
 struct ScanMisc {  // lives in shared memory at off_misc
@@ -51,20 +55,6 @@ struct ScanMisc {  // lives in shared memory at off_misc
 };
 
 // ---------------------------------------------------------------- warp-level sorted lists in smem
-// L sorted descending, length kp (multiple of 32); precondition x > L[kp-1]; x is warp-uniform.
-__device__ __forceinline__ void warp_insert_desc(uint64_t* L, int kp, uint64_t x, int lane) {
-    for (int base = kp - 32; base >= 0; base -= 32) {
-        const int j = base + lane;
-        const uint64_t cur = L[j];
-        const uint64_t prev = j > 0 ? L[j - 1] : ~0ull;
-        __syncwarp();
-        L[j] = cur > x ? cur : (prev > x ? x : prev);
-        __syncwarp();
-        const uint64_t head_prev = __shfl_sync(0xffffffffu, prev, 0);
-        if (head_prev > x) break;  // everything before this block already ranks above x
-    }
-}
-
 // A, B sorted descending (kp a power of two >= 32).  A <- top kp of A u B, sorted descending.
 __device__ __forceinline__ void warp_merge_desc(uint64_t* A, const uint64_t* B, int kp, int lane) {
     for (int j = lane; j < kp; j += 32) {
@@ -86,67 +76,121 @@ __device__ __forceinline__ void warp_merge_desc(uint64_t* A, const uint64_t* B, 
     }
 }
 
-// ---------------------------------------------------------------- per-row dot product from smem
+// one key per lane -> sorted descending across lanes (bitonic network on shuffles)
+__device__ __forceinline__ uint64_t warp_sort_desc(uint64_t v, int lane) {
+#pragma unroll
+    for (int k = 2; k <= 32; k <<= 1) {
+#pragma unroll
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            const uint64_t o = __shfl_xor_sync(0xffffffffu, v, j);
+            const bool desc_block = (lane & k) == 0;
+            const bool lower = (lane & j) == 0;
+            const bool keep_max = (lower == desc_block);
+            v = keep_max ? (v > o ? v : o) : (v < o ? v : o);
+        }
+    }
+    return v;
+}
+
+// Merge the cnt (<= 32) buffered keys of this warp into its sorted list L; B is warp-private scratch.
+__device__ __forceinline__ uint64_t warp_flush(uint64_t* L, uint64_t* B, const uint64_t* buf, int cnt, int kp,
+                                               int lane) {
+    __syncwarp();
+    uint64_t v = lane < cnt ? buf[lane] : 0ull;
+    v = warp_sort_desc(v, lane);
+    B[lane] = v;
+    for (int j = 32 + lane; j < kp; j += 32) B[j] = 0ull;
+    __syncwarp();
+    warp_merge_desc(L, B, kp, lane);
+    return L[kp - 1];
+}
+
+// ---------------------------------------------------------------- per-row dot products from smem
 template <typename T>
 struct Elem;
 template <>
 struct Elem<float> {
-    static constexpr int kPerChunk = 4;  // elements per 16-byte chunk
-    static constexpr int kQV = 1;        // float4 of query per chunk
+    static constexpr int kQV = 1;  // float4 of query per 16-byte chunk
 };
 template <>
 struct Elem<uint16_t> {  // bf16 bits
-    static constexpr int kPerChunk = 8;
     static constexpr int kQV = 2;
 };
 
 template <typename T>
-__device__ __forceinline__ void chunk_fma(const float4& v, const float4* q, float& a0, float& a1, float& a2,
-                                          float& a3) {
+__device__ __forceinline__ void chunk_fma(const float4& v, const float4* q, float (&acc)[4]) {
     if constexpr (sizeof(T) == 4) {
-        a0 = fmaf(v.x, q[0].x, a0);
-        a1 = fmaf(v.y, q[0].y, a1);
-        a2 = fmaf(v.z, q[0].z, a2);
-        a3 = fmaf(v.w, q[0].w, a3);
+        acc[0] = fmaf(v.x, q[0].x, acc[0]);
+        acc[1] = fmaf(v.y, q[0].y, acc[1]);
+        acc[2] = fmaf(v.z, q[0].z, acc[2]);
+        acc[3] = fmaf(v.w, q[0].w, acc[3]);
     } else {
         const uint32_t w0 = __float_as_uint(v.x), w1 = __float_as_uint(v.y);
         const uint32_t w2 = __float_as_uint(v.z), w3 = __float_as_uint(v.w);
-        a0 = fmaf(__uint_as_float(w0 << 16), q[0].x, a0);
-        a1 = fmaf(__uint_as_float(w0 & 0xFFFF0000u), q[0].y, a1);
-        a2 = fmaf(__uint_as_float(w1 << 16), q[0].z, a2);
-        a3 = fmaf(__uint_as_float(w1 & 0xFFFF0000u), q[0].w, a3);
-        a0 = fmaf(__uint_as_float(w2 << 16), q[1].x, a0);
-        a1 = fmaf(__uint_as_float(w2 & 0xFFFF0000u), q[1].y, a1);
-        a2 = fmaf(__uint_as_float(w3 << 16), q[1].z, a2);
-        a3 = fmaf(__uint_as_float(w3 & 0xFFFF0000u), q[1].w, a3);
+        acc[0] = fmaf(__uint_as_float(w0 << 16), q[0].x, acc[0]);
+        acc[1] = fmaf(__uint_as_float(w0 & 0xFFFF0000u), q[0].y, acc[1]);
+        acc[2] = fmaf(__uint_as_float(w1 << 16), q[0].z, acc[2]);
+        acc[3] = fmaf(__uint_as_float(w1 & 0xFFFF0000u), q[0].w, acc[3]);
+        acc[0] = fmaf(__uint_as_float(w2 << 16), q[1].x, acc[0]);
+        acc[1] = fmaf(__uint_as_float(w2 & 0xFFFF0000u), q[1].y, acc[1]);
+        acc[2] = fmaf(__uint_as_float(w3 << 16), q[1].z, acc[2]);
+        acc[3] = fmaf(__uint_as_float(w3 & 0xFFFF0000u), q[1].w, acc[3]);
     }
 }
 
-// DV > 0: query chunks for this lane live in registers (qreg); DV == 0: read them from smem (qhat).
-template <typename T, int DV>
-__device__ __forceinline__ float row_dot(const uint8_t* row, const float4* qreg, const float* qhat, int lane,
-                                         int nchunks) {
+// Scores kGroup rows (p[0..3]) against the query.  On return every lane holds the full dot product
+// of the row slot (lane>>4)*2 + ((lane>>3)&1).  The reduction tree is the standard xor butterfly
+// (16, 8, 4, 2, 1) for every row, whatever its slot in the group.
+template <typename T, int DV, bool FULL>
+__device__ __forceinline__ float group_dot(const uint8_t* const (&p)[kGroup], const float4* qreg, const float* qhat,
+                                           int lane, int nchunks) {
     constexpr int QV = Elem<T>::kQV;
-    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+    float acc[kGroup][4];
+#pragma unroll
+    for (int r = 0; r < kGroup; ++r) acc[r][0] = acc[r][1] = acc[r][2] = acc[r][3] = 0.f;
     if constexpr (DV > 0) {
 #pragma unroll
         for (int c = 0; c < DV; ++c) {
             const int ch = c * 32 + lane;
-            if (ch < nchunks) {
-                const float4 v = lds128(row + ch * 16);
-                chunk_fma<T>(v, qreg + c * QV, a0, a1, a2, a3);
+            if (FULL || ch < nchunks) {
+#pragma unroll
+                for (int r = 0; r < kGroup; ++r) {
+                    const float4 v = lds128(p[r] + ch * 16);
+                    chunk_fma<T>(v, qreg + c * QV, acc[r]);
+                }
             }
         }
     } else {
         for (int ch = lane; ch < nchunks; ch += 32) {
-            const float4 v = lds128(row + ch * 16);
             float4 q[QV];
 #pragma unroll
             for (int u = 0; u < QV; ++u) q[u] = lds128(qhat + (ch * QV + u) * 4);
-            chunk_fma<T>(v, q, a0, a1, a2, a3);
+#pragma unroll
+            for (int r = 0; r < kGroup; ++r) {
+                const float4 v = lds128(p[r] + ch * 16);
+                chunk_fma<T>(v, q, acc[r]);
+            }
         }
     }
-    return warp_sum((a0 + a1) + (a2 + a3));
+    float s[kGroup];
+#pragma unroll
+    for (int r = 0; r < kGroup; ++r) s[r] = (acc[r][0] + acc[r][1]) + (acc[r][2] + acc[r][3]);
+    // transposed butterfly: 4 rows -> 2 -> 1 while halving the lanes that carry each row
+    const bool hi = (lane & 16) != 0;
+    float k0 = hi ? s[2] : s[0];
+    const float g0 = hi ? s[0] : s[2];
+    float k1 = hi ? s[3] : s[1];
+    const float g1 = hi ? s[1] : s[3];
+    k0 += __shfl_xor_sync(0xffffffffu, g0, 16);
+    k1 += __shfl_xor_sync(0xffffffffu, g1, 16);
+    const bool hi2 = (lane & 8) != 0;
+    float k = hi2 ? k1 : k0;
+    const float g = hi2 ? k0 : k1;
+    k += __shfl_xor_sync(0xffffffffu, g, 8);
+    k += __shfl_xor_sync(0xffffffffu, k, 4);
+    k += __shfl_xor_sync(0xffffffffu, k, 2);
+    k += __shfl_xor_sync(0xffffffffu, k, 1);
+    return k;
 }
 
 template <typename T>
@@ -157,8 +201,41 @@ __device__ __forceinline__ float elem_at(const uint8_t* row, int i) {
         return bf16_bits_to_f32(reinterpret_cast<const uint16_t*>(row)[i]);
 }
 
+// Sequential fp64 accumulation of fp32 products over one staged row (RagIndex.cs:127-133).
+// kind 0: sum q[i]*x[i]   kind 1: sum x[i]*x[i]   (row == nullptr: x := q, i.e. the query norm)
+template <typename T>
+__device__ __forceinline__ double exact_chain(const uint8_t* row, bool f32row, const float* q, int dim, int kind) {
+    double acc = 0.0;  // :127
+    int i = 0;
+    for (; i + 4 <= dim; i += 4) {
+        float x[4];
+        if (row == nullptr) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) x[j] = q[i + j];
+        } else if (f32row) {
+            const float4 v = *reinterpret_cast<const float4*>(row + static_cast<size_t>(i) * 4);
+            x[0] = v.x, x[1] = v.y, x[2] = v.z, x[3] = v.w;
+        } else {
+            const uint2 v = *reinterpret_cast<const uint2*>(row + static_cast<size_t>(i) * 2);
+            x[0] = __uint_as_float(v.x << 16), x[1] = __uint_as_float(v.x & 0xFFFF0000u);
+            x[2] = __uint_as_float(v.y << 16), x[3] = __uint_as_float(v.y & 0xFFFF0000u);
+        }
+        float pr[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) pr[j] = kind ? __fmul_rn(x[j], x[j]) : __fmul_rn(q[i + j], x[j]);  // :130-132
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc = __dadd_rn(acc, static_cast<double>(pr[j]));
+    }
+    for (; i < dim; ++i) {
+        const float x = row == nullptr ? q[i] : (f32row ? reinterpret_cast<const float*>(row)[i] : elem_at<T>(row, i));
+        const float pr = kind ? __fmul_rn(x, x) : __fmul_rn(q[i], x);
+        acc = __dadd_rn(acc, static_cast<double>(pr));
+    }
+    return acc;
+}
+
 // ---------------------------------------------------------------- the kernel
-template <typename T, int DV>
+template <typename T, int DV, bool FULL>
 __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanArgs a, const ScanLayout L) {
     extern __shared__ __align__(128) uint8_t smem[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -169,17 +246,22 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
     float* qraw = reinterpret_cast<float*>(smem + L.off_qraw);
     float* qhat = reinterpret_cast<float*>(smem + L.off_qhat);
     uint64_t* lists = reinterpret_cast<uint64_t*>(smem + L.off_lists);
+    uint64_t* cbuf = reinterpret_cast<uint64_t*>(smem + L.off_buf);
     ScanMisc* misc = reinterpret_cast<ScanMisc*>(smem + L.off_misc);
 
     const int kp = a.kp;
     const int R = static_cast<int>(L.rows_per_tile);
+    const int n_stages = static_cast<int>(L.n_stages);
     const int64_t n_tiles = (a.n_rows + R - 1) / R;
+    // tiles of this CTA: blockIdx.x, blockIdx.x + gridDim.x, ...   (local sequence number `it`)
+    const int64_t my_tiles = n_tiles > blockIdx.x ? (n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
     const uint8_t* mat = static_cast<const uint8_t*>(a.mat);
 
     if (tid == 0) {
-        for (uint32_t s = 0; s < L.n_stages; ++s) {
+        if (blockIdx.x == 0) a.scratch.stamps[0] = globaltimer_ns();
+        for (int s = 0; s < n_stages; ++s) {
             mbar_init(full + s, 1);
-            mbar_init(empty + s, kConsumerWarps);
+            mbar_init(empty + s, 1);  // one consumer warp drains a tile
         }
         fence_barrier_init();
     }
@@ -189,11 +271,11 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
         // ---------------- producer: stream tiles of R rows (+ their reciprocal norms)
         if (lane == 0) {
             const uint64_t pol = l2_policy_evict_first();
-            uint32_t it = 0;
-            for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
-                const uint32_t s = it % L.n_stages, ph = (it / L.n_stages) & 1u;
+            int s = 0;
+            uint32_t ph = 0;
+            for (int64_t it = 0; it < my_tiles; ++it) {
                 mbar_wait(empty + s, ph ^ 1u);
-                const int64_t row0 = tile * R;
+                const int64_t row0 = (blockIdx.x + it * gridDim.x) * R;
                 const int nrows = static_cast<int>(min(static_cast<int64_t>(R), a.n_rows - row0));
                 const uint32_t bytes = static_cast<uint32_t>(nrows) * L.row_bytes;
                 const uint32_t rnb = static_cast<uint32_t>((nrows + 3) & ~3) * 4u;
@@ -201,14 +283,17 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
                 mbar_arrive_expect_tx(full + s, bytes + rnb);
                 bulk_g2s_hint(dst, mat + static_cast<size_t>(row0) * L.row_bytes, bytes, full + s, pol);
                 bulk_g2s(dst + L.tile_bytes, a.rnorm + row0, rnb, full + s);
+                if (++s == n_stages) {
+                    s = 0;
+                    ph ^= 1u;
+                }
             }
         }
         __syncwarp();
     } else {
         // ---------------- consumers: query prologue (overlaps the first tiles already in flight)
-        const int ctid = tid;  // 0 .. kConsumerWarps*32-1
         double part = 0.0;
-        for (int i = ctid; i < static_cast<int>(L.qpad); i += kConsumerWarps * 32) {
+        for (int i = tid; i < static_cast<int>(L.qpad); i += kConsumerWarps * 32) {
             const float v = i < a.dim ? a.d_query[i] : 0.f;
             qraw[i] = v;
             part += static_cast<double>(v) * static_cast<double>(v);
@@ -220,7 +305,7 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
 #pragma unroll
         for (int w = 0; w < kConsumerWarps; ++w) nq += misc->red[w];
         const float rq = nq > 0.0 ? static_cast<float>(1.0 / sqrt(nq)) : 0.f;
-        for (int i = ctid; i < static_cast<int>(L.qpad); i += kConsumerWarps * 32) qhat[i] = qraw[i] * rq;
+        for (int i = tid; i < static_cast<int>(L.qpad); i += kConsumerWarps * 32) qhat[i] = qraw[i] * rq;
         named_bar_sync(1, kConsumerWarps * 32);
 
         float4 qreg[(DV > 0 ? DV : 1) * QV];
@@ -232,41 +317,69 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
         }
 
         uint64_t* myL = lists + warp * kp;
+        uint64_t* myB = lists + (kConsumerWarps + warp) * kp;
+        uint64_t* mybuf = cbuf + warp * 32;
         for (int j = lane; j < kp; j += 32) myL[j] = 0ull;
         __syncwarp();
         uint64_t thr = 0ull;
+        int cnt = 0;
         const int nchunks = static_cast<int>(L.nchunks);
+        const int rsel = ((lane >> 4) << 1) | ((lane >> 3) & 1);  // row slot this lane ends up holding
 
-        uint32_t it = 0;
-        for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
-            const uint32_t s = it % L.n_stages, ph = (it / L.n_stages) & 1u;
+        // Local tile `it` lives in stage it % n_stages and is scored by warp it % n_consumers.  n_consumers
+        // divides n_stages, so a warp only ever waits on stages whose previous phase it drained itself
+        // (an mbarrier parity wait can only tell adjacent phases apart).
+        const int nc = static_cast<int>(L.n_consumers);
+        int s = warp;
+        uint32_t ph = 0;
+        for (int64_t it = warp; warp < nc && it < my_tiles; it += nc) {
             mbar_wait(full + s, ph);
             const uint8_t* st = smem + static_cast<size_t>(s) * L.stage_bytes;
             const float* rn = reinterpret_cast<const float*>(st + L.tile_bytes);
-            const int64_t row0 = tile * R;
+            const int64_t row0 = (blockIdx.x + it * gridDim.x) * R;
             const int nrows = static_cast<int>(min(static_cast<int64_t>(R), a.n_rows - row0));
-            for (int r = warp; r < nrows; r += kConsumerWarps) {
-                const float d = row_dot<T, DV>(st + static_cast<size_t>(r) * L.row_bytes, qreg, qhat, lane, nchunks);
-                const float sc = d * rn[r] + 0.0f;  // +0.0f: -0.0 -> +0.0 (the reference never yields -0.0)
+            const int last = nrows - 1;
+            for (int g0 = 0; g0 < nrows; g0 += kGroup) {
+                const uint8_t* p[kGroup];
+#pragma unroll
+                for (int r = 0; r < kGroup; ++r) p[r] = st + static_cast<size_t>(min(g0 + r, last)) * L.row_bytes;
+                const float d = group_dot<T, DV, FULL>(p, qreg, qhat, lane, nchunks);
+                const int r = g0 + rsel;
+                const bool valid = r <= last;
+                const float sc = d * rn[valid ? r : last] + 0.0f;  // +0.0f: -0.0 -> +0.0 (the reference never yields -0.0)
                 const uint64_t key = make_key(sc, static_cast<uint32_t>(row0 + r));
-                if (key > thr) {
-                    warp_insert_desc(myL, kp, key, lane);
-                    thr = myL[kp - 1];
+                unsigned m = __ballot_sync(0xffffffffu, valid && key > thr);
+                while (m) {  // rare: a row beat the warp's current k'-th best
+                    const int src = __ffs(m) - 1;
+                    const uint64_t kk = __shfl_sync(0xffffffffu, key, src);
+                    m &= ~(0xFFu << (src & ~7));
+                    if (lane == 0) mybuf[cnt] = kk;
+                    if (++cnt == 32) {
+                        thr = warp_flush(myL, myB, mybuf, cnt, kp, lane);
+                        cnt = 0;
+                        m &= __ballot_sync(0xffffffffu, valid && key > thr);
+                    }
                 }
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(empty + s);
+            s += nc;
+            if (s >= n_stages) {
+                s -= n_stages;
+                ph ^= 1u;
+            }
         }
+        if (cnt > 0) warp_flush(myL, myB, mybuf, cnt, kp, lane);
 
         // ---------------- CTA-level merge of the warp lists (tree), then publish to global scratch
         named_bar_sync(1, kConsumerWarps * 32);
-        for (int s = 1; s < kConsumerWarps; s <<= 1) {
-            if ((warp % (2 * s)) == 0 && warp + s < kConsumerWarps)
-                warp_merge_desc(lists + warp * kp, lists + (warp + s) * kp, kp, lane);
+        for (int w = 1; w < kConsumerWarps; w <<= 1) {
+            if ((warp % (2 * w)) == 0 && warp + w < kConsumerWarps)
+                warp_merge_desc(lists + warp * kp, lists + (warp + w) * kp, kp, lane);
             named_bar_sync(1, kConsumerWarps * 32);
         }
         uint64_t* gl = a.scratch.cta_lists + static_cast<size_t>(blockIdx.x) * kp;
-        for (int j = ctid; j < kp; j += kConsumerWarps * 32) gl[j] = lists[j];
+        for (int j = tid; j < kp; j += kConsumerWarps * 32) gl[j] = lists[j];
         __threadfence();
         named_bar_sync(1, kConsumerWarps * 32);
         if (tid == 0) {
@@ -284,25 +397,34 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
     // Last CTA: grid-level merge, exact rescoring (RagIndex.cs:124-135), final order (:64-66)
     // =====================================================================================
     __threadfence();
-    if (warp < kConsumerWarps) {
-        uint64_t* A = lists + warp * kp;
-        uint64_t* B = lists + (kConsumerWarps + warp) * kp;
-        for (int j = lane; j < kp; j += 32) A[j] = 0ull;
-        __syncwarp();
-        for (int c = warp; c < static_cast<int>(gridDim.x); c += kConsumerWarps) {
-            const uint64_t* gl = a.scratch.cta_lists + static_cast<size_t>(c) * kp;
-            for (int j = lane; j < kp; j += 32) B[j] = __ldcg(gl + j);
-            __syncwarp();
-            warp_merge_desc(A, B, kp, lane);
+    if (tid == 0) a.scratch.stamps[1] = globaltimer_ns();
+    const uint32_t ring_bytes = L.n_stages * L.stage_bytes;  // idle now: reused as staging space
+    {
+        uint64_t* stage = reinterpret_cast<uint64_t*>(smem);
+        const int nlists = static_cast<int>(gridDim.x);
+        const int cap_lists = max(1, static_cast<int>(ring_bytes / (static_cast<uint32_t>(kp) * 8u)));
+        if (warp < kConsumerWarps) {
+            for (int j = lane; j < kp; j += 32) lists[warp * kp + j] = 0ull;
+        }
+        for (int l0 = 0; l0 < nlists; l0 += cap_lists) {
+            const int nl = min(cap_lists, nlists - l0);
+            const uint64_t* src = a.scratch.cta_lists + static_cast<size_t>(l0) * kp;
+            const int total = nl * kp;
+#pragma unroll 8
+            for (int i = tid; i < total; i += kScanThreads) stage[i] = __ldcg(src + i);  // all loads in flight
+            __syncthreads();
+            if (warp < kConsumerWarps)
+                for (int c = warp; c < nl; c += kConsumerWarps) warp_merge_desc(lists + warp * kp, stage + c * kp, kp, lane);
+            __syncthreads();
+        }
+        for (int w = 1; w < kConsumerWarps; w <<= 1) {
+            if (warp < kConsumerWarps && (warp % (2 * w)) == 0 && warp + w < kConsumerWarps)
+                warp_merge_desc(lists + warp * kp, lists + (warp + w) * kp, kp, lane);
+            __syncthreads();
         }
     }
-    __syncthreads();
-    for (int s = 1; s < kConsumerWarps; s <<= 1) {
-        if (warp < kConsumerWarps && (warp % (2 * s)) == 0 && warp + s < kConsumerWarps)
-            warp_merge_desc(lists + warp * kp, lists + (warp + s) * kp, kp, lane);
-        __syncthreads();
-    }
     // lists[0..kp) : the kp best approximate keys of the whole shard, descending
+    if (tid == 0) a.scratch.stamps[2] = globaltimer_ns();
 
     const int n_cand = static_cast<int>(min(static_cast<int64_t>(kp), a.n_rows));
     // Rows are staged in the (now idle) tile ring.  A row that was stored inexactly (normalised with
@@ -310,52 +432,40 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
     // so the fp64 score below is the reference's value for the row as it was added.
     const uint32_t raw_bytes = a.raw_slot ? static_cast<uint32_t>(a.raw_ld) * 4u : 0u;
     const uint32_t rs = max(L.row_bytes, raw_bytes) + 16;  // padded smem row stride: spreads rows over banks
-    const int cap = max(1, static_cast<int>((L.n_stages * L.stage_bytes) / rs));
+    const int cap = max(1, static_cast<int>(ring_bytes / rs));
     const int nchunks = static_cast<int>(L.nchunks);
+    const int raw_chunks = static_cast<int>(raw_bytes / 16);
     uint8_t* rowbuf = smem;
 
     for (int b0 = 0; b0 < n_cand; b0 += cap) {
         const int nb = min(cap, n_cand - b0);
+        // stage: one warp per row, every lane keeps several 16-byte loads in flight
         for (int c = warp; c < nb; c += kScanThreads / 32) {
             const uint32_t row = key_row(lists[b0 + c]);
             const int32_t slot = a.raw_slot ? a.raw_slot[row] : -1;
-            const uint4* src;
-            int nch;
-            if (slot >= 0) {
-                src = reinterpret_cast<const uint4*>(a.raw_rows + static_cast<size_t>(slot) * a.raw_ld);
-                nch = static_cast<int>(raw_bytes / 16);
-            } else {
-                src = reinterpret_cast<const uint4*>(mat + static_cast<size_t>(row) * L.row_bytes);
-                nch = nchunks;
-            }
+            const uint4* src = slot >= 0 ? reinterpret_cast<const uint4*>(a.raw_rows + static_cast<size_t>(slot) * a.raw_ld)
+                                         : reinterpret_cast<const uint4*>(mat + static_cast<size_t>(row) * L.row_bytes);
+            const int nch = slot >= 0 ? raw_chunks : nchunks;
             uint4* dst = reinterpret_cast<uint4*>(rowbuf + static_cast<size_t>(c) * rs);
+#pragma unroll 8
             for (int ch = lane; ch < nch; ch += 32) dst[ch] = __ldg(src + ch);
             if (lane == 0) misc->raw_fmt[c] = slot >= 0 ? 1 : 0;
         }
         __syncthreads();
+        if (tid == 0 && b0 == 0) a.scratch.stamps[3] = globaltimer_ns();
         const int nchains = 2 * nb + (b0 == 0 ? 1 : 0);
         for (int id = tid; id < nchains; id += kScanThreads) {
-            double acc = 0.0;  // :127
             if (id == 2 * nb) {
-                for (int i = 0; i < a.dim; ++i) acc = __dadd_rn(acc, static_cast<double>(__fmul_rn(qraw[i], qraw[i])));  // :131
-                misc->na = acc;
+                misc->na = exact_chain<T>(nullptr, true, qraw, a.dim, 1);  // :131
             } else {
                 const int c = id >> 1;
                 const uint8_t* row = rowbuf + static_cast<size_t>(c) * rs;
                 const bool f32row = (sizeof(T) == 4) || misc->raw_fmt[c];
-                if (id & 1) {
-                    for (int i = 0; i < a.dim; ++i) {
-                        const float x = f32row ? reinterpret_cast<const float*>(row)[i] : elem_at<T>(row, i);
-                        acc = __dadd_rn(acc, static_cast<double>(__fmul_rn(x, x)));  // :132
-                    }
-                    misc->nb[c] = acc;
-                } else {
-                    for (int i = 0; i < a.dim; ++i) {
-                        const float x = f32row ? reinterpret_cast<const float*>(row)[i] : elem_at<T>(row, i);
-                        acc = __dadd_rn(acc, static_cast<double>(__fmul_rn(qraw[i], x)));  // :130
-                    }
-                    misc->dot[c] = acc;
-                }
+                const double v = exact_chain<T>(row, f32row, qraw, a.dim, id & 1);
+                if (id & 1)
+                    misc->nb[c] = v;  // :132
+                else
+                    misc->dot[c] = v;  // :130
             }
         }
         __syncthreads();
@@ -366,6 +476,7 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
         __syncthreads();
     }
 
+    if (tid == 0) a.scratch.stamps[4] = globaltimer_ns();
     // final order: (fp64 score desc with double.CompareTo semantics, row asc); rank by counting
     for (int c = tid; c < n_cand; c += kScanThreads) {
         const double sc = misc->ex[c];
@@ -419,6 +530,7 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
         if (misc->inexact == 0) flags |= RAGSTORE_HIT_EXACT_ROWS;
         if (a.out_flags) *a.out_flags = flags;
         if (a.out_found) *a.out_found = a.k_take;
+        a.scratch.stamps[5] = globaltimer_ns();
     }
 }
 
@@ -433,59 +545,76 @@ static bool make_layout(const ScanArgs& a, int dv, ScanLayout& L) {
     const uint32_t epc = 16 / esz;
     L.qpad = dv > 0 ? static_cast<uint32_t>(dv) * 32u * epc : static_cast<uint32_t>(a.ld);
     if (L.qpad < static_cast<uint32_t>(a.ld)) return false;
-    const uint32_t fixed_lists = sizeof(uint64_t) * 2u * kConsumerWarps * static_cast<uint32_t>(a.kp);
-    const uint32_t fixed = 16u * 8u * 2u /*barriers*/ + 2u * L.qpad * 4u + fixed_lists + sizeof(ScanMisc) + 512u;
+    const uint32_t lists_bytes = sizeof(uint64_t) * 2u * kConsumerWarps * static_cast<uint32_t>(a.kp);
+    const uint32_t buf_bytes = sizeof(uint64_t) * 32u * kConsumerWarps;
+    const uint32_t bars_bytes = 16u * 8u * 2u;
+    const uint32_t fixed = bars_bytes + 2u * L.qpad * 4u + lists_bytes + buf_bytes + sizeof(ScanMisc) + 512u;
     if (fixed + 2u * (4u * L.row_bytes + 128u) > kSmemBudget) return false;
     if (a.raw_slot && static_cast<uint32_t>(a.raw_ld) * 4u + 16u > 2u * (4u * L.row_bytes + 128u)) return false;
     const uint32_t ring = kSmemBudget - fixed;
-    // rows per tile: a multiple of 4 (16-byte granularity of the reciprocal-norm slice), ~32 KB
-    uint32_t R = (32u * 1024u) / L.row_bytes;
-    R = R < 4 ? 4 : (R > 64 ? 64 : (R & ~3u));
-    while (R > 4 && 2u * (R * L.row_bytes + R * 4u + 128u) > ring) R -= 4;
+    // Rows per tile R: a multiple of 4 (row group of a warp; 16-byte granularity of the reciprocal-norm
+    // slice).  Stages: 16, 8 or fewer, with min(8, stages) consumer warps so that each warp owns
+    // fixed stages.  Pick the R (<= ~24 KB tiles) that keeps the most bytes in flight.
+    uint32_t Rmax = (24u * 1024u) / L.row_bytes;
+    Rmax = Rmax < 4 ? 4 : (Rmax > 64 ? 64 : (Rmax & ~3u));
+    uint32_t best_R = 0, best_ns = 0, best_bytes = 0;
+    for (uint32_t R = Rmax; R >= 4; R -= 4) {
+        const uint32_t sb = (R * L.row_bytes + R * 4u + 127u) & ~127u;
+        uint32_t ns = ring / sb;
+        ns = ns >= 16 ? 16 : (ns >= 8 ? 8 : ns);
+        if (ns < 2) continue;
+        if (ns * sb > best_bytes) best_bytes = ns * sb, best_R = R, best_ns = ns;
+    }
+    if (best_R == 0) return false;
+    const uint32_t R = best_R;
     L.rows_per_tile = R;
     L.tile_bytes = R * L.row_bytes;
     L.stage_bytes = (L.tile_bytes + R * 4u + 127u) & ~127u;
-    uint32_t ns = ring / L.stage_bytes;
-    if (ns < 2) return false;
-    L.n_stages = ns > 8 ? 8 : ns;
+    L.n_stages = best_ns;
+    L.n_consumers = best_ns < kConsumerWarps ? best_ns : kConsumerWarps;
     uint32_t off = L.n_stages * L.stage_bytes;
     L.off_bars = off;
-    off += 16u * 8u * 2u;
+    off += bars_bytes;
     L.off_qraw = off;
     off += L.qpad * 4u;
     L.off_qhat = off;
     off += L.qpad * 4u;
     off = (off + 15u) & ~15u;
     L.off_lists = off;
-    off += fixed_lists;
+    off += lists_bytes;
+    L.off_buf = off;
+    off += buf_bytes;
     off = (off + 15u) & ~15u;
     L.off_misc = off;
     off += sizeof(ScanMisc);
     L.total = off;
-    return L.total <= 227u * 1024u && L.n_stages <= 16;
+    return L.total <= 227u * 1024u;
 }
 
-template <typename T, int DV>
+template <typename T, int DV, bool FULL>
 static int launch_one(const ScanArgs& a, const ScanLayout& L, int grid, cudaStream_t stream) {
-    auto kfn = scan_topk_kernel<T, DV>;
+    auto kfn = scan_topk_kernel<T, DV, FULL>;
     cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     if (e != cudaSuccess) return static_cast<int>(e);
     kfn<<<grid, kScanThreads, L.total, stream>>>(a, L);
     return static_cast<int>(cudaGetLastError());
 }
 
+template <typename T, int DV>
+static int launch_full(const ScanArgs& a, const ScanLayout& L, int grid, cudaStream_t st, bool full) {
+    return full ? launch_one<T, DV, true>(a, L, grid, st) : launch_one<T, DV, false>(a, L, grid, st);
+}
+
 template <typename T>
-static int dispatch_dv(const ScanArgs& a, int dv, const ScanLayout& L, int grid, cudaStream_t st) {
+static int dispatch_dv(const ScanArgs& a, int dv, bool full, const ScanLayout& L, int grid, cudaStream_t st) {
     switch (dv) {
-        case 1: return launch_one<T, 1>(a, L, grid, st);
-        case 2: return launch_one<T, 2>(a, L, grid, st);
-        case 3: return launch_one<T, 3>(a, L, grid, st);
-        case 4: return launch_one<T, 4>(a, L, grid, st);
-        case 5: return launch_one<T, 5>(a, L, grid, st);
-        case 6: return launch_one<T, 6>(a, L, grid, st);
-        case 7: return launch_one<T, 7>(a, L, grid, st);
-        case 8: return launch_one<T, 8>(a, L, grid, st);
-        default: return launch_one<T, 0>(a, L, grid, st);
+        case 1: return launch_full<T, 1>(a, L, grid, st, full);
+        case 2: return launch_full<T, 2>(a, L, grid, st, full);
+        case 3: return launch_full<T, 3>(a, L, grid, st, full);
+        case 4: return launch_full<T, 4>(a, L, grid, st, full);
+        case 6: return launch_full<T, 6>(a, L, grid, st, full);
+        case 8: return launch_full<T, 8>(a, L, grid, st, full);
+        default: return launch_one<T, 0, false>(a, L, grid, st);
     }
 }
 
@@ -496,14 +625,17 @@ int launch_scan(const ScanArgs& a, cudaStream_t stream) {
     const uint32_t esz = a.dtype == RAGSTORE_F32 ? 4u : 2u;
     const uint32_t nchunks = static_cast<uint32_t>(a.ld) * esz / 16u;
     int dv = static_cast<int>((nchunks + 31u) / 32u);
-    if (dv > 8) dv = 0;
+    if (dv == 5) dv = 6;  // instantiated register-query widths: 1,2,3,4,6,8 chunks per lane
+    if (dv == 7) dv = 8;
+    if (dv > 8) dv = 0;   // wider rows read the query from shared memory
+    const bool full = dv > 0 && nchunks == static_cast<uint32_t>(dv) * 32u;
     ScanLayout L;
     if (!make_layout(a, dv, L)) return static_cast<int>(cudaErrorInvalidConfiguration);
     const int64_t n_tiles = (a.n_rows + L.rows_per_tile - 1) / L.rows_per_tile;
     int grid = static_cast<int>(n_tiles < a.sm_count ? n_tiles : a.sm_count);
     if (grid > kMaxCtas) grid = kMaxCtas;
-    if (a.dtype == RAGSTORE_F32) return dispatch_dv<float>(a, dv, L, grid, stream);
-    return dispatch_dv<uint16_t>(a, dv, L, grid, stream);
+    if (a.dtype == RAGSTORE_F32) return dispatch_dv<float>(a, dv, full, L, grid, stream);
+    return dispatch_dv<uint16_t>(a, dv, full, L, grid, stream);
 }
 
 int scan_configure_device() { return 0; }

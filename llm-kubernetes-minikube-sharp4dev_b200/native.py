@@ -52,6 +52,7 @@ def lib():
             "ragstore_search_shard_device": (C.c_int, [vp, vp, C.c_int, vp, vp, vp]),
             "ragstore_merge_shards_device": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, vp, vp, vp, C.c_int, vp]),
             "ragstore_info": (C.c_int, [vp, i64p, C.c_int]),
+            "ragstore_debug_stamps": (C.c_int, [vp, C.POINTER(C.c_uint64), C.c_int]),
             "ragstore_device_views": (C.c_int, [vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]),
             "ragstore_synth_fill_device": (C.c_int, [vp, C.c_int64, C.c_int64, C.c_int, C.c_int64, C.c_uint64, C.c_int, C.c_int, vp]),
         }
@@ -138,6 +139,11 @@ class RagStore:
         keys = ["dim", "ld", "dtype", "count", "capacity", "n_inexact_rows", "device", "sm_count",
                 "has_sidecar", "sidecar_rows", "matrix_bytes_mapped", "uses_vmm"]
         return dict(zip(keys, list(v)))
+
+    def debug_stamps(self):
+        v = (C.c_uint64 * 8)()
+        check(lib().ragstore_debug_stamps(self._h, v, 8))
+        return list(v)
 
     def device_views(self):
         m, r, e = C.c_void_p(), C.c_void_p(), C.c_void_p()

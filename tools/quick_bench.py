@@ -35,10 +35,13 @@ def run(n, d, k, dtype, iters=20):
     gbs = n * d * esz / med / 1e6
     print(f"n={n} d={d} k={k} dtype={dtype}: fill {t_fill:.1f}s  median {med:.4f} ms  min {ms[0]:.4f}  -> {gbs:.0f} GB/s ({gbs/6542.1:.3f} of measured copy peak), "
           f"{n/med/1e6:.3f} G vec/s; idx={idx[:3].tolist()} flags={flg.item()}", flush=True)
+    t = st.debug_stamps()
+    print("   phases us: scan %.1f | grid-merge %.1f | stage rows %.1f | chains %.1f | rank+out %.1f" % tuple((t[i+1]-t[i])/1e3 for i in range(5)), flush=True)
     st.close()
 
 if __name__ == "__main__":
     F, B = rb.RAGSTORE_F32, rb.RAGSTORE_BF16
-    for (n, d, k, t) in [(10000, 768, 10, F), (10000, 768, 100, F), (10000, 768, 10, B), (10000, 768, 100, B),
-                         (2000000, 768, 10, F), (2000000, 768, 100, F), (2000000, 768, 10, B), (2000000, 768, 100, B)]:
+    for (n, d, k, t) in [(10000, 768, 5, F), (10000, 768, 100, F), (10000, 768, 100, B),
+                         (1000000, 768, 10, F), (4000000, 768, 10, F), (2000000, 768, 100, F), (2000000, 768, 10, B), (2000000, 768, 100, B),
+                         (1000000, 1024, 10, F), (1000000, 384, 10, F), (1000000, 1000, 10, F), (300000, 4096, 10, F)]:
         run(n, d, k, t)
