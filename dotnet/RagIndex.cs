@@ -1,0 +1,72 @@
+// RagIndex.cs -- device-backed drop-in for Minimal_RAG.Helpers.RagIndex (same public members, same results).
+// SOURCE ONLY: never compiled here (no dotnet).  The text pipeline and the embedding client are the
+// reference's own and stay where they are; only the store call and the search body change.
+using System;
+using System.Collections.Generic;
+using System.Threading.Tasks;
+using Microsoft.Extensions.Logging;
+
+namespace Minimal_RAG.Helpers
+{
+    class RagIndex : IDisposable
+    {
+        // what used to be List<RagChunk>: the text stays managed, the embedding lives in HBM
+        readonly List<(string Id, string Source, string Text)> _meta = new();
+        readonly string _embedModel;
+        IntPtr _store;
+        int _dim;
+        const long CapacityRows = 1L << 26;   // address space only; HBM is mapped as rows arrive
+
+        public RagIndex(string embedModel) => _embedModel = embedModel;
+
+        public async Task BuildFromFolderAsync(string folder, int chunkSize, int overlap, ILogger logger)
+        {
+            // ... unchanged enumeration / SplitByMarkdownHeaders / Sanitize from the reference ...
+            // inside the per-chunk loop, the reference's
+            //     _chunks.Add(new RagChunk($"{Path.GetFileName(file)}#{i++}", file, clean, emb));
+            // becomes:
+            //     Add($"{Path.GetFileName(file)}#{i++}", file, clean, emb);
+            await Task.CompletedTask;
+        }
+
+        unsafe void Add(string id, string source, string text, float[] emb)
+        {
+            if (_store == IntPtr.Zero)
+            {
+                _dim = emb.Length;
+                NativeMethods.Check(NativeMethods.ragstore_create(_dim, NativeMethods.RAGSTORE_F32, CapacityRows, 0, 0, out _store));
+            }
+            fixed (float* p = emb)
+                NativeMethods.Check(NativeMethods.ragstore_add(_store, p, 1, emb.Length, NativeMethods.RAGSTORE_ADD_HOST, out long row));
+            _meta.Add((id, source, text));       // row id == list position, as in the reference
+        }
+
+        public async Task<List<RagHit>> QueryAsync(string query, int topK = 5)
+        {
+            var q = await Embedder.EmbedAsync(_embedModel, query);
+            return Search(q, topK);
+        }
+
+        unsafe List<RagHit> Search(float[] q, int topK)
+        {
+            var hits = new List<RagHit>();
+            if (_store == IntPtr.Zero) return hits;                     // empty index -> empty list
+            int want = Math.Max(1, topK);
+            var idx = new long[want]; var score = new double[want];
+            int found, flags;
+            fixed (float* pq = q) fixed (long* pi = idx) fixed (double* ps = score)
+                NativeMethods.Check(NativeMethods.ragstore_search(_store, pq, 1, q.Length, topK, pi, ps, &found, &flags));
+            for (int j = 0; j < found; j++)
+            {
+                var m = _meta[(int)idx[j]];
+                hits.Add(new RagHit(m.Id, m.Source, m.Text, score[j]));
+            }
+            return hits;
+        }
+
+        public void Dispose()
+        {
+            if (_store != IntPtr.Zero) { NativeMethods.ragstore_destroy(_store); _store = IntPtr.Zero; }
+        }
+    }
+}
