@@ -143,6 +143,30 @@ RAGSTORE_API int ragstore_merge_shards_device(const ragstore_cand* d_gathered, i
                                               double* d_score, int32_t* d_found, int device,
                                               void* stream);
 
+/* No counterpart in the reference: an extra search entry point for hosts that are not allowed to
+ * allocate device memory -- a server that gave all of HBM to its own arena at start-up, or a request
+ * thread that cannot afford the device-wide synchronisation and driver locks of cudaMalloc/cudaFree.
+ * It runs the same scan + top-k + exact-rescoring launch as ragstore_search_device on buffers the
+ * caller owns, and calls no cudaMalloc, cudaFree or other allocating routine, ever.
+ *   d_matrix  n_rows x dim, row-major, fp32 or bf16 (dtype), rows a multiple of 16 bytes, unit norm
+ *   d_rnorm   reciprocal norm of each stored row, fp32, readable up to the next multiple of 4 rows
+ *   d_query   dim raw fp32 values;  outputs as ragstore_search_device for one query
+ * The kernel's scratch (per-CTA candidate lists + a ticket) lives in a fixed array inside the
+ * library image: ragstore_noalloc_scratch_bytes() (about 321 KB) is held on every GPU that loads the
+ * library, until the process exits.  Limits that follow from the fixed size: top_k <= 256 and at most
+ * 160 SMs; beyond them the call returns RAGSTORE_ERR_UNSUPPORTED and says why.
+ * The first call on each device resolves the array's device address; make that first call before any
+ * stream capture begins.  All calls share the one array: it keeps the previous call's contents (the
+ * call clears the ticket it needs zeroed, in stream order), and two calls whose kernels overlap on the
+ * same GPU race on it -- issue them on one stream, or otherwise order them.
+ * Errors of this entry point are reported by ragstore_noalloc_last_error(). */
+RAGSTORE_API int ragstore_search_noalloc(const void* d_matrix, const float* d_rnorm, int64_t n_rows,
+                                         int dim, int dtype, const float* d_query, int top_k,
+                                         int64_t* d_idx, double* d_score, int32_t* d_found,
+                                         int32_t* d_flags, int device, void* stream);
+RAGSTORE_API int64_t ragstore_noalloc_scratch_bytes(void);
+RAGSTORE_API const char* ragstore_noalloc_last_error(void);
+
 /* ---- utilities ----------------------------------------------------------------------------- */
 
 /* Last error text of the calling thread (empty string if none). Returns the length written. */

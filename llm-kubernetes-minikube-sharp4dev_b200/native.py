@@ -52,6 +52,9 @@ def lib():
             "ragstore_search_shard_device": (C.c_int, [vp, vp, C.c_int, vp, vp, vp]),
             "ragstore_merge_shards_device": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, vp, vp, vp, C.c_int, vp]),
             "ragstore_info": (C.c_int, [vp, i64p, C.c_int]),
+            "ragstore_search_noalloc": (C.c_int, [vp, vp, C.c_int64, C.c_int, C.c_int, vp, C.c_int, vp, vp, vp, vp, C.c_int, vp]),
+            "ragstore_noalloc_scratch_bytes": (C.c_int64, []),
+            "ragstore_noalloc_last_error": (C.c_char_p, []),
             "ragstore_debug_stamps": (C.c_int, [vp, C.POINTER(C.c_uint64), C.c_int]),
             "ragstore_device_views": (C.c_int, [vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]),
             "ragstore_synth_fill_device": (C.c_int, [vp, C.c_int64, C.c_int64, C.c_int, C.c_int64, C.c_uint64, C.c_int, C.c_int, vp]),
@@ -173,6 +176,15 @@ class RagStore:
 
     def search_shard_device(self, d_query, top_k: int, d_cand, d_flags=None, stream: int = 0):
         check(lib().ragstore_search_shard_device(self._h, _ptr(d_query), int(top_k), _ptr(d_cand), _ptr(d_flags), C.c_void_p(stream)))
+
+
+def search_noalloc(d_matrix, d_rnorm, n_rows: int, dim: int, dtype: int, d_query, top_k: int, d_idx, d_score, d_found,
+                   d_flags=None, device: int = 0, stream: int = 0):
+    """ragstore_search_noalloc: caller-owned device buffers in and out, fixed in-library scratch, no allocation."""
+    rc = lib().ragstore_search_noalloc(_ptr(d_matrix), _ptr(d_rnorm), n_rows, dim, dtype, _ptr(d_query), int(top_k),
+                                       _ptr(d_idx), _ptr(d_score), _ptr(d_found), _ptr(d_flags), device, C.c_void_p(stream))
+    if rc != 0:
+        raise RagStoreError(rc, lib().ragstore_noalloc_last_error().decode("utf-8", "replace"))
 
 
 def merge_shards_device(d_gathered, n_shards: int, per_shard: int, top_k: int, d_idx, d_score, d_found, device: int = 0, stream: int = 0):
