@@ -193,15 +193,13 @@ def measure_workload(name, args, torch, dist, rb, native, rank, world, dev, do_e
                 st.search_device(q, 1, k, d_idx, d_score, d_found, d_flags, stream=ts.cuda_stream)
             launches_per_step = 1
         else:
-            d_cand = torch.zeros(k * 16, dtype=torch.uint8, device="cuda")
-            d_all = torch.zeros(world * k * 16, dtype=torch.uint8, device="cuda")
+            sh = rb.ShardedSearcher(st, rank, world, rank * rows, max_k=max(k, 1), device=dev)
+            d_cand, d_all, d_idx, d_score, d_found, d_flags = sh.d_cand, sh.d_all, sh.d_idx, sh.d_score, sh.d_found, sh.d_flags
 
             def step():
                 q = d_q[qi[0] % n_q]
                 qi[0] += 1
-                st.search_shard_device(q, k, d_cand, d_flags, stream=ts.cuda_stream)
-                dist.all_gather_into_tensor(d_all, d_cand)          # NCCL over NVLink: world * k * 16 bytes
-                native.merge_shards_device(d_all, world, k, k, d_idx, d_score, d_found, device=dev, stream=ts.cuda_stream)
+                sh.search_device(q, k)      # shard scan -> NCCL all-gather (world * k * 16 B) -> merge kernel
             launches_per_step = 2
 
         with ClockSampler(dev) as clk:

@@ -11,3 +11,4 @@ from .native import (  # noqa: F401
     RAGSTORE_HIT_CERTIFIED, RAGSTORE_HIT_EXACT_ROWS, RagStore, RagStoreError, lib, lib_path,
 )
 from .rag_index import RagChunk, RagHit, RagIndex  # noqa: F401
+from .sharded import ShardedSearcher, gather_layout, shard_range  # noqa: F401,E402

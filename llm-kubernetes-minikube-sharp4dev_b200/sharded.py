@@ -1,0 +1,71 @@
+"""Row-sharded search across the GPUs of one node: one process per GPU, each owning a
+contiguous block of rows; a query is scored by every shard, each shard's exactly-rescored top-k is
+all-gathered (k * 16 bytes per rank, NCCL over NVLink) and every rank merges the G * k records on its GPU.
+The order (score desc, global id asc) is what a single RagIndex over the whole corpus returns
+(reference Helpers/RagIndex.cs:64-65)."""
+from __future__ import annotations
+
+from typing import Callable, Optional, Tuple
+
+CAND_BYTES = 16  # struct ragstore_cand { double score; int64 id; }
+
+
+def shard_range(n_total: int, world: int, rank: int) -> Tuple[int, int]:
+    """Rows [lo, hi) owned by `rank`: contiguous blocks of ceil(N/G) rows; global id == insertion order."""
+    per = (n_total + world - 1) // world
+    lo = min(n_total, rank * per)
+    return lo, min(n_total, lo + per)
+
+
+def gather_layout(world: int, k: int) -> Tuple[int, int]:
+    """(bytes per rank, total bytes) of the all-gather payload."""
+    per = max(1, k) * CAND_BYTES
+    return per, per * world
+
+
+class ShardedSearcher:
+    """One shard (a RagStore on this rank's GPU) + the exchange.  `all_gather(out, inp)` defaults to
+    torch.distributed.all_gather_into_tensor; tests inject their own."""
+
+    def __init__(self, store, rank: int, world: int, row_base: int, max_k: int = 256,
+                 all_gather: Optional[Callable] = None, device: Optional[int] = None):
+        import torch
+        from . import native
+        self.torch, self.native = torch, native
+        self.store, self.rank, self.world = store, rank, world
+        self.device = torch.cuda.current_device() if device is None else device
+        store.set_row_base(row_base)
+        self.max_k = max_k
+        self.d_cand = torch.zeros(max_k * CAND_BYTES, dtype=torch.uint8, device="cuda")
+        self.d_all = torch.zeros(world * max_k * CAND_BYTES, dtype=torch.uint8, device="cuda")
+        self.d_idx = torch.zeros(max_k, dtype=torch.int64, device="cuda")
+        self.d_score = torch.zeros(max_k, dtype=torch.float64, device="cuda")
+        self.d_found = torch.zeros(1, dtype=torch.int32, device="cuda")
+        self.d_flags = torch.zeros(1, dtype=torch.int32, device="cuda")
+        if all_gather is None:
+            import torch.distributed as dist
+            all_gather = dist.all_gather_into_tensor
+        self._all_gather = all_gather
+
+    def search_device(self, d_query, k: int):
+        """Enqueue shard search -> all-gather -> merge on the current torch stream; results stay on the device
+        (self.d_idx / d_score / d_found).  Every rank ends with the same global top-k."""
+        req = max(1, int(k))
+        if req > self.max_k:
+            raise ValueError("k above max_k")
+        stream = self.torch.cuda.current_stream().cuda_stream
+        per, total = gather_layout(self.world, req)
+        self.store.search_shard_device(d_query, k, self.d_cand, self.d_flags, stream=stream)
+        if self.world > 1:
+            self._all_gather(self.d_all[:total], self.d_cand[:per])
+            src = self.d_all
+        else:
+            src = self.d_cand
+        self.native.merge_shards_device(src, self.world, req, k, self.d_idx, self.d_score, self.d_found,
+                                        device=self.device, stream=stream)
+
+    def search(self, d_query, k: int):
+        self.search_device(d_query, k)
+        self.torch.cuda.current_stream().synchronize()
+        n = int(self.d_found.item())
+        return self.d_idx[:n].cpu().numpy(), self.d_score[:n].cpu().numpy()

@@ -218,3 +218,41 @@ def test_rag_index_mirror():
     assert [h.Score for h in hits] == list(esc)
     assert rb.RagIndex("m").QueryEmbedding(emb["t1"], 3) == []
     ri.close()
+
+
+@pytest.mark.parametrize("n,k,dtype", [(5000, 10, 0), (3001, 100, 0), (4000, 100, 1)])
+def test_row_sharded_search_on_one_gpu(n, k, dtype):
+    """Three shards emulated as three stores on one GPU; the gather is a concatenation.  The merged result must
+    be what one index over the whole corpus returns (global ids, ties to the lower id across shards)."""
+    import torch
+    from ragstore_b200 import native
+    dim, world = 256, 3
+    bf = dtype == 1
+    full = oc.synth_rows(0, n, dim, 1234, round_bf16=bf)
+    full[n // 2 + 5] = full[3]                 # a duplicate living in another shard
+    full[n - 1] = full[3]
+    q = oc.synth_rows(1, 1, dim, 5678)[0]
+    eidx, esc = oc.query(full, q, k, n_threads=4)
+    d_q = torch.from_numpy(q).cuda()
+    req = max(1, k)
+    d_all = torch.zeros(world * req * 16, dtype=torch.uint8, device="cuda")
+    stream = torch.cuda.Stream()
+    stores = []
+    for r in range(world):
+        lo, hi = rb.shard_range(n, world, r)
+        st = rb.RagStore(dim, hi - lo, dtype)
+        st.add(full[lo:hi], prenormalised=bf)
+        st.set_row_base(lo)
+        st.search_shard_device(d_q, k, d_all[r * req * 16:], None, stream=stream.cuda_stream)
+        stores.append(st)
+    d_idx = torch.zeros(req, dtype=torch.int64, device="cuda")
+    d_sc = torch.zeros(req, dtype=torch.float64, device="cuda")
+    d_found = torch.zeros(1, dtype=torch.int32, device="cuda")
+    native.merge_shards_device(d_all, world, req, k, d_idx, d_sc, d_found, stream=stream.cuda_stream)
+    stream.synchronize()
+    f = int(d_found.item())
+    assert f == len(eidx)
+    assert d_idx[:f].cpu().tolist() == [int(i) for i in eidx]
+    assert np.array_equal(d_sc[:f].cpu().numpy().view(np.uint64), esc.view(np.uint64))
+    for st in stores:
+        st.close()
