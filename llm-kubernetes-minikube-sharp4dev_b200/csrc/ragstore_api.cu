@@ -99,6 +99,7 @@ struct ragstore {
     float* raw_rows = nullptr;
     int raw_ld = 0;
     int64_t raw_used = 0;          // sidecar rows in use (host copy, refreshed after every add)
+    int64_t inexact_rows = 0;      // rows stored inexactly (host copy, refreshed after every add)
     unsigned long long* d_inexact = nullptr;  // [0] inexact rows, then [1] raw_count (u32), [2] min_norm_bits (u32)
     unsigned int* d_raw_count = nullptr;
     uint32_t* d_min_norm = nullptr;
@@ -170,8 +171,9 @@ ScanArgs base_args(const ragstore* s, int64_t n, int take, int kp) {
     ScanArgs a{};
     a.mat = s->mat;
     a.rnorm = s->rnorm;
-    a.exact = s->exact;
-    a.raw_slot = s->raw_slot;
+    // the per-row lookups are skipped altogether while every row is stored exactly (the common case)
+    a.exact = s->inexact_rows > 0 ? s->exact : nullptr;
+    a.raw_slot = s->raw_used > 0 ? s->raw_slot : nullptr;
     a.raw_rows = s->raw_rows;
     a.raw_ld = s->raw_ld;
     a.min_norm_bits = s->d_min_norm;
@@ -386,10 +388,11 @@ int ragstore_add(ragstore_t* s, const float* rows, int64_t n_rows, int row_dim, 
         const int rc = launch_normalise(a, s->ingest_stream);
         if (rc) return fail(RAGSTORE_ERR_CUDA, "normalise kernel launch", cudaGetErrorString(static_cast<cudaError_t>(rc)));
         // the sidecar bound for the next chunk needs this chunk's count; this also fences staging reuse
-        unsigned int raw_now = 0;
-        CU_TRY(cudaMemcpyAsync(&raw_now, s->d_raw_count, sizeof(raw_now), cudaMemcpyDeviceToHost, s->ingest_stream));
+        unsigned long long counters[2] = {0, 0};   // [0] inexact rows, [1] low word: sidecar rows
+        CU_TRY(cudaMemcpyAsync(counters, s->d_inexact, sizeof(counters), cudaMemcpyDeviceToHost, s->ingest_stream));
         CU_TRY(cudaStreamSynchronize(s->ingest_stream));
-        s->raw_used = raw_now;
+        s->inexact_rows = static_cast<int64_t>(counters[0]);
+        s->raw_used = static_cast<int64_t>(counters[1] & 0xFFFFFFFFull);
     }
     CU_TRY(cudaStreamSynchronize(s->ingest_stream));
     s->count.store(first + n_rows, std::memory_order_release);  // publish: searches see a prefix

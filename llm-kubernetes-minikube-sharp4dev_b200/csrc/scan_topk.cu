@@ -52,27 +52,54 @@ struct ScanMisc {  // lives in shared memory at off_misc
     double dot[kMaxKp];
     double nb[kMaxKp];
     uint8_t raw_fmt[kMaxKp];  // 1 = the staged row is the fp32 original from the sidecar
+    unsigned long long stage_bar;  // mbarrier for the bulk copies that stage candidate rows
 };
 
-// ---------------------------------------------------------------- warp-level sorted lists in smem
-// A, B sorted descending (kp a power of two >= 32).  A <- top kp of A u B, sorted descending.
-__device__ __forceinline__ void warp_merge_desc(uint64_t* A, const uint64_t* B, int kp, int lane) {
-    for (int j = lane; j < kp; j += 32) {
-        const uint64_t x = A[j], y = B[kp - 1 - j];
-        A[j] = x > y ? x : y;  // bitonic sequence holding the kp largest
+// ---------------------------------------------------------------- warp-level sorted lists
+// Lists live in shared memory (kp = 32*S keys, sorted descending, position j = slot*32 + lane) but are
+// merged in registers: A <- top kp of A u B.  Element-wise max of A with reversed B leaves a bitonic
+// sequence holding the kp largest keys; a bitonic merge (slot strides in registers, lane strides by
+// shuffle) sorts it.  No shared-memory round trips inside the network.
+template <int S>
+__device__ __forceinline__ void warp_merge_desc_t(uint64_t* A, const uint64_t* B, int lane) {
+    uint64_t a[S];
+#pragma unroll
+    for (int s = 0; s < S; ++s) {
+        const uint64_t x = A[s * 32 + lane];
+        const uint64_t y = B[(S - 1 - s) * 32 + 31 - lane];
+        a[s] = x > y ? x : y;
     }
-    __syncwarp();
-    for (int stride = kp >> 1; stride > 0; stride >>= 1) {
-        for (int t = lane; t < (kp >> 1); t += 32) {
-            const int i = ((t & ~(stride - 1)) << 1) | (t & (stride - 1));
-            const int j = i + stride;
-            const uint64_t x = A[i], y = A[j];
-            if (x < y) {
-                A[i] = y;
-                A[j] = x;
+#pragma unroll
+    for (int ss = S >> 1; ss > 0; ss >>= 1) {
+#pragma unroll
+        for (int s = 0; s < S; ++s) {
+            if ((s & ss) == 0) {
+                const uint64_t x = a[s], y = a[s + ss];
+                a[s] = x > y ? x : y;
+                a[s + ss] = x > y ? y : x;
             }
         }
-        __syncwarp();
+    }
+#pragma unroll
+    for (int st = 16; st > 0; st >>= 1) {
+        const bool lower = (lane & st) == 0;
+#pragma unroll
+        for (int s = 0; s < S; ++s) {
+            const uint64_t o = __shfl_xor_sync(0xffffffffu, a[s], st);
+            a[s] = lower ? (a[s] > o ? a[s] : o) : (a[s] < o ? a[s] : o);
+        }
+    }
+#pragma unroll
+    for (int s = 0; s < S; ++s) A[s * 32 + lane] = a[s];
+    __syncwarp();
+}
+
+__device__ __forceinline__ void warp_merge_desc(uint64_t* A, const uint64_t* B, int kp, int lane) {
+    switch (kp) {
+        case 32: warp_merge_desc_t<1>(A, B, lane); break;
+        case 64: warp_merge_desc_t<2>(A, B, lane); break;
+        case 128: warp_merge_desc_t<4>(A, B, lane); break;
+        default: warp_merge_desc_t<8>(A, B, lane); break;
     }
 }
 
@@ -203,6 +230,9 @@ __device__ __forceinline__ float elem_at(const uint8_t* row, int i) {
 
 // Sequential fp64 accumulation of fp32 products over one staged row (RagIndex.cs:127-133).
 // kind 0: sum q[i]*x[i]   kind 1: sum x[i]*x[i]   (row == nullptr: x := q, i.e. the query norm)
+// The additions form one dependent chain (that IS the reference's arithmetic): 8.1 cycles per DADD on
+// B200 (tools/ubench/fp64_lat.cu).  Loads, products and the fp32->fp64 conversions of a 4-element
+// block are independent of the chain and overlap with it; measured ~9 cycles per element.
 template <typename T>
 __device__ __forceinline__ double exact_chain(const uint8_t* row, bool f32row, const float* q, int dim, int kind) {
     double acc = 0.0;  // :127
@@ -263,6 +293,7 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
             mbar_init(full + s, 1);
             mbar_init(empty + s, 1);  // one consumer warp drains a tile
         }
+        mbar_init(reinterpret_cast<uint64_t*>(&misc->stage_bar), 1);
         fence_barrier_init();
     }
     __syncthreads();
@@ -433,39 +464,55 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
     const uint32_t raw_bytes = a.raw_slot ? static_cast<uint32_t>(a.raw_ld) * 4u : 0u;
     const uint32_t rs = max(L.row_bytes, raw_bytes) + 16;  // padded smem row stride: spreads rows over banks
     const int cap = max(1, static_cast<int>(ring_bytes / rs));
-    const int nchunks = static_cast<int>(L.nchunks);
-    const int raw_chunks = static_cast<int>(raw_bytes / 16);
     uint8_t* rowbuf = smem;
 
     for (int b0 = 0; b0 < n_cand; b0 += cap) {
         const int nb = min(cap, n_cand - b0);
-        // stage: one warp per row, every lane keeps several 16-byte loads in flight
-        for (int c = warp; c < nb; c += kScanThreads / 32) {
-            const uint32_t row = key_row(lists[b0 + c]);
-            const int32_t slot = a.raw_slot ? a.raw_slot[row] : -1;
-            const uint4* src = slot >= 0 ? reinterpret_cast<const uint4*>(a.raw_rows + static_cast<size_t>(slot) * a.raw_ld)
-                                         : reinterpret_cast<const uint4*>(mat + static_cast<size_t>(row) * L.row_bytes);
-            const int nch = slot >= 0 ? raw_chunks : nchunks;
-            uint4* dst = reinterpret_cast<uint4*>(rowbuf + static_cast<size_t>(c) * rs);
-#pragma unroll 8
-            for (int ch = lane; ch < nch; ch += 32) dst[ch] = __ldg(src + ch);
-            if (lane == 0) misc->raw_fmt[c] = slot >= 0 ? 1 : 0;
+        // stage: one bulk async copy per candidate row, all in flight at once, one mbarrier for the batch
+        if (warp == 0) {
+            fence_proxy_async();  // the ring was last touched through the generic proxy (list staging / previous batch)
+            uint64_t* sbar = reinterpret_cast<uint64_t*>(&misc->stage_bar);
+            uint32_t my_bytes = 0;
+            for (int c = lane; c < nb; c += 32) {
+                const uint32_t row = key_row(lists[b0 + c]);
+                const int32_t slot = a.raw_slot ? a.raw_slot[row] : -1;
+                my_bytes += slot >= 0 ? raw_bytes : L.row_bytes;
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) my_bytes += __shfl_xor_sync(0xffffffffu, my_bytes, o);
+            if (lane == 0) mbar_arrive_expect_tx(sbar, my_bytes);
+            __syncwarp();
+            for (int c = lane; c < nb; c += 32) {
+                const uint32_t row = key_row(lists[b0 + c]);
+                const int32_t slot = a.raw_slot ? a.raw_slot[row] : -1;
+                const void* src = slot >= 0 ? static_cast<const void*>(a.raw_rows + static_cast<size_t>(slot) * a.raw_ld)
+                                            : static_cast<const void*>(mat + static_cast<size_t>(row) * L.row_bytes);
+                bulk_g2s(rowbuf + static_cast<size_t>(c) * rs, src, slot >= 0 ? raw_bytes : L.row_bytes, sbar);
+                misc->raw_fmt[c] = slot >= 0 ? 1 : 0;
+            }
         }
+        mbar_wait(reinterpret_cast<uint64_t*>(&misc->stage_bar), static_cast<uint32_t>(b0 / cap) & 1u);
         __syncthreads();
         if (tid == 0 && b0 == 0) a.scratch.stamps[3] = globaltimer_ns();
-        const int nchains = 2 * nb + (b0 == 0 ? 1 : 0);
-        for (int id = tid; id < nchains; id += kScanThreads) {
-            if (id == 2 * nb) {
+        // chains: threads [0, nbp) run the dot products, [nbp, 2*nbp) the row norms, thread 2*nbp the query
+        // norm -- every warp runs one kind only, so the two kinds never serialise inside a warp
+        const int nbp = (nb + 31) & ~31;
+        const int nslots = 2 * nbp + (b0 == 0 ? 1 : 0);
+        for (int id = tid; id < nslots; id += kScanThreads) {
+            if (id == 2 * nbp) {
                 misc->na = exact_chain<T>(nullptr, true, qraw, a.dim, 1);  // :131
             } else {
-                const int c = id >> 1;
-                const uint8_t* row = rowbuf + static_cast<size_t>(c) * rs;
-                const bool f32row = (sizeof(T) == 4) || misc->raw_fmt[c];
-                const double v = exact_chain<T>(row, f32row, qraw, a.dim, id & 1);
-                if (id & 1)
-                    misc->nb[c] = v;  // :132
-                else
-                    misc->dot[c] = v;  // :130
+                const int kind = id >= nbp ? 1 : 0;
+                const int c = id - kind * nbp;
+                if (c < nb) {
+                    const uint8_t* row = rowbuf + static_cast<size_t>(c) * rs;
+                    const bool f32row = (sizeof(T) == 4) || misc->raw_fmt[c];
+                    const double v = exact_chain<T>(row, f32row, qraw, a.dim, kind);
+                    if (kind)
+                        misc->nb[c] = v;  // :132
+                    else
+                        misc->dot[c] = v;  // :130
+                }
             }
         }
         __syncthreads();
