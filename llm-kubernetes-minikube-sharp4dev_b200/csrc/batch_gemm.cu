@@ -1,0 +1,440 @@
+// batch_gemm.cu -- K3: batched-query scoring on the 5th-generation tensor cores (tcgen05 + TMEM),
+// with the top-k filter fused into the accumulator read-back.  This is the one place on the path that
+// is a dense contraction: scores[q][row] = sum_d Q[q][d] * C[row][d]   (SURVEY.md 2.1 "K3", config 3).
+//
+// Replaces the reference's per-request loop over `Cosine` (Helpers/RagIndex.cs:62-63,124-135) for a
+// whole batch of queries at once; selection and exact rescoring follow the same rules as the
+// single-query kernel (topk_device.cuh), so the returned hits are the reference's.
+//
+// Shape (B200 / sm_100a), one persistent CTA per SM, 384 threads:
+//   warp 0      TMA producer: 2-D tiled bulk tensor copies (cp.async.bulk.tensor, 128B swizzle) of a
+//               128-row corpus tile slice and of the 128/256-query slice into a 3..5-stage ring;
+//   warp 1      MMA issuer: one lane issues tcgen05.mma.cta_group::1.kind::tf32 (M=128 queries, N=128
+//               corpus rows, K=8 per instruction), accumulators in TMEM, double buffered (2 x 256
+//               columns), tcgen05.commit releases ring stages and publishes finished accumulators;
+//   warp 2      allocates / frees the 512 TMEM columns;
+//   warps 4-11  epilogue: thread <-> query (TMEM lane), tcgen05.ld of its 128 scores per tile, a
+//               register threshold and a thread-private sorted candidate list in shared memory --
+//               no atomics, no overflow, and the M x N score block is never written anywhere.
+// Queries are the M operand on purpose: a TMEM lane then carries ONE query's scores across corpus rows,
+// which is what makes the per-query running top-k thread-private.
+// tf32 products differ from the reference's by up to 2^-9 relative, so this kernel only nominates
+// k' = 32 candidates per query; batch_finalize_kernel re-scores them with the reference's exact
+// fp64 arithmetic and certifies the margin (eps = 2.1e-3); uncertified queries are redone by the
+// fp32 scan kernel (host side, ragstore_api.cu).
+#include <cuda.h>
+
+#include "topk_device.cuh"
+
+namespace rag {
+
+constexpr int kBM = 128;            // queries per MMA (M)
+constexpr int kBN = 128;            // corpus rows per tile (N)
+constexpr int kBKBytes = 128;       // bytes of K per ring stage row = one 128B swizzle atom row
+constexpr int kBatchThreads = 384;
+constexpr int kEpiWarp0 = 4;        // first epilogue warp
+constexpr int kBatchKp = 32;        // candidates kept per query and CTA
+constexpr uint32_t kOperandBytes = 128 * kBKBytes;  // one 128-row operand slice: 16 KB
+
+struct BatchLayout {
+    uint32_t n_stages, stage_bytes, mblocks;
+    uint32_t off_bars, off_tmem, off_lists, total;
+};
+
+// ---------------------------------------------------------------- PTX wrappers (tcgen05 / TMA)
+__device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
+            smem_u32(smem_dst)),
+        "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+        : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(map)) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tmem_alloc(uint32_t* smem_dst, uint32_t cols) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_dst)), "r"(cols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t cols) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols) : "memory");
+}
+// arrives on the mbarrier once every tcgen05.mma issued so far by this thread has completed
+__device__ __forceinline__ void tc_commit(uint64_t* bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+                 : "memory");
+}
+// D[tmem] (+)= A[smem] * B[smem]^T, tf32 inputs, fp32 accumulate
+__device__ __forceinline__ void mma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// 32 lanes x 32 consecutive 32-bit columns: thread i of the warp gets lane (base + i)
+__device__ __forceinline__ void tmem_ld_32x32(uint32_t taddr, uint32_t (&v)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+          "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
+          "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
+          "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+        : "r"(taddr)
+        : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// Shared-memory matrix descriptor for a K-major operand slice written by TMA with 128B swizzle:
+// rows are 128 bytes apart, 8-row groups 1024 bytes apart (SBO), LBO unused, descriptor version 1.
+__device__ __forceinline__ uint64_t make_sw128_desc(uint32_t smem_addr) {
+    uint64_t d = 0;
+    d |= static_cast<uint64_t>((smem_addr >> 4) & 0x3FFFu);        // start address, 16-byte units
+    d |= static_cast<uint64_t>(1u) << 16;                          // leading byte offset (ignored for swizzled K-major)
+    d |= static_cast<uint64_t>(1024u >> 4) << 32;                  // stride byte offset: 8 rows x 128 B
+    d |= static_cast<uint64_t>(1u) << 46;                          // descriptor version (Blackwell)
+    d |= static_cast<uint64_t>(2u) << 61;                          // layout type: SWIZZLE_128B
+    return d;
+}
+
+// instruction descriptor: D fp32, A/B tf32, both K-major, M = 128, N = 128
+constexpr uint32_t kIdescTf32 = (1u << 4) | (2u << 7) | (2u << 10) | ((kBN >> 3) << 17) | ((kBM >> 4) << 24);
+
+struct BatchArgs {
+    int64_t n_rows;
+    int nq;            // real queries in this launch (<= 128 * mblocks)
+    int mblocks;       // 1 or 2 blocks of 128 queries
+    int nkb;           // k-blocks of 32 fp32 per row
+    uint64_t* glists;  // [nq][n_ctas][kBatchKp] candidate keys, written by this kernel
+};
+
+// Thread-private insertion into the query's sorted candidate list (lists[pos][query]); returns the new
+// threshold: the score of the last entry once the list is full, -inf before.  Kept out of line: it runs
+// O(k log N) times per query over the whole scan, while the compare that guards it runs N times.
+__device__ __noinline__ float list_insert(uint64_t* lists, int NQ, int q, float sc, uint32_t row) {
+    const uint64_t key = make_key(sc + 0.0f, row);
+    int p = kBatchKp - 1;
+    while (p > 0) {
+        const uint64_t up = lists[(p - 1) * NQ + q];
+        if (up >= key) break;
+        lists[p * NQ + q] = up;
+        --p;
+    }
+    lists[p * NQ + q] = key;
+    const uint64_t last = lists[(kBatchKp - 1) * NQ + q];
+    return last ? key_score(last) : -CUDART_INF_F;
+}
+
+// ---------------------------------------------------------------- the tensor-core kernel
+__global__ void __launch_bounds__(kBatchThreads, 1)
+batch_score_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_c,
+                   const BatchArgs a, const BatchLayout L) {
+    extern __shared__ uint8_t smem_raw[];
+    // 128B-swizzled operand tiles must start on a 1024-byte boundary
+    uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int n_stages = static_cast<int>(L.n_stages);
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem + L.off_bars);
+    uint64_t* empty = full + n_stages;
+    uint64_t* tmem_full = empty + n_stages;   // [2]
+    uint64_t* tmem_empty = tmem_full + 2;     // [2]
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(smem + L.off_tmem);
+    uint64_t* lists = reinterpret_cast<uint64_t*>(smem + L.off_lists);  // [pos][query] : conflict-free across lanes
+    const int NQ = kBM * a.mblocks;
+
+    const int64_t n_tiles = (a.n_rows + kBN - 1) / kBN;
+    const int64_t my_tiles = n_tiles > blockIdx.x ? (n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+
+    if (tid == 0) {
+        for (int s = 0; s < n_stages; ++s) {
+            mbar_init(full + s, 1);
+            mbar_init(empty + s, 1);
+        }
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(tmem_full + s, 1);
+            mbar_init(tmem_empty + s, 4 * a.mblocks);  // one arrival per participating epilogue warp
+        }
+        fence_barrier_init();
+    }
+    if (warp == 2) tmem_alloc(tmem_ptr, 512);
+    for (int i = tid; i < kBatchKp * NQ; i += kBatchThreads) lists[i] = 0ull;
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr;
+
+    if (warp == 0) {
+        // ------------------------------------------------ TMA producer
+        if (lane == 0) {
+            tma_prefetch_desc(&tmap_q);
+            tma_prefetch_desc(&tmap_c);
+            int s = 0;
+            uint32_t ph = 0;
+            const uint32_t tx = (static_cast<uint32_t>(a.mblocks) + 1u) * kOperandBytes;
+            for (int64_t it = 0; it < my_tiles; ++it) {
+                const int row0 = static_cast<int>((blockIdx.x + it * gridDim.x) * kBN);
+                for (int kb = 0; kb < a.nkb; ++kb) {
+                    mbar_wait(empty + s, ph ^ 1u);
+                    uint8_t* st = smem + static_cast<size_t>(s) * L.stage_bytes;
+                    mbar_arrive_expect_tx(full + s, tx);
+                    for (int m = 0; m < a.mblocks; ++m) tma_load_2d(st + m * kOperandBytes, &tmap_q, full + s, kb * 32, m * kBM);
+                    tma_load_2d(st + a.mblocks * kOperandBytes, &tmap_c, full + s, kb * 32, row0);
+                    if (++s == n_stages) {
+                        s = 0;
+                        ph ^= 1u;
+                    }
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        // ------------------------------------------------ MMA issuer (one lane)
+        if (lane == 0) {
+            int s = 0;
+            uint32_t ph = 0;
+            for (int64_t it = 0; it < my_tiles; ++it) {
+                const uint32_t as = static_cast<uint32_t>(it & 1), aph = static_cast<uint32_t>((it >> 1) & 1);
+                mbar_wait(tmem_empty + as, aph ^ 1u);  // the epilogue has drained this accumulator
+                tc_fence_after();
+                for (int kb = 0; kb < a.nkb; ++kb) {
+                    mbar_wait(full + s, ph);
+                    tc_fence_after();
+                    const uint32_t st = smem_u32(smem + static_cast<size_t>(s) * L.stage_bytes);
+                    const uint32_t b_addr = st + a.mblocks * kOperandBytes;
+#pragma unroll
+                    for (int k4 = 0; k4 < 4; ++k4) {  // 4 x K=8 tf32 per 128-byte slice
+                        const uint64_t bdesc = make_sw128_desc(b_addr + k4 * 32);
+                        for (int m = 0; m < a.mblocks; ++m) {
+                            const uint64_t adesc = make_sw128_desc(st + m * kOperandBytes + k4 * 32);
+                            mma_tf32(tmem_base + as * 256u + m * 128u, adesc, bdesc, kIdescTf32, (kb | k4) != 0);
+                        }
+                    }
+                    tc_commit(empty + s);  // ring stage reusable once these MMAs have read it
+                    if (++s == n_stages) {
+                        s = 0;
+                        ph ^= 1u;
+                    }
+                }
+                tc_commit(tmem_full + as);  // accumulator complete
+            }
+        }
+        __syncwarp();
+    } else if (warp >= kEpiWarp0) {
+        // ------------------------------------------------ epilogue: thread <-> query
+        const int q = (warp - kEpiWarp0) * 32 + lane;  // 0 .. 255
+        const int mblock = q >> 7;
+        const bool live = q < a.nq;
+        const uint32_t lane_base = static_cast<uint32_t>((warp & 3) * 32) << 16;  // TMEM lanes this warp may read
+        float thr = -CUDART_INF_F;
+        if (mblock < a.mblocks) {
+            for (int64_t it = 0; it < my_tiles; ++it) {
+                const uint32_t as = static_cast<uint32_t>(it & 1), aph = static_cast<uint32_t>((it >> 1) & 1);
+                mbar_wait(tmem_full + as, aph);
+                tc_fence_after();
+                const int64_t row0 = (blockIdx.x + it * gridDim.x) * kBN;
+                const int nvalid = static_cast<int>(min(static_cast<int64_t>(kBN), a.n_rows - row0));
+                for (int c0 = 0; c0 < kBN; c0 += 32) {
+                    uint32_t v[32];
+                    tmem_ld_32x32(tmem_base + lane_base + as * 256u + mblock * 128u + c0, v);
+                    if (live) {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) {
+                            const float sc = __uint_as_float(v[j]);
+                            if (sc > thr && c0 + j < nvalid)  // rows ascend, so equal scores never displace
+                                thr = list_insert(lists, NQ, q, sc, static_cast<uint32_t>(row0 + c0 + j));
+                        }
+                    }
+                }
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(tmem_empty + as);
+            }
+        }
+        // publish this CTA's list of the query: glists[q][cta][pos]
+        if (live) {
+            uint64_t* g = a.glists + (static_cast<size_t>(q) * gridDim.x + blockIdx.x) * kBatchKp;
+#pragma unroll 4
+            for (int p = 0; p < kBatchKp; ++p) g[p] = lists[p * NQ + q];
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 512);
+    }
+}
+
+// ---------------------------------------------------------------- per-query merge + exact rescoring
+struct BatchFinalizeArgs {
+    ScanArgs scan;          // store views, k_take, kp, eps, row_base; d_query / out_* are per-launch bases
+    const float* d_queries; // raw queries [nq][dim]
+    const uint64_t* glists; // [nq][nlists][kp]
+    int nlists;
+    int out_stride;         // hits per query in out_idx / out_score
+    uint32_t ring_bytes, row_bytes, qpad;
+};
+
+template <typename T>
+__global__ void __launch_bounds__(kScanThreads, 1) batch_finalize_kernel(const BatchFinalizeArgs b) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    const int q = blockIdx.x, tid = threadIdx.x;
+    uint8_t* ring = smem;
+    float* qraw = reinterpret_cast<float*>(smem + b.ring_bytes);
+    uint64_t* lists = reinterpret_cast<uint64_t*>(smem + b.ring_bytes + b.qpad * 4u);
+    ScanMisc* misc = reinterpret_cast<ScanMisc*>(reinterpret_cast<uint8_t*>(lists) + sizeof(uint64_t) * 2u * kConsumerWarps * b.scan.kp);
+    ScanArgs a = b.scan;
+    a.d_query = b.d_queries + static_cast<size_t>(q) * a.dim;
+    a.out_idx = a.out_idx ? a.out_idx + static_cast<size_t>(q) * b.out_stride : nullptr;
+    a.out_score = a.out_score ? a.out_score + static_cast<size_t>(q) * b.out_stride : nullptr;
+    a.out_found = a.out_found ? a.out_found + q : nullptr;
+    a.out_flags = a.out_flags ? a.out_flags + q : nullptr;
+    a.scratch.stamps = nullptr;
+    for (int i = tid; i < static_cast<int>(b.qpad); i += kScanThreads) qraw[i] = i < a.dim ? a.d_query[i] : 0.f;
+    if (tid == 0) {
+        mbar_init(reinterpret_cast<uint64_t*>(&misc->stage_bar), 1);
+        fence_barrier_init();
+        misc->inexact = 0;
+    }
+    __syncthreads();
+    FinalizeCtx f;
+    f.ring = ring;
+    f.ring_bytes = b.ring_bytes;
+    f.row_bytes = b.row_bytes;
+    f.lists = lists;
+    f.misc = misc;
+    f.qraw = qraw;
+    f.glists = b.glists + static_cast<size_t>(q) * b.nlists * a.kp;
+    f.nlists = b.nlists;
+    finalize_candidates<T>(a, f);
+}
+
+// normalised, zero-padded copy of the queries: the tensor-core operand (rows >= nq are zero)
+__global__ void __launch_bounds__(256) prep_queries_kernel(const float* __restrict__ q, float* __restrict__ qhat, int nq,
+                                                           int nq_pad, int dim, int ld) {
+    const int lane = threadIdx.x & 31;
+    const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (row >= nq_pad) return;
+    float* dst = qhat + static_cast<size_t>(row) * ld;
+    if (row >= nq) {
+        for (int i = lane; i < ld; i += 32) dst[i] = 0.f;
+        return;
+    }
+    const float* src = q + static_cast<size_t>(row) * dim;
+    double acc = 0.0;
+    for (int i = lane; i < dim; i += 32) acc += static_cast<double>(src[i]) * static_cast<double>(src[i]);
+    acc = warp_sum(acc);
+    const float r = acc > 0.0 ? static_cast<float>(1.0 / sqrt(acc)) : 0.f;
+    for (int i = lane; i < ld; i += 32) dst[i] = i < dim ? src[i] * r : 0.f;
+}
+
+// ---------------------------------------------------------------- host side
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                    const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                    CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static PFN_encodeTiled encode_fn() {
+    static PFN_encodeTiled fn = [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+            q != cudaDriverEntryPointSuccess)
+            p = nullptr;
+        cudaGetLastError();
+        return reinterpret_cast<PFN_encodeTiled>(p);
+    }();
+    return fn;
+}
+
+static bool make_map_f32(CUtensorMap* m, const void* base, uint64_t rows, uint64_t ld) {
+    PFN_encodeTiled enc = encode_fn();
+    if (!enc) return false;
+    const cuuint64_t dims[2] = {ld, rows};
+    const cuuint64_t strides[1] = {ld * 4};
+    const cuuint32_t box[2] = {32, 128};
+    const cuuint32_t estr[2] = {1, 1};
+    return enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(base), dims, strides, box, estr,
+               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+size_t batch_scratch_bytes(int sm_count) {
+    return sizeof(uint64_t) * size_t(kBatchMaxQ) * size_t(sm_count) * kBatchKp   // candidate lists
+           + sizeof(float) * size_t(kBatchMaxQ) * size_t(kBatchMaxLd);          // normalised query operand
+}
+
+int launch_batch_search(const BatchSearchArgs& b, cudaStream_t stream) {
+    const ScanArgs& s = b.scan;
+    if (s.dtype != RAGSTORE_F32 || b.nq < 1 || b.nq > kBatchMaxQ || s.ld > kBatchMaxLd || s.kp != kBatchKp ||
+        s.n_rows < 1 || s.n_rows >= 0x7FFFFFFFll)
+        return static_cast<int>(cudaErrorInvalidValue);
+    const int mblocks = b.nq > kBM ? 2 : 1;
+    const int nq_pad = mblocks * kBM;
+    uint64_t* glists = reinterpret_cast<uint64_t*>(b.scratch);
+    float* qhat = reinterpret_cast<float*>(b.scratch + sizeof(uint64_t) * size_t(kBatchMaxQ) * size_t(s.sm_count) * kBatchKp);
+
+    prep_queries_kernel<<<(nq_pad * 32 + 255) / 256, 256, 0, stream>>>(b.d_queries, qhat, b.nq, nq_pad, s.dim, s.ld);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return static_cast<int>(e);
+
+    CUtensorMap map_q, map_c;
+    if (!make_map_f32(&map_q, qhat, static_cast<uint64_t>(nq_pad), static_cast<uint64_t>(s.ld)) ||
+        !make_map_f32(&map_c, s.mat, static_cast<uint64_t>(s.n_rows), static_cast<uint64_t>(s.ld)))
+        return static_cast<int>(cudaErrorNotSupported);
+
+    BatchLayout L;
+    L.mblocks = mblocks;
+    L.stage_bytes = (mblocks + 1) * kOperandBytes;
+    const uint32_t lists_bytes = sizeof(uint64_t) * kBatchKp * nq_pad;
+    const uint32_t budget = 225u * 1024u - 1024u /*alignment slack*/ - lists_bytes - 256u;
+    L.n_stages = budget / L.stage_bytes;
+    if (L.n_stages > 8) L.n_stages = 8;
+    if (L.n_stages < 2) return static_cast<int>(cudaErrorInvalidConfiguration);
+    L.off_bars = L.n_stages * L.stage_bytes;
+    L.off_tmem = L.off_bars + 8u * (2u * L.n_stages + 4u);
+    L.off_lists = (L.off_tmem + 16u + 15u) & ~15u;
+    L.total = L.off_lists + lists_bytes + 1024u;
+
+    BatchArgs a;
+    a.n_rows = s.n_rows;
+    a.nq = b.nq;
+    a.mblocks = mblocks;
+    a.nkb = (s.ld + 31) / 32;
+    a.glists = glists;
+    const int64_t n_tiles = (s.n_rows + kBN - 1) / kBN;
+    const int grid = static_cast<int>(n_tiles < s.sm_count ? n_tiles : s.sm_count);
+    e = cudaFuncSetAttribute(batch_score_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    batch_score_kernel<<<grid, kBatchThreads, L.total, stream>>>(map_q, map_c, a, L);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return static_cast<int>(e);
+
+    BatchFinalizeArgs f;
+    f.scan = s;
+    f.d_queries = b.d_queries;
+    f.glists = glists;
+    f.nlists = grid;
+    f.out_stride = b.out_stride;
+    f.row_bytes = static_cast<uint32_t>(s.ld) * 4u;
+    f.qpad = static_cast<uint32_t>(s.ld);
+    const uint32_t fixed = f.qpad * 4u + sizeof(uint64_t) * 2u * kConsumerWarps * s.kp + sizeof(ScanMisc) + 256u;
+    uint32_t ring = 200u * 1024u - fixed;
+    const uint32_t need = static_cast<uint32_t>(s.kp) * (f.row_bytes + 16u);  // room for every candidate row at once
+    if (ring > need) ring = need;
+    const uint32_t lists_need = static_cast<uint32_t>(grid) * s.kp * 8u;
+    if (ring < lists_need && lists_need + fixed <= 200u * 1024u) ring = lists_need;
+    f.ring_bytes = (ring + 127u) & ~127u;
+    const size_t fin_smem = f.ring_bytes + fixed;
+    e = cudaFuncSetAttribute(batch_finalize_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    batch_finalize_kernel<float><<<b.nq, kScanThreads, fin_smem, stream>>>(f);
+    return static_cast<int>(cudaGetLastError());
+}
+
+}  // namespace rag

@@ -55,6 +55,7 @@ constexpr int kNumCtx = 4;       // concurrent host searches per store
 struct SearchCtx {
     cudaStream_t st = nullptr;
     ScanScratch scratch{};
+    uint8_t* batch_scratch = nullptr;  // candidate lists + query operand of the tensor-core path
     float* d_q = nullptr;
     int64_t* d_idx = nullptr;
     double* d_score = nullptr;
@@ -91,6 +92,7 @@ struct ragstore {
     int64_t capacity = 0;
     std::atomic<int64_t> count{0};
     int64_t row_base = 0;
+    mutable std::atomic<int64_t> n_scan_launches{0}, n_batch_launches{0};  // kernel launches issued by searches
     VmmBuffer mat_buf, rnorm_buf, exact_buf, slot_buf, raw_buf;  // address-stable, grown on demand
     void* mat = nullptr;
     float* rnorm = nullptr;
@@ -109,6 +111,7 @@ struct ragstore {
     float* d_stage = nullptr;
     size_t stage_floats = 0;
     ScanScratch dev_scratch{};
+    uint8_t* dev_batch_scratch = nullptr;
     std::vector<SearchCtx> ctxs;
     std::vector<int> free_ctx;
     std::mutex ctx_mu;
@@ -133,10 +136,11 @@ void free_scratch(ScanScratch& s) {
     s = ScanScratch{};
 }
 
-int alloc_ctx(SearchCtx& c, int ld) {
+int alloc_ctx(SearchCtx& c, int ld, int sm_count) {
     CU_TRY(cudaStreamCreateWithFlags(&c.st, cudaStreamNonBlocking));
     int rc = alloc_scratch(c.scratch);
     if (rc) return rc;
+    CU_TRY(cudaMalloc(&c.batch_scratch, batch_scratch_bytes(sm_count)));
     const size_t nq = kCtxQueries;
     CU_TRY(cudaMalloc(&c.d_q, nq * ld * sizeof(float)));
     CU_TRY(cudaMalloc(&c.d_idx, nq * kMaxKp * sizeof(int64_t)));
@@ -154,6 +158,7 @@ int alloc_ctx(SearchCtx& c, int ld) {
 void free_ctx(SearchCtx& c) {
     if (c.st) cudaStreamDestroy(c.st);
     free_scratch(c.scratch);
+    cudaFree(c.batch_scratch);
     cudaFree(c.d_q);
     cudaFree(c.d_idx);
     cudaFree(c.d_score);
@@ -187,6 +192,31 @@ ScanArgs base_args(const ragstore* s, int64_t n, int take, int kp) {
     a.eps = scan_eps(s->ld, s->dtype);
     a.sm_count = s->sm_count;
     return a;
+}
+
+// tf32 products (10-bit mantissas, both operands) + fp32 accumulation vs the reference's score
+constexpr float kBatchEps = 2.1e-3f;
+
+bool batch_eligible(const ragstore* s, int64_t n, int nq, int kp) {
+    return s->dtype == RAGSTORE_F32 && nq >= kBatchMinQ && n >= kBatchMinRows && kp == 32 && s->ld <= kBatchMaxLd;
+}
+
+// One tensor-core launch for up to kBatchMaxQ queries (outputs laid out with `stride` hits per query).
+int run_batch(const ragstore* s, int64_t n, int take, const float* d_q, int nq, int64_t* d_idx, double* d_score,
+              int32_t* d_found, int32_t* d_flags, int stride, uint8_t* scratch, cudaStream_t st) {
+    BatchSearchArgs b{};
+    b.scan = base_args(s, n, take, 32);
+    b.scan.eps = kBatchEps;
+    b.scan.out_idx = d_idx;
+    b.scan.out_score = d_score;
+    b.scan.out_found = d_found;
+    b.scan.out_flags = d_flags;
+    b.d_queries = d_q;
+    b.nq = nq;
+    b.out_stride = stride;
+    b.scratch = scratch;
+    s->n_batch_launches.fetch_add(1, std::memory_order_relaxed);
+    return launch_batch_search(b, st);
 }
 
 }  // namespace
@@ -275,9 +305,10 @@ int ragstore_create(int dim, int dtype, int64_t capacity_rows, int device, uint3
     if ((e = cudaStreamCreateWithFlags(&s->dev_stream, cudaStreamNonBlocking)) != cudaSuccess) return bail(fail(RAGSTORE_ERR_CUDA, "cudaStreamCreate", cudaGetErrorString(e)));
     int rc = alloc_scratch(s->dev_scratch);
     if (rc) return bail(rc);
+    if ((e = cudaMalloc(&s->dev_batch_scratch, batch_scratch_bytes(s->sm_count))) != cudaSuccess) return bail(fail(RAGSTORE_ERR_CUDA, "cudaMalloc(batch scratch)", cudaGetErrorString(e)));
     s->ctxs.resize(kNumCtx);
     for (int i = 0; i < kNumCtx; ++i) {
-        rc = alloc_ctx(s->ctxs[i], s->ld);
+        rc = alloc_ctx(s->ctxs[i], s->ld, s->sm_count);
         if (rc) return bail(rc);
         s->free_ctx.push_back(i);
     }
@@ -291,6 +322,7 @@ int ragstore_destroy(ragstore_t* s) {
     cudaDeviceSynchronize();
     for (auto& c : s->ctxs) free_ctx(c);
     free_scratch(s->dev_scratch);
+    cudaFree(s->dev_batch_scratch);
     if (s->ingest_stream) cudaStreamDestroy(s->ingest_stream);
     if (s->dev_stream) cudaStreamDestroy(s->dev_stream);
     cudaFree(s->d_stage);
@@ -404,9 +436,10 @@ int ragstore_info(ragstore_t* s, int64_t* out, int n) {
     DeviceGuard g(s->device);
     unsigned long long inexact = 0;
     CU_TRY(cudaMemcpy(&inexact, s->d_inexact, sizeof(inexact), cudaMemcpyDeviceToHost));
-    const int64_t v[12] = {s->dim, s->ld, s->dtype, s->count.load(), s->capacity, static_cast<int64_t>(inexact), s->device, s->sm_count,
-                           s->raw_slot ? 1 : 0, s->raw_used, static_cast<int64_t>(s->mat_buf.mapped()), s->mat_buf.uses_vmm() ? 1 : 0};
-    for (int i = 0; i < n && i < 12; ++i) out[i] = v[i];
+    const int64_t v[14] = {s->dim, s->ld, s->dtype, s->count.load(), s->capacity, static_cast<int64_t>(inexact), s->device, s->sm_count,
+                           s->raw_slot ? 1 : 0, s->raw_used, static_cast<int64_t>(s->mat_buf.mapped()), s->mat_buf.uses_vmm() ? 1 : 0,
+                           s->n_scan_launches.load(), s->n_batch_launches.load()};
+    for (int i = 0; i < n && i < 14; ++i) out[i] = v[i];
     return RAGSTORE_OK;
 }
 
@@ -441,6 +474,18 @@ int ragstore_search_device(ragstore_t* s, const float* d_queries, int n_queries,
     }
     if (take > kMaxKp) return fail(RAGSTORE_ERR_UNSUPPORTED, "top_k above 256 is not covered yet");
     const int kp = choose_kp(take);
+    if (batch_eligible(s, n, n_queries, kp)) {
+        // tensor-core path: the corpus is swept once per 256 queries instead of once per query
+        for (int q0 = 0; q0 < n_queries; q0 += kBatchMaxQ) {
+            const int nq = std::min(kBatchMaxQ, n_queries - q0);
+            const int rc = run_batch(s, n, take, d_queries + static_cast<size_t>(q0) * s->dim, nq,
+                                     d_idx + static_cast<size_t>(q0) * req, d_score + static_cast<size_t>(q0) * req,
+                                     d_found ? d_found + q0 : nullptr, d_flags ? d_flags + q0 : nullptr, req,
+                                     s->dev_batch_scratch, st);
+            if (rc) return fail(RAGSTORE_ERR_CUDA, "batched search launch", cudaGetErrorString(static_cast<cudaError_t>(rc)));
+        }
+        return RAGSTORE_OK;
+    }
     for (int q = 0; q < n_queries; ++q) {
         ScanArgs a = base_args(s, n, take, kp);
         a.d_query = d_queries + static_cast<size_t>(q) * s->dim;
@@ -449,6 +494,7 @@ int ragstore_search_device(ragstore_t* s, const float* d_queries, int n_queries,
         a.out_score = d_score + static_cast<size_t>(q) * req;
         a.out_found = d_found ? d_found + q : nullptr;
         a.out_flags = d_flags ? d_flags + q : nullptr;
+        s->n_scan_launches.fetch_add(1, std::memory_order_relaxed);
         const int rc = launch_scan(a, st);
         if (rc) return fail(RAGSTORE_ERR_CUDA, "scan kernel launch", cudaGetErrorString(static_cast<cudaError_t>(rc)));
     }
@@ -479,6 +525,7 @@ int ragstore_search_shard_device(ragstore_t* s, const float* d_query, int top_k,
     a.out_flags = d_flags;
     a.out_cand = d_out;
     a.cand_slots = req;
+    s->n_scan_launches.fetch_add(1, std::memory_order_relaxed);
     const int rc = launch_scan(a, st);
     if (rc) return fail(RAGSTORE_ERR_CUDA, "scan kernel launch", cudaGetErrorString(static_cast<cudaError_t>(rc)));
     return RAGSTORE_OK;
@@ -555,8 +602,17 @@ int ragstore_search(ragstore_t* s, const float* queries, int n_queries, int quer
         std::vector<int> todo(nq);
         for (int i = 0; i < nq; ++i) todo[i] = i;
         int kp = kp0;
+        bool batch_pass = batch_eligible(s, n, nq, kp0);
         while (!todo.empty()) {
+            if (batch_pass) {
+                // first pass on the tensor cores; queries whose margin the tf32 scores cannot certify are
+                // redone below by the fp32 scan kernel
+                const int rc = run_batch(s, n, take, c.d_q, nq, c.d_idx, c.d_score, c.d_found, c.d_flags, kMaxKp,
+                                         c.batch_scratch, c.st);
+                if (rc) return fail(RAGSTORE_ERR_CUDA, "batched search launch", cudaGetErrorString(static_cast<cudaError_t>(rc)));
+            }
             for (int i : todo) {
+                if (batch_pass) break;
                 ScanArgs a = base_args(s, n, take, kp);
                 a.d_query = c.d_q + static_cast<size_t>(i) * s->dim;
                 a.scratch = c.scratch;
@@ -564,6 +620,7 @@ int ragstore_search(ragstore_t* s, const float* queries, int n_queries, int quer
                 a.out_score = c.d_score + static_cast<size_t>(i) * kMaxKp;
                 a.out_found = c.d_found + i;
                 a.out_flags = c.d_flags + i;
+                s->n_scan_launches.fetch_add(1, std::memory_order_relaxed);
                 const int rc = launch_scan(a, c.st);
                 if (rc) return fail(RAGSTORE_ERR_CUDA, "scan kernel launch", cudaGetErrorString(static_cast<cudaError_t>(rc)));
             }
@@ -575,8 +632,8 @@ int ragstore_search(ragstore_t* s, const float* queries, int n_queries, int quer
             std::vector<int> again;
             for (int i : todo) {
                 const bool cert = (c.h_flags[i] & RAGSTORE_HIT_CERTIFIED) != 0;
-                if (!cert && kp < kMaxKp) {
-                    again.push_back(i);  // widen the candidate list and rescan this query
+                if (!cert && (batch_pass || kp < kMaxKp)) {
+                    again.push_back(i);  // rescan this query (fp32 scan after a tf32 pass; else a wider list)
                     continue;
                 }
                 const size_t o = static_cast<size_t>(q0 + i) * req;
@@ -586,7 +643,10 @@ int ragstore_search(ragstore_t* s, const float* queries, int n_queries, int quer
                 if (out_flags) out_flags[q0 + i] = c.h_flags[i];
             }
             todo.swap(again);
-            kp = kMaxKp;
+            if (batch_pass)
+                batch_pass = false;  // next pass: fp32 scan with the same list length
+            else
+                kp = kMaxKp;
         }
     }
     return RAGSTORE_OK;

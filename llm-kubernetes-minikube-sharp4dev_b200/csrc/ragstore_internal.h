@@ -73,6 +73,21 @@ struct NormaliseArgs {
 };
 int launch_normalise(const NormaliseArgs& a, cudaStream_t stream);
 
+// ---- batched (tensor-core) path, batch_gemm.cu
+constexpr int kBatchMaxQ = 256;    // queries per launch (two 128-row MMA blocks)
+constexpr int kBatchMinQ = 16;     // below this the per-query scan kernel is used
+constexpr int kBatchMaxLd = 4096;  // padded row length covered by the query operand buffer
+constexpr int64_t kBatchMinRows = 4096;
+struct BatchSearchArgs {
+    ScanArgs scan;           // store views, k_take, kp (must be 32), eps, outputs as per-launch bases
+    const float* d_queries;  // raw queries [nq][dim], device
+    int nq;
+    int out_stride;          // hits per query in scan.out_idx / scan.out_score
+    uint8_t* scratch;        // batch_scratch_bytes(sm_count) bytes of device memory
+};
+size_t batch_scratch_bytes(int sm_count);
+int launch_batch_search(const BatchSearchArgs& b, cudaStream_t stream);
+
 int launch_synth(float* d_out, int64_t row0, int64_t n_rows, int dim, int64_t ld, uint64_t seed,
                  int round_bf16, cudaStream_t stream);
 

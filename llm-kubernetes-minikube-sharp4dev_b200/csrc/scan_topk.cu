@@ -27,8 +27,7 @@
 // HBM traffic: every stored element is read exactly once (d * sizeof(elem) + 4 bytes per row).
 #include <math_constants.h>
 
-#include "common.cuh"
-#include "ragstore_internal.h"
+#include "topk_device.cuh"
 
 namespace rag {
 
@@ -41,96 +40,6 @@ struct ScanLayout {
     uint32_t off_bars, off_qraw, off_qhat, off_lists, off_buf, off_misc, total;
     uint32_t n_consumers;  // consumer warps that take tiles; divides n_stages, so a warp owns fixed stages
 };
-
-struct ScanMisc {  // lives in shared memory at off_misc
-    double na;
-    double ek;
-    double red[kConsumerWarps];
-    int is_last;
-    int inexact;
-    double ex[kMaxKp];
-    double dot[kMaxKp];
-    double nb[kMaxKp];
-    uint8_t raw_fmt[kMaxKp];  // 1 = the staged row is the fp32 original from the sidecar
-    unsigned long long stage_bar;  // mbarrier for the bulk copies that stage candidate rows
-};
-
-// ---------------------------------------------------------------- warp-level sorted lists
-// Lists live in shared memory (kp = 32*S keys, sorted descending, position j = slot*32 + lane) but are
-// merged in registers: A <- top kp of A u B.  Element-wise max of A with reversed B leaves a bitonic
-// sequence holding the kp largest keys; a bitonic merge (slot strides in registers, lane strides by
-// shuffle) sorts it.  No shared-memory round trips inside the network.
-template <int S>
-__device__ __forceinline__ void warp_merge_desc_t(uint64_t* A, const uint64_t* B, int lane) {
-    uint64_t a[S];
-#pragma unroll
-    for (int s = 0; s < S; ++s) {
-        const uint64_t x = A[s * 32 + lane];
-        const uint64_t y = B[(S - 1 - s) * 32 + 31 - lane];
-        a[s] = x > y ? x : y;
-    }
-#pragma unroll
-    for (int ss = S >> 1; ss > 0; ss >>= 1) {
-#pragma unroll
-        for (int s = 0; s < S; ++s) {
-            if ((s & ss) == 0) {
-                const uint64_t x = a[s], y = a[s + ss];
-                a[s] = x > y ? x : y;
-                a[s + ss] = x > y ? y : x;
-            }
-        }
-    }
-#pragma unroll
-    for (int st = 16; st > 0; st >>= 1) {
-        const bool lower = (lane & st) == 0;
-#pragma unroll
-        for (int s = 0; s < S; ++s) {
-            const uint64_t o = __shfl_xor_sync(0xffffffffu, a[s], st);
-            a[s] = lower ? (a[s] > o ? a[s] : o) : (a[s] < o ? a[s] : o);
-        }
-    }
-#pragma unroll
-    for (int s = 0; s < S; ++s) A[s * 32 + lane] = a[s];
-    __syncwarp();
-}
-
-__device__ __forceinline__ void warp_merge_desc(uint64_t* A, const uint64_t* B, int kp, int lane) {
-    switch (kp) {
-        case 32: warp_merge_desc_t<1>(A, B, lane); break;
-        case 64: warp_merge_desc_t<2>(A, B, lane); break;
-        case 128: warp_merge_desc_t<4>(A, B, lane); break;
-        default: warp_merge_desc_t<8>(A, B, lane); break;
-    }
-}
-
-// one key per lane -> sorted descending across lanes (bitonic network on shuffles)
-__device__ __forceinline__ uint64_t warp_sort_desc(uint64_t v, int lane) {
-#pragma unroll
-    for (int k = 2; k <= 32; k <<= 1) {
-#pragma unroll
-        for (int j = k >> 1; j > 0; j >>= 1) {
-            const uint64_t o = __shfl_xor_sync(0xffffffffu, v, j);
-            const bool desc_block = (lane & k) == 0;
-            const bool lower = (lane & j) == 0;
-            const bool keep_max = (lower == desc_block);
-            v = keep_max ? (v > o ? v : o) : (v < o ? v : o);
-        }
-    }
-    return v;
-}
-
-// Merge the cnt (<= 32) buffered keys of this warp into its sorted list L; B is warp-private scratch.
-__device__ __forceinline__ uint64_t warp_flush(uint64_t* L, uint64_t* B, const uint64_t* buf, int cnt, int kp,
-                                               int lane) {
-    __syncwarp();
-    uint64_t v = lane < cnt ? buf[lane] : 0ull;
-    v = warp_sort_desc(v, lane);
-    B[lane] = v;
-    for (int j = 32 + lane; j < kp; j += 32) B[j] = 0ull;
-    __syncwarp();
-    warp_merge_desc(L, B, kp, lane);
-    return L[kp - 1];
-}
 
 // ---------------------------------------------------------------- per-row dot products from smem
 template <typename T>
@@ -220,50 +129,6 @@ __device__ __forceinline__ float group_dot(const uint8_t* const (&p)[kGroup], co
     return k;
 }
 
-template <typename T>
-__device__ __forceinline__ float elem_at(const uint8_t* row, int i) {
-    if constexpr (sizeof(T) == 4)
-        return reinterpret_cast<const float*>(row)[i];
-    else
-        return bf16_bits_to_f32(reinterpret_cast<const uint16_t*>(row)[i]);
-}
-
-// Sequential fp64 accumulation of fp32 products over one staged row (RagIndex.cs:127-133).
-// kind 0: sum q[i]*x[i]   kind 1: sum x[i]*x[i]   (row == nullptr: x := q, i.e. the query norm)
-// The additions form one dependent chain (that IS the reference's arithmetic): 8.1 cycles per DADD on
-// B200 (tools/ubench/fp64_lat.cu).  Loads, products and the fp32->fp64 conversions of a 4-element
-// block are independent of the chain and overlap with it; measured ~9 cycles per element.
-template <typename T>
-__device__ __forceinline__ double exact_chain(const uint8_t* row, bool f32row, const float* q, int dim, int kind) {
-    double acc = 0.0;  // :127
-    int i = 0;
-    for (; i + 4 <= dim; i += 4) {
-        float x[4];
-        if (row == nullptr) {
-#pragma unroll
-            for (int j = 0; j < 4; ++j) x[j] = q[i + j];
-        } else if (f32row) {
-            const float4 v = *reinterpret_cast<const float4*>(row + static_cast<size_t>(i) * 4);
-            x[0] = v.x, x[1] = v.y, x[2] = v.z, x[3] = v.w;
-        } else {
-            const uint2 v = *reinterpret_cast<const uint2*>(row + static_cast<size_t>(i) * 2);
-            x[0] = __uint_as_float(v.x << 16), x[1] = __uint_as_float(v.x & 0xFFFF0000u);
-            x[2] = __uint_as_float(v.y << 16), x[3] = __uint_as_float(v.y & 0xFFFF0000u);
-        }
-        float pr[4];
-#pragma unroll
-        for (int j = 0; j < 4; ++j) pr[j] = kind ? __fmul_rn(x[j], x[j]) : __fmul_rn(q[i + j], x[j]);  // :130-132
-#pragma unroll
-        for (int j = 0; j < 4; ++j) acc = __dadd_rn(acc, static_cast<double>(pr[j]));
-    }
-    for (; i < dim; ++i) {
-        const float x = row == nullptr ? q[i] : (f32row ? reinterpret_cast<const float*>(row)[i] : elem_at<T>(row, i));
-        const float pr = kind ? __fmul_rn(x, x) : __fmul_rn(q[i], x);
-        acc = __dadd_rn(acc, static_cast<double>(pr));
-    }
-    return acc;
-}
-
 // ---------------------------------------------------------------- the kernel
 template <typename T, int DV, bool FULL>
 __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanArgs a, const ScanLayout L) {
@@ -288,7 +153,7 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
     const uint8_t* mat = static_cast<const uint8_t*>(a.mat);
 
     if (tid == 0) {
-        if (blockIdx.x == 0) a.scratch.stamps[0] = globaltimer_ns();
+        if (blockIdx.x == 0) stamp(a, 0);
         for (int s = 0; s < n_stages; ++s) {
             mbar_init(full + s, 1);
             mbar_init(empty + s, 1);  // one consumer warp drains a tile
@@ -428,157 +293,17 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
     // Last CTA: grid-level merge, exact rescoring (RagIndex.cs:124-135), final order (:64-66)
     // =====================================================================================
     __threadfence();
-    if (tid == 0) a.scratch.stamps[1] = globaltimer_ns();
-    const uint32_t ring_bytes = L.n_stages * L.stage_bytes;  // idle now: reused as staging space
-    {
-        uint64_t* stage = reinterpret_cast<uint64_t*>(smem);
-        const int nlists = static_cast<int>(gridDim.x);
-        const int cap_lists = max(1, static_cast<int>(ring_bytes / (static_cast<uint32_t>(kp) * 8u)));
-        if (warp < kConsumerWarps) {
-            for (int j = lane; j < kp; j += 32) lists[warp * kp + j] = 0ull;
-        }
-        for (int l0 = 0; l0 < nlists; l0 += cap_lists) {
-            const int nl = min(cap_lists, nlists - l0);
-            const uint64_t* src = a.scratch.cta_lists + static_cast<size_t>(l0) * kp;
-            const int total = nl * kp;
-#pragma unroll 8
-            for (int i = tid; i < total; i += kScanThreads) stage[i] = __ldcg(src + i);  // all loads in flight
-            __syncthreads();
-            if (warp < kConsumerWarps)
-                for (int c = warp; c < nl; c += kConsumerWarps) warp_merge_desc(lists + warp * kp, stage + c * kp, kp, lane);
-            __syncthreads();
-        }
-        for (int w = 1; w < kConsumerWarps; w <<= 1) {
-            if (warp < kConsumerWarps && (warp % (2 * w)) == 0 && warp + w < kConsumerWarps)
-                warp_merge_desc(lists + warp * kp, lists + (warp + w) * kp, kp, lane);
-            __syncthreads();
-        }
-    }
-    // lists[0..kp) : the kp best approximate keys of the whole shard, descending
-    if (tid == 0) a.scratch.stamps[2] = globaltimer_ns();
-
-    const int n_cand = static_cast<int>(min(static_cast<int64_t>(kp), a.n_rows));
-    // Rows are staged in the (now idle) tile ring.  A row that was stored inexactly (normalised with
-    // scale != 1, or rounded to bf16) is rescored from its ORIGINAL fp32 values kept in the sidecar,
-    // so the fp64 score below is the reference's value for the row as it was added.
-    const uint32_t raw_bytes = a.raw_slot ? static_cast<uint32_t>(a.raw_ld) * 4u : 0u;
-    const uint32_t rs = max(L.row_bytes, raw_bytes) + 16;  // padded smem row stride: spreads rows over banks
-    const int cap = max(1, static_cast<int>(ring_bytes / rs));
-    uint8_t* rowbuf = smem;
-
-    for (int b0 = 0; b0 < n_cand; b0 += cap) {
-        const int nb = min(cap, n_cand - b0);
-        // stage: one bulk async copy per candidate row, all in flight at once, one mbarrier for the batch
-        if (warp == 0) {
-            fence_proxy_async();  // the ring was last touched through the generic proxy (list staging / previous batch)
-            uint64_t* sbar = reinterpret_cast<uint64_t*>(&misc->stage_bar);
-            uint32_t my_bytes = 0;
-            for (int c = lane; c < nb; c += 32) {
-                const uint32_t row = key_row(lists[b0 + c]);
-                const int32_t slot = a.raw_slot ? a.raw_slot[row] : -1;
-                my_bytes += slot >= 0 ? raw_bytes : L.row_bytes;
-            }
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) my_bytes += __shfl_xor_sync(0xffffffffu, my_bytes, o);
-            if (lane == 0) mbar_arrive_expect_tx(sbar, my_bytes);
-            __syncwarp();
-            for (int c = lane; c < nb; c += 32) {
-                const uint32_t row = key_row(lists[b0 + c]);
-                const int32_t slot = a.raw_slot ? a.raw_slot[row] : -1;
-                const void* src = slot >= 0 ? static_cast<const void*>(a.raw_rows + static_cast<size_t>(slot) * a.raw_ld)
-                                            : static_cast<const void*>(mat + static_cast<size_t>(row) * L.row_bytes);
-                bulk_g2s(rowbuf + static_cast<size_t>(c) * rs, src, slot >= 0 ? raw_bytes : L.row_bytes, sbar);
-                misc->raw_fmt[c] = slot >= 0 ? 1 : 0;
-            }
-        }
-        mbar_wait(reinterpret_cast<uint64_t*>(&misc->stage_bar), static_cast<uint32_t>(b0 / cap) & 1u);
-        __syncthreads();
-        if (tid == 0 && b0 == 0) a.scratch.stamps[3] = globaltimer_ns();
-        // chains: threads [0, nbp) run the dot products, [nbp, 2*nbp) the row norms, thread 2*nbp the query
-        // norm -- every warp runs one kind only, so the two kinds never serialise inside a warp
-        const int nbp = (nb + 31) & ~31;
-        const int nslots = 2 * nbp + (b0 == 0 ? 1 : 0);
-        for (int id = tid; id < nslots; id += kScanThreads) {
-            if (id == 2 * nbp) {
-                misc->na = exact_chain<T>(nullptr, true, qraw, a.dim, 1);  // :131
-            } else {
-                const int kind = id >= nbp ? 1 : 0;
-                const int c = id - kind * nbp;
-                if (c < nb) {
-                    const uint8_t* row = rowbuf + static_cast<size_t>(c) * rs;
-                    const bool f32row = (sizeof(T) == 4) || misc->raw_fmt[c];
-                    const double v = exact_chain<T>(row, f32row, qraw, a.dim, kind);
-                    if (kind)
-                        misc->nb[c] = v;  // :132
-                    else
-                        misc->dot[c] = v;  // :130
-                }
-            }
-        }
-        __syncthreads();
-        for (int c = tid; c < nb; c += kScanThreads) {
-            const double den = __dadd_rn(__dmul_rn(__dsqrt_rn(misc->na), __dsqrt_rn(misc->nb[c])), 1e-9);
-            misc->ex[b0 + c] = __ddiv_rn(misc->dot[c], den);  // :134
-        }
-        __syncthreads();
-    }
-
-    if (tid == 0) a.scratch.stamps[4] = globaltimer_ns();
-    // final order: (fp64 score desc with double.CompareTo semantics, row asc); rank by counting
-    for (int c = tid; c < n_cand; c += kScanThreads) {
-        const double sc = misc->ex[c];
-        const uint64_t kc = ord_f64(sc);
-        const uint32_t rc = key_row(lists[c]);
-        int rank = 0;
-        for (int u = 0; u < n_cand; ++u) {
-            const uint64_t ku = ord_f64(misc->ex[u]);
-            const uint32_t ru = key_row(lists[u]);
-            rank += (ku > kc) || (ku == kc && ru < rc);
-        }
-        const int64_t gid = a.row_base + static_cast<int64_t>(rc);
-        if (rank < a.k_take) {
-            if (a.out_idx) a.out_idx[rank] = gid;
-            if (a.out_score) a.out_score[rank] = sc;
-            if (a.exact && a.exact[rc] == 0 && !(a.raw_slot && a.raw_slot[rc] >= 0)) atomicAdd(&misc->inexact, 1);
-            if (rank == a.k_take - 1) misc->ek = sc;
-        }
-        if (a.out_cand && rank < a.cand_slots && rank < a.k_take) {
-            a.out_cand[rank].score = sc;
-            a.out_cand[rank].id = gid;
-        }
-    }
-    if (a.out_cand) {
-        for (int j = a.k_take + tid; j < a.cand_slots; j += kScanThreads) {
-            a.out_cand[j].score = -CUDART_INF;
-            a.out_cand[j].id = -1;
-        }
-    }
-    __syncthreads();
-    if (tid == 0) {
-        bool cert;
-        if (a.n_rows <= static_cast<int64_t>(kp)) {
-            cert = true;  // every row was rescored
-        } else {
-            // Rows outside the survivors have approximate score <= bound.  Their reference score is at
-            // most bound + eps, where eps covers the fp32 rounding of the scan AND the reference's
-            // "+1e-9" in the denominator (RagIndex.cs:134), which moves a score by at most
-            // 1e-9 / (|q| * smallest row norm) towards zero.
-            const double bound = static_cast<double>(key_score(lists[kp - 1]));
-            double shrink = 0.0;
-            if (a.min_norm_bits) {
-                const double d = sqrt(misc->na) * static_cast<double>(__uint_as_float(*a.min_norm_bits));
-                shrink = 1e-9 / d;  // +inf when the query is zero: then only a full rescore certifies
-            }
-            cert = misc->ek > bound + static_cast<double>(a.eps) + shrink;  // false if either side is NaN
-            if (misc->na == 0.0) cert = true;  // zero query: every reference score is exactly +0.0 (or NaN, ranked last)
-        }
-        int32_t flags = 0;
-        if (cert) flags |= RAGSTORE_HIT_CERTIFIED;
-        if (misc->inexact == 0) flags |= RAGSTORE_HIT_EXACT_ROWS;
-        if (a.out_flags) *a.out_flags = flags;
-        if (a.out_found) *a.out_found = a.k_take;
-        a.scratch.stamps[5] = globaltimer_ns();
-    }
+    if (tid == 0) stamp(a, 1);
+    FinalizeCtx f;
+    f.ring = smem;
+    f.ring_bytes = L.n_stages * L.stage_bytes;  // the tile ring is idle now: reused as staging space
+    f.row_bytes = L.row_bytes;
+    f.lists = lists;
+    f.misc = misc;
+    f.qraw = qraw;
+    f.glists = a.scratch.cta_lists;
+    f.nlists = static_cast<int>(gridDim.x);
+    finalize_candidates<T>(a, f);
 }
 
 // ---------------------------------------------------------------- host side

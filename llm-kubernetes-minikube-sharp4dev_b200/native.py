@@ -137,10 +137,10 @@ class RagStore:
         check(lib().ragstore_set_row_base(self._h, base))
 
     def info(self) -> dict:
-        v = (C.c_int64 * 12)()
-        check(lib().ragstore_info(self._h, v, 12))
+        v = (C.c_int64 * 14)()
+        check(lib().ragstore_info(self._h, v, 14))
         keys = ["dim", "ld", "dtype", "count", "capacity", "n_inexact_rows", "device", "sm_count",
-                "has_sidecar", "sidecar_rows", "matrix_bytes_mapped", "uses_vmm"]
+                "has_sidecar", "sidecar_rows", "matrix_bytes_mapped", "uses_vmm", "scan_launches", "batch_launches"]
         return dict(zip(keys, list(v)))
 
     def debug_stamps(self):

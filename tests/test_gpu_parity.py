@@ -256,3 +256,55 @@ def test_row_sharded_search_on_one_gpu(n, k, dtype):
     assert np.array_equal(d_sc[:f].cpu().numpy().view(np.uint64), esc.view(np.uint64))
     for st in stores:
         st.close()
+
+
+@pytest.mark.parametrize("n,d,nq,k", [(20000, 768, 16, 10), (20000, 1024, 100, 10), (30000, 1000, 256, 5), (12345, 256, 300, 10), (5000, 64, 129, 6)])
+def test_batched_queries_tensor_core_path(n, d, nq, k):
+    """>= 16 queries in one call go through the tcgen05 GEMM kernel (tf32) + exact rescoring; the hits must still be
+    the reference's: identical indices and bit-identical fp64 scores (tf32 only nominates candidates)."""
+    rows = oc.synth_rows(0, n, d, 1234)
+    qs = oc.synth_rows(0, nq, d, 5678)
+    with rb.RagStore(d, n) as st:
+        st.add(rows)
+        idx, sc, found, flags = st.search(qs, k)
+        info = st.info()
+    assert info["batch_launches"] >= (nq + 255) // 256          # the tensor-core path really ran
+    for i in range(nq):
+        eidx, esc = oc.query(rows, qs[i], k, n_threads=4)
+        assert list(idx[i, :found[i]]) == list(eidx), i
+        assert np.array_equal(sc[i, :found[i]].view(np.uint64), esc.view(np.uint64)), i
+        assert flags[i] & rb.RAGSTORE_HIT_CERTIFIED
+    # most queries must be certified by the tf32 pass itself (few fp32 rescans)
+    assert info["scan_launches"] <= max(2, nq // 4)
+
+
+def test_batched_device_search_matches_single_query_path():
+    import torch
+    from ragstore_b200 import native
+    n, d, nq, k = 50000, 768, 64, 10
+    with rb.RagStore(d, n) as st:
+        buf = torch.empty((n, d), dtype=torch.float32, device="cuda")
+        native.synth_fill_device(buf, 0, n, d, d, 99)
+        torch.cuda.synchronize()
+        st.add_device(buf, n, d)
+        qs = torch.empty((nq, d), dtype=torch.float32, device="cuda")
+        native.synth_fill_device(qs, 0, nq, d, d, 77)
+        stream = torch.cuda.Stream()
+        out = []
+        for batch in (True, False):
+            idx = torch.zeros((nq, k), dtype=torch.int64, device="cuda")
+            sc = torch.zeros((nq, k), dtype=torch.float64, device="cuda")
+            fnd = torch.zeros(nq, dtype=torch.int32, device="cuda")
+            flg = torch.zeros(nq, dtype=torch.int32, device="cuda")
+            torch.cuda.synchronize()
+            if batch:
+                st.search_device(qs, nq, k, idx, sc, fnd, flg, stream=stream.cuda_stream)
+            else:
+                for i in range(nq):
+                    st.search_device(qs[i], 1, k, idx[i], sc[i], fnd[i:], flg[i:], stream=stream.cuda_stream)
+            stream.synchronize()
+            out.append((idx.cpu().numpy(), sc.cpu().numpy(), flg.cpu().numpy()))
+        cert = (out[0][2] & rb.RAGSTORE_HIT_CERTIFIED) != 0
+        assert cert.mean() > 0.9
+        assert np.array_equal(out[0][0][cert], out[1][0][cert])
+        assert np.array_equal(out[0][1][cert].view(np.uint64), out[1][1][cert].view(np.uint64))
