@@ -34,6 +34,7 @@ constexpr int kBKBytes = 128;       // bytes of K per ring stage row = one 128B 
 constexpr int kBatchThreads = 384;
 constexpr int kEpiWarp0 = 4;        // first epilogue warp
 constexpr int kBatchKp = 32;        // candidates kept per query and CTA
+constexpr int kCluster = 2;         // CTAs that share (multicast) the query operand
 constexpr uint32_t kOperandBytes = 128 * kBKBytes;  // one 128-row operand slice: 16 KB
 
 struct BatchLayout {
@@ -48,6 +49,24 @@ __device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* m
             smem_u32(smem_dst)),
         "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
         : "memory");
+}
+// same, delivered to the same shared-memory offset (and mbarrier offset) of every CTA in cta_mask
+__device__ __forceinline__ void tma_load_2d_mc(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1,
+                                               uint16_t cta_mask) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster"
+        " [%0], [%1, {%4, %5}], [%2], %3;" ::"r"(smem_u32(smem_dst)),
+        "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "h"(cta_mask), "r"(c0), "r"(c1)
+        : "memory");
+}
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(map)) : "memory");
@@ -65,6 +84,13 @@ __device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t cols) {
 // arrives on the mbarrier once every tcgen05.mma issued so far by this thread has completed
 __device__ __forceinline__ void tc_commit(uint64_t* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+                 : "memory");
+}
+// the same arrival on the barrier at this offset in every CTA of cta_mask
+__device__ __forceinline__ void tc_commit_mc(uint64_t* bar, uint16_t cta_mask) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
+                     smem_u32(bar)),
+                 "h"(cta_mask)
                  : "memory");
 }
 // D[tmem] (+)= A[smem] * B[smem]^T, tf32 inputs, fp32 accumulate
@@ -114,25 +140,35 @@ struct BatchArgs {
     uint64_t* glists;  // [nq][n_ctas][kBatchKp] candidate keys, written by this kernel
 };
 
-// Thread-private insertion into the query's sorted candidate list (lists[pos][query]); returns the new
-// threshold: the score of the last entry once the list is full, -inf before.  Kept out of line: it runs
-// O(k log N) times per query over the whole scan, while the compare that guards it runs N times.
-__device__ __noinline__ float list_insert(uint64_t* lists, int NQ, int q, float sc, uint32_t row) {
+// Thread-private candidate list of a query: kBatchKp keys in shared memory (lists[pos][query]), kept
+// UNSORTED with the position of the current minimum tracked in a register.  An insert overwrites the
+// minimum and rescans the 32 slots for the new one (independent loads; ~100 cycles) instead of shifting
+// a sorted list (a dependent load-compare-store chain per slot).  state = (count << 8) | min_pos.
+// Returns (threshold bits << 32) | new state; the threshold stays -inf until the list is full.
+__device__ __noinline__ uint64_t list_insert(uint64_t* lists, int NQ, int q, float sc, uint32_t row, uint32_t state) {
     const uint64_t key = make_key(sc + 0.0f, row);
-    int p = kBatchKp - 1;
-    while (p > 0) {
-        const uint64_t up = lists[(p - 1) * NQ + q];
-        if (up >= key) break;
-        lists[p * NQ + q] = up;
-        --p;
+    uint32_t cnt = state >> 8, minpos = state & 0xFFu;
+    if (cnt < kBatchKp) {
+        lists[cnt * NQ + q] = key;
+        ++cnt;
+        if (cnt < kBatchKp) return (static_cast<uint64_t>(__float_as_uint(-CUDART_INF_F)) << 32) | (cnt << 8);
+    } else {
+        lists[minpos * NQ + q] = key;
     }
-    lists[p * NQ + q] = key;
-    const uint64_t last = lists[(kBatchKp - 1) * NQ + q];
-    return last ? key_score(last) : -CUDART_INF_F;
+    uint64_t best = ~0ull;
+#pragma unroll
+    for (int p = 0; p < kBatchKp; ++p) {
+        const uint64_t v = lists[p * NQ + q];
+        if (v < best) {
+            best = v;
+            minpos = p;
+        }
+    }
+    return (static_cast<uint64_t>(__float_as_uint(key_score(best))) << 32) | (cnt << 8) | minpos;
 }
 
 // ---------------------------------------------------------------- the tensor-core kernel
-__global__ void __launch_bounds__(kBatchThreads, 1)
+__global__ void __cluster_dims__(kCluster, 1, 1) __launch_bounds__(kBatchThreads, 1)
 batch_score_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_c,
                    const BatchArgs a, const BatchLayout L) {
     extern __shared__ uint8_t smem_raw[];
@@ -148,13 +184,21 @@ batch_score_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
     uint64_t* lists = reinterpret_cast<uint64_t*>(smem + L.off_lists);  // [pos][query] : conflict-free across lanes
     const int NQ = kBM * a.mblocks;
 
+    // Clusters of kCluster CTAs walk the corpus together: in round `it` cluster c takes tiles
+    // (c + it * n_clusters) * kCluster + rank.  The CTAs of a cluster need the SAME query slices at the
+    // same time, so each loads 1/kCluster of a slice and multicasts it to all of them: query traffic
+    // out of L2 drops by kCluster.  A CTA whose tile lies past the end scores zero rows (TMA zero fill).
+    const uint32_t crank = cluster_ctarank();
     const int64_t n_tiles = (a.n_rows + kBN - 1) / kBN;
-    const int64_t my_tiles = n_tiles > blockIdx.x ? (n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+    const int64_t n_clusters = gridDim.x / kCluster, cluster_id = blockIdx.x / kCluster;
+    const int64_t n_groups = (n_tiles + kCluster - 1) / kCluster;
+    const int64_t my_tiles = n_groups > cluster_id ? (n_groups - cluster_id + n_clusters - 1) / n_clusters : 0;
+    const uint16_t cmask = static_cast<uint16_t>((1u << kCluster) - 1u);
 
     if (tid == 0) {
         for (int s = 0; s < n_stages; ++s) {
             mbar_init(full + s, 1);
-            mbar_init(empty + s, 1);
+            mbar_init(empty + s, kCluster);  // every CTA of the cluster must be done with the stage
         }
         for (int s = 0; s < 2; ++s) {
             mbar_init(tmem_full + s, 1);
@@ -166,6 +210,7 @@ batch_score_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
     for (int i = tid; i < kBatchKp * NQ; i += kBatchThreads) lists[i] = 0ull;
     tc_fence_before();
     __syncthreads();
+    cluster_sync_all();  // peers' barriers are initialised before anything is multicast at them
     tc_fence_after();
     const uint32_t tmem_base = *tmem_ptr;
 
@@ -177,13 +222,15 @@ batch_score_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
             int s = 0;
             uint32_t ph = 0;
             const uint32_t tx = (static_cast<uint32_t>(a.mblocks) + 1u) * kOperandBytes;
+            const int q_rows = NQ / kCluster;                       // this CTA's share of the query slice
+            const uint32_t q_off = crank * static_cast<uint32_t>(q_rows) * kBKBytes;
             for (int64_t it = 0; it < my_tiles; ++it) {
-                const int row0 = static_cast<int>((blockIdx.x + it * gridDim.x) * kBN);
+                const int row0 = static_cast<int>(((cluster_id + it * n_clusters) * kCluster + crank) * kBN);
                 for (int kb = 0; kb < a.nkb; ++kb) {
                     mbar_wait(empty + s, ph ^ 1u);
                     uint8_t* st = smem + static_cast<size_t>(s) * L.stage_bytes;
                     mbar_arrive_expect_tx(full + s, tx);
-                    for (int m = 0; m < a.mblocks; ++m) tma_load_2d(st + m * kOperandBytes, &tmap_q, full + s, kb * 32, m * kBM);
+                    tma_load_2d_mc(st + q_off, &tmap_q, full + s, kb * 32, static_cast<int>(crank) * q_rows, cmask);
                     tma_load_2d(st + a.mblocks * kOperandBytes, &tmap_c, full + s, kb * 32, row0);
                     if (++s == n_stages) {
                         s = 0;
@@ -215,7 +262,7 @@ batch_score_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
                             mma_tf32(tmem_base + as * 256u + m * 128u, adesc, bdesc, kIdescTf32, (kb | k4) != 0);
                         }
                     }
-                    tc_commit(empty + s);  // ring stage reusable once these MMAs have read it
+                    tc_commit_mc(empty + s, cmask);  // stage reusable (here and in the peers) once these MMAs have read it
                     if (++s == n_stages) {
                         s = 0;
                         ph ^= 1u;
@@ -232,12 +279,13 @@ batch_score_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
         const bool live = q < a.nq;
         const uint32_t lane_base = static_cast<uint32_t>((warp & 3) * 32) << 16;  // TMEM lanes this warp may read
         float thr = -CUDART_INF_F;
+        uint32_t lstate = 0;
         if (mblock < a.mblocks) {
             for (int64_t it = 0; it < my_tiles; ++it) {
                 const uint32_t as = static_cast<uint32_t>(it & 1), aph = static_cast<uint32_t>((it >> 1) & 1);
                 mbar_wait(tmem_full + as, aph);
                 tc_fence_after();
-                const int64_t row0 = (blockIdx.x + it * gridDim.x) * kBN;
+                const int64_t row0 = ((cluster_id + it * n_clusters) * kCluster + crank) * kBN;
                 const int nvalid = static_cast<int>(min(static_cast<int64_t>(kBN), a.n_rows - row0));
                 for (int c0 = 0; c0 < kBN; c0 += 32) {
                     uint32_t v[32];
@@ -246,8 +294,11 @@ batch_score_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
 #pragma unroll
                         for (int j = 0; j < 32; ++j) {
                             const float sc = __uint_as_float(v[j]);
-                            if (sc > thr && c0 + j < nvalid)  // rows ascend, so equal scores never displace
-                                thr = list_insert(lists, NQ, q, sc, static_cast<uint32_t>(row0 + c0 + j));
+                            if (sc > thr && c0 + j < nvalid) {  // rows ascend, so equal scores never displace
+                                const uint64_t r = list_insert(lists, NQ, q, sc, static_cast<uint32_t>(row0 + c0 + j), lstate);
+                                lstate = static_cast<uint32_t>(r);
+                                thr = __uint_as_float(static_cast<uint32_t>(r >> 32));
+                            }
                         }
                     }
                 }
@@ -256,8 +307,19 @@ batch_score_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
                 if (lane == 0) mbar_arrive(tmem_empty + as);
             }
         }
-        // publish this CTA's list of the query: glists[q][cta][pos]
+        // sort the (thread-private) list descending, then publish it: glists[q][cta][pos]
         if (live) {
+            for (int i = 1; i < kBatchKp; ++i) {
+                const uint64_t key = lists[i * NQ + q];
+                int p = i;
+                while (p > 0) {
+                    const uint64_t up = lists[(p - 1) * NQ + q];
+                    if (up >= key) break;
+                    lists[p * NQ + q] = up;
+                    --p;
+                }
+                lists[p * NQ + q] = key;
+            }
             uint64_t* g = a.glists + (static_cast<size_t>(q) * gridDim.x + blockIdx.x) * kBatchKp;
 #pragma unroll 4
             for (int p = 0; p < kBatchKp; ++p) g[p] = lists[p * NQ + q];
@@ -265,6 +327,7 @@ batch_score_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
     }
     tc_fence_before();
     __syncthreads();
+    cluster_sync_all();  // no CTA leaves while a peer may still multicast into it
     if (warp == 2) {
         tc_fence_after();
         tmem_dealloc(tmem_base, 512);
@@ -352,12 +415,12 @@ static PFN_encodeTiled encode_fn() {
     return fn;
 }
 
-static bool make_map_f32(CUtensorMap* m, const void* base, uint64_t rows, uint64_t ld) {
+static bool make_map_f32(CUtensorMap* m, const void* base, uint64_t rows, uint64_t ld, uint32_t box_rows) {
     PFN_encodeTiled enc = encode_fn();
     if (!enc) return false;
     const cuuint64_t dims[2] = {ld, rows};
     const cuuint64_t strides[1] = {ld * 4};
-    const cuuint32_t box[2] = {32, 128};
+    const cuuint32_t box[2] = {32, box_rows};
     const cuuint32_t estr[2] = {1, 1};
     return enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(base), dims, strides, box, estr,
                CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
@@ -372,7 +435,7 @@ size_t batch_scratch_bytes(int sm_count) {
 int launch_batch_search(const BatchSearchArgs& b, cudaStream_t stream) {
     const ScanArgs& s = b.scan;
     if (s.dtype != RAGSTORE_F32 || b.nq < 1 || b.nq > kBatchMaxQ || s.ld > kBatchMaxLd || s.kp != kBatchKp ||
-        s.n_rows < 1 || s.n_rows >= 0x7FFFFFFFll)
+        s.n_rows < 1 || s.n_rows >= 0x7FFF0000ll)
         return static_cast<int>(cudaErrorInvalidValue);
     const int mblocks = b.nq > kBM ? 2 : 1;
     const int nq_pad = mblocks * kBM;
@@ -384,8 +447,8 @@ int launch_batch_search(const BatchSearchArgs& b, cudaStream_t stream) {
     if (e != cudaSuccess) return static_cast<int>(e);
 
     CUtensorMap map_q, map_c;
-    if (!make_map_f32(&map_q, qhat, static_cast<uint64_t>(nq_pad), static_cast<uint64_t>(s.ld)) ||
-        !make_map_f32(&map_c, s.mat, static_cast<uint64_t>(s.n_rows), static_cast<uint64_t>(s.ld)))
+    if (!make_map_f32(&map_q, qhat, static_cast<uint64_t>(nq_pad), static_cast<uint64_t>(s.ld), nq_pad / kCluster) ||
+        !make_map_f32(&map_c, s.mat, static_cast<uint64_t>(s.n_rows), static_cast<uint64_t>(s.ld), kBN))
         return static_cast<int>(cudaErrorNotSupported);
 
     BatchLayout L;
@@ -408,7 +471,9 @@ int launch_batch_search(const BatchSearchArgs& b, cudaStream_t stream) {
     a.nkb = (s.ld + 31) / 32;
     a.glists = glists;
     const int64_t n_tiles = (s.n_rows + kBN - 1) / kBN;
-    const int grid = static_cast<int>(n_tiles < s.sm_count ? n_tiles : s.sm_count);
+    int grid = static_cast<int>(n_tiles < s.sm_count ? n_tiles : s.sm_count);
+    grid = (grid + kCluster - 1) / kCluster * kCluster;          // whole clusters
+    if (grid > s.sm_count) grid = s.sm_count / kCluster * kCluster;
     e = cudaFuncSetAttribute(batch_score_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     if (e != cudaSuccess) return static_cast<int>(e);
     batch_score_kernel<<<grid, kBatchThreads, L.total, stream>>>(map_q, map_c, a, L);
