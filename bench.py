@@ -11,6 +11,7 @@ Workloads (BASELINE.json configs):
   config2   1M  x 768 fp32, top-10      <- default at N = 1 (configs[1], the one `metric` is quoted on)
   target10m 10M x 768 fp32, top-10      (north_star target; also measured as `extra.target10m` by default)
   config4   bf16 x 768, top-100, 12.5M rows per GPU (100M over 8), NCCL all-gather merge
+  config3   10M x 1024 fp32, 256 queries per step, top-10: the tcgen05/TMEM tf32 GEMM path (single GPU)
 N > 1 runs the chosen workload row-sharded with the per-GPU shard size fixed (weak scaling).
 
 value   = corpus vectors scanned per second, whole job, inputs resident in HBM when the clock starts
@@ -35,7 +36,9 @@ WORKLOADS = {
     "config2": (1_000_000, 768, "f32", 10, "1M x 768 fp32 corpus, single query, top-10"),
     "target10m": (10_000_000, 768, "f32", 10, "10M x 768 fp32 corpus, single query, top-10 (north_star target)"),
     "config4": (12_500_000, 768, "bf16", 100, "100M x 768 bf16 row-sharded over 8 (12.5M rows per GPU), single query, top-100"),
+    "config3": (10_000_000, 1024, "f32", 10, "10M x 1024 fp32 corpus, batched 256 queries, top-10 (tcgen05 tf32 GEMM + exact rescoring)"),
 }
+BATCH_QUERIES = {"config3": 256}   # queries per step for the batched (tensor-core) workloads
 CORPUS_SEED, QUERY_SEED = 1234, 5678
 
 
@@ -186,7 +189,21 @@ def measure_workload(name, args, torch, dist, rb, native, rank, world, dev, do_e
         d_found = torch.zeros(1, dtype=torch.int32, device="cuda")
         d_flags = torch.zeros(1, dtype=torch.int32, device="cuda")
         qi = [0]
-        if world == 1:
+        nqb = BATCH_QUERIES.get(name, 1)
+        if world == 1 and nqb > 1:
+            n_q = nqb
+            d_q = torch.empty((n_q, dim), dtype=torch.float32, device="cuda")
+            native.synth_fill_device(d_q, 0, n_q, dim, dim, QUERY_SEED, device=dev, stream=ts.cuda_stream)
+            d_idx = torch.zeros((nqb, k), dtype=torch.int64, device="cuda")
+            d_score = torch.zeros((nqb, k), dtype=torch.float64, device="cuda")
+            d_found = torch.zeros(nqb, dtype=torch.int32, device="cuda")
+            d_flags = torch.zeros(nqb, dtype=torch.int32, device="cuda")
+
+            def step():
+                qi[0] += 1
+                st.search_device(d_q, nqb, k, d_idx, d_score, d_found, d_flags, stream=ts.cuda_stream)
+            launches_per_step = 3      # normalise queries, tcgen05 scoring, per-query finalize
+        elif world == 1:
             def step():
                 q = d_q[qi[0] % n_q]
                 qi[0] += 1
@@ -209,7 +226,10 @@ def measure_workload(name, args, torch, dist, rb, native, rank, world, dev, do_e
         res = {"ms_per_step": ms / args.steps, "value": total_rows * args.steps / (ms * 1e-3), "clocks": clocks,
                "ingest_vectors_per_s": rows / ingest_s, "launches_per_step": launches_per_step,
                "rows_per_gpu": rows, "dim": dim, "top_k": k, "storage": dtype, "desc": desc}
-        res["queries_per_s"] = args.steps / (ms * 1e-3)
+        res["queries_per_s"] = nqb * args.steps / (ms * 1e-3)
+        res["queries_per_step"] = nqb
+        if nqb > 1:
+            res["tensor_tflops"] = 2.0 * nqb * rows * dim * args.steps / (ms * 1e-3) / 1e12
         # dominant kernel: the fused scan; at world == 1 a step IS one launch of it
         if world == 1:
             kern_ms = ms / args.steps
@@ -221,23 +241,26 @@ def measure_workload(name, args, torch, dist, rb, native, rank, world, dev, do_e
         res["achieved_gbs"] = rows * dim * esz / (kern_ms * 1e-3) / 1e9
         last_q_index = (qi[0] - 1) % n_q
         torch.cuda.synchronize()
-        res["flags"] = int(d_flags.item())
-        res["top_idx"] = [int(x) for x in d_idx.cpu().tolist()]
-        res["top_score"] = [float(x) for x in d_score.cpu().tolist()]
+        res["flags"] = int(d_flags.flatten()[0].item())
+        res["certified_fraction"] = float(((d_flags & 1) != 0).float().mean().item())
+        res["top_idx"] = [int(x) for x in d_idx.reshape(-1, k)[0].cpu().tolist()]
+        res["top_score"] = [float(x) for x in d_score.reshape(-1, k)[0].cpu().tolist()]
         res["last_query_index"] = last_q_index
 
     # e2e: the call the C# RagIndex makes -- host query in, host hits out, synchronous
     if do_e2e and world == 1:
         hq = d_q.cpu().numpy()
+        hq_step = (lambda i: hq) if nqb > 1 else (lambda i: hq[i % n_q])
         for i in range(max(3, args.warmup // 4)):
-            st.search(hq[i % n_q], k)
-        n_e2e = max(20, args.steps // 4)
+            st.search(hq_step(i), k)
+        n_e2e = max(5, args.steps // 4)
         t0 = time.perf_counter()
         for i in range(n_e2e):
-            idx, sc, found, flags = st.search(hq[i % n_q], k)
+            idx, sc, found, flags = st.search(hq_step(i), k)
         dt = time.perf_counter() - t0
-        res["e2e"] = {"value": rows * n_e2e / dt, "unit": "vectors/s", "h2d_bytes_per_step": dim * 4,
-                      "d2h_bytes_per_step": 256 * 16 + 8, "ms_per_step": dt / n_e2e * 1e3, "steps": n_e2e,
+        res["e2e"] = {"value": rows * n_e2e / dt, "unit": "vectors/s", "h2d_bytes_per_step": nqb * dim * 4,
+                      "d2h_bytes_per_step": nqb * (256 * 16 + 8), "ms_per_step": dt / n_e2e * 1e3, "steps": n_e2e,
+                      "queries_per_s": nqb * n_e2e / dt,
                       "api": "ragstore_search (C ABI, host buffers, synchronous)"}
     elif do_e2e:
         # sharded: host query -> every rank's device, hits back to the host on every rank
@@ -275,7 +298,7 @@ def measure_workload(name, args, torch, dist, rb, native, rank, world, dev, do_e
         from oracle import oracle_c as oc
         sample_rows = min(rows, 1_000_000)
         corpus = oc.synth_rows(0, sample_rows, dim, CORPUS_SEED, round_bf16=(dtype == "bf16"))
-        q = oc.synth_rows(res["last_query_index"], 1, dim, QUERY_SEED)[0]
+        q = oc.synth_rows(0 if nqb > 1 else res["last_query_index"], 1, dim, QUERY_SEED)[0]
         reps, t_used = 0, 0.0
         while t_used < 8.0 and reps < 50:
             t0 = time.perf_counter()
@@ -358,7 +381,8 @@ def main():
             except Exception:
                 traffic = None
         out = {
-            "metric": "corpus vectors scanned/sec (single query, top-k)", "value": r["value"], "unit": "vectors/s",
+            "metric": "corpus vectors scanned/sec (single query, top-k)" if r.get("queries_per_step", 1) == 1 else "corpus vectors scanned/sec (per sweep of a 256-query batch, top-k)",
+            "value": r["value"], "unit": "vectors/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_per_step"],
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32" if r["storage"] == "f32" else "bf16 storage, f32 accumulate", "data": "synthetic",
@@ -369,8 +393,12 @@ def main():
                        "rescoring": "exact fp64 (reference arithmetic) for k' >= k candidates inside the same launch"},
             "roofline": {"bound": "hbm", "achieved": r["achieved_gbs"], "peak": peak, "unit": "GB/s", "frac": r["achieved_gbs"] / peak,
                          "traffic": traffic, "peak_source": peak_src, "frac_of_8TBs_spec": r["achieved_gbs"] / 8000.0,
-                         "kernel": "scan_topk_kernel", "kernel_ms": r["kernel_ms"],
+                         "kernel": "batch_score_kernel (+prep, +finalize; whole step timed)" if r.get("queries_per_step", 1) > 1 else "scan_topk_kernel",
+                         "kernel_ms": r["kernel_ms"],
                          "algorithmic_bytes_per_launch": r["rows_per_gpu"] * r["dim"] * (4 if r["storage"] == "f32" else 2)},
+            "tensor": ({"achieved_tflops": r["tensor_tflops"], "kind": "tf32 (tcgen05.mma kind::tf32, fp32 accumulate in TMEM)",
+                        "peak_tflops_bf16_measured": 1625.3, "frac_of_half_bf16_measured": r["tensor_tflops"] / (1625.3 / 2),
+                        "certified_fraction": r.get("certified_fraction")} if "tensor_tflops" in r else None),
             "cpu_baseline": r.get("cpu_baseline"),
             "e2e": {k: v for k, v in r.get("e2e", {}).items()} if "e2e" in r else None,
             "gpu_launches": args.steps * r["launches_per_step"],

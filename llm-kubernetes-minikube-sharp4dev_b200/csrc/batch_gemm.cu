@@ -24,12 +24,14 @@
 // fp32 scan kernel (host side, ragstore_api.cu).
 #include <cuda.h>
 
+#include <cstdlib>
+
 #include "topk_device.cuh"
 
 namespace rag {
 
 constexpr int kBM = 128;            // queries per MMA (M)
-constexpr int kBN = 128;            // corpus rows per tile (N)
+constexpr int kBN = 256;            // corpus rows per tile (MMA N)
 constexpr int kBKBytes = 128;       // bytes of K per ring stage row = one 128B swizzle atom row
 constexpr int kBatchThreads = 384;
 constexpr int kEpiWarp0 = 4;        // first epilogue warp
@@ -58,6 +60,12 @@ __device__ __forceinline__ void tma_load_2d_mc(void* smem_dst, const CUtensorMap
         " [%0], [%1, {%4, %5}], [%2], %3;" ::"r"(smem_u32(smem_dst)),
         "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "h"(cta_mask), "r"(c0), "r"(c1)
         : "memory");
+}
+// L2 prefetch of a tensor box (no shared-memory destination): decouples DRAM latency from the ring
+__device__ __forceinline__ void tma_prefetch_2d(const CUtensorMap* map, int c0, int c1) {
+    asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global [%0, {%1, %2}];" ::"l"(reinterpret_cast<uint64_t>(map)), "r"(c0),
+                 "r"(c1)
+                 : "memory");
 }
 __device__ __forceinline__ uint32_t cluster_ctarank() {
     uint32_t r;
@@ -138,36 +146,60 @@ struct BatchArgs {
     int mblocks;       // 1 or 2 blocks of 128 queries
     int nkb;           // k-blocks of 32 fp32 per row
     uint64_t* glists;  // [nq][n_ctas][kBatchKp] candidate keys, written by this kernel
+    int debug;         // profiling experiments: 1 = epilogue drains without scanning, 2 = no MMA issue
 };
 
-// Thread-private candidate list of a query: kBatchKp keys in shared memory (lists[pos][query]), kept
-// UNSORTED with the position of the current minimum tracked in a register.  An insert overwrites the
-// minimum and rescans the 32 slots for the new one (independent loads; ~100 cycles) instead of shifting
-// a sorted list (a dependent load-compare-store chain per slot).  state = (count << 8) | min_pos.
-// Returns (threshold bits << 32) | new state; the threshold stays -inf until the list is full.
-__device__ __noinline__ uint64_t list_insert(uint64_t* lists, int NQ, int q, float sc, uint32_t row, uint32_t state) {
-    const uint64_t key = make_key(sc + 0.0f, row);
-    uint32_t cnt = state >> 8, minpos = state & 0xFFu;
-    if (cnt < kBatchKp) {
-        lists[cnt * NQ + q] = key;
-        ++cnt;
-        if (cnt < kBatchKp) return (static_cast<uint64_t>(__float_as_uint(-CUDART_INF_F)) << 32) | (cnt << 8);
-    } else {
-        lists[minpos * NQ + q] = key;
-    }
-    uint64_t best = ~0ull;
+// ---------------------------------------------------------------- thread-private candidate lists
+// A TMEM lane (= epilogue thread) carries one query, so its running top-32 is private to the thread:
+// the 32 approximate scores live in REGISTERS (unsorted, -inf = empty), the matching row ids in shared
+// memory (rows[slot][query]).  An insert overwrites the current minimum and re-finds the minimum with a
+// compare tree -- no atomics, no shared-memory traffic on the hot compare path, no overflow.  Which of
+// several EQUAL minimum scores is evicted is arbitrary; that can only matter for rows tied with the
+// worst survivor, a case the certificate (bound + eps < k-th exact score) rejects, so such a query is
+// redone by the fp32 scan kernel.
+struct ArgMin {
+    float v;
+    int i;
+};
+__device__ __forceinline__ ArgMin amin(const ArgMin& a, const ArgMin& b) { return b.v < a.v ? b : a; }
+
+__device__ __forceinline__ void list_insert(float (&S)[kBatchKp], int& minpos, float& thr, uint32_t* rows, int NQ, int q,
+                                            float sc, uint32_t row) {
 #pragma unroll
-    for (int p = 0; p < kBatchKp; ++p) {
-        const uint64_t v = lists[p * NQ + q];
-        if (v < best) {
-            best = v;
-            minpos = p;
-        }
-    }
-    return (static_cast<uint64_t>(__float_as_uint(key_score(best))) << 32) | (cnt << 8) | minpos;
+    for (int p = 0; p < kBatchKp; ++p) S[p] = (p == minpos) ? sc : S[p];
+    rows[minpos * NQ + q] = row;
+    ArgMin t16[16], t8[8], t4[4], t2[2];
+#pragma unroll
+    for (int p = 0; p < 16; ++p) t16[p] = amin(ArgMin{S[2 * p], 2 * p}, ArgMin{S[2 * p + 1], 2 * p + 1});
+#pragma unroll
+    for (int p = 0; p < 8; ++p) t8[p] = amin(t16[2 * p], t16[2 * p + 1]);
+#pragma unroll
+    for (int p = 0; p < 4; ++p) t4[p] = amin(t8[2 * p], t8[2 * p + 1]);
+#pragma unroll
+    for (int p = 0; p < 2; ++p) t2[p] = amin(t4[2 * p], t4[2 * p + 1]);
+    const ArgMin m = amin(t2[0], t2[1]);
+    minpos = m.i;
+    thr = m.v;
+}
+
+__device__ __forceinline__ void tmem_ld_32x16(uint32_t taddr, uint32_t (&v)[16]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+          "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+        : "r"(taddr)
+        : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
 // ---------------------------------------------------------------- the tensor-core kernel
+// MB = blocks of 128 queries (1 or 2).  Tile = 256 corpus rows: one MMA is M=128 (queries) x N=256 (rows),
+// so MB = 1 double-buffers its accumulator (2 x 256 TMEM columns) while MB = 2 uses all 512 columns for
+// one tile.  Per ring stage a CTA ingests 32 KB of corpus + MB x 16 KB of queries: the L2->SM ingest per
+// corpus byte (1.5x / 2x) is what bounds this kernel (measured ~46 B/clk/SM for 128-byte TMA rows), which
+// is why the tile is as tall as TMEM allows.
+template <int MB>
 __global__ void __cluster_dims__(kCluster, 1, 1) __launch_bounds__(kBatchThreads, 1)
 batch_score_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_c,
                    const BatchArgs a, const BatchLayout L) {
@@ -176,18 +208,19 @@ batch_score_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
     uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int n_stages = static_cast<int>(L.n_stages);
+    constexpr int AS = MB == 1 ? 2 : 1;       // accumulator stages
+    constexpr int NQ = kBM * MB;
     uint64_t* full = reinterpret_cast<uint64_t*>(smem + L.off_bars);
     uint64_t* empty = full + n_stages;
-    uint64_t* tmem_full = empty + n_stages;   // [2]
-    uint64_t* tmem_empty = tmem_full + 2;     // [2]
+    uint64_t* tmem_full = empty + n_stages;   // [AS]
+    uint64_t* tmem_empty = tmem_full + 2;     // [AS]
     uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(smem + L.off_tmem);
-    uint64_t* lists = reinterpret_cast<uint64_t*>(smem + L.off_lists);  // [pos][query] : conflict-free across lanes
-    const int NQ = kBM * a.mblocks;
+    uint32_t* rows = reinterpret_cast<uint32_t*>(smem + L.off_lists);  // [slot][query]
 
     // Clusters of kCluster CTAs walk the corpus together: in round `it` cluster c takes tiles
     // (c + it * n_clusters) * kCluster + rank.  The CTAs of a cluster need the SAME query slices at the
-    // same time, so each loads 1/kCluster of a slice and multicasts it to all of them: query traffic
-    // out of L2 drops by kCluster.  A CTA whose tile lies past the end scores zero rows (TMA zero fill).
+    // same time, so each loads 1/kCluster of a slice and multicasts it to all of them: query reads
+    // out of L2 drop by kCluster.  A CTA whose tile lies past the end scores zero rows (TMA zero fill).
     const uint32_t crank = cluster_ctarank();
     const int64_t n_tiles = (a.n_rows + kBN - 1) / kBN;
     const int64_t n_clusters = gridDim.x / kCluster, cluster_id = blockIdx.x / kCluster;
@@ -200,14 +233,14 @@ batch_score_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
             mbar_init(full + s, 1);
             mbar_init(empty + s, kCluster);  // every CTA of the cluster must be done with the stage
         }
-        for (int s = 0; s < 2; ++s) {
+        for (int s = 0; s < AS; ++s) {
             mbar_init(tmem_full + s, 1);
-            mbar_init(tmem_empty + s, 4 * a.mblocks);  // one arrival per participating epilogue warp
+            mbar_init(tmem_empty + s, 4 * MB);  // one arrival per epilogue warp
         }
         fence_barrier_init();
     }
     if (warp == 2) tmem_alloc(tmem_ptr, 512);
-    for (int i = tid; i < kBatchKp * NQ; i += kBatchThreads) lists[i] = 0ull;
+    for (int i = tid; i < kBatchKp * NQ; i += kBatchThreads) rows[i] = 0xFFFFFFFFu;
     tc_fence_before();
     __syncthreads();
     cluster_sync_all();  // peers' barriers are initialised before anything is multicast at them
@@ -221,8 +254,8 @@ batch_score_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
             tma_prefetch_desc(&tmap_c);
             int s = 0;
             uint32_t ph = 0;
-            const uint32_t tx = (static_cast<uint32_t>(a.mblocks) + 1u) * kOperandBytes;
-            const int q_rows = NQ / kCluster;                       // this CTA's share of the query slice
+            constexpr uint32_t tx = MB * kOperandBytes + 2u * kOperandBytes;
+            constexpr int q_rows = NQ / kCluster;  // this CTA's share of the query slice
             const uint32_t q_off = crank * static_cast<uint32_t>(q_rows) * kBKBytes;
             for (int64_t it = 0; it < my_tiles; ++it) {
                 const int row0 = static_cast<int>(((cluster_id + it * n_clusters) * kCluster + crank) * kBN);
@@ -231,7 +264,7 @@ batch_score_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
                     uint8_t* st = smem + static_cast<size_t>(s) * L.stage_bytes;
                     mbar_arrive_expect_tx(full + s, tx);
                     tma_load_2d_mc(st + q_off, &tmap_q, full + s, kb * 32, static_cast<int>(crank) * q_rows, cmask);
-                    tma_load_2d(st + a.mblocks * kOperandBytes, &tmap_c, full + s, kb * 32, row0);
+                    tma_load_2d(st + MB * kOperandBytes, &tmap_c, full + s, kb * 32, row0);
                     if (++s == n_stages) {
                         s = 0;
                         ph ^= 1u;
@@ -246,20 +279,21 @@ batch_score_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
             int s = 0;
             uint32_t ph = 0;
             for (int64_t it = 0; it < my_tiles; ++it) {
-                const uint32_t as = static_cast<uint32_t>(it & 1), aph = static_cast<uint32_t>((it >> 1) & 1);
+                const uint32_t as = static_cast<uint32_t>(it % AS), aph = static_cast<uint32_t>((it / AS) & 1);
                 mbar_wait(tmem_empty + as, aph ^ 1u);  // the epilogue has drained this accumulator
                 tc_fence_after();
                 for (int kb = 0; kb < a.nkb; ++kb) {
                     mbar_wait(full + s, ph);
                     tc_fence_after();
                     const uint32_t st = smem_u32(smem + static_cast<size_t>(s) * L.stage_bytes);
-                    const uint32_t b_addr = st + a.mblocks * kOperandBytes;
+                    const uint32_t b_addr = st + MB * kOperandBytes;
 #pragma unroll
                     for (int k4 = 0; k4 < 4; ++k4) {  // 4 x K=8 tf32 per 128-byte slice
                         const uint64_t bdesc = make_sw128_desc(b_addr + k4 * 32);
-                        for (int m = 0; m < a.mblocks; ++m) {
+#pragma unroll
+                        for (int m = 0; m < MB; ++m) {
                             const uint64_t adesc = make_sw128_desc(st + m * kOperandBytes + k4 * 32);
-                            mma_tf32(tmem_base + as * 256u + m * 128u, adesc, bdesc, kIdescTf32, (kb | k4) != 0);
+                            if (!(a.debug & 2)) mma_tf32(tmem_base + (as * MB + m) * 256u, adesc, bdesc, kIdescTf32, (kb | k4) != 0);
                         }
                     }
                     tc_commit_mc(empty + s, cmask);  // stage reusable (here and in the peers) once these MMAs have read it
@@ -272,57 +306,66 @@ batch_score_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
             }
         }
         __syncwarp();
-    } else if (warp >= kEpiWarp0) {
+    } else if (warp >= kEpiWarp0 && warp < kEpiWarp0 + 4 * MB) {
         // ------------------------------------------------ epilogue: thread <-> query
-        const int q = (warp - kEpiWarp0) * 32 + lane;  // 0 .. 255
+        const int q = (warp - kEpiWarp0) * 32 + lane;  // 0 .. NQ-1
         const int mblock = q >> 7;
         const bool live = q < a.nq;
         const uint32_t lane_base = static_cast<uint32_t>((warp & 3) * 32) << 16;  // TMEM lanes this warp may read
-        float thr = -CUDART_INF_F;
-        uint32_t lstate = 0;
-        if (mblock < a.mblocks) {
-            for (int64_t it = 0; it < my_tiles; ++it) {
-                const uint32_t as = static_cast<uint32_t>(it & 1), aph = static_cast<uint32_t>((it >> 1) & 1);
-                mbar_wait(tmem_full + as, aph);
-                tc_fence_after();
-                const int64_t row0 = ((cluster_id + it * n_clusters) * kCluster + crank) * kBN;
-                const int nvalid = static_cast<int>(min(static_cast<int64_t>(kBN), a.n_rows - row0));
-                for (int c0 = 0; c0 < kBN; c0 += 32) {
-                    uint32_t v[32];
-                    tmem_ld_32x32(tmem_base + lane_base + as * 256u + mblock * 128u + c0, v);
-                    if (live) {
+        float S[kBatchKp];
 #pragma unroll
-                        for (int j = 0; j < 32; ++j) {
-                            const float sc = __uint_as_float(v[j]);
-                            if (sc > thr && c0 + j < nvalid) {  // rows ascend, so equal scores never displace
-                                const uint64_t r = list_insert(lists, NQ, q, sc, static_cast<uint32_t>(row0 + c0 + j), lstate);
-                                lstate = static_cast<uint32_t>(r);
-                                thr = __uint_as_float(static_cast<uint32_t>(r >> 32));
-                            }
-                        }
-                    }
+        for (int p = 0; p < kBatchKp; ++p) S[p] = -CUDART_INF_F;
+        float thr = -CUDART_INF_F;
+        int minpos = 0;
+        for (int64_t it = 0; it < my_tiles; ++it) {
+            const uint32_t as = static_cast<uint32_t>(it % AS), aph = static_cast<uint32_t>((it / AS) & 1);
+            mbar_wait(tmem_full + as, aph);
+            tc_fence_after();
+            const int64_t row0 = ((cluster_id + it * n_clusters) * kCluster + crank) * kBN;
+            const int nvalid = static_cast<int>(min(static_cast<int64_t>(kBN), a.n_rows - row0));
+            for (int c0 = 0; c0 < kBN; c0 += 16) {
+                uint32_t v[16];
+                tmem_ld_32x16(tmem_base + lane_base + (as * MB + mblock) * 256u + c0, v);
+                // Hits are rare once the lists have warmed up.  Each lane marks the columns whose score beats ITS
+                // threshold; the warp then revisits only the marked columns (one-column TMEM load) and the lanes
+                // concerned insert.  One copy of the insert code instead of sixteen keeps the loop in the I-cache.
+                unsigned mine = 0;
+                if (live && !(a.debug & 1)) {
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) mine |= (__uint_as_float(v[j]) > thr ? 1u : 0u) << j;
                 }
-                tc_fence_before();
-                __syncwarp();
-                if (lane == 0) mbar_arrive(tmem_empty + as);
+                unsigned any = __reduce_or_sync(0xffffffffu, mine);
+                while (any) {
+                    const int j = __ffs(any) - 1;
+                    any &= any - 1;
+                    uint32_t one;
+                    asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(one) : "r"(tmem_base + lane_base + (as * MB + mblock) * 256u + c0 + j) : "memory");
+                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                    const float sc = __uint_as_float(one);
+                    if (((mine >> j) & 1u) && sc > thr && c0 + j < nvalid)  // rows ascend, so an equal score never displaces
+                        list_insert(S, minpos, thr, rows, NQ, q, sc, static_cast<uint32_t>(row0 + c0 + j));
+                }
             }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(tmem_empty + as);
         }
-        // sort the (thread-private) list descending, then publish it: glists[q][cta][pos]
-        if (live) {
-            for (int i = 1; i < kBatchKp; ++i) {
-                const uint64_t key = lists[i * NQ + q];
-                int p = i;
-                while (p > 0) {
-                    const uint64_t up = lists[(p - 1) * NQ + q];
-                    if (up >= key) break;
-                    lists[p * NQ + q] = up;
-                    --p;
-                }
-                lists[p * NQ + q] = key;
-            }
-            uint64_t* g = a.glists + (static_cast<size_t>(q) * gridDim.x + blockIdx.x) * kBatchKp;
-#pragma unroll 4
-            for (int p = 0; p < kBatchKp; ++p) g[p] = lists[p * NQ + q];
+        // The ring is idle now (every stage was consumed before the last accumulator completed): reuse it to
+        // hand each query's 32 keys to a warp, which sorts them (one key per lane) and publishes them.
+        uint64_t* keys = reinterpret_cast<uint64_t*>(smem);  // [query][slot]
+        named_bar_sync(2, 128 * MB);
+#pragma unroll
+        for (int p = 0; p < kBatchKp; ++p) {
+            const uint32_t r = rows[p * NQ + q];
+            keys[q * kBatchKp + p] = (S[p] > -CUDART_INF_F && r != 0xFFFFFFFFu) ? make_key(S[p] + 0.0f, r) : 0ull;
+        }
+        __syncwarp();
+        const int q0 = (warp - kEpiWarp0) * 32;
+        const int n_live = max(0, min(32, a.nq - q0));
+        for (int i = 0; i < n_live; ++i) {
+            uint64_t k = keys[(q0 + i) * kBatchKp + lane];
+            k = warp_sort_desc(k, lane);
+            a.glists[(static_cast<size_t>(q0 + i) * gridDim.x + blockIdx.x) * kBatchKp + lane] = k;  // glists[q][cta][pos]
         }
     }
     tc_fence_before();
@@ -453,9 +496,9 @@ int launch_batch_search(const BatchSearchArgs& b, cudaStream_t stream) {
 
     BatchLayout L;
     L.mblocks = mblocks;
-    L.stage_bytes = (mblocks + 1) * kOperandBytes;
-    const uint32_t lists_bytes = sizeof(uint64_t) * kBatchKp * nq_pad;
-    const uint32_t budget = 225u * 1024u - 1024u /*alignment slack*/ - lists_bytes - 256u;
+    L.stage_bytes = (mblocks + 2) * kOperandBytes;                       // queries + 256 corpus rows
+    const uint32_t lists_bytes = sizeof(uint32_t) * kBatchKp * nq_pad;   // row ids of the candidate lists
+    const uint32_t budget = 227u * 1024u - 1024u /*alignment slack*/ - lists_bytes - 512u;
     L.n_stages = budget / L.stage_bytes;
     if (L.n_stages > 8) L.n_stages = 8;
     if (L.n_stages < 2) return static_cast<int>(cudaErrorInvalidConfiguration);
@@ -470,13 +513,20 @@ int launch_batch_search(const BatchSearchArgs& b, cudaStream_t stream) {
     a.mblocks = mblocks;
     a.nkb = (s.ld + 31) / 32;
     a.glists = glists;
+    a.debug = std::getenv("RAGSTORE_BATCH_DEBUG") ? atoi(std::getenv("RAGSTORE_BATCH_DEBUG")) : 0;
     const int64_t n_tiles = (s.n_rows + kBN - 1) / kBN;
     int grid = static_cast<int>(n_tiles < s.sm_count ? n_tiles : s.sm_count);
     grid = (grid + kCluster - 1) / kCluster * kCluster;          // whole clusters
     if (grid > s.sm_count) grid = s.sm_count / kCluster * kCluster;
-    e = cudaFuncSetAttribute(batch_score_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-    if (e != cudaSuccess) return static_cast<int>(e);
-    batch_score_kernel<<<grid, kBatchThreads, L.total, stream>>>(map_q, map_c, a, L);
+    if (mblocks == 2) {
+        e = cudaFuncSetAttribute(batch_score_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        if (e != cudaSuccess) return static_cast<int>(e);
+        batch_score_kernel<2><<<grid, kBatchThreads, L.total, stream>>>(map_q, map_c, a, L);
+    } else {
+        e = cudaFuncSetAttribute(batch_score_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        if (e != cudaSuccess) return static_cast<int>(e);
+        batch_score_kernel<1><<<grid, kBatchThreads, L.total, stream>>>(map_q, map_c, a, L);
+    }
     e = cudaGetLastError();
     if (e != cudaSuccess) return static_cast<int>(e);
 

@@ -29,8 +29,5 @@ def run(n, d, nq, k, iters=5):
     st.close()
 
 if __name__ == "__main__":
-    run(1000000, 1024, 128, 10)
-    run(4000000, 1024, 128, 10)
-    run(1000000, 1024, 256, 10)
-    run(4000000, 1024, 256, 10)
-    run(8000000, 1024, 256, 10, iters=3)
+    run(2000000, 1024, 256, 10)
+    run(6000000, 1024, 256, 10, iters=3)
