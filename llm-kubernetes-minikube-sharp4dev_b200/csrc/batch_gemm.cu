@@ -182,6 +182,16 @@ __device__ __forceinline__ void list_insert(float (&S)[kBatchKp], int& minpos, f
     thr = m.v;
 }
 
+__device__ __forceinline__ void tmem_ld_32x16_nowait(uint32_t taddr, uint32_t (&v)[16]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+          "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+        : "r"(taddr)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ void tmem_ld_32x16(uint32_t taddr, uint32_t (&v)[16]) {
     asm volatile(
         "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
@@ -323,27 +333,34 @@ batch_score_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
             tc_fence_after();
             const int64_t row0 = ((cluster_id + it * n_clusters) * kCluster + crank) * kBN;
             const int nvalid = static_cast<int>(min(static_cast<int64_t>(kBN), a.n_rows - row0));
-            for (int c0 = 0; c0 < kBN; c0 += 16) {
-                uint32_t v[16];
-                tmem_ld_32x16(tmem_base + lane_base + (as * MB + mblock) * 256u + c0, v);
+            for (int cb = 0; cb < kBN; cb += 64) {
+                // four 16-column loads in flight per wait: the TMEM read latency is paid once per 64 columns
+                uint32_t v[4][16];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) tmem_ld_32x16_nowait(tmem_base + lane_base + (as * MB + mblock) * 256u + cb + u * 16, v[u]);
+                tmem_ld_wait();
                 // Hits are rare once the lists have warmed up.  Each lane marks the columns whose score beats ITS
                 // threshold; the warp then revisits only the marked columns (one-column TMEM load) and the lanes
-                // concerned insert.  One copy of the insert code instead of sixteen keeps the loop in the I-cache.
-                unsigned mine = 0;
+                // concerned insert.  One copy of the insert code keeps the loop in the I-cache.
+                unsigned long long mine = 0;
                 if (live && !(a.debug & 1)) {
 #pragma unroll
-                    for (int j = 0; j < 16; ++j) mine |= (__uint_as_float(v[j]) > thr ? 1u : 0u) << j;
+                    for (int u = 0; u < 4; ++u)
+#pragma unroll
+                        for (int j = 0; j < 16; ++j) mine |= static_cast<unsigned long long>(__uint_as_float(v[u][j]) > thr ? 1u : 0u) << (u * 16 + j);
                 }
-                unsigned any = __reduce_or_sync(0xffffffffu, mine);
+                unsigned lo = __reduce_or_sync(0xffffffffu, static_cast<unsigned>(mine));
+                unsigned hi = __reduce_or_sync(0xffffffffu, static_cast<unsigned>(mine >> 32));
+                unsigned long long any = (static_cast<unsigned long long>(hi) << 32) | lo;
                 while (any) {
-                    const int j = __ffs(any) - 1;
+                    const int j = __ffsll(static_cast<long long>(any)) - 1;
                     any &= any - 1;
                     uint32_t one;
-                    asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(one) : "r"(tmem_base + lane_base + (as * MB + mblock) * 256u + c0 + j) : "memory");
+                    asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(one) : "r"(tmem_base + lane_base + (as * MB + mblock) * 256u + cb + j) : "memory");
                     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
                     const float sc = __uint_as_float(one);
-                    if (((mine >> j) & 1u) && sc > thr && c0 + j < nvalid)  // rows ascend, so an equal score never displaces
-                        list_insert(S, minpos, thr, rows, NQ, q, sc, static_cast<uint32_t>(row0 + c0 + j));
+                    if (((mine >> j) & 1ull) && sc > thr && cb + j < nvalid)  // rows ascend, so an equal score never displaces
+                        list_insert(S, minpos, thr, rows, NQ, q, sc, static_cast<uint32_t>(row0 + cb + j));
                 }
             }
             tc_fence_before();
@@ -374,6 +391,231 @@ batch_score_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
     if (warp == 2) {
         tc_fence_after();
         tmem_dealloc(tmem_base, 512);
+    }
+}
+
+// ---------------------------------------------------------------- the CTA-pair (cta_group::2) kernel
+// For 129..256 queries.  Two CTAs (one TPC pair) form one MMA: M = 256 queries (each CTA keeps ITS 128
+// queries as its half of A), N = 256 corpus rows (each CTA loads 128 of them as its half of B; the
+// tensor cores read both halves).  Per ring stage a CTA ingests 16 KB of queries + 16 KB of corpus for
+// 256 rows of the pair, i.e. half the L2->SM bytes per corpus row of the single-CTA kernel, and its
+// TMEM holds 128 queries x 256 rows = 256 columns, so the accumulator is double buffered and the
+// epilogue of tile t overlaps the MMAs of tile t+1.
+// Barriers: both CTAs' TMA loads complete on the LEADER's full barrier; the leader's MMA lane commits
+// (multicast) to both CTAs' empty / tmem_full barriers; both epilogues arrive on the leader's tmem_empty.
+constexpr int kPairThreads = 256;   // warp0 TMA, warp1 MMA (leader), warp2 TMEM, warp3 idle, warps 4-7 epilogue
+constexpr uint32_t kIdescTf32Pair = (1u << 4) | (2u << 7) | (2u << 10) | ((256u >> 3) << 17) | ((256u >> 4) << 24);
+
+__device__ __forceinline__ void tma_load_2d_2sm(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1) {
+    // executed by both CTAs of the pair; the peer bit of the barrier address is cleared so that the
+    // transaction bytes are counted on the leader's (even rank) barrier
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::
+            "r"(smem_u32(smem_dst)),
+        "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar) & 0xFEFFFFFFu), "r"(c0), "r"(c1)
+        : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint64_t* local_bar, uint32_t target_rank) {
+    uint32_t raddr;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(raddr) : "r"(smem_u32(local_bar)), "r"(target_rank));
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(raddr) : "memory");
+}
+__device__ __forceinline__ void mbar_wait_cluster(uint64_t* bar, uint32_t parity) {
+    uint32_t ok = 0;
+    while (!ok) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(ok)
+            : "r"(smem_u32(bar)), "r"(parity)
+            : "memory");
+    }
+}
+__device__ __forceinline__ void tmem_alloc_2sm(uint32_t* smem_dst, uint32_t cols) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_dst)), "r"(cols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc_2sm(uint32_t taddr, uint32_t cols) {
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols) : "memory");
+}
+__device__ __forceinline__ void tc_commit_2sm_mc(uint64_t* bar, uint16_t cta_mask) {
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
+                     smem_u32(bar)),
+                 "h"(cta_mask)
+                 : "memory");
+}
+__device__ __forceinline__ void mma_tf32_2sm(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPairThreads, 1)
+batch_score_kernel_2sm(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_c,
+                       const BatchArgs a, const BatchLayout L) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int n_stages = static_cast<int>(L.n_stages);
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem + L.off_bars);  // used in the leader only
+    uint64_t* empty = full + n_stages;
+    uint64_t* tmem_full = empty + n_stages;   // [2]
+    uint64_t* tmem_empty = tmem_full + 2;     // [2], used in the leader only
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(smem + L.off_tmem);
+    uint32_t* rows = reinterpret_cast<uint32_t*>(smem + L.off_lists);  // [slot][local query]
+    constexpr int NQL = kBM;  // queries handled by this CTA
+
+    const uint32_t crank = cluster_ctarank();
+    const bool leader = crank == 0;
+    const int64_t n_ptiles = (a.n_rows + kBN - 1) / kBN;  // pair tiles of 256 rows
+    const int64_t n_pairs = gridDim.x / 2, pair_id = blockIdx.x / 2;
+    const int64_t my_tiles = n_ptiles > pair_id ? (n_ptiles - pair_id + n_pairs - 1) / n_pairs : 0;
+
+    if (tid == 0) {
+        for (int s = 0; s < n_stages; ++s) {
+            mbar_init(full + s, 2);   // leader's expect_tx arrival + the peer's arrival
+            mbar_init(empty + s, 1);  // the leader's multicast commit
+        }
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(tmem_full + s, 1);   // the leader's multicast commit
+            mbar_init(tmem_empty + s, 8);  // four epilogue warps in each CTA
+        }
+        fence_barrier_init();
+    }
+    for (int i = tid; i < kBatchKp * NQL; i += kPairThreads) rows[i] = 0xFFFFFFFFu;
+    __syncthreads();
+    cluster_sync_all();
+    if (warp == 2) tmem_alloc_2sm(tmem_ptr, 512);
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr;
+
+    if (warp == 0) {
+        // ------------------------------------------------ TMA producer (both CTAs)
+        if (lane == 0) {
+            tma_prefetch_desc(&tmap_q);
+            tma_prefetch_desc(&tmap_c);
+            int s = 0;
+            uint32_t ph = 0;
+            for (int64_t it = 0; it < my_tiles; ++it) {
+                const int row0 = static_cast<int>((pair_id + it * n_pairs) * kBN + crank * 128);
+                for (int kb = 0; kb < a.nkb; ++kb) {
+                    mbar_wait(empty + s, ph ^ 1u);
+                    uint8_t* st = smem + static_cast<size_t>(s) * L.stage_bytes;
+                    if (leader)
+                        mbar_arrive_expect_tx(full + s, 4u * kOperandBytes);  // both CTAs' A and B halves
+                    else
+                        mbar_arrive_cluster(full + s, 0);
+                    tma_load_2d_2sm(st, &tmap_q, full + s, kb * 32, static_cast<int>(crank) * kBM);
+                    tma_load_2d_2sm(st + kOperandBytes, &tmap_c, full + s, kb * 32, row0);
+                    if (++s == n_stages) {
+                        s = 0;
+                        ph ^= 1u;
+                    }
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        // ------------------------------------------------ MMA issuer: one lane of the leader CTA
+        if (leader && lane == 0) {
+            int s = 0;
+            uint32_t ph = 0;
+            for (int64_t it = 0; it < my_tiles; ++it) {
+                const uint32_t as = static_cast<uint32_t>(it & 1), aph = static_cast<uint32_t>((it >> 1) & 1);
+                mbar_wait_cluster(tmem_empty + as, aph ^ 1u);  // both epilogues have drained this accumulator
+                tc_fence_after();
+                for (int kb = 0; kb < a.nkb; ++kb) {
+                    mbar_wait_cluster(full + s, ph);
+                    tc_fence_after();
+                    const uint32_t st = smem_u32(smem + static_cast<size_t>(s) * L.stage_bytes);
+#pragma unroll
+                    for (int k4 = 0; k4 < 4; ++k4) {
+                        const uint64_t adesc = make_sw128_desc(st + k4 * 32);
+                        const uint64_t bdesc = make_sw128_desc(st + kOperandBytes + k4 * 32);
+                        if (!(a.debug & 2)) mma_tf32_2sm(tmem_base + as * 256u, adesc, bdesc, kIdescTf32Pair, (kb | k4) != 0);
+                    }
+                    tc_commit_2sm_mc(empty + s, 0x3);  // both CTAs may refill the stage once these MMAs are done
+                    if (++s == n_stages) {
+                        s = 0;
+                        ph ^= 1u;
+                    }
+                }
+                tc_commit_2sm_mc(tmem_full + as, 0x3);  // accumulator complete, in both CTAs
+            }
+        }
+        __syncwarp();
+    } else if (warp >= kEpiWarp0) {
+        // ------------------------------------------------ epilogue: thread <-> one of this CTA's 128 queries
+        const int ql = (warp - kEpiWarp0) * 32 + lane;
+        const int q = static_cast<int>(crank) * kBM + ql;
+        const bool live = q < a.nq;
+        const uint32_t lane_base = static_cast<uint32_t>((warp & 3) * 32) << 16;
+        float S[kBatchKp];
+#pragma unroll
+        for (int p = 0; p < kBatchKp; ++p) S[p] = -CUDART_INF_F;
+        float thr = -CUDART_INF_F;
+        int minpos = 0;
+        for (int64_t it = 0; it < my_tiles; ++it) {
+            const uint32_t as = static_cast<uint32_t>(it & 1), aph = static_cast<uint32_t>((it >> 1) & 1);
+            mbar_wait(tmem_full + as, aph);
+            tc_fence_after();
+            const int64_t row0 = (pair_id + it * n_pairs) * kBN;
+            const int nvalid = static_cast<int>(min(static_cast<int64_t>(kBN), a.n_rows - row0));
+            for (int c0 = 0; c0 < kBN; c0 += 16) {
+                uint32_t v[16];
+                tmem_ld_32x16(tmem_base + lane_base + as * 256u + c0, v);
+                unsigned mine = 0;
+                if (live && !(a.debug & 1)) {
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) mine |= (__uint_as_float(v[j]) > thr ? 1u : 0u) << j;
+                }
+                unsigned any = __reduce_or_sync(0xffffffffu, mine);
+                while (any) {
+                    const int j = __ffs(any) - 1;
+                    any &= any - 1;
+                    uint32_t one;
+                    asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(one) : "r"(tmem_base + lane_base + as * 256u + c0 + j) : "memory");
+                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                    const float sc = __uint_as_float(one);
+                    if (((mine >> j) & 1u) && sc > thr && c0 + j < nvalid)
+                        list_insert(S, minpos, thr, rows, NQL, ql, sc, static_cast<uint32_t>(row0 + c0 + j));
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_cluster(tmem_empty + as, 0);
+        }
+        uint64_t* keys = reinterpret_cast<uint64_t*>(smem);  // [local query][slot]; the ring is idle now
+        named_bar_sync(2, 128);
+#pragma unroll
+        for (int p = 0; p < kBatchKp; ++p) {
+            const uint32_t r = rows[p * NQL + ql];
+            keys[ql * kBatchKp + p] = (S[p] > -CUDART_INF_F && r != 0xFFFFFFFFu) ? make_key(S[p] + 0.0f, r) : 0ull;
+        }
+        __syncwarp();
+        const int ql0 = (warp - kEpiWarp0) * 32;
+        const int qg0 = static_cast<int>(crank) * kBM + ql0;
+        const int n_live = max(0, min(32, a.nq - qg0));
+        for (int i = 0; i < n_live; ++i) {
+            uint64_t k = keys[(ql0 + i) * kBatchKp + lane];
+            k = warp_sort_desc(k, lane);
+            a.glists[(static_cast<size_t>(qg0 + i) * n_pairs + pair_id) * kBatchKp + lane] = k;  // glists[q][pair][pos]
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();
+    if (warp == 2) {
+        tc_fence_after();
+        tmem_dealloc_2sm(tmem_base, 512);
     }
 }
 
@@ -490,18 +732,25 @@ int launch_batch_search(const BatchSearchArgs& b, cudaStream_t stream) {
     if (e != cudaSuccess) return static_cast<int>(e);
 
     CUtensorMap map_q, map_c;
-    if (!make_map_f32(&map_q, qhat, static_cast<uint64_t>(nq_pad), static_cast<uint64_t>(s.ld), nq_pad / kCluster) ||
-        !make_map_f32(&map_c, s.mat, static_cast<uint64_t>(s.n_rows), static_cast<uint64_t>(s.ld), kBN))
+    const char* mode_env = std::getenv("RAGSTORE_BATCH_2SM");
+    const bool pair_maps = mblocks == 2 && mode_env && mode_env[0] == '1';
+    if (!make_map_f32(&map_q, qhat, static_cast<uint64_t>(nq_pad), static_cast<uint64_t>(s.ld), pair_maps ? kBM : nq_pad / kCluster) ||
+        !make_map_f32(&map_c, s.mat, static_cast<uint64_t>(s.n_rows), static_cast<uint64_t>(s.ld), pair_maps ? 128 : kBN))
         return static_cast<int>(cudaErrorNotSupported);
 
+    const char* mode = std::getenv("RAGSTORE_BATCH_2SM");
+    // The CTA-pair (cta_group::2) kernel is correct but measured slower for tf32 (2.9 vs 4.7 TB/s of corpus: the pair's
+    // operand exchange paces 4-byte operands), so it is opt-in: RAGSTORE_BATCH_2SM=1.
+    const bool pair = mblocks == 2 && mode && mode[0] == '1';
     BatchLayout L;
     L.mblocks = mblocks;
-    L.stage_bytes = (mblocks + 2) * kOperandBytes;                       // queries + 256 corpus rows
-    const uint32_t lists_bytes = sizeof(uint32_t) * kBatchKp * nq_pad;   // row ids of the candidate lists
+    L.stage_bytes = pair ? 2 * kOperandBytes : (mblocks + 2) * kOperandBytes;
+    const uint32_t lists_bytes = sizeof(uint32_t) * kBatchKp * (pair ? kBM : nq_pad);   // row ids of the candidate lists
+    const uint32_t keys_bytes = sizeof(uint64_t) * kBatchKp * (pair ? kBM : nq_pad);    // publish staging (reuses the ring)
     const uint32_t budget = 227u * 1024u - 1024u /*alignment slack*/ - lists_bytes - 512u;
     L.n_stages = budget / L.stage_bytes;
     if (L.n_stages > 8) L.n_stages = 8;
-    if (L.n_stages < 2) return static_cast<int>(cudaErrorInvalidConfiguration);
+    if (L.n_stages < 2 || L.n_stages * L.stage_bytes < keys_bytes) return static_cast<int>(cudaErrorInvalidConfiguration);
     L.off_bars = L.n_stages * L.stage_bytes;
     L.off_tmem = L.off_bars + 8u * (2u * L.n_stages + 4u);
     L.off_lists = (L.off_tmem + 16u + 15u) & ~15u;
@@ -515,10 +764,17 @@ int launch_batch_search(const BatchSearchArgs& b, cudaStream_t stream) {
     a.glists = glists;
     a.debug = std::getenv("RAGSTORE_BATCH_DEBUG") ? atoi(std::getenv("RAGSTORE_BATCH_DEBUG")) : 0;
     const int64_t n_tiles = (s.n_rows + kBN - 1) / kBN;
-    int grid = static_cast<int>(n_tiles < s.sm_count ? n_tiles : s.sm_count);
+    const int64_t n_units = pair ? 2 * n_tiles : n_tiles;       // CTAs that have work
+    int grid = static_cast<int>(n_units < s.sm_count ? n_units : s.sm_count);
     grid = (grid + kCluster - 1) / kCluster * kCluster;          // whole clusters
     if (grid > s.sm_count) grid = s.sm_count / kCluster * kCluster;
-    if (mblocks == 2) {
+    int nlists = grid;
+    if (pair) {
+        e = cudaFuncSetAttribute(batch_score_kernel_2sm, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        if (e != cudaSuccess) return static_cast<int>(e);
+        batch_score_kernel_2sm<<<grid, kPairThreads, L.total, stream>>>(map_q, map_c, a, L);
+        nlists = grid / 2;
+    } else if (mblocks == 2) {
         e = cudaFuncSetAttribute(batch_score_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
         if (e != cudaSuccess) return static_cast<int>(e);
         batch_score_kernel<2><<<grid, kBatchThreads, L.total, stream>>>(map_q, map_c, a, L);
@@ -534,7 +790,7 @@ int launch_batch_search(const BatchSearchArgs& b, cudaStream_t stream) {
     f.scan = s;
     f.d_queries = b.d_queries;
     f.glists = glists;
-    f.nlists = grid;
+    f.nlists = nlists;
     f.out_stride = b.out_stride;
     f.row_bytes = static_cast<uint32_t>(s.ld) * 4u;
     f.qpad = static_cast<uint32_t>(s.ld);
@@ -542,7 +798,7 @@ int launch_batch_search(const BatchSearchArgs& b, cudaStream_t stream) {
     uint32_t ring = 200u * 1024u - fixed;
     const uint32_t need = static_cast<uint32_t>(s.kp) * (f.row_bytes + 16u);  // room for every candidate row at once
     if (ring > need) ring = need;
-    const uint32_t lists_need = static_cast<uint32_t>(grid) * s.kp * 8u;
+    const uint32_t lists_need = static_cast<uint32_t>(nlists) * s.kp * 8u;
     if (ring < lists_need && lists_need + fixed <= 200u * 1024u) ring = lists_need;
     f.ring_bytes = (ring + 127u) & ~127u;
     const size_t fin_smem = f.ring_bytes + fixed;
