@@ -49,7 +49,7 @@ struct DeviceGuard {
     }
 };
 
-constexpr int kCtxQueries = 64;  // queries per host-search context batch
+constexpr int kCtxQueries = 256; // queries per host-search context batch (= one tensor-core launch)
 constexpr int kNumCtx = 4;       // concurrent host searches per store
 
 struct SearchCtx {
@@ -108,8 +108,11 @@ struct ragstore {
     cudaStream_t ingest_stream = nullptr;
     cudaStream_t dev_stream = nullptr;
     std::mutex add_mu;
-    float* d_stage = nullptr;
+    float* d_stage = nullptr;      // device staging (bf16 stores fed from the host), two chunks
     size_t stage_floats = 0;
+    float* h_stage[2] = {nullptr, nullptr};   // pinned host staging, one per pipeline slot
+    cudaEvent_t ingest_ev[2] = {nullptr, nullptr};
+    unsigned long long* h_counters = nullptr; // pinned: per slot [inexact rows, sidecar rows]
     ScanScratch dev_scratch{};
     uint8_t* dev_batch_scratch = nullptr;
     std::vector<SearchCtx> ctxs;
@@ -326,6 +329,11 @@ int ragstore_destroy(ragstore_t* s) {
     if (s->ingest_stream) cudaStreamDestroy(s->ingest_stream);
     if (s->dev_stream) cudaStreamDestroy(s->dev_stream);
     cudaFree(s->d_stage);
+    for (int b = 0; b < 2; ++b) {
+        if (s->h_stage[b]) cudaFreeHost(s->h_stage[b]);
+        if (s->ingest_ev[b]) cudaEventDestroy(s->ingest_ev[b]);
+    }
+    if (s->h_counters) cudaFreeHost(s->h_counters);
     cudaFree(s->d_inexact);
     s->raw_buf.release();
     s->slot_buf.release();
@@ -361,11 +369,44 @@ int ragstore_add(ragstore_t* s, const float* rows, int64_t n_rows, int row_dim, 
     const bool on_device = (flags & RAGSTORE_ADD_DEVICE) != 0;
     const bool in_place = (s->dtype == RAGSTORE_F32);  // fp32: land rows in the matrix, normalise in place
     const size_t esz = s->elem_size();
-    const int64_t chunk_rows = std::max<int64_t>(1, (int64_t(64) << 20) / (int64_t(s->dim) * 4));
+    // Two-deep pipeline of ~32 MB chunks: while chunk i is copied over PCIe and normalised, chunk i+1 is being
+    // staged into the other pinned buffer (host sources) -- the upload kernel never waits for the CPU copy.
+    const int64_t chunk_rows = std::max<int64_t>(1, (int64_t(32) << 20) / (int64_t(s->dim) * 4));
+    const size_t chunk_floats = static_cast<size_t>(chunk_rows) * s->dim;
+    if (!on_device && !s->h_stage[0]) {
+        for (int b = 0; b < 2; ++b) CU_TRY(cudaMallocHost(&s->h_stage[b], chunk_floats * sizeof(float)));
+    }
+    if (!in_place && !on_device && s->stage_floats < 2 * chunk_floats) {
+        cudaFree(s->d_stage);
+        s->d_stage = nullptr;
+        s->stage_floats = 0;
+        CU_TRY(cudaMalloc(&s->d_stage, 2 * chunk_floats * sizeof(float)));
+        s->stage_floats = 2 * chunk_floats;
+    }
+    if (!s->ingest_ev[0]) {
+        for (int b = 0; b < 2; ++b) CU_TRY(cudaEventCreateWithFlags(&s->ingest_ev[b], cudaEventDisableTiming));
+        CU_TRY(cudaMallocHost(&s->h_counters, 2 * 2 * sizeof(unsigned long long)));
+    }
+    bool used[2] = {false, false};
+    int64_t rows_in_flight[2] = {0, 0};
 
-    for (int64_t r0 = 0; r0 < n_rows; r0 += chunk_rows) {
+    auto retire = [&](int b) -> int {  // wait for the chunk that last used buffer b and take over its counters
+        if (!used[b]) return RAGSTORE_OK;
+        CU_TRY(cudaEventSynchronize(s->ingest_ev[b]));
+        s->inexact_rows = static_cast<int64_t>(s->h_counters[2 * b]);
+        s->raw_used = static_cast<int64_t>(s->h_counters[2 * b + 1] & 0xFFFFFFFFull);
+        used[b] = false;
+        rows_in_flight[b] = 0;
+        return RAGSTORE_OK;
+    };
+
+    int64_t chunk = 0;
+    for (int64_t r0 = 0; r0 < n_rows; r0 += chunk_rows, ++chunk) {
+        const int b = static_cast<int>(chunk & 1);
         const int64_t n = std::min(chunk_rows, n_rows - r0);
         const float* src = rows + r0 * s->dim;
+        int rc = retire(b);
+        if (rc) return rc;
         {   // map physical memory behind the rows about to land (addresses of existing rows never move)
             const size_t upto = static_cast<size_t>(first + r0 + n);
             const size_t upto4 = ((upto + 3) & ~size_t(3)) + 64;
@@ -374,7 +415,9 @@ int ragstore_add(ragstore_t* s, const float* rows, int64_t n_rows, int row_dim, 
             if (!vr) vr = s->exact_buf.ensure(upto4, true, s->ingest_stream);
             if (!vr && s->raw_slot) vr = s->slot_buf.ensure(upto4 * sizeof(int32_t), true, s->ingest_stream);
             if (!vr && s->raw_slot) {
-                const size_t worst = std::min<size_t>(static_cast<size_t>(s->raw_used + n), static_cast<size_t>(s->capacity));
+                // sidecar slots: everything known to be used + every row still in flight + this chunk
+                const size_t worst = std::min<size_t>(static_cast<size_t>(s->raw_used + rows_in_flight[b ^ 1] + n),
+                                                      static_cast<size_t>(s->capacity));
                 vr = s->raw_buf.ensure(worst * s->raw_ld * sizeof(float), false, s->ingest_stream);
             }
             if (vr) return fail(RAGSTORE_ERR_CUDA, "mapping device memory for new rows", cudaGetErrorString(static_cast<cudaError_t>(vr)));
@@ -395,37 +438,39 @@ int ragstore_add(ragstore_t* s, const float* rows, int64_t n_rows, int row_dim, 
         a.dtype = s->dtype;
         a.prenormalised = (flags & RAGSTORE_ADD_PRENORMALISED) ? 1 : 0;
         a.inexact_counter = s->d_inexact;
+        const float* h2d_src = src;
+        if (!on_device) {  // stage through pinned memory so that the PCIe copy is truly asynchronous
+            memcpy(s->h_stage[b], src, static_cast<size_t>(n) * s->dim * sizeof(float));
+            h2d_src = s->h_stage[b];
+        }
         if (on_device && !in_place) {
             a.src = src;
             a.src_ld = s->dim;
         } else if (in_place) {
-            CU_TRY(cudaMemcpy2DAsync(dst_row, static_cast<size_t>(s->ld) * 4, src, static_cast<size_t>(s->dim) * 4,
+            CU_TRY(cudaMemcpy2DAsync(dst_row, static_cast<size_t>(s->ld) * 4, h2d_src, static_cast<size_t>(s->dim) * 4,
                                      static_cast<size_t>(s->dim) * 4, static_cast<size_t>(n),
                                      on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, s->ingest_stream));
             a.src = reinterpret_cast<const float*>(dst_row);
             a.src_ld = s->ld;
         } else {
-            const size_t need = static_cast<size_t>(chunk_rows) * s->dim;
-            if (s->stage_floats < need) {
-                cudaFree(s->d_stage);
-                s->d_stage = nullptr;
-                s->stage_floats = 0;
-                CU_TRY(cudaMalloc(&s->d_stage, need * sizeof(float)));
-                s->stage_floats = need;
-            }
-            CU_TRY(cudaMemcpyAsync(s->d_stage, src, static_cast<size_t>(n) * s->dim * 4, cudaMemcpyHostToDevice, s->ingest_stream));
-            a.src = s->d_stage;
+            float* dstage = s->d_stage + static_cast<size_t>(b) * chunk_floats;
+            CU_TRY(cudaMemcpyAsync(dstage, h2d_src, static_cast<size_t>(n) * s->dim * 4, cudaMemcpyHostToDevice, s->ingest_stream));
+            a.src = dstage;
             a.src_ld = s->dim;
         }
-        const int rc = launch_normalise(a, s->ingest_stream);
+        rc = launch_normalise(a, s->ingest_stream);
         if (rc) return fail(RAGSTORE_ERR_CUDA, "normalise kernel launch", cudaGetErrorString(static_cast<cudaError_t>(rc)));
-        // the sidecar bound for the next chunk needs this chunk's count; this also fences staging reuse
-        unsigned long long counters[2] = {0, 0};   // [0] inexact rows, [1] low word: sidecar rows
-        CU_TRY(cudaMemcpyAsync(counters, s->d_inexact, sizeof(counters), cudaMemcpyDeviceToHost, s->ingest_stream));
-        CU_TRY(cudaStreamSynchronize(s->ingest_stream));
-        s->inexact_rows = static_cast<int64_t>(counters[0]);
-        s->raw_used = static_cast<int64_t>(counters[1] & 0xFFFFFFFFull);
+        // counters after this chunk ([0] inexact rows, [1] low word: sidecar rows), read back without stalling
+        CU_TRY(cudaMemcpyAsync(s->h_counters + 2 * b, s->d_inexact, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s->ingest_stream));
+        CU_TRY(cudaEventRecord(s->ingest_ev[b], s->ingest_stream));
+        used[b] = true;
+        rows_in_flight[b] = n;
     }
+    // drain in issue order so that the newest counters win
+    const int last = static_cast<int>((chunk - 1) & 1);
+    int rc = retire(last ^ 1);
+    if (!rc) rc = retire(last);
+    if (rc) return rc;
     CU_TRY(cudaStreamSynchronize(s->ingest_stream));
     s->count.store(first + n_rows, std::memory_order_release);  // publish: searches see a prefix
     return RAGSTORE_OK;
@@ -595,6 +640,7 @@ int ragstore_search(ragstore_t* s, const float* queries, int n_queries, int quer
     SearchCtx& c = s->ctxs[ci];
 
     int kp0 = choose_kp(take);
+    const int hs = take;  // hits per query in the context buffers (compact: only what is copied back)
     for (int q0 = 0; q0 < n_queries; q0 += kCtxQueries) {
         const int nq = std::min(kCtxQueries, n_queries - q0);
         memcpy(c.h_q, queries + static_cast<size_t>(q0) * s->dim, static_cast<size_t>(nq) * s->dim * sizeof(float));
@@ -607,7 +653,7 @@ int ragstore_search(ragstore_t* s, const float* queries, int n_queries, int quer
             if (batch_pass) {
                 // first pass on the tensor cores; queries whose margin the tf32 scores cannot certify are
                 // redone below by the fp32 scan kernel
-                const int rc = run_batch(s, n, take, c.d_q, nq, c.d_idx, c.d_score, c.d_found, c.d_flags, kMaxKp,
+                const int rc = run_batch(s, n, take, c.d_q, nq, c.d_idx, c.d_score, c.d_found, c.d_flags, hs,
                                          c.batch_scratch, c.st);
                 if (rc) return fail(RAGSTORE_ERR_CUDA, "batched search launch", cudaGetErrorString(static_cast<cudaError_t>(rc)));
             }
@@ -616,16 +662,16 @@ int ragstore_search(ragstore_t* s, const float* queries, int n_queries, int quer
                 ScanArgs a = base_args(s, n, take, kp);
                 a.d_query = c.d_q + static_cast<size_t>(i) * s->dim;
                 a.scratch = c.scratch;
-                a.out_idx = c.d_idx + static_cast<size_t>(i) * kMaxKp;
-                a.out_score = c.d_score + static_cast<size_t>(i) * kMaxKp;
+                a.out_idx = c.d_idx + static_cast<size_t>(i) * hs;
+                a.out_score = c.d_score + static_cast<size_t>(i) * hs;
                 a.out_found = c.d_found + i;
                 a.out_flags = c.d_flags + i;
                 s->n_scan_launches.fetch_add(1, std::memory_order_relaxed);
                 const int rc = launch_scan(a, c.st);
                 if (rc) return fail(RAGSTORE_ERR_CUDA, "scan kernel launch", cudaGetErrorString(static_cast<cudaError_t>(rc)));
             }
-            CU_TRY(cudaMemcpyAsync(c.h_idx, c.d_idx, static_cast<size_t>(nq) * kMaxKp * sizeof(int64_t), cudaMemcpyDeviceToHost, c.st));
-            CU_TRY(cudaMemcpyAsync(c.h_score, c.d_score, static_cast<size_t>(nq) * kMaxKp * sizeof(double), cudaMemcpyDeviceToHost, c.st));
+            CU_TRY(cudaMemcpyAsync(c.h_idx, c.d_idx, static_cast<size_t>(nq) * hs * sizeof(int64_t), cudaMemcpyDeviceToHost, c.st));
+            CU_TRY(cudaMemcpyAsync(c.h_score, c.d_score, static_cast<size_t>(nq) * hs * sizeof(double), cudaMemcpyDeviceToHost, c.st));
             CU_TRY(cudaMemcpyAsync(c.h_found, c.d_found, static_cast<size_t>(nq) * sizeof(int32_t), cudaMemcpyDeviceToHost, c.st));
             CU_TRY(cudaMemcpyAsync(c.h_flags, c.d_flags, static_cast<size_t>(nq) * sizeof(int32_t), cudaMemcpyDeviceToHost, c.st));
             CU_TRY(cudaStreamSynchronize(c.st));
@@ -637,8 +683,8 @@ int ragstore_search(ragstore_t* s, const float* queries, int n_queries, int quer
                     continue;
                 }
                 const size_t o = static_cast<size_t>(q0 + i) * req;
-                memcpy(out_idx + o, c.h_idx + static_cast<size_t>(i) * kMaxKp, sizeof(int64_t) * take);
-                memcpy(out_score + o, c.h_score + static_cast<size_t>(i) * kMaxKp, sizeof(double) * take);
+                memcpy(out_idx + o, c.h_idx + static_cast<size_t>(i) * hs, sizeof(int64_t) * take);
+                memcpy(out_score + o, c.h_score + static_cast<size_t>(i) * hs, sizeof(double) * take);
                 out_found[q0 + i] = c.h_found[i];
                 if (out_flags) out_flags[q0 + i] = c.h_flags[i];
             }

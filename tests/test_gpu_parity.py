@@ -308,3 +308,85 @@ def test_batched_device_search_matches_single_query_path():
         assert cert.mean() > 0.9
         assert np.array_equal(out[0][0][cert], out[1][0][cert])
         assert np.array_equal(out[0][1][cert].view(np.uint64), out[1][1][cert].view(np.uint64))
+
+
+def test_streaming_appends_concurrent_with_searches():
+    """Config-5 semantics: appends run while searches are served; every search must equal the oracle on the prefix
+    of rows that was published when it ran (a batch boundary between the counts read before and after the call)."""
+    import threading
+    d, batch, nb, k = 128, 2000, 20, 10
+    rows = oc.synth_rows(0, batch * nb, d, 31)
+    qs = oc.synth_rows(0, 8, d, 32)
+    results, errors = [], []
+    with rb.RagStore(d, batch * nb) as st:
+        st.add(rows[:batch])
+
+        def writer():
+            try:
+                for b in range(1, nb):
+                    st.add(rows[b * batch:(b + 1) * batch])
+            except Exception as e:   # pragma: no cover
+                errors.append(e)
+
+        def reader(seed):
+            try:
+                i = seed
+                while not done.is_set() or i < seed + 4:
+                    before = st.count()
+                    idx, sc, found, flags = st.search(qs[i % 8], k)
+                    after = st.count()
+                    results.append((i % 8, before, after, idx[0].copy(), sc[0].copy()))
+                    i += 1
+            except Exception as e:   # pragma: no cover
+                errors.append(e)
+
+        done = threading.Event()
+        readers = [threading.Thread(target=reader, args=(s,)) for s in (0, 3, 5)]
+        w = threading.Thread(target=writer)
+        for t in readers:
+            t.start()
+        w.start()
+        w.join()
+        done.set()
+        for t in readers:
+            t.join()
+        assert not errors, errors
+        assert st.count() == batch * nb
+    assert len(results) >= 12
+    cache = {}
+    for qi, before, after, idx, sc in results:
+        ok = False
+        for n in range(before, after + 1, batch):      # prefixes are whole batches
+            if n % batch:
+                continue
+            key = (qi, n)
+            if key not in cache:
+                cache[key] = oc.query(rows[:n], qs[qi], k, n_threads=4)
+            eidx, esc = cache[key]
+            if list(idx) == list(eidx) and np.array_equal(sc.view(np.uint64), esc.view(np.uint64)):
+                ok = True
+                break
+        assert ok, (qi, before, after, idx)
+
+
+@pytest.mark.parametrize("dtype", [0, 1])
+def test_large_host_add_goes_through_the_chunk_pipeline(dtype):
+    """> 2 pipeline chunks of host rows (32 MB each), non-unit norms so that the sidecar fills across chunks."""
+    n, d, k = 150_000, 192, 10
+    rng = np.random.default_rng(9)
+    rows = oc.synth_rows(0, n, d, 5, round_bf16=(dtype == 1))
+    scale = np.ones((n, 1), dtype=np.float32)
+    scale[::3] = 2.0                                         # every third row is not unit-norm
+    rows = rows * scale
+    q = oc.synth_rows(0, 1, d, 6)[0]
+    flags = rb.RAGSTORE_CREATE_SIDECAR_ON
+    with rb.RagStore(d, n, dtype, 0, flags) as st:
+        st.add(rows)
+        info = st.info()
+        idx, sc, found, fl = st.search(q, k)
+    eidx, esc = oc.query(rows, q, k, n_threads=4)
+    assert info["count"] == n and info["sidecar_rows"] == info["n_inexact_rows"]
+    assert info["n_inexact_rows"] >= n // 3 - 1
+    assert list(idx[0]) == list(eidx)
+    assert np.array_equal(sc[0].view(np.uint64), esc.view(np.uint64))
+    assert fl[0] & rb.RAGSTORE_HIT_EXACT_ROWS
