@@ -12,6 +12,7 @@ Workloads (BASELINE.json configs):
   target10m 10M x 768 fp32, top-10      (north_star target; also measured as `extra.target10m` by default)
   config4   bf16 x 768, top-100, 12.5M rows per GPU (100M over 8), NCCL all-gather merge
   config3   10M x 1024 fp32, 256 queries per step, top-10: the tcgen05/TMEM tf32 GEMM path (single GPU)
+  config5   streaming: 64k-row host batches appended while 1k-query batches are served (any N; block-cyclic)
 N > 1 runs the chosen workload row-sharded with the per-GPU shard size fixed (weak scaling).
 
 value   = corpus vectors scanned per second, whole job, inputs resident in HBM when the clock starts
@@ -38,6 +39,9 @@ WORKLOADS = {
     "config4": (12_500_000, 768, "bf16", 100, "100M x 768 bf16 row-sharded over 8 (12.5M rows per GPU), single query, top-100"),
     "config3": (10_000_000, 1024, "f32", 10, "10M x 1024 fp32 corpus, batched 256 queries, top-10 (tcgen05 tf32 GEMM + exact rescoring)"),
 }
+STREAM = {"name": "config5", "total_rows": 10_000_000, "dim": 768, "top_k": 10, "batch_rows": 65536, "queries_per_batch": 1024,
+          "desc": "streaming ingest + query: 10M x 768 fp32 appended in 64k-row host batches through the upload/normalise kernel "
+                  "while 1k-query batches (top-10) are served; rows dealt block-cyclically over the GPUs"}
 BATCH_QUERIES = {"config3": 256}   # queries per step for the batched (tensor-core) workloads
 CORPUS_SEED, QUERY_SEED = 1234, 5678
 
@@ -318,14 +322,96 @@ def measure_workload(name, args, torch, dist, rb, native, rank, world, dev, do_e
     return res
 
 
+def run_streaming(args, torch, dist, rb, native, rank, world, dev):
+    """config5: host batches appended (K1) by a writer thread while the main thread serves 1k-query batches."""
+    import threading
+    c = STREAM
+    dim, k, B, QB = c["dim"], c["top_k"], c["batch_rows"], c["queries_per_batch"]
+    total = args.rows * world if args.rows else c["total_rows"]
+    n_batches = max(1, total // B // world)                 # batches appended by THIS rank
+    st = rb.RagStore(dim, n_batches * B, rb.RAGSTORE_F32, dev)
+    st.set_row_blocking(B, world, rank)
+    ts = torch.cuda.Stream()
+    with torch.cuda.stream(ts):
+        d_batch = torch.empty((B, dim), dtype=torch.float32, device="cuda")
+        native.synth_fill_device(d_batch, rank * B, B, dim, dim, CORPUS_SEED, device=dev, stream=ts.cuda_stream)
+        h_pin = d_batch.cpu().pin_memory() if args.pinned else None
+        h_batch = h_pin.numpy() if args.pinned else d_batch.cpu().numpy()   # the host-side batch the "application" appends
+        del d_batch
+        d_q = torch.empty((QB, dim), dtype=torch.float32, device="cuda")
+        native.synth_fill_device(d_q, 0, QB, dim, dim, QUERY_SEED, device=dev, stream=ts.cuda_stream)
+        sh = rb.ShardedSearcher(st, rank, world, 0, max_k=k, device=dev)
+        st.add(h_batch)                                      # first batch in before serving starts (also warms up)
+        for _ in range(2):
+            sh.search_batch_device(d_q, QB, k)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        stop = threading.Event()
+        t_ingest = [0.0]
+
+        def writer():
+            t0 = time.perf_counter()
+            for _ in range(n_batches - 1):
+                st.add(h_batch)
+            t_ingest[0] = time.perf_counter() - t0
+            stop.set()
+
+        w = threading.Thread(target=writer)
+        qbatches = 0
+        t0 = time.perf_counter()
+        w.start()
+        with ClockSampler(dev) as clk:
+            while True:
+                # every rank must agree on when to stop: the flag is reduced with the batch
+                flag = torch.tensor([1 if stop.is_set() else 0], dtype=torch.int32, device="cuda")
+                if world > 1:
+                    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+                sh.search_batch_device(d_q, QB, k)
+                ts.synchronize()
+                qbatches += 1
+                if int(flag.item()) == 1:
+                    break
+        w.join()
+        t_serve = time.perf_counter() - t0
+        tt = torch.tensor([t_ingest[0], t_serve], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        t_ing, t_srv = float(tt[0].item()), float(tt[1].item())
+    rows_streamed = (n_batches - 1) * B * world
+    info = st.info()
+    out = None
+    if rank == 0:
+        out = {"metric": "streaming ingest vectors/sec while serving 1k-query batches (top-10)", "value": rows_streamed / t_ing,
+               "unit": "vectors/s", "n_gpus": world, "steps": n_batches - 1, "warmup": 1, "ms_per_step": t_ing / max(1, n_batches - 1) * 1e3,
+               "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+               "queries_per_s": qbatches * QB / t_srv, "query_batches_served": qbatches,
+               "config": {"workload": "config5", "desc": c["desc"], "rows_total": n_batches * B * world, "rows_per_gpu": n_batches * B,
+                          "dim": dim, "top_k": k, "batch_rows": B, "queries_per_batch": QB, "parallelism": f"block-cyclic x{world}",
+                          "start": "one batch per GPU preloaded, the rest appended during the timed region",
+                          "host_batches": "page-locked (direct PCIe copy)" if args.pinned else "pageable (staged through the library's pinned ring)"},
+               "roofline": {"bound": "pcie (host->device copy of the appended rows; not an HBM or tensor bound)",
+                            "achieved": rows_streamed * dim * 4 / t_ing / 1e9 / world, "peak": 64.0, "unit": "GB/s per GPU",
+                            "frac": rows_streamed * dim * 4 / t_ing / 1e9 / world / 64.0, "traffic": None,
+                            "peak_source": "nominal PCIe Gen5 x16"},
+               "cpu_baseline": None,
+               "e2e": {"value": rows_streamed / t_ing, "unit": "vectors/s", "h2d_bytes_per_step": B * dim * 4 * world, "d2h_bytes_per_step": 0,
+                       "api": "ragstore_add (host rows) concurrent with ragstore_search_shard_batch_device + all-gather + merge"},
+               "gpu_launches": int(info["batch_launches"]) * 3 + (n_batches - 1) * 2, "clocks": clk.summary(),
+               "final_count_rank0": info["count"], "sidecar_rows": info["sidecar_rows"]}
+    st.close()
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=400)
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="config2", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default="config2", choices=sorted(WORKLOADS) + ["config5"])
     ap.add_argument("--rows", type=int, default=0, help="override rows per GPU")
+    ap.add_argument("--pinned", action="store_true", help="config5: the application's batches live in page-locked memory")
     ap.add_argument("--no-extra", action="store_true", help="skip the extra target10m / config1 measurements")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
@@ -350,6 +436,13 @@ def main():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
+    if args.workload == "config5":
+        out = run_streaming(args, torch, dist, rb, native, rank, world, local)
+        if rank == 0:
+            print(json.dumps(out), flush=True)
+        if world > 1:
+            dist.destroy_process_group()
+        return
     main_res = measure_workload(args.workload, args, torch, dist, rb, native, rank, world, local)
     extra = {}
     if world == 1 and not args.no_extra and not args.rows:

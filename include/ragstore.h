@@ -108,6 +108,13 @@ RAGSTORE_API int ragstore_count(ragstore_t* s, int64_t* out_rows);
 /* Global id of local row 0 (row-sharded corpora).  Default 0. */
 RAGSTORE_API int ragstore_set_row_base(ragstore_t* s, int64_t row_base);
 
+/* Streaming ingest over several shards: batches of block_rows rows are dealt
+ * round-robin to n_shards stores; with this set, local row r of shard `shard_index` reports the global id
+ * ((r / block_rows) * n_shards + shard_index) * block_rows + r % block_rows (+ row_base), i.e. its place in
+ * the global insertion order -- the row id the reference's single list would have given it (RagIndex.cs:48).
+ * block_rows = 0 switches back to contiguous ids. */
+RAGSTORE_API int ragstore_set_row_blocking(ragstore_t* s, int64_t block_rows, int n_shards, int shard_index);
+
 /* ---- search side -------------------------------------------------------------------------- */
 
 /* Replaces the body of QueryAsync after the embedding call (RagIndex.cs:62-66) for n_queries
@@ -134,6 +141,19 @@ RAGSTORE_API int ragstore_search_device(ragstore_t* s, const float* d_queries, i
  * max(1,top_k) records.  The records of all shards are then all-gathered (NCCL) by the host. */
 RAGSTORE_API int ragstore_search_shard_device(ragstore_t* s, const float* d_query, int top_k,
                                               ragstore_cand* d_out, int32_t* d_flags, void* stream);
+
+/* Batched form of step 1: n_queries queries at once (tensor-core path when eligible); d_out holds
+ * n_queries x max(1,top_k) records, query-major. */
+RAGSTORE_API int ragstore_search_shard_batch_device(ragstore_t* s, const float* d_queries, int n_queries,
+                                                    int top_k, ragstore_cand* d_out, int32_t* d_flags,
+                                                    void* stream);
+
+/* Batched form of step 2: d_gathered is [n_shards][n_queries][per_shard] (what an all-gather of the
+ * per-rank buffers of the call above produces); outputs are n_queries x max(1,top_k). */
+RAGSTORE_API int ragstore_merge_shards_batch_device(const ragstore_cand* d_gathered, int n_shards,
+                                                    int n_queries, int per_shard, int top_k,
+                                                    int64_t* d_idx, double* d_score, int32_t* d_found,
+                                                    int device, void* stream);
 
 /* Row-sharded search, step 2 (every rank, after the all-gather): merge n_shards x per_shard
  * records into the global top max(1,top_k) under (score desc, id asc) -- the order a single

@@ -643,6 +643,7 @@ __global__ void __launch_bounds__(kScanThreads, 1) batch_finalize_kernel(const B
     a.out_score = a.out_score ? a.out_score + static_cast<size_t>(q) * b.out_stride : nullptr;
     a.out_found = a.out_found ? a.out_found + q : nullptr;
     a.out_flags = a.out_flags ? a.out_flags + q : nullptr;
+    a.out_cand = a.out_cand ? a.out_cand + static_cast<size_t>(q) * a.cand_slots : nullptr;
     a.scratch.stamps = nullptr;
     for (int i = tid; i < static_cast<int>(b.qpad); i += kScanThreads) qraw[i] = i < a.dim ? a.d_query[i] : 0.f;
     if (tid == 0) {

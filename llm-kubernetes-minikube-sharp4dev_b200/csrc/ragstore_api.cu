@@ -92,6 +92,8 @@ struct ragstore {
     int64_t capacity = 0;
     std::atomic<int64_t> count{0};
     int64_t row_base = 0;
+    int64_t row_block = 0;
+    int row_nshards = 1, row_shard = 0;
     mutable std::atomic<int64_t> n_scan_launches{0}, n_batch_launches{0};  // kernel launches issued by searches
     VmmBuffer mat_buf, rnorm_buf, exact_buf, slot_buf, raw_buf;  // address-stable, grown on demand
     void* mat = nullptr;
@@ -190,6 +192,9 @@ ScanArgs base_args(const ragstore* s, int64_t n, int take, int kp) {
     a.ld = s->ld;
     a.dtype = s->dtype;
     a.row_base = s->row_base;
+    a.row_block = s->row_block;
+    a.row_nshards = s->row_nshards;
+    a.row_shard = s->row_shard;
     a.k_take = take;
     a.kp = kp;
     a.eps = scan_eps(s->ld, s->dtype);
@@ -356,6 +361,15 @@ int ragstore_set_row_base(ragstore_t* s, int64_t row_base) {
     return RAGSTORE_OK;
 }
 
+int ragstore_set_row_blocking(ragstore_t* s, int64_t block_rows, int n_shards, int shard_index) {
+    if (!s || block_rows < 0 || n_shards < 1 || shard_index < 0 || shard_index >= n_shards)
+        return fail(RAGSTORE_ERR_INVALID, "ragstore_set_row_blocking: bad argument");
+    s->row_block = block_rows;
+    s->row_nshards = n_shards;
+    s->row_shard = shard_index;
+    return RAGSTORE_OK;
+}
+
 int ragstore_add(ragstore_t* s, const float* rows, int64_t n_rows, int row_dim, uint32_t flags, int64_t* out_first_row) {
     if (!s || (!rows && n_rows > 0) || n_rows < 0) return fail(RAGSTORE_ERR_INVALID, "ragstore_add: null/negative argument");
     if (row_dim != s->dim) return fail(RAGSTORE_ERR_INVALID, "ragstore_add: row_dim differs from the store's dim");
@@ -368,12 +382,18 @@ int ragstore_add(ragstore_t* s, const float* rows, int64_t n_rows, int row_dim, 
     if (!g.ok) return fail(RAGSTORE_ERR_CUDA, "cudaSetDevice failed");
     const bool on_device = (flags & RAGSTORE_ADD_DEVICE) != 0;
     const bool in_place = (s->dtype == RAGSTORE_F32);  // fp32: land rows in the matrix, normalise in place
+    bool src_pinned = false;  // page-locked caller memory goes over PCIe directly, without the staging copy
+    if (!on_device) {
+        cudaPointerAttributes pa{};
+        if (cudaPointerGetAttributes(&pa, rows) == cudaSuccess) src_pinned = (pa.type == cudaMemoryTypeHost);
+        cudaGetLastError();
+    }
     const size_t esz = s->elem_size();
     // Two-deep pipeline of ~32 MB chunks: while chunk i is copied over PCIe and normalised, chunk i+1 is being
     // staged into the other pinned buffer (host sources) -- the upload kernel never waits for the CPU copy.
     const int64_t chunk_rows = std::max<int64_t>(1, (int64_t(32) << 20) / (int64_t(s->dim) * 4));
     const size_t chunk_floats = static_cast<size_t>(chunk_rows) * s->dim;
-    if (!on_device && !s->h_stage[0]) {
+    if (!on_device && !src_pinned && !s->h_stage[0]) {
         for (int b = 0; b < 2; ++b) CU_TRY(cudaMallocHost(&s->h_stage[b], chunk_floats * sizeof(float)));
     }
     if (!in_place && !on_device && s->stage_floats < 2 * chunk_floats) {
@@ -439,7 +459,7 @@ int ragstore_add(ragstore_t* s, const float* rows, int64_t n_rows, int row_dim, 
         a.prenormalised = (flags & RAGSTORE_ADD_PRENORMALISED) ? 1 : 0;
         a.inexact_counter = s->d_inexact;
         const float* h2d_src = src;
-        if (!on_device) {  // stage through pinned memory so that the PCIe copy is truly asynchronous
+        if (!on_device && !src_pinned) {  // stage through pinned memory so that the PCIe copy is truly asynchronous
             memcpy(s->h_stage[b], src, static_cast<size_t>(n) * s->dim * sizeof(float));
             h2d_src = s->h_stage[b];
         }
@@ -576,6 +596,66 @@ int ragstore_search_shard_device(ragstore_t* s, const float* d_query, int top_k,
     return RAGSTORE_OK;
 }
 
+int ragstore_search_shard_batch_device(ragstore_t* s, const float* d_queries, int n_queries, int top_k, ragstore_cand* d_out,
+                                       int32_t* d_flags, void* stream) {
+    if (!s || !d_queries || !d_out || n_queries < 1) return fail(RAGSTORE_ERR_INVALID, "ragstore_search_shard_batch_device: bad argument");
+    DeviceGuard g(s->device);
+    cudaStream_t st = stream ? static_cast<cudaStream_t>(stream) : s->dev_stream;
+    const int64_t n = s->count.load(std::memory_order_acquire);
+    const int req = top_k < 1 ? 1 : top_k;
+    if (req > kMaxKp) return fail(RAGSTORE_ERR_UNSUPPORTED, "top_k above 256 is not covered yet");
+    const int take = static_cast<int>(std::min<int64_t>(n, req));
+    // padding first ({NaN, -1}); shards with rows then overwrite their first `take` records per query
+    CU_TRY(cudaMemsetAsync(d_out, 0xFF, sizeof(ragstore_cand) * static_cast<size_t>(req) * n_queries, st));
+    if (d_flags) CU_TRY(cudaMemsetAsync(d_flags, 0, sizeof(int32_t) * n_queries, st));
+    if (n == 0) return RAGSTORE_OK;
+    const int kp = choose_kp(take);
+    if (batch_eligible(s, n, n_queries, kp)) {
+        for (int q0 = 0; q0 < n_queries; q0 += kBatchMaxQ) {
+            const int nq = std::min(kBatchMaxQ, n_queries - q0);
+            BatchSearchArgs b{};
+            b.scan = base_args(s, n, take, 32);
+            b.scan.eps = kBatchEps;
+            b.scan.out_flags = d_flags ? d_flags + q0 : nullptr;
+            b.scan.out_cand = d_out + static_cast<size_t>(q0) * req;
+            b.scan.cand_slots = req;
+            b.d_queries = d_queries + static_cast<size_t>(q0) * s->dim;
+            b.nq = nq;
+            b.out_stride = req;
+            b.scratch = s->dev_batch_scratch;
+            s->n_batch_launches.fetch_add(1, std::memory_order_relaxed);
+            const int rc = launch_batch_search(b, st);
+            if (rc) return fail(RAGSTORE_ERR_CUDA, "batched search launch", cudaGetErrorString(static_cast<cudaError_t>(rc)));
+        }
+        return RAGSTORE_OK;
+    }
+    for (int q = 0; q < n_queries; ++q) {
+        ScanArgs a = base_args(s, n, take, kp);
+        a.d_query = d_queries + static_cast<size_t>(q) * s->dim;
+        a.scratch = s->dev_scratch;
+        a.out_flags = d_flags ? d_flags + q : nullptr;
+        a.out_cand = d_out + static_cast<size_t>(q) * req;
+        a.cand_slots = req;
+        s->n_scan_launches.fetch_add(1, std::memory_order_relaxed);
+        const int rc = launch_scan(a, st);
+        if (rc) return fail(RAGSTORE_ERR_CUDA, "scan kernel launch", cudaGetErrorString(static_cast<cudaError_t>(rc)));
+    }
+    return RAGSTORE_OK;
+}
+
+int ragstore_merge_shards_batch_device(const ragstore_cand* d_gathered, int n_shards, int n_queries, int per_shard, int top_k,
+                                       int64_t* d_idx, double* d_score, int32_t* d_found, int device, void* stream) {
+    if (!d_gathered || !d_idx || !d_score || !d_found || n_shards <= 0 || per_shard <= 0 || n_queries <= 0)
+        return fail(RAGSTORE_ERR_INVALID, "ragstore_merge_shards_batch_device: bad argument");
+    DeviceGuard g(device);
+    if (!g.ok) return fail(RAGSTORE_ERR_NO_DEVICE, "ragstore_merge_shards_batch_device: no such device");
+    const int req = top_k < 1 ? 1 : top_k;
+    const int rc = launch_merge_shards(d_gathered, n_shards, n_queries, per_shard, req, d_idx, d_score, d_found,
+                                       static_cast<cudaStream_t>(stream));
+    if (rc) return fail(RAGSTORE_ERR_CUDA, "merge kernel launch", cudaGetErrorString(static_cast<cudaError_t>(rc)));
+    return RAGSTORE_OK;
+}
+
 int ragstore_merge_shards_device(const ragstore_cand* d_gathered, int n_shards, int per_shard, int top_k,
                                  int64_t* d_idx, double* d_score, int32_t* d_found, int device, void* stream) {
     if (!d_gathered || !d_idx || !d_score || !d_found || n_shards <= 0 || per_shard <= 0)
@@ -583,7 +663,7 @@ int ragstore_merge_shards_device(const ragstore_cand* d_gathered, int n_shards, 
     DeviceGuard g(device);
     if (!g.ok) return fail(RAGSTORE_ERR_NO_DEVICE, "ragstore_merge_shards_device: no such device");
     const int req = top_k < 1 ? 1 : top_k;
-    const int rc = launch_merge_shards(d_gathered, n_shards * per_shard, req, d_idx, d_score, d_found,
+    const int rc = launch_merge_shards(d_gathered, n_shards, 1, per_shard, req, d_idx, d_score, d_found,
                                        static_cast<cudaStream_t>(stream));
     if (rc) return fail(RAGSTORE_ERR_CUDA, "merge kernel launch", cudaGetErrorString(static_cast<cudaError_t>(rc)));
     return RAGSTORE_OK;

@@ -33,6 +33,8 @@ struct ScanArgs {
     int64_t n_rows;
     int dim, ld, dtype;
     int64_t row_base;
+    int64_t row_block;      // > 0: block-cyclic global ids (streaming ingest over several shards), see global_row_id()
+    int row_nshards, row_shard;
     // query + selection
     const float* d_query;   // raw fp32 [dim]
     int k_take;             // min(n_rows, max(1, top_k))
@@ -91,7 +93,7 @@ int launch_batch_search(const BatchSearchArgs& b, cudaStream_t stream);
 int launch_synth(float* d_out, int64_t row0, int64_t n_rows, int dim, int64_t ld, uint64_t seed,
                  int round_bf16, cudaStream_t stream);
 
-int launch_merge_shards(const ragstore_cand* d_gathered, int n_items, int k_take, int64_t* d_idx,
-                        double* d_score, int32_t* d_found, cudaStream_t stream);
+int launch_merge_shards(const ragstore_cand* d_gathered, int n_shards, int n_queries, int per_shard, int k_take,
+                        int64_t* d_idx, double* d_score, int32_t* d_found, cudaStream_t stream);
 
 }  // namespace rag

@@ -147,6 +147,15 @@ __device__ __forceinline__ double exact_chain(const uint8_t* row, bool f32row, c
 // Shared by the single-query scan (its last CTA) and the batched path (one CTA per query): merges
 // `nlists` sorted candidate lists of kp keys from global memory, rescores the survivors with the
 // reference's fp64 arithmetic (RagIndex.cs:124-135), orders them (:64-66) and writes the hits.
+// Global id of a local row.  Contiguous shards: row_base + local.  Streaming ingest spreads batches of
+// `row_block` rows round-robin over `row_nshards` shards; the global id is then the row's position in the
+// global insertion order, so (score desc, id asc) is the order of one index fed with the same stream.
+__device__ __forceinline__ int64_t global_row_id(const ScanArgs& a, uint32_t local) {
+    if (a.row_block <= 0) return a.row_base + static_cast<int64_t>(local);
+    const int64_t blk = static_cast<int64_t>(local) / a.row_block, off = static_cast<int64_t>(local) % a.row_block;
+    return a.row_base + (blk * a.row_nshards + a.row_shard) * a.row_block + off;
+}
+
 struct FinalizeCtx {
     uint8_t* ring;          // idle shared memory used as staging space
     uint32_t ring_bytes;
@@ -276,7 +285,7 @@ __device__ __forceinline__ void finalize_candidates(const ScanArgs& a, const Fin
             const uint32_t ru = key_row(lists[u]);
             rank += (ku > kc) || (ku == kc && ru < rc);
         }
-        const int64_t gid = a.row_base + static_cast<int64_t>(rc);
+        const int64_t gid = global_row_id(a, rc);
         if (rank < a.k_take) {
             if (a.out_idx) a.out_idx[rank] = gid;
             if (a.out_score) a.out_score[rank] = sc;

@@ -50,6 +50,9 @@ def lib():
             "ragstore_search": (C.c_int, [vp, f32p, C.c_int, C.c_int, C.c_int, i64p, f64p, i32p, i32p]),
             "ragstore_search_device": (C.c_int, [vp, vp, C.c_int, C.c_int, vp, vp, vp, vp, vp]),
             "ragstore_search_shard_device": (C.c_int, [vp, vp, C.c_int, vp, vp, vp]),
+            "ragstore_set_row_blocking": (C.c_int, [vp, C.c_int64, C.c_int, C.c_int]),
+            "ragstore_search_shard_batch_device": (C.c_int, [vp, vp, C.c_int, C.c_int, vp, vp, vp]),
+            "ragstore_merge_shards_batch_device": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, vp, vp, C.c_int, vp]),
             "ragstore_merge_shards_device": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, vp, vp, vp, C.c_int, vp]),
             "ragstore_info": (C.c_int, [vp, i64p, C.c_int]),
             "ragstore_search_noalloc": (C.c_int, [vp, vp, C.c_int64, C.c_int, C.c_int, vp, C.c_int, vp, vp, vp, vp, C.c_int, vp]),
@@ -136,6 +139,13 @@ class RagStore:
     def set_row_base(self, base: int):
         check(lib().ragstore_set_row_base(self._h, base))
 
+    def set_row_blocking(self, block_rows: int, n_shards: int, shard_index: int):
+        check(lib().ragstore_set_row_blocking(self._h, block_rows, n_shards, shard_index))
+
+    def search_shard_batch_device(self, d_queries, n_queries: int, top_k: int, d_cand, d_flags=None, stream: int = 0):
+        check(lib().ragstore_search_shard_batch_device(self._h, _ptr(d_queries), n_queries, int(top_k), _ptr(d_cand), _ptr(d_flags),
+                                                       C.c_void_p(stream)))
+
     def info(self) -> dict:
         v = (C.c_int64 * 14)()
         check(lib().ragstore_info(self._h, v, 14))
@@ -190,6 +200,12 @@ def search_noalloc(d_matrix, d_rnorm, n_rows: int, dim: int, dtype: int, d_query
 def merge_shards_device(d_gathered, n_shards: int, per_shard: int, top_k: int, d_idx, d_score, d_found, device: int = 0, stream: int = 0):
     check(lib().ragstore_merge_shards_device(_ptr(d_gathered), n_shards, per_shard, int(top_k), _ptr(d_idx), _ptr(d_score),
                                              _ptr(d_found), device, C.c_void_p(stream)))
+
+
+def merge_shards_batch_device(d_gathered, n_shards: int, n_queries: int, per_shard: int, top_k: int, d_idx, d_score, d_found,
+                              device: int = 0, stream: int = 0):
+    check(lib().ragstore_merge_shards_batch_device(_ptr(d_gathered), n_shards, n_queries, per_shard, int(top_k), _ptr(d_idx),
+                                                   _ptr(d_score), _ptr(d_found), device, C.c_void_p(stream)))
 
 
 def synth_fill_device(d_out, row0: int, n_rows: int, dim: int, ld: int, seed: int, round_bf16: bool = False, device: int = 0, stream: int = 0):

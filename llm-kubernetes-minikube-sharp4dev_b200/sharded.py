@@ -64,6 +64,29 @@ class ShardedSearcher:
         self.native.merge_shards_device(src, self.world, req, k, self.d_idx, self.d_score, self.d_found,
                                         device=self.device, stream=stream)
 
+    def search_batch_device(self, d_queries, n_queries: int, k: int):
+        """Batched form (tensor-core path on each shard): returns device tensors (idx [nq, k], score, found)."""
+        torch = self.torch
+        req = max(1, int(k))
+        need = n_queries * req * CAND_BYTES
+        if getattr(self, "_b_cap", 0) < need:
+            self._b_cand = torch.zeros(need, dtype=torch.uint8, device="cuda")
+            self._b_all = torch.zeros(self.world * need, dtype=torch.uint8, device="cuda")
+            self._b_idx = torch.zeros(n_queries * req, dtype=torch.int64, device="cuda")
+            self._b_score = torch.zeros(n_queries * req, dtype=torch.float64, device="cuda")
+            self._b_found = torch.zeros(n_queries, dtype=torch.int32, device="cuda")
+            self._b_cap = need
+        stream = torch.cuda.current_stream().cuda_stream
+        self.store.search_shard_batch_device(d_queries, n_queries, k, self._b_cand, None, stream=stream)
+        if self.world > 1:
+            self._all_gather(self._b_all[: self.world * need], self._b_cand[:need])
+            src = self._b_all
+        else:
+            src = self._b_cand
+        self.native.merge_shards_batch_device(src, self.world, n_queries, req, k, self._b_idx, self._b_score, self._b_found,
+                                              device=self.device, stream=stream)
+        return self._b_idx[: n_queries * req].view(n_queries, req), self._b_score[: n_queries * req].view(n_queries, req), self._b_found[:n_queries]
+
     def search(self, d_query, k: int):
         self.search_device(d_query, k)
         self.torch.cuda.current_stream().synchronize()

@@ -390,3 +390,39 @@ def test_large_host_add_goes_through_the_chunk_pipeline(dtype):
     assert list(idx[0]) == list(eidx)
     assert np.array_equal(sc[0].view(np.uint64), esc.view(np.uint64))
     assert fl[0] & rb.RAGSTORE_HIT_EXACT_ROWS
+
+
+@pytest.mark.parametrize("nq", [3, 40])
+def test_block_cyclic_shards_batched_queries(nq):
+    """Streaming over 2 shards: batches of 1000 rows dealt round-robin; global id = place in the insertion order.
+    Batched shard search (tensor-core path for nq >= 16) + batched merge must equal one index over the stream."""
+    import torch
+    from ragstore_b200 import native
+    d, block, nb, k, world = 128, 1000, 14, 10, 2
+    full = oc.synth_rows(0, block * nb, d, 77)
+    full[block * 3 + 5] = full[17]          # duplicates living in different shards
+    full[block * 6 + 1] = full[17]
+    qs = oc.synth_rows(0, nq, d, 78)
+    qs[0] = full[17]
+    stores = [rb.RagStore(d, block * nb, rb.RAGSTORE_F32) for _ in range(world)]
+    for s, st in enumerate(stores):
+        st.set_row_blocking(block, world, s)
+    for j in range(nb):
+        stores[j % world].add(full[j * block:(j + 1) * block])
+    d_q = torch.from_numpy(qs).cuda()
+    d_all = torch.zeros(world * nq * k * 16, dtype=torch.uint8, device="cuda")
+    stream = torch.cuda.Stream()
+    for s, st in enumerate(stores):
+        st.search_shard_batch_device(d_q, nq, k, d_all[s * nq * k * 16:], None, stream=stream.cuda_stream)
+    d_idx = torch.zeros((nq, k), dtype=torch.int64, device="cuda")
+    d_sc = torch.zeros((nq, k), dtype=torch.float64, device="cuda")
+    d_found = torch.zeros(nq, dtype=torch.int32, device="cuda")
+    native.merge_shards_batch_device(d_all, world, nq, k, k, d_idx, d_sc, d_found, stream=stream.cuda_stream)
+    stream.synchronize()
+    idx, sc = d_idx.cpu().numpy(), d_sc.cpu().numpy()
+    for i in range(nq):
+        eidx, esc = oc.query(full, qs[i], k, n_threads=4)
+        assert list(idx[i]) == list(eidx), i
+        assert np.array_equal(sc[i].view(np.uint64), esc.view(np.uint64)), i
+    for st in stores:
+        st.close()
