@@ -6,6 +6,7 @@
 // LINQ search becomes one fused kernel launch per query.  There is no CPU scoring path in this
 // library: without a CUDA device every call fails with RAGSTORE_ERR_NO_DEVICE.
 #include <atomic>
+#include <chrono>
 #include <condition_variable>
 #include <cstdio>
 #include <cstring>
@@ -115,6 +116,23 @@ struct ragstore {
     float* h_stage[2] = {nullptr, nullptr};   // pinned host staging, one per pipeline slot
     cudaEvent_t ingest_ev[2] = {nullptr, nullptr};
     unsigned long long* h_counters = nullptr; // pinned: per slot [inexact rows, sidecar rows]
+    // coalescing of concurrent single-query callers (ragstore_search_coalesced)
+    struct Pending {
+        const float* q;
+        int top_k;
+        int64_t* idx;
+        double* score;
+        int32_t* found;
+        int32_t* flags;
+        int status = 0;
+        bool done = false;
+        std::string err;
+    };
+    std::mutex co_mu;
+    std::condition_variable co_cv;
+    std::vector<Pending*> co_queue;
+    bool co_leader = false;
+    int co_window_us = 150, co_max_batch = 256;
     ScanScratch dev_scratch{};
     uint8_t* dev_batch_scratch = nullptr;
     std::vector<SearchCtx> ctxs;
@@ -776,6 +794,76 @@ int ragstore_search(ragstore_t* s, const float* queries, int n_queries, int quer
         }
     }
     return RAGSTORE_OK;
+}
+
+int ragstore_set_coalescing(ragstore_t* s, int window_us, int max_batch) {
+    if (!s || window_us < 0 || max_batch < 1) return fail(RAGSTORE_ERR_INVALID, "ragstore_set_coalescing: bad argument");
+    std::lock_guard<std::mutex> lk(s->co_mu);
+    s->co_window_us = window_us;
+    s->co_max_batch = std::min(max_batch, 1024);
+    return RAGSTORE_OK;
+}
+
+int ragstore_search_coalesced(ragstore_t* s, const float* query, int query_dim, int top_k, int64_t* out_idx, double* out_score,
+                              int32_t* out_found, int32_t* out_flags) {
+    if (!s || !query || !out_idx || !out_score || !out_found) return fail(RAGSTORE_ERR_INVALID, "ragstore_search_coalesced: null argument");
+    if (query_dim != s->dim)  // the -1 corner case needs no GPU work: answer it directly
+        return ragstore_search(s, query, 1, query_dim, top_k, out_idx, out_score, out_found, out_flags);
+    ragstore::Pending me{query, top_k, out_idx, out_score, out_found, out_flags};
+    std::unique_lock<std::mutex> lk(s->co_mu);
+    s->co_queue.push_back(&me);
+    if (s->co_leader) {
+        s->co_cv.notify_all();  // lets a waiting leader see that its batch has grown
+        s->co_cv.wait(lk, [&] { return me.done; });
+        if (me.status) g_err = me.err;
+        return me.status;
+    }
+    s->co_leader = true;  // this caller runs batches until the queue is empty
+    std::vector<float> qbuf;
+    std::vector<int64_t> ibuf;
+    std::vector<double> sbuf;
+    std::vector<int32_t> fbuf, gbuf;
+    while (!s->co_queue.empty()) {
+        // give concurrent callers a short window to join the batch
+        const auto deadline = std::chrono::steady_clock::now() + std::chrono::microseconds(s->co_window_us);
+        s->co_cv.wait_until(lk, deadline, [&] { return static_cast<int>(s->co_queue.size()) >= s->co_max_batch; });
+        const int nb = std::min<int>(static_cast<int>(s->co_queue.size()), s->co_max_batch);
+        std::vector<ragstore::Pending*> batch(s->co_queue.begin(), s->co_queue.begin() + nb);
+        s->co_queue.erase(s->co_queue.begin(), s->co_queue.begin() + nb);
+        lk.unlock();
+        int kmax = 1;
+        for (auto* p : batch) kmax = std::max(kmax, p->top_k);
+        qbuf.resize(static_cast<size_t>(nb) * s->dim);
+        ibuf.resize(static_cast<size_t>(nb) * kmax);
+        sbuf.resize(static_cast<size_t>(nb) * kmax);
+        fbuf.resize(nb);
+        gbuf.resize(nb);
+        for (int i = 0; i < nb; ++i) memcpy(qbuf.data() + static_cast<size_t>(i) * s->dim, batch[i]->q, sizeof(float) * s->dim);
+        // one sweep of the corpus for the whole batch (tensor-core path from 16 queries up)
+        const int rc = ragstore_search(s, qbuf.data(), nb, s->dim, kmax, ibuf.data(), sbuf.data(), fbuf.data(), gbuf.data());
+        const std::string err = rc ? g_err : std::string();
+        for (int i = 0; i < nb; ++i) {
+            ragstore::Pending* p = batch[i];
+            if (!rc) {
+                // a hit list for k is the prefix of the hit list for any larger k (the order is total)
+                const int want = p->top_k < 1 ? 1 : p->top_k;
+                const int n = std::min(want, fbuf[i]);
+                memcpy(p->idx, ibuf.data() + static_cast<size_t>(i) * kmax, sizeof(int64_t) * n);
+                memcpy(p->score, sbuf.data() + static_cast<size_t>(i) * kmax, sizeof(double) * n);
+                *p->found = n;
+                if (p->flags) *p->flags = gbuf[i];
+            }
+            p->status = rc;
+            p->err = err;
+        }
+        lk.lock();
+        for (auto* p : batch) p->done = true;
+        s->co_cv.notify_all();
+    }
+    s->co_leader = false;
+    lk.unlock();
+    if (me.status) g_err = me.err;
+    return me.status;
 }
 
 int ragstore_synth_fill_device(float* d_out, int64_t row0, int64_t n_rows, int dim, int64_t ld, uint64_t seed,

@@ -48,6 +48,8 @@ def lib():
             "ragstore_count": (C.c_int, [vp, i64p]),
             "ragstore_set_row_base": (C.c_int, [vp, C.c_int64]),
             "ragstore_search": (C.c_int, [vp, f32p, C.c_int, C.c_int, C.c_int, i64p, f64p, i32p, i32p]),
+            "ragstore_search_coalesced": (C.c_int, [vp, f32p, C.c_int, C.c_int, i64p, f64p, i32p, i32p]),
+            "ragstore_set_coalescing": (C.c_int, [vp, C.c_int, C.c_int]),
             "ragstore_search_device": (C.c_int, [vp, vp, C.c_int, C.c_int, vp, vp, vp, vp, vp]),
             "ragstore_search_shard_device": (C.c_int, [vp, vp, C.c_int, vp, vp, vp]),
             "ragstore_set_row_blocking": (C.c_int, [vp, C.c_int64, C.c_int, C.c_int]),
@@ -178,6 +180,21 @@ class RagStore:
                                     idx.ctypes.data_as(C.POINTER(C.c_int64)), score.ctypes.data_as(C.POINTER(C.c_double)),
                                     found.ctypes.data_as(C.POINTER(C.c_int32)), flags.ctypes.data_as(C.POINTER(C.c_int32))))
         return idx, score, found, flags
+
+    def search_coalesced(self, query: np.ndarray, top_k: int):
+        """One query per call; concurrent callers share a corpus sweep (ragstore_search_coalesced)."""
+        q = np.ascontiguousarray(query, dtype=np.float32).reshape(-1)
+        req = max(1, int(top_k))
+        idx = np.full(req, -1, dtype=np.int64)
+        score = np.full(req, np.nan, dtype=np.float64)
+        found, flags = C.c_int32(0), C.c_int32(0)
+        check(lib().ragstore_search_coalesced(self._h, q.ctypes.data_as(C.POINTER(C.c_float)), q.shape[0], int(top_k),
+                                              idx.ctypes.data_as(C.POINTER(C.c_int64)), score.ctypes.data_as(C.POINTER(C.c_double)),
+                                              C.byref(found), C.byref(flags)))
+        return idx[:found.value], score[:found.value], flags.value
+
+    def set_coalescing(self, window_us: int, max_batch: int = 256):
+        check(lib().ragstore_set_coalescing(self._h, window_us, max_batch))
 
     # ---- device-resident variants (torch tensors or raw pointers), asynchronous on `stream`
     def search_device(self, d_queries, n_queries: int, top_k: int, d_idx, d_score, d_found=None, d_flags=None, stream: int = 0):

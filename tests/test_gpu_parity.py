@@ -426,3 +426,38 @@ def test_block_cyclic_shards_batched_queries(nq):
         assert np.array_equal(sc[i].view(np.uint64), esc.view(np.uint64)), i
     for st in stores:
         st.close()
+
+
+def test_concurrent_single_queries_are_coalesced():
+    """N1: many threads each ask ONE query (the ASP.NET handlers of the reference); callers arriving together share a
+    corpus sweep.  Every caller must get exactly what a lone QueryAsync would return, for its own k."""
+    import threading
+    n, d, nthreads = 30000, 256, 64
+    rows = oc.synth_rows(0, n, d, 3)
+    qs = oc.synth_rows(0, nthreads, d, 4)
+    ks = [5 if i % 3 else 10 for i in range(nthreads)]
+    out = [None] * nthreads
+    with rb.RagStore(d, n) as st:
+        st.add(rows)
+        st.set_coalescing(20000, 256)        # generous window so that the threads of this test really meet
+        start = threading.Barrier(nthreads)
+
+        def ask(i):
+            start.wait()
+            out[i] = st.search_coalesced(qs[i], ks[i])
+
+        ts = [threading.Thread(target=ask, args=(i,)) for i in range(nthreads)]
+        for t in ts:
+            t.start()
+        for t in ts:
+            t.join()
+        info = st.info()
+        lone = st.search_coalesced(qs[0], 7)          # a lone caller still gets its answer (after the window)
+    assert info["batch_launches"] >= 1 and info["batch_launches"] + info["scan_launches"] < nthreads // 2
+    for i in range(nthreads):
+        eidx, esc = oc.query(rows, qs[i], ks[i], n_threads=2)
+        idx, sc, flags = out[i]
+        assert list(idx) == list(eidx), i
+        assert np.array_equal(sc.view(np.uint64), esc.view(np.uint64)), i
+    eidx, esc = oc.query(rows, qs[0], 7)
+    assert list(lone[0]) == list(eidx) and np.array_equal(lone[1].view(np.uint64), esc.view(np.uint64))
