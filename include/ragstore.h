@@ -198,6 +198,22 @@ RAGSTORE_API int ragstore_search_noalloc(const void* d_matrix, const float* d_rn
 RAGSTORE_API int64_t ragstore_noalloc_scratch_bytes(void);
 RAGSTORE_API const char* ragstore_noalloc_last_error(void);
 
+/* the score post-filters the two callers apply to a hit list, computed in one place:
+ *   out_best       hits.Max(h => h.Score)                                  (Program.cs:77, :125)
+ *   out_low_score  best < low_score_floor   (0.20 in /rag/search)           (Program.cs:78,82)
+ *   out_cited[i]   scores[i] >= max(evidence_min_score, best * best_factor) (0.35 and 0.6 in /agent_rag, :126)
+ * Pure host arithmetic on <= k doubles; any output may be NULL. */
+RAGSTORE_API int ragstore_hit_filters(const double* scores, int found, double evidence_min_score,
+                                      double best_factor, double low_score_floor, uint8_t* out_cited,
+                                      double* out_best, int32_t* out_low_score);
+
+/* the reference rebuilds its index from text at every start (Program.cs:50: one embedding
+ * HTTP call per chunk).  ragstore_save writes the device-resident store (normalised matrix, reciprocal
+ * norms, exact flags, sidecar) as one flat little-endian image; ragstore_load maps it back into HBM.
+ * A loaded store answers exactly as the saved one did.  capacity_rows: 0 = just the saved rows. */
+RAGSTORE_API int ragstore_save(ragstore_t* s, const char* path);
+RAGSTORE_API int ragstore_load(const char* path, int device, int64_t capacity_rows, ragstore_t** out);
+
 /* ---- utilities ----------------------------------------------------------------------------- */
 
 /* Last error text of the calling thread (empty string if none). Returns the length written. */

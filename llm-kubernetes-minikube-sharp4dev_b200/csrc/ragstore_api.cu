@@ -796,6 +796,151 @@ int ragstore_search(ragstore_t* s, const float* queries, int n_queries, int quer
     return RAGSTORE_OK;
 }
 
+int ragstore_hit_filters(const double* scores, int found, double evidence_min_score, double best_factor,
+                         double low_score_floor, uint8_t* out_cited, double* out_best, int32_t* out_low_score) {
+    if (found < 0 || (found > 0 && !scores)) return fail(RAGSTORE_ERR_INVALID, "ragstore_hit_filters: bad argument");
+    if (found == 0) {  // the callers return early on an empty hit list (Program.cs:74,117)
+        if (out_best) *out_best = 0.0;
+        if (out_low_score) *out_low_score = 0;
+        return RAGSTORE_OK;
+    }
+    double best = scores[0];  // hits.Max(h => h.Score): NaN never wins a comparison, as in Enumerable.Max
+    for (int i = 1; i < found; ++i)
+        if (scores[i] > best || best != best) best = scores[i];
+    const double cut = evidence_min_score > best * best_factor ? evidence_min_score : best * best_factor;  // Math.Max (:126)
+    if (out_cited)
+        for (int i = 0; i < found; ++i) out_cited[i] = scores[i] >= cut ? 1 : 0;
+    if (out_best) *out_best = best;
+    if (out_low_score) *out_low_score = best < low_score_floor ? 1 : 0;  // :82
+    return RAGSTORE_OK;
+}
+
+// ---------------------------------------------------------------- persistence
+namespace {
+struct SaveHeader {
+    char magic[8];  // "RAGSTOR1"
+    int32_t version, dim, ld, dtype, has_sidecar, raw_ld;
+    uint32_t min_norm_bits, pad;
+    int64_t count, inexact_rows, sidecar_rows;
+};
+
+int copy_out(FILE* f, const void* d_src, size_t bytes, void* h_pin, size_t pin_bytes) {
+    const uint8_t* p = static_cast<const uint8_t*>(d_src);
+    for (size_t off = 0; off < bytes; off += pin_bytes) {
+        const size_t n = std::min(pin_bytes, bytes - off);
+        CU_TRY(cudaMemcpy(h_pin, p + off, n, cudaMemcpyDeviceToHost));
+        if (fwrite(h_pin, 1, n, f) != n) return fail(RAGSTORE_ERR_INVALID, "ragstore_save: short write");
+    }
+    return RAGSTORE_OK;
+}
+int copy_in(FILE* f, void* d_dst, size_t bytes, void* h_pin, size_t pin_bytes) {
+    uint8_t* p = static_cast<uint8_t*>(d_dst);
+    for (size_t off = 0; off < bytes; off += pin_bytes) {
+        const size_t n = std::min(pin_bytes, bytes - off);
+        if (fread(h_pin, 1, n, f) != n) return fail(RAGSTORE_ERR_INVALID, "ragstore_load: file truncated");
+        CU_TRY(cudaMemcpy(p + off, h_pin, n, cudaMemcpyHostToDevice));
+    }
+    return RAGSTORE_OK;
+}
+}  // namespace
+
+int ragstore_save(ragstore_t* s, const char* path) {
+    if (!s || !path) return fail(RAGSTORE_ERR_INVALID, "ragstore_save: null argument");
+    std::lock_guard<std::mutex> lk(s->add_mu);  // no append while the image is written
+    DeviceGuard g(s->device);
+    FILE* f = fopen(path, "wb");
+    if (!f) return fail(RAGSTORE_ERR_INVALID, "ragstore_save: cannot open file", path);
+    const size_t pin_bytes = size_t(32) << 20;
+    void* h_pin = nullptr;
+    if (cudaMallocHost(&h_pin, pin_bytes) != cudaSuccess) {
+        fclose(f);
+        return fail(RAGSTORE_ERR_CUDA, "ragstore_save: cudaMallocHost");
+    }
+    SaveHeader h{};
+    memcpy(h.magic, "RAGSTOR1", 8);
+    h.version = 1;
+    h.dim = s->dim;
+    h.ld = s->ld;
+    h.dtype = s->dtype;
+    h.has_sidecar = s->raw_slot ? 1 : 0;
+    h.raw_ld = s->raw_ld;
+    h.count = s->count.load();
+    h.inexact_rows = s->inexact_rows;
+    h.sidecar_rows = s->raw_used;
+    int rc = RAGSTORE_OK;
+    if (cudaMemcpy(&h.min_norm_bits, s->d_min_norm, 4, cudaMemcpyDeviceToHost) != cudaSuccess) rc = fail(RAGSTORE_ERR_CUDA, "ragstore_save: read min norm");
+    if (!rc && fwrite(&h, sizeof(h), 1, f) != 1) rc = fail(RAGSTORE_ERR_INVALID, "ragstore_save: short write");
+    const size_t n = static_cast<size_t>(h.count);
+    if (!rc) rc = copy_out(f, s->mat, n * s->ld * s->elem_size(), h_pin, pin_bytes);
+    if (!rc) rc = copy_out(f, s->rnorm, n * sizeof(float), h_pin, pin_bytes);
+    if (!rc) rc = copy_out(f, s->exact, n, h_pin, pin_bytes);
+    if (!rc && h.has_sidecar) rc = copy_out(f, s->raw_slot, n * sizeof(int32_t), h_pin, pin_bytes);
+    if (!rc && h.has_sidecar) rc = copy_out(f, s->raw_rows, static_cast<size_t>(h.sidecar_rows) * s->raw_ld * sizeof(float), h_pin, pin_bytes);
+    cudaFreeHost(h_pin);
+    if (fclose(f) != 0 && !rc) rc = fail(RAGSTORE_ERR_INVALID, "ragstore_save: close failed");
+    return rc;
+}
+
+int ragstore_load(const char* path, int device, int64_t capacity_rows, ragstore_t** out) {
+    if (!path || !out) return fail(RAGSTORE_ERR_INVALID, "ragstore_load: null argument");
+    *out = nullptr;
+    FILE* f = fopen(path, "rb");
+    if (!f) return fail(RAGSTORE_ERR_INVALID, "ragstore_load: cannot open file", path);
+    SaveHeader h{};
+    if (fread(&h, sizeof(h), 1, f) != 1 || memcmp(h.magic, "RAGSTOR1", 8) != 0 || h.version != 1) {
+        fclose(f);
+        return fail(RAGSTORE_ERR_INVALID, "ragstore_load: not a ragstore image (version 1)");
+    }
+    const int64_t cap = std::max<int64_t>(std::max<int64_t>(capacity_rows, h.count), 1);
+    ragstore_t* s = nullptr;
+    int rc = ragstore_create(h.dim, h.dtype, cap, device, h.has_sidecar ? RAGSTORE_CREATE_SIDECAR_ON : RAGSTORE_CREATE_SIDECAR_OFF, &s);
+    if (rc) {
+        fclose(f);
+        return rc;
+    }
+    if (s->ld != h.ld || s->raw_ld != h.raw_ld) {
+        fclose(f);
+        ragstore_destroy(s);
+        return fail(RAGSTORE_ERR_INVALID, "ragstore_load: image layout differs from this build");
+    }
+    DeviceGuard g(device);
+    const size_t pin_bytes = size_t(32) << 20;
+    void* h_pin = nullptr;
+    if (cudaMallocHost(&h_pin, pin_bytes) != cudaSuccess) rc = fail(RAGSTORE_ERR_CUDA, "ragstore_load: cudaMallocHost");
+    const size_t n = static_cast<size_t>(h.count), n4 = ((n + 3) & ~size_t(3)) + 64;
+    if (!rc && n) {
+        int vr = s->mat_buf.ensure(n * s->ld * s->elem_size(), false, s->ingest_stream);
+        if (!vr) vr = s->rnorm_buf.ensure(n4 * sizeof(float), true, s->ingest_stream);
+        if (!vr) vr = s->exact_buf.ensure(n4, true, s->ingest_stream);
+        if (!vr && h.has_sidecar) vr = s->slot_buf.ensure(n4 * sizeof(int32_t), true, s->ingest_stream);
+        if (!vr && h.has_sidecar && h.sidecar_rows) vr = s->raw_buf.ensure(static_cast<size_t>(h.sidecar_rows) * s->raw_ld * sizeof(float), false, s->ingest_stream);
+        if (vr) rc = fail(RAGSTORE_ERR_CUDA, "ragstore_load: mapping device memory", cudaGetErrorString(static_cast<cudaError_t>(vr)));
+        if (!rc && cudaStreamSynchronize(s->ingest_stream) != cudaSuccess) rc = fail(RAGSTORE_ERR_CUDA, "ragstore_load: sync");
+        if (!rc) rc = copy_in(f, s->mat, n * s->ld * s->elem_size(), h_pin, pin_bytes);
+        if (!rc) rc = copy_in(f, s->rnorm, n * sizeof(float), h_pin, pin_bytes);
+        if (!rc) rc = copy_in(f, s->exact, n, h_pin, pin_bytes);
+        if (!rc && h.has_sidecar) rc = copy_in(f, s->raw_slot, n * sizeof(int32_t), h_pin, pin_bytes);
+        if (!rc && h.has_sidecar) rc = copy_in(f, s->raw_rows, static_cast<size_t>(h.sidecar_rows) * s->raw_ld * sizeof(float), h_pin, pin_bytes);
+    }
+    if (!rc) {
+        const unsigned long long counters[2] = {static_cast<unsigned long long>(h.inexact_rows), static_cast<unsigned long long>(h.sidecar_rows)};
+        if (cudaMemcpy(s->d_inexact, counters, sizeof(counters), cudaMemcpyHostToDevice) != cudaSuccess ||
+            cudaMemcpy(s->d_min_norm, &h.min_norm_bits, 4, cudaMemcpyHostToDevice) != cudaSuccess)
+            rc = fail(RAGSTORE_ERR_CUDA, "ragstore_load: restoring counters");
+    }
+    if (h_pin) cudaFreeHost(h_pin);
+    fclose(f);
+    if (rc) {
+        ragstore_destroy(s);
+        return rc;
+    }
+    s->inexact_rows = h.inexact_rows;
+    s->raw_used = h.sidecar_rows;
+    s->count.store(h.count, std::memory_order_release);
+    *out = s;
+    return RAGSTORE_OK;
+}
+
 int ragstore_set_coalescing(ragstore_t* s, int window_us, int max_batch) {
     if (!s || window_us < 0 || max_batch < 1) return fail(RAGSTORE_ERR_INVALID, "ragstore_set_coalescing: bad argument");
     std::lock_guard<std::mutex> lk(s->co_mu);

@@ -48,6 +48,9 @@ def lib():
             "ragstore_count": (C.c_int, [vp, i64p]),
             "ragstore_set_row_base": (C.c_int, [vp, C.c_int64]),
             "ragstore_search": (C.c_int, [vp, f32p, C.c_int, C.c_int, C.c_int, i64p, f64p, i32p, i32p]),
+            "ragstore_hit_filters": (C.c_int, [f64p, C.c_int, C.c_double, C.c_double, C.c_double, C.POINTER(C.c_uint8), f64p, i32p]),
+            "ragstore_save": (C.c_int, [vp, C.c_char_p]),
+            "ragstore_load": (C.c_int, [C.c_char_p, C.c_int, C.c_int64, C.POINTER(vp)]),
             "ragstore_search_coalesced": (C.c_int, [vp, f32p, C.c_int, C.c_int, i64p, f64p, i32p, i32p]),
             "ragstore_set_coalescing": (C.c_int, [vp, C.c_int, C.c_int]),
             "ragstore_search_device": (C.c_int, [vp, vp, C.c_int, C.c_int, vp, vp, vp, vp, vp]),
@@ -94,10 +97,25 @@ def _ptr(x):
 class RagStore:
     """Owning wrapper of one ragstore_t (one device-resident shard)."""
 
-    def __init__(self, dim: int, capacity_rows: int, dtype: int = RAGSTORE_F32, device: int = 0, flags: int = 0):
-        self._h = C.c_void_p()
-        check(lib().ragstore_create(dim, dtype, capacity_rows, device, flags, C.byref(self._h)))
+    def __init__(self, dim: int, capacity_rows: int, dtype: int = RAGSTORE_F32, device: int = 0, flags: int = 0, _handle=None):
+        if _handle is not None:
+            self._h = _handle
+        else:
+            self._h = C.c_void_p()
+            check(lib().ragstore_create(dim, dtype, capacity_rows, device, flags, C.byref(self._h)))
         self.dim, self.dtype, self.device, self.capacity = dim, dtype, device, capacity_rows
+
+    def save(self, path: str):
+        check(lib().ragstore_save(self._h, path.encode()))
+
+    @classmethod
+    def load(cls, path: str, device: int = 0, capacity_rows: int = 0) -> "RagStore":
+        h = C.c_void_p()
+        check(lib().ragstore_load(path.encode(), device, capacity_rows, C.byref(h)))
+        st = cls(0, 0, 0, device, _handle=h)
+        i = st.info()
+        st.dim, st.dtype, st.capacity = i["dim"], i["dtype"], i["capacity"]
+        return st
 
     def close(self):
         if getattr(self, "_h", None) is not None and self._h:
@@ -212,6 +230,16 @@ def search_noalloc(d_matrix, d_rnorm, n_rows: int, dim: int, dtype: int, d_query
                                        _ptr(d_idx), _ptr(d_score), _ptr(d_found), _ptr(d_flags), device, C.c_void_p(stream))
     if rc != 0:
         raise RagStoreError(rc, lib().ragstore_noalloc_last_error().decode("utf-8", "replace"))
+
+
+def hit_filters(scores, evidence_min_score: float = 0.35, best_factor: float = 0.6, low_score_floor: float = 0.20):
+    """(cited mask, best score, low-score flag) of a hit list: Program.cs:77-89,125-128 in one call."""
+    sc = np.ascontiguousarray(scores, dtype=np.float64)
+    cited = np.zeros(sc.shape[0], dtype=np.uint8)
+    best, low = C.c_double(0.0), C.c_int32(0)
+    check(lib().ragstore_hit_filters(sc.ctypes.data_as(C.POINTER(C.c_double)), sc.shape[0], evidence_min_score, best_factor, low_score_floor,
+                                     cited.ctypes.data_as(C.POINTER(C.c_uint8)), C.byref(best), C.byref(low)))
+    return cited.astype(bool), best.value, bool(low.value)
 
 
 def merge_shards_device(d_gathered, n_shards: int, per_shard: int, top_k: int, d_idx, d_score, d_found, device: int = 0, stream: int = 0):

@@ -45,3 +45,20 @@ def test_product_does_not_import_oracle():
                 txt = open(os.path.join(dirpath, f), errors="replace").read()
                 assert not re.search(r"^\s*(from|import)\s+oracle\b", txt, re.M), f
                 assert "liboracle" not in txt, f
+
+
+def test_hit_filters_match_the_callers_of_the_reference():
+    """N2: /rag/search low-score note (Program.cs:77-89) and /agent_rag citation rule (:125-128), host arithmetic only."""
+    from ragstore_b200 import native
+    scores = [0.71, 0.50, 0.43, 0.42, 0.10, -0.2]
+    cited, best, low = native.hit_filters(scores)                 # max(0.35, 0.6 * 0.71 = 0.426)
+    assert best == 0.71 and not low
+    assert list(cited) == [True, True, True, False, False, False]
+    cited, best, low = native.hit_filters([0.30, 0.19])            # best*0.6 = 0.18 < 0.35 -> nothing cited; not low (0.30 >= 0.20)
+    assert list(cited) == [False, False] and best == 0.30 and not low
+    cited, best, low = native.hit_filters([0.15, 0.12])
+    assert low and best == 0.15
+    cited, best, low = native.hit_filters([])
+    assert list(cited) == [] and not low
+    cited, best, low = native.hit_filters([0.9, 0.54, 0.5399999])  # boundary: >= 0.6*best
+    assert list(cited) == [True, True, False]

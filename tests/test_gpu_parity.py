@@ -461,3 +461,30 @@ def test_concurrent_single_queries_are_coalesced():
         assert np.array_equal(sc.view(np.uint64), esc.view(np.uint64)), i
     eidx, esc = oc.query(rows, qs[0], 7)
     assert list(lone[0]) == list(eidx) and np.array_equal(lone[1].view(np.uint64), esc.view(np.uint64))
+
+
+@pytest.mark.parametrize("dtype", [0, 1])
+def test_save_and_load_round_trip(tmp_path, dtype):
+    """N3: a store image written to disk and mapped back answers exactly as before (including sidecar rows), and
+    keeps accepting appends."""
+    n, d, k = 6000, 200, 10
+    rows = oc.synth_rows(0, n, d, 55, round_bf16=(dtype == 1))
+    rows[::5] *= 3.0                                            # inexact rows -> sidecar
+    q = oc.synth_rows(0, 4, d, 56)
+    path = str(tmp_path / "store.rag")
+    with rb.RagStore(d, n, dtype, 0, rb.RAGSTORE_CREATE_SIDECAR_ON) as st:
+        st.add(rows[:5000])
+        before = st.search(q, k)
+        st.save(path)
+    st2 = rb.RagStore.load(path, capacity_rows=n)
+    try:
+        assert st2.count() == 5000 and st2.info()["sidecar_rows"] > 0
+        after = st2.search(q, k)
+        assert np.array_equal(before[0], after[0]) and np.array_equal(before[1].view(np.uint64), after[1].view(np.uint64))
+        assert np.array_equal(before[3], after[3])
+        st2.add(rows[5000:])
+        idx, sc, found, flags = st2.search(q[0], k)
+        eidx, esc = oc.query(rows, q[0], k, n_threads=4)
+        assert list(idx[0]) == list(eidx) and np.array_equal(sc[0].view(np.uint64), esc.view(np.uint64))
+    finally:
+        st2.close()
