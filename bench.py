@@ -60,8 +60,12 @@ def measured_peaks():
 class ClockSampler:
     """Samples SM clock + throttle reasons through NVML while the timed region runs."""
 
-    def __init__(self, index):
+    def __init__(self, index, enabled=True):
         self.samples, self.reasons, self.max_mhz, self._stop = [], set(), None, threading.Event()
+        self.nv = None
+        if not enabled:          # only rank 0 polls NVML: N processes hammering its global lock perturb each other
+            self.t = None
+            return
         try:
             import pynvml
             pynvml.nvmlInit()
@@ -85,7 +89,7 @@ class ClockSampler:
                         self.reasons.add(k)
             except Exception:
                 pass
-            time.sleep(0.005)
+            time.sleep(0.02)
 
     def __enter__(self):
         if self.nv:
@@ -223,7 +227,7 @@ def measure_workload(name, args, torch, dist, rb, native, rank, world, dev, do_e
                 sh.search_device(q, k)      # shard scan -> NCCL all-gather (world * k * 16 B) -> merge kernel
             launches_per_step = 2
 
-        with ClockSampler(dev) as clk:
+        with ClockSampler(dev, enabled=(rank == 0)) as clk:
             ms = time_device_steps(torch, dist, world, step, args.steps, args.warmup)
         clocks = clk.summary()
         total_rows = rows * world
@@ -361,7 +365,7 @@ def run_streaming(args, torch, dist, rb, native, rank, world, dev):
         qbatches = 0
         t0 = time.perf_counter()
         w.start()
-        with ClockSampler(dev) as clk:
+        with ClockSampler(dev, enabled=(rank == 0)) as clk:
             while True:
                 # every rank must agree on when to stop: the flag is reduced with the batch
                 flag = torch.tensor([1 if stop.is_set() else 0], dtype=torch.int32, device="cuda")
