@@ -166,15 +166,10 @@ int alloc_ctx(SearchCtx& c, int ld, int sm_count) {
     CU_TRY(cudaMalloc(&c.batch_scratch, batch_scratch_bytes(sm_count)));
     const size_t nq = kCtxQueries;
     CU_TRY(cudaMalloc(&c.d_q, nq * ld * sizeof(float)));
-    CU_TRY(cudaMalloc(&c.d_idx, nq * kMaxKp * sizeof(int64_t)));
-    CU_TRY(cudaMalloc(&c.d_score, nq * kMaxKp * sizeof(double)));
-    CU_TRY(cudaMalloc(&c.d_found, nq * sizeof(int32_t)));
-    CU_TRY(cudaMalloc(&c.d_flags, nq * sizeof(int32_t)));
+    // one block per side: [idx][score][found][flags] packed per call, so the hits come back in ONE copy
+    CU_TRY(cudaMalloc(&c.d_idx, nq * kMaxKp * 16 + nq * 8));
     CU_TRY(cudaMallocHost(&c.h_q, nq * ld * sizeof(float)));
-    CU_TRY(cudaMallocHost(&c.h_idx, nq * kMaxKp * sizeof(int64_t)));
-    CU_TRY(cudaMallocHost(&c.h_score, nq * kMaxKp * sizeof(double)));
-    CU_TRY(cudaMallocHost(&c.h_found, nq * sizeof(int32_t)));
-    CU_TRY(cudaMallocHost(&c.h_flags, nq * sizeof(int32_t)));
+    CU_TRY(cudaMallocHost(&c.h_idx, nq * kMaxKp * 16 + nq * 8));
     return RAGSTORE_OK;
 }
 
@@ -184,14 +179,8 @@ void free_ctx(SearchCtx& c) {
     cudaFree(c.batch_scratch);
     cudaFree(c.d_q);
     cudaFree(c.d_idx);
-    cudaFree(c.d_score);
-    cudaFree(c.d_found);
-    cudaFree(c.d_flags);
     cudaFreeHost(c.h_q);
     cudaFreeHost(c.h_idx);
-    cudaFreeHost(c.h_score);
-    cudaFreeHost(c.h_found);
-    cudaFreeHost(c.h_flags);
     c = SearchCtx{};
 }
 
@@ -741,6 +730,15 @@ int ragstore_search(ragstore_t* s, const float* queries, int n_queries, int quer
     const int hs = take;  // hits per query in the context buffers (compact: only what is copied back)
     for (int q0 = 0; q0 < n_queries; q0 += kCtxQueries) {
         const int nq = std::min(kCtxQueries, n_queries - q0);
+        {   // pack this call's outputs: [idx nq*hs][score nq*hs][found nq][flags nq]
+            const size_t nh = static_cast<size_t>(nq) * hs;
+            c.d_score = reinterpret_cast<double*>(c.d_idx + nh);
+            c.d_found = reinterpret_cast<int32_t*>(c.d_score + nh);
+            c.d_flags = c.d_found + nq;
+            c.h_score = reinterpret_cast<double*>(c.h_idx + nh);
+            c.h_found = reinterpret_cast<int32_t*>(c.h_score + nh);
+            c.h_flags = c.h_found + nq;
+        }
         memcpy(c.h_q, queries + static_cast<size_t>(q0) * s->dim, static_cast<size_t>(nq) * s->dim * sizeof(float));
         CU_TRY(cudaMemcpyAsync(c.d_q, c.h_q, static_cast<size_t>(nq) * s->dim * sizeof(float), cudaMemcpyHostToDevice, c.st));
         std::vector<int> todo(nq);
@@ -768,10 +766,7 @@ int ragstore_search(ragstore_t* s, const float* queries, int n_queries, int quer
                 const int rc = launch_scan(a, c.st);
                 if (rc) return fail(RAGSTORE_ERR_CUDA, "scan kernel launch", cudaGetErrorString(static_cast<cudaError_t>(rc)));
             }
-            CU_TRY(cudaMemcpyAsync(c.h_idx, c.d_idx, static_cast<size_t>(nq) * hs * sizeof(int64_t), cudaMemcpyDeviceToHost, c.st));
-            CU_TRY(cudaMemcpyAsync(c.h_score, c.d_score, static_cast<size_t>(nq) * hs * sizeof(double), cudaMemcpyDeviceToHost, c.st));
-            CU_TRY(cudaMemcpyAsync(c.h_found, c.d_found, static_cast<size_t>(nq) * sizeof(int32_t), cudaMemcpyDeviceToHost, c.st));
-            CU_TRY(cudaMemcpyAsync(c.h_flags, c.d_flags, static_cast<size_t>(nq) * sizeof(int32_t), cudaMemcpyDeviceToHost, c.st));
+            CU_TRY(cudaMemcpyAsync(c.h_idx, c.d_idx, static_cast<size_t>(nq) * hs * 16 + static_cast<size_t>(nq) * 8, cudaMemcpyDeviceToHost, c.st));
             CU_TRY(cudaStreamSynchronize(c.st));
             std::vector<int> again;
             for (int i : todo) {

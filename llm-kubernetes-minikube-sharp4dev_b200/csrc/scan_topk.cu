@@ -27,6 +27,8 @@
 // HBM traffic: every stored element is read exactly once (d * sizeof(elem) + 4 bytes per row).
 #include <math_constants.h>
 
+#include <cstdlib>
+
 #include "topk_device.cuh"
 
 namespace rag {
@@ -39,6 +41,7 @@ struct ScanLayout {
     uint32_t qpad;       // floats in each query buffer (zero padded)
     uint32_t off_bars, off_qraw, off_qhat, off_lists, off_buf, off_misc, total;
     uint32_t n_consumers;  // consumer warps that take tiles; divides n_stages, so a warp owns fixed stages
+    uint32_t no_hint;      // experiments: 1 = plain bulk copies without the L2 evict_first policy
 };
 
 // ---------------------------------------------------------------- per-row dot products from smem
@@ -177,7 +180,10 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
                 const uint32_t rnb = static_cast<uint32_t>((nrows + 3) & ~3) * 4u;
                 uint8_t* dst = smem + static_cast<size_t>(s) * L.stage_bytes;
                 mbar_arrive_expect_tx(full + s, bytes + rnb);
-                bulk_g2s_hint(dst, mat + static_cast<size_t>(row0) * L.row_bytes, bytes, full + s, pol);
+                if (L.no_hint)
+                    bulk_g2s(dst, mat + static_cast<size_t>(row0) * L.row_bytes, bytes, full + s);
+                else
+                    bulk_g2s_hint(dst, mat + static_cast<size_t>(row0) * L.row_bytes, bytes, full + s, pol);
                 bulk_g2s(dst + L.tile_bytes, a.rnorm + row0, rnb, full + s);
                 if (++s == n_stages) {
                     s = 0;
@@ -327,7 +333,12 @@ static bool make_layout(const ScanArgs& a, int dv, ScanLayout& L) {
     // Rows per tile R: a multiple of 4 (row group of a warp; 16-byte granularity of the reciprocal-norm
     // slice).  Stages: 16, 8 or fewer, with min(8, stages) consumer warps so that each warp owns
     // fixed stages.  Pick the R (<= ~24 KB tiles) that keeps the most bytes in flight.
-    uint32_t Rmax = (24u * 1024u) / L.row_bytes;
+    static const uint32_t tile_kb = [] {  // tuning knob for experiments; default 24 KB tiles
+        const char* e = std::getenv("RAGSTORE_SCAN_TILE_KB");
+        const int v = e ? atoi(e) : 0;
+        return static_cast<uint32_t>(v >= 4 && v <= 96 ? v : 24);
+    }();
+    uint32_t Rmax = (tile_kb * 1024u) / L.row_bytes;
     Rmax = Rmax < 4 ? 4 : (Rmax > 64 ? 64 : (Rmax & ~3u));
     uint32_t best_R = 0, best_ns = 0, best_bytes = 0;
     for (uint32_t R = Rmax; R >= 4; R -= 4) {
@@ -344,6 +355,7 @@ static bool make_layout(const ScanArgs& a, int dv, ScanLayout& L) {
     L.stage_bytes = (L.tile_bytes + R * 4u + 127u) & ~127u;
     L.n_stages = best_ns;
     L.n_consumers = best_ns < kConsumerWarps ? best_ns : kConsumerWarps;
+    L.no_hint = std::getenv("RAGSTORE_SCAN_NOHINT") ? 1u : 0u;
     uint32_t off = L.n_stages * L.stage_bytes;
     L.off_bars = off;
     off += bars_bytes;
