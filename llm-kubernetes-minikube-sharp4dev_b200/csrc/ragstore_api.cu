@@ -470,13 +470,14 @@ int ragstore_add(ragstore_t* s, const float* rows, int64_t n_rows, int row_dim, 
             memcpy(s->h_stage[b], src, static_cast<size_t>(n) * s->dim * sizeof(float));
             h2d_src = s->h_stage[b];
         }
-        if (on_device && !in_place) {
+        if (on_device) {
+            // device-resident source: K1 reads it where it lies and writes the normalised rows (one pass, no copy)
             a.src = src;
             a.src_ld = s->dim;
         } else if (in_place) {
             CU_TRY(cudaMemcpy2DAsync(dst_row, static_cast<size_t>(s->ld) * 4, h2d_src, static_cast<size_t>(s->dim) * 4,
                                      static_cast<size_t>(s->dim) * 4, static_cast<size_t>(n),
-                                     on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, s->ingest_stream));
+                                     cudaMemcpyHostToDevice, s->ingest_stream));
             a.src = reinterpret_cast<const float*>(dst_row);
             a.src_ld = s->ld;
         } else {

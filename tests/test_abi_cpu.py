@@ -62,3 +62,31 @@ def test_hit_filters_match_the_callers_of_the_reference():
     assert list(cited) == [] and not low
     cited, best, low = native.hit_filters([0.9, 0.54, 0.5399999])  # boundary: >= 0.6*best
     assert list(cited) == [True, True, False]
+
+
+def _build_c_smoke():
+    import subprocess
+    exe = os.path.join(ROOT, "tests", "c", "abi_smoke")
+    so_dir = os.path.join(ROOT, "llm-kubernetes-minikube-sharp4dev_b200")
+    subprocess.check_call(["gcc", "-std=c11", "-O1", "-o", exe, os.path.join(ROOT, "tests", "c", "abi_smoke.c"),
+                           "-L" + so_dir, "-lragstore", "-Wl,-rpath," + so_dir])
+    return exe
+
+
+def test_c_abi_from_plain_c_without_gpu():
+    """The header compiles as C and the library links from C; without a GPU it refuses cleanly (exit code 3)."""
+    import subprocess
+    import torch
+    exe = _build_c_smoke()
+    r = subprocess.run([exe], capture_output=True, text=True)
+    if torch.cuda.is_available():
+        assert r.returncode == 0, r.stderr
+    else:
+        assert r.returncode == 3, (r.returncode, r.stdout, r.stderr)
+
+
+@pytest.mark.gpu
+def test_c_abi_from_plain_c_on_gpu():
+    import subprocess
+    r = subprocess.run([_build_c_smoke()], capture_output=True, text=True)
+    assert r.returncode == 0 and "abi_smoke ok" in r.stdout, (r.stdout, r.stderr)
