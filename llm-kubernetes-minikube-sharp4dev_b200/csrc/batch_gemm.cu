@@ -147,6 +147,8 @@ struct BatchArgs {
     int nkb;           // k-blocks of 32 fp32 per row
     uint64_t* glists;  // [nq][n_ctas][kBatchKp] candidate keys, written by this kernel
     int debug;         // profiling experiments: 1 = epilogue drains without scanning, 2 = no MMA issue
+    int tile_stride;   // 1 = every tile; s > 1 = the sampling pass: tiles 0, s, 2s, ...
+    const float* thr0; // [nq] initial thresholds from the sampling pass (rows scoring below can be skipped), or null
 };
 
 // ---------------------------------------------------------------- thread-private candidate lists
@@ -232,7 +234,8 @@ batch_score_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
     // same time, so each loads 1/kCluster of a slice and multicasts it to all of them: query reads
     // out of L2 drop by kCluster.  A CTA whose tile lies past the end scores zero rows (TMA zero fill).
     const uint32_t crank = cluster_ctarank();
-    const int64_t n_tiles = (a.n_rows + kBN - 1) / kBN;
+    const int64_t all_tiles = (a.n_rows + kBN - 1) / kBN;
+    const int64_t n_tiles = (all_tiles + a.tile_stride - 1) / a.tile_stride;  // tiles this launch visits
     const int64_t n_clusters = gridDim.x / kCluster, cluster_id = blockIdx.x / kCluster;
     const int64_t n_groups = (n_tiles + kCluster - 1) / kCluster;
     const int64_t my_tiles = n_groups > cluster_id ? (n_groups - cluster_id + n_clusters - 1) / n_clusters : 0;
@@ -268,7 +271,7 @@ batch_score_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
             constexpr int q_rows = NQ / kCluster;  // this CTA's share of the query slice
             const uint32_t q_off = crank * static_cast<uint32_t>(q_rows) * kBKBytes;
             for (int64_t it = 0; it < my_tiles; ++it) {
-                const int row0 = static_cast<int>(((cluster_id + it * n_clusters) * kCluster + crank) * kBN);
+                const int row0 = static_cast<int>(((cluster_id + it * n_clusters) * kCluster + crank) * a.tile_stride * kBN);
                 for (int kb = 0; kb < a.nkb; ++kb) {
                     mbar_wait(empty + s, ph ^ 1u);
                     uint8_t* st = smem + static_cast<size_t>(s) * L.stage_bytes;
@@ -327,11 +330,20 @@ batch_score_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
         for (int p = 0; p < kBatchKp; ++p) S[p] = -CUDART_INF_F;
         float thr = -CUDART_INF_F;
         int minpos = 0;
+        // Sampling-pass threshold: the k'-th best score among the sampled rows is a lower bound of the k'-th best
+        // overall, so rows scoring BELOW it need never enter a list.  Ties with it are kept (nextafter), and the
+        // list slots start at this value so that it stays the threshold until 32 better rows have been seen.
+        const float floor0 = (a.thr0 && live) ? nextafterf(a.thr0[q], -CUDART_INF_F) : -CUDART_INF_F;
+        if (floor0 > -CUDART_INF_F) {
+#pragma unroll
+            for (int p = 0; p < kBatchKp; ++p) S[p] = floor0;
+            thr = floor0;
+        }
         for (int64_t it = 0; it < my_tiles; ++it) {
             const uint32_t as = static_cast<uint32_t>(it % AS), aph = static_cast<uint32_t>((it / AS) & 1);
             mbar_wait(tmem_full + as, aph);
             tc_fence_after();
-            const int64_t row0 = ((cluster_id + it * n_clusters) * kCluster + crank) * kBN;
+            const int64_t row0 = ((cluster_id + it * n_clusters) * kCluster + crank) * a.tile_stride * kBN;
             const int nvalid = static_cast<int>(min(static_cast<int64_t>(kBN), a.n_rows - row0));
             for (int cb = 0; cb < kBN; cb += 64) {
                 // four 16-column loads in flight per wait: the TMEM read latency is paid once per 64 columns
@@ -342,16 +354,29 @@ batch_score_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
                 // Hits are rare once the lists have warmed up.  Each lane marks the columns whose score beats ITS
                 // threshold; the warp then revisits only the marked columns (one-column TMEM load) and the lanes
                 // concerned insert.  One copy of the insert code keeps the loop in the I-cache.
-                unsigned long long mine = 0;
-                if (live && !(a.debug & 1)) {
+                // steady state: one max over the 64 scores and one vote; the per-column mask is built only when some
+                // lane of the warp actually has a score above its threshold
+                float mx[4];
 #pragma unroll
-                    for (int u = 0; u < 4; ++u)
+                for (int u = 0; u < 4; ++u) {
+                    mx[u] = __uint_as_float(v[u][0]);
 #pragma unroll
-                        for (int j = 0; j < 16; ++j) mine |= static_cast<unsigned long long>(__uint_as_float(v[u][j]) > thr ? 1u : 0u) << (u * 16 + j);
+                    for (int j = 1; j < 16; ++j) mx[u] = fmaxf(mx[u], __uint_as_float(v[u][j]));
                 }
-                unsigned lo = __reduce_or_sync(0xffffffffu, static_cast<unsigned>(mine));
-                unsigned hi = __reduce_or_sync(0xffffffffu, static_cast<unsigned>(mine >> 32));
-                unsigned long long any = (static_cast<unsigned long long>(hi) << 32) | lo;
+                const bool hot = live && !(a.debug & 1) && fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3])) > thr;
+                unsigned long long mine = 0, any = 0;
+                if (__any_sync(0xffffffffu, hot)) {
+                    if (hot) {
+#pragma unroll
+                        for (int u = 0; u < 4; ++u)
+#pragma unroll
+                            for (int j = 0; j < 16; ++j)
+                                mine |= static_cast<unsigned long long>(__uint_as_float(v[u][j]) > thr ? 1u : 0u) << (u * 16 + j);
+                    }
+                    const unsigned lo = __reduce_or_sync(0xffffffffu, static_cast<unsigned>(mine));
+                    const unsigned hi = __reduce_or_sync(0xffffffffu, static_cast<unsigned>(mine >> 32));
+                    any = (static_cast<unsigned long long>(hi) << 32) | lo;
+                }
                 while (any) {
                     const int j = __ffsll(static_cast<long long>(any)) - 1;
                     any &= any - 1;
@@ -619,11 +644,24 @@ batch_score_kernel_2sm(const __grid_constant__ CUtensorMap tmap_q, const __grid_
     }
 }
 
+// ---------------------------------------------------------------- sampling-pass thresholds
+// One CTA per query: merges the per-CTA lists of the sampling pass and keeps the k'-th best approximate score.
+__global__ void __launch_bounds__(kScanThreads, 1) batch_thresholds_kernel(const uint64_t* glists, int nlists, int kp,
+                                                                           uint32_t stage_bytes, float* thr0) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    uint64_t* stage = reinterpret_cast<uint64_t*>(smem);
+    uint64_t* lists = reinterpret_cast<uint64_t*>(smem + stage_bytes);
+    const int q = blockIdx.x;
+    merge_global_lists(glists + static_cast<size_t>(q) * nlists * kp, nlists, kp, lists, stage, stage_bytes);
+    if (threadIdx.x == 0) thr0[q] = lists[kp - 1] ? key_score(lists[kp - 1]) : -CUDART_INF_F;
+}
+
 // ---------------------------------------------------------------- per-query merge + exact rescoring
 struct BatchFinalizeArgs {
     ScanArgs scan;          // store views, k_take, kp, eps, row_base; d_query / out_* are per-launch bases
     const float* d_queries; // raw queries [nq][dim]
     const uint64_t* glists; // [nq][nlists][kp]
+    const float* thr0;      // [nq] sampling-pass thresholds (null: single pass)
     int nlists;
     int out_stride;         // hits per query in out_idx / out_score
     uint32_t ring_bytes, row_bytes, qpad;
@@ -661,6 +699,7 @@ __global__ void __launch_bounds__(kScanThreads, 1) batch_finalize_kernel(const B
     f.qraw = qraw;
     f.glists = b.glists + static_cast<size_t>(q) * b.nlists * a.kp;
     f.nlists = b.nlists;
+    f.bound_floor = b.thr0 ? b.thr0[q] : -CUDART_INF_F;
     finalize_candidates<T>(a, f);
 }
 
@@ -715,7 +754,8 @@ static bool make_map_f32(CUtensorMap* m, const void* base, uint64_t rows, uint64
 
 size_t batch_scratch_bytes(int sm_count) {
     return sizeof(uint64_t) * size_t(kBatchMaxQ) * size_t(sm_count) * kBatchKp   // candidate lists
-           + sizeof(float) * size_t(kBatchMaxQ) * size_t(kBatchMaxLd);          // normalised query operand
+           + sizeof(float) * size_t(kBatchMaxQ) * size_t(kBatchMaxLd)           // normalised query operand
+           + sizeof(float) * size_t(kBatchMaxQ);                                 // sampling-pass thresholds
 }
 
 int launch_batch_search(const BatchSearchArgs& b, cudaStream_t stream) {
@@ -727,6 +767,7 @@ int launch_batch_search(const BatchSearchArgs& b, cudaStream_t stream) {
     const int nq_pad = mblocks * kBM;
     uint64_t* glists = reinterpret_cast<uint64_t*>(b.scratch);
     float* qhat = reinterpret_cast<float*>(b.scratch + sizeof(uint64_t) * size_t(kBatchMaxQ) * size_t(s.sm_count) * kBatchKp);
+    float* thr0 = qhat + size_t(kBatchMaxQ) * size_t(kBatchMaxLd);
 
     prep_queries_kernel<<<(nq_pad * 32 + 255) / 256, 256, 0, stream>>>(b.d_queries, qhat, b.nq, nq_pad, s.dim, s.ld);
     cudaError_t e = cudaGetLastError();
@@ -770,27 +811,61 @@ int launch_batch_search(const BatchSearchArgs& b, cudaStream_t stream) {
     grid = (grid + kCluster - 1) / kCluster * kCluster;          // whole clusters
     if (grid > s.sm_count) grid = s.sm_count / kCluster * kCluster;
     int nlists = grid;
+    a.tile_stride = 1;
+    a.thr0 = nullptr;
+    const float* thr_used = nullptr;
+    auto launch_main = [&]() -> cudaError_t {
+        if (mblocks == 2) {
+            cudaError_t e2 = cudaFuncSetAttribute(batch_score_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+            if (e2 != cudaSuccess) return e2;
+            batch_score_kernel<2><<<grid, kBatchThreads, L.total, stream>>>(map_q, map_c, a, L);
+        } else {
+            cudaError_t e2 = cudaFuncSetAttribute(batch_score_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+            if (e2 != cudaSuccess) return e2;
+            batch_score_kernel<1><<<grid, kBatchThreads, L.total, stream>>>(map_q, map_c, a, L);
+        }
+        return cudaGetLastError();
+    };
     if (pair) {
         e = cudaFuncSetAttribute(batch_score_kernel_2sm, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
         if (e != cudaSuccess) return static_cast<int>(e);
         batch_score_kernel_2sm<<<grid, kPairThreads, L.total, stream>>>(map_q, map_c, a, L);
         nlists = grid / 2;
-    } else if (mblocks == 2) {
-        e = cudaFuncSetAttribute(batch_score_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-        if (e != cudaSuccess) return static_cast<int>(e);
-        batch_score_kernel<2><<<grid, kBatchThreads, L.total, stream>>>(map_q, map_c, a, L);
+        e = cudaGetLastError();
     } else {
-        e = cudaFuncSetAttribute(batch_score_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-        if (e != cudaSuccess) return static_cast<int>(e);
-        batch_score_kernel<1><<<grid, kBatchThreads, L.total, stream>>>(map_q, map_c, a, L);
+        // Two passes on large corpora.  The cost of the fused top-k is the list warm-up: each CTA sees only 1/148 of
+        // the rows, so its thresholds rise slowly and ~1000 ln(tiles) insert events per warp stall the accumulator
+        // drain.  A sampling pass over every s-th tile (same kernel) gives, per query, the k'-th best score of the
+        // sample -- a lower bound of the k'-th best overall -- and the full pass starts from it: only ~32*s rows per
+        // query in the WHOLE corpus still beat it.
+        const char* tp = std::getenv("RAGSTORE_BATCH_TWOPASS");
+        const bool two_pass = n_tiles >= 32ll * grid && !(tp && tp[0] == '0');
+        if (two_pass) {
+            int stride = static_cast<int>(n_tiles / (8ll * grid));
+            stride = stride > 16 ? 16 : (stride < 2 ? 2 : stride);
+            a.tile_stride = stride;
+            e = launch_main();
+            if (e != cudaSuccess) return static_cast<int>(e);
+            const uint32_t stage_bytes = ((static_cast<uint32_t>(grid) * kBatchKp * 8u) + 127u) & ~127u;
+            const size_t tsm = stage_bytes + sizeof(uint64_t) * 2u * kConsumerWarps * kBatchKp;
+            e = cudaFuncSetAttribute(batch_thresholds_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+            if (e != cudaSuccess) return static_cast<int>(e);
+            batch_thresholds_kernel<<<b.nq, kScanThreads, tsm, stream>>>(glists, grid, kBatchKp, stage_bytes, thr0);
+            e = cudaGetLastError();
+            if (e != cudaSuccess) return static_cast<int>(e);
+            a.tile_stride = 1;
+            a.thr0 = thr0;
+            thr_used = thr0;
+        }
+        e = launch_main();
     }
-    e = cudaGetLastError();
     if (e != cudaSuccess) return static_cast<int>(e);
 
     BatchFinalizeArgs f;
     f.scan = s;
     f.d_queries = b.d_queries;
     f.glists = glists;
+    f.thr0 = thr_used;
     f.nlists = nlists;
     f.out_stride = b.out_stride;
     f.row_bytes = static_cast<uint32_t>(s.ld) * 4u;

@@ -20,6 +20,7 @@ struct ScanMisc {  // lives in shared memory at off_misc
     double nb[kMaxKp];
     uint8_t raw_fmt[kMaxKp];  // 1 = the staged row is the fp32 original from the sidecar
     unsigned long long stage_bar;  // mbarrier for the bulk copies that stage candidate rows
+    int n_cand;                    // survivors actually present in the merged list
 };
 
 // ---------------------------------------------------------------- warp-level sorted lists
@@ -156,6 +157,33 @@ __device__ __forceinline__ int64_t global_row_id(const ScanArgs& a, uint32_t loc
     return a.row_base + (blk * a.row_nshards + a.row_shard) * a.row_block + off;
 }
 
+// Merges `nlists` sorted lists of kp keys (global memory) into lists[0..kp) (shared, 2*kConsumerWarps*kp keys of
+// scratch); `stage` is idle shared memory of stage_bytes.  Called by all kScanThreads threads of the CTA.
+__device__ __forceinline__ void merge_global_lists(const uint64_t* glists, int nlists, int kp, uint64_t* lists, uint64_t* stage,
+                                                   uint32_t stage_bytes) {
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int cap_lists = max(1, static_cast<int>(stage_bytes / (static_cast<uint32_t>(kp) * 8u)));
+    if (warp < kConsumerWarps) {
+        for (int j = lane; j < kp; j += 32) lists[warp * kp + j] = 0ull;
+    }
+    for (int l0 = 0; l0 < nlists; l0 += cap_lists) {
+        const int nl = min(cap_lists, nlists - l0);
+        const uint64_t* src = glists + static_cast<size_t>(l0) * kp;
+        const int total = nl * kp;
+#pragma unroll 8
+        for (int i = tid; i < total; i += kScanThreads) stage[i] = __ldcg(src + i);  // all loads in flight
+        __syncthreads();
+        if (warp < kConsumerWarps)
+            for (int c = warp; c < nl; c += kConsumerWarps) warp_merge_desc(lists + warp * kp, stage + c * kp, kp, lane);
+        __syncthreads();
+    }
+    for (int w = 1; w < kConsumerWarps; w <<= 1) {
+        if (warp < kConsumerWarps && (warp % (2 * w)) == 0 && warp + w < kConsumerWarps)
+            warp_merge_desc(lists + warp * kp, lists + (warp + w) * kp, kp, lane);
+        __syncthreads();
+    }
+}
+
 struct FinalizeCtx {
     uint8_t* ring;          // idle shared memory used as staging space
     uint32_t ring_bytes;
@@ -165,6 +193,7 @@ struct FinalizeCtx {
     const float* qraw;      // shared: the raw query, dim floats (16-byte aligned)
     const uint64_t* glists; // global: nlists * kp keys
     int nlists;
+    float bound_floor;      // every row that was never offered to a list scored <= this (-inf if none)
 };
 
 __device__ __forceinline__ void stamp(const ScanArgs& a, int i) {
@@ -180,34 +209,22 @@ __device__ __forceinline__ void finalize_candidates(const ScanArgs& a, const Fin
     const float* qraw = f.qraw;
     const uint8_t* mat = static_cast<const uint8_t*>(a.mat);
     const uint32_t ring_bytes = f.ring_bytes;
-    {
-        uint64_t* stage = reinterpret_cast<uint64_t*>(f.ring);
-        const int nlists = f.nlists;
-        const int cap_lists = max(1, static_cast<int>(ring_bytes / (static_cast<uint32_t>(kp) * 8u)));
-        if (warp < kConsumerWarps) {
-            for (int j = lane; j < kp; j += 32) lists[warp * kp + j] = 0ull;
-        }
-        for (int l0 = 0; l0 < nlists; l0 += cap_lists) {
-            const int nl = min(cap_lists, nlists - l0);
-            const uint64_t* src = f.glists + static_cast<size_t>(l0) * kp;
-            const int total = nl * kp;
-#pragma unroll 8
-            for (int i = tid; i < total; i += kScanThreads) stage[i] = __ldcg(src + i);  // all loads in flight
-            __syncthreads();
-            if (warp < kConsumerWarps)
-                for (int c = warp; c < nl; c += kConsumerWarps) warp_merge_desc(lists + warp * kp, stage + c * kp, kp, lane);
-            __syncthreads();
-        }
-        for (int w = 1; w < kConsumerWarps; w <<= 1) {
-            if (warp < kConsumerWarps && (warp % (2 * w)) == 0 && warp + w < kConsumerWarps)
-                warp_merge_desc(lists + warp * kp, lists + (warp + w) * kp, kp, lane);
-            __syncthreads();
-        }
-    }
+    merge_global_lists(f.glists, f.nlists, kp, lists, reinterpret_cast<uint64_t*>(f.ring), ring_bytes);
     // lists[0..kp) : the kp best approximate keys of the whole shard, descending
     if (tid == 0) stamp(a, 2);
 
-    const int n_cand = static_cast<int>(min(static_cast<int64_t>(kp), a.n_rows));
+    // survivors = leading non-empty keys (the list is sorted, empty slots are 0 and sit at the end)
+    int n_cand = static_cast<int>(min(static_cast<int64_t>(kp), a.n_rows));
+    {
+        int cnt = 0;
+        for (int j = tid; j < n_cand; j += kScanThreads) cnt += lists[j] != 0ull;
+        if (tid == 0) misc->n_cand = 0;
+        __syncthreads();
+        if (cnt) atomicAdd(&misc->n_cand, cnt);
+        __syncthreads();
+        n_cand = misc->n_cand;
+    }
+    const int k_take = min(a.k_take, n_cand);
     // Rows are staged in the (now idle) tile ring.  A row that was stored inexactly (normalised with
     // scale != 1, or rounded to bf16) is rescored from its ORIGINAL fp32 values kept in the sidecar,
     // so the fp64 score below is the reference's value for the row as it was added.
@@ -286,19 +303,19 @@ __device__ __forceinline__ void finalize_candidates(const ScanArgs& a, const Fin
             rank += (ku > kc) || (ku == kc && ru < rc);
         }
         const int64_t gid = global_row_id(a, rc);
-        if (rank < a.k_take) {
+        if (rank < k_take) {
             if (a.out_idx) a.out_idx[rank] = gid;
             if (a.out_score) a.out_score[rank] = sc;
             if (a.exact && a.exact[rc] == 0 && !(a.raw_slot && a.raw_slot[rc] >= 0)) atomicAdd(&misc->inexact, 1);
-            if (rank == a.k_take - 1) misc->ek = sc;
+            if (rank == k_take - 1) misc->ek = sc;
         }
-        if (a.out_cand && rank < a.cand_slots && rank < a.k_take) {
+        if (a.out_cand && rank < a.cand_slots && rank < k_take) {
             a.out_cand[rank].score = sc;
             a.out_cand[rank].id = gid;
         }
     }
     if (a.out_cand) {
-        for (int j = a.k_take + tid; j < a.cand_slots; j += kScanThreads) {
+        for (int j = k_take + tid; j < a.cand_slots; j += kScanThreads) {
             a.out_cand[j].score = -CUDART_INF;
             a.out_cand[j].id = -1;
         }
@@ -313,7 +330,8 @@ __device__ __forceinline__ void finalize_candidates(const ScanArgs& a, const Fin
             // most bound + eps, where eps covers the fp32 rounding of the scan AND the reference's
             // "+1e-9" in the denominator (RagIndex.cs:134), which moves a score by at most
             // 1e-9 / (|q| * smallest row norm) towards zero.
-            const double bound = static_cast<double>(key_score(lists[kp - 1]));
+            double bound = lists[kp - 1] ? static_cast<double>(key_score(lists[kp - 1])) : -CUDART_INF;
+            if (static_cast<double>(f.bound_floor) > bound) bound = static_cast<double>(f.bound_floor);
             double shrink = 0.0;
             if (a.min_norm_bits) {
                 const double d = sqrt(misc->na) * static_cast<double>(__uint_as_float(*a.min_norm_bits));
@@ -321,12 +339,13 @@ __device__ __forceinline__ void finalize_candidates(const ScanArgs& a, const Fin
             }
             cert = misc->ek > bound + static_cast<double>(a.eps) + shrink;  // false if either side is NaN
             if (misc->na == 0.0) cert = true;  // zero query: every reference score is exactly +0.0 (or NaN, ranked last)
+            if (k_take < a.k_take) cert = false;  // fewer survivors than requested hits: nothing to certify against
         }
         int32_t flags = 0;
         if (cert) flags |= RAGSTORE_HIT_CERTIFIED;
         if (misc->inexact == 0) flags |= RAGSTORE_HIT_EXACT_ROWS;
         if (a.out_flags) *a.out_flags = flags;
-        if (a.out_found) *a.out_found = a.k_take;
+        if (a.out_found) *a.out_found = k_take;
         stamp(a, 5);
     }
 }
