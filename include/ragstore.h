@@ -224,7 +224,8 @@ RAGSTORE_API int ragstore_version(void);
 
 /* Store facts for tests and the bench: fills up to n of
  * [dim, ld (padded row length), dtype, count, capacity, n_inexact_rows, device, sm_count,
- *  has_sidecar, sidecar_rows, matrix_bytes_mapped, uses_vmm, scan_launches, batch_launches]. */
+ *  has_sidecar, sidecar_rows, matrix_bytes_mapped, uses_vmm, scan_launches, batch_launches,
+ *  last_add_kernel_ns (device time of the upload/normalise launches of the last ragstore_add)]. */
 RAGSTORE_API int ragstore_info(ragstore_t* s, int64_t* out, int n);
 
 /* Profiling aid: %globaltimer (ns) at the phase boundaries of the store's most recent

@@ -115,6 +115,8 @@ struct ragstore {
     size_t stage_floats = 0;
     float* h_stage[2] = {nullptr, nullptr};   // pinned host staging, one per pipeline slot
     cudaEvent_t ingest_ev[2] = {nullptr, nullptr};
+    cudaEvent_t k1_ev0[2] = {nullptr, nullptr}, k1_ev1[2] = {nullptr, nullptr};  // bracket the K1 launches (profiling aid)
+    double last_add_kernel_us = 0.0;
     unsigned long long* h_counters = nullptr; // pinned: per slot [inexact rows, sidecar rows]
     // coalescing of concurrent single-query callers (ragstore_search_coalesced)
     struct Pending {
@@ -344,6 +346,8 @@ int ragstore_destroy(ragstore_t* s) {
     for (int b = 0; b < 2; ++b) {
         if (s->h_stage[b]) cudaFreeHost(s->h_stage[b]);
         if (s->ingest_ev[b]) cudaEventDestroy(s->ingest_ev[b]);
+        if (s->k1_ev0[b]) cudaEventDestroy(s->k1_ev0[b]);
+        if (s->k1_ev1[b]) cudaEventDestroy(s->k1_ev1[b]);
     }
     if (s->h_counters) cudaFreeHost(s->h_counters);
     cudaFree(s->d_inexact);
@@ -398,7 +402,9 @@ int ragstore_add(ragstore_t* s, const float* rows, int64_t n_rows, int row_dim, 
     const size_t esz = s->elem_size();
     // Two-deep pipeline of ~32 MB chunks: while chunk i is copied over PCIe and normalised, chunk i+1 is being
     // staged into the other pinned buffer (host sources) -- the upload kernel never waits for the CPU copy.
-    const int64_t chunk_rows = std::max<int64_t>(1, (int64_t(32) << 20) / (int64_t(s->dim) * 4));
+    // host sources: ~32 MB staging chunks; device sources need no staging, so larger chunks (the chunk also bounds
+    // how much sidecar memory is mapped ahead of need)
+    const int64_t chunk_rows = on_device ? int64_t(1) << 17 : std::max<int64_t>(1, (int64_t(32) << 20) / (int64_t(s->dim) * 4));
     const size_t chunk_floats = static_cast<size_t>(chunk_rows) * s->dim;
     if (!on_device && !src_pinned && !s->h_stage[0]) {
         for (int b = 0; b < 2; ++b) CU_TRY(cudaMallocHost(&s->h_stage[b], chunk_floats * sizeof(float)));
@@ -411,15 +417,22 @@ int ragstore_add(ragstore_t* s, const float* rows, int64_t n_rows, int row_dim, 
         s->stage_floats = 2 * chunk_floats;
     }
     if (!s->ingest_ev[0]) {
-        for (int b = 0; b < 2; ++b) CU_TRY(cudaEventCreateWithFlags(&s->ingest_ev[b], cudaEventDisableTiming));
+        for (int b = 0; b < 2; ++b) {
+            CU_TRY(cudaEventCreateWithFlags(&s->ingest_ev[b], cudaEventDisableTiming));
+            CU_TRY(cudaEventCreate(&s->k1_ev0[b]));
+            CU_TRY(cudaEventCreate(&s->k1_ev1[b]));
+        }
         CU_TRY(cudaMallocHost(&s->h_counters, 2 * 2 * sizeof(unsigned long long)));
     }
+    s->last_add_kernel_us = 0.0;
     bool used[2] = {false, false};
     int64_t rows_in_flight[2] = {0, 0};
 
     auto retire = [&](int b) -> int {  // wait for the chunk that last used buffer b and take over its counters
         if (!used[b]) return RAGSTORE_OK;
         CU_TRY(cudaEventSynchronize(s->ingest_ev[b]));
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, s->k1_ev0[b], s->k1_ev1[b]) == cudaSuccess) s->last_add_kernel_us += 1e3 * ms;
         s->inexact_rows = static_cast<int64_t>(s->h_counters[2 * b]);
         s->raw_used = static_cast<int64_t>(s->h_counters[2 * b + 1] & 0xFFFFFFFFull);
         used[b] = false;
@@ -486,7 +499,9 @@ int ragstore_add(ragstore_t* s, const float* rows, int64_t n_rows, int row_dim, 
             a.src = dstage;
             a.src_ld = s->dim;
         }
+        CU_TRY(cudaEventRecord(s->k1_ev0[b], s->ingest_stream));
         rc = launch_normalise(a, s->ingest_stream);
+        CU_TRY(cudaEventRecord(s->k1_ev1[b], s->ingest_stream));
         if (rc) return fail(RAGSTORE_ERR_CUDA, "normalise kernel launch", cudaGetErrorString(static_cast<cudaError_t>(rc)));
         // counters after this chunk ([0] inexact rows, [1] low word: sidecar rows), read back without stalling
         CU_TRY(cudaMemcpyAsync(s->h_counters + 2 * b, s->d_inexact, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s->ingest_stream));
@@ -509,10 +524,10 @@ int ragstore_info(ragstore_t* s, int64_t* out, int n) {
     DeviceGuard g(s->device);
     unsigned long long inexact = 0;
     CU_TRY(cudaMemcpy(&inexact, s->d_inexact, sizeof(inexact), cudaMemcpyDeviceToHost));
-    const int64_t v[14] = {s->dim, s->ld, s->dtype, s->count.load(), s->capacity, static_cast<int64_t>(inexact), s->device, s->sm_count,
+    const int64_t v[15] = {s->dim, s->ld, s->dtype, s->count.load(), s->capacity, static_cast<int64_t>(inexact), s->device, s->sm_count,
                            s->raw_slot ? 1 : 0, s->raw_used, static_cast<int64_t>(s->mat_buf.mapped()), s->mat_buf.uses_vmm() ? 1 : 0,
-                           s->n_scan_launches.load(), s->n_batch_launches.load()};
-    for (int i = 0; i < n && i < 14; ++i) out[i] = v[i];
+                           s->n_scan_launches.load(), s->n_batch_launches.load(), static_cast<int64_t>(s->last_add_kernel_us * 1000.0)};
+    for (int i = 0; i < n && i < 15; ++i) out[i] = v[i];
     return RAGSTORE_OK;
 }
 

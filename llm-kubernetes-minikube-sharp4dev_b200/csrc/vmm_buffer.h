@@ -89,8 +89,10 @@ public:
         if (bytes > reserved_) return static_cast<int>(cudaErrorMemoryAllocation);
         if (!vmm_) return 0;
         const VmmApi& api = VmmApi::get();
-        // grow geometrically (at least the request, at most +1 GiB beyond it) in granularity units
-        size_t want = std::max(bytes - mapped_, std::min<size_t>(mapped_, size_t(1) << 30));
+        // grow geometrically (at least the request; doubling, capped at +16 GiB) in granularity units, so that a
+        // store fed by many appends maps memory O(log) times; if the generous amount is not available, map the need
+        const size_t need = (bytes - mapped_ + gran_ - 1) / gran_ * gran_;
+        size_t want = std::max(bytes - mapped_, std::min<size_t>(mapped_, size_t(16) << 30));
         want = (want + gran_ - 1) / gran_ * gran_;
         want = std::min(want, reserved_ - mapped_);
         CUmemAllocationProp prop = {};
@@ -98,7 +100,10 @@ public:
         prop.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
         prop.location.id = device_;
         CUmemGenericAllocationHandle h;
-        if (api.create(&h, want, &prop, 0) != CUDA_SUCCESS) return static_cast<int>(cudaErrorMemoryAllocation);
+        if (api.create(&h, want, &prop, 0) != CUDA_SUCCESS) {
+            want = std::min(need, reserved_ - mapped_);
+            if (api.create(&h, want, &prop, 0) != CUDA_SUCCESS) return static_cast<int>(cudaErrorMemoryAllocation);
+        }
         if (api.map(base_ + mapped_, want, 0, h, 0) != CUDA_SUCCESS) {
             api.release(h);
             return static_cast<int>(cudaErrorMemoryAllocation);

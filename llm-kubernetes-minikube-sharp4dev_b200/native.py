@@ -167,10 +167,10 @@ class RagStore:
                                                        C.c_void_p(stream)))
 
     def info(self) -> dict:
-        v = (C.c_int64 * 14)()
-        check(lib().ragstore_info(self._h, v, 14))
+        v = (C.c_int64 * 15)()
+        check(lib().ragstore_info(self._h, v, 15))
         keys = ["dim", "ld", "dtype", "count", "capacity", "n_inexact_rows", "device", "sm_count",
-                "has_sidecar", "sidecar_rows", "matrix_bytes_mapped", "uses_vmm", "scan_launches", "batch_launches"]
+                "has_sidecar", "sidecar_rows", "matrix_bytes_mapped", "uses_vmm", "scan_launches", "batch_launches", "last_add_kernel_ns"]
         return dict(zip(keys, list(v)))
 
     def debug_stamps(self):
