@@ -57,6 +57,17 @@ def measured_peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def measured_tensor_peaks():
+    """(burst, sustained) dense bf16 TFLOP/s; tf32 runs at half the bf16 rate on the tensor pipe."""
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(p) as f:
+            j = json.load(f)
+        return float(j["bf16_tflops"]), float(j.get("bf16_tflops_sustained", j["bf16_tflops"])), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 1590.0, 1400.0, "fallback (B200_PROFILING.md)"
+
+
 class ClockSampler:
     """Samples SM clock + throttle reasons through NVML while the timed region runs."""
 
@@ -524,7 +535,11 @@ def main():
                          "kernel_ms": r["kernel_ms"],
                          "algorithmic_bytes_per_launch": r["rows_per_gpu"] * r["dim"] * (4 if r["storage"] == "f32" else 2)},
             "tensor": ({"achieved_tflops": r["tensor_tflops"], "kind": "tf32 (tcgen05.mma kind::tf32, fp32 accumulate in TMEM)",
-                        "peak_tflops_bf16_measured": 1625.3, "frac_of_half_bf16_measured": r["tensor_tflops"] / (1625.3 / 2),
+                        "peak_tflops_bf16_burst": measured_tensor_peaks()[0], "peak_tflops_bf16_sustained": measured_tensor_peaks()[1],
+                        "peak_source": measured_tensor_peaks()[2],
+                        "frac_of_tf32_burst": r["tensor_tflops"] / (measured_tensor_peaks()[0] / 2),
+                        "frac_of_tf32_sustained": r["tensor_tflops"] / (measured_tensor_peaks()[1] / 2),
+                        "note": "tf32 peak taken as half the measured bf16 cuBLAS rate; this kernel runs inside a long step (power-capped clocks), so the sustained figure is the fair denominator; the step is bound by L2->SM ingest, see DESIGN.md K3",
                         "certified_fraction": r.get("certified_fraction")} if "tensor_tflops" in r else None),
             "cpu_baseline": r.get("cpu_baseline"),
             "e2e": {k: v for k, v in r.get("e2e", {}).items()} if "e2e" in r else None,

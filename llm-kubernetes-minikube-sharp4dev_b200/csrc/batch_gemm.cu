@@ -24,6 +24,7 @@
 // fp32 scan kernel (host side, ragstore_api.cu).
 #include <cuda.h>
 
+#include <cstdio>
 #include <cstdlib>
 
 #include "topk_device.cuh"
@@ -149,6 +150,7 @@ struct BatchArgs {
     int debug;         // profiling experiments: 1 = epilogue drains without scanning, 2 = no MMA issue
     int tile_stride;   // 1 = every tile; s > 1 = the sampling pass: tiles 0, s, 2s, ...
     const float* thr0; // [nq] initial thresholds from the sampling pass (rows scoring below can be skipped), or null
+    int sample;        // 1 = sampling pass: keep only each thread's 4 best scores (no lists), written to `glists` as floats
 };
 
 // ---------------------------------------------------------------- thread-private candidate lists
@@ -339,10 +341,47 @@ batch_score_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
             for (int p = 0; p < kBatchKp; ++p) S[p] = floor0;
             thr = floor0;
         }
+        if (a.sample) {
+            // Sampling pass: only thresholds are wanted, so a thread keeps just its 4 best scores (registers, no row
+            // ids, no lists): the warm-up that makes list maintenance expensive costs almost nothing here.
+            float t0 = -CUDART_INF_F, t1 = -CUDART_INF_F, t2 = -CUDART_INF_F, t3 = -CUDART_INF_F;  // t0 >= t1 >= t2 >= t3
+            for (int64_t it = 0; it < my_tiles; ++it) {
+                const uint32_t as = static_cast<uint32_t>(it % AS), aph = static_cast<uint32_t>((it / AS) & 1);
+                mbar_wait(tmem_full + as, aph);
+                tc_fence_after();
+                const int64_t row0 = ((cluster_id + it * n_clusters) * kCluster + crank) * a.tile_stride * kBN;
+                const int nvalid = static_cast<int>(min(static_cast<int64_t>(kBN), a.n_rows - row0));
+                for (int cb = 0; cb < kBN; cb += 32) {
+                    uint32_t v[32];
+                    tmem_ld_32x32(tmem_base + lane_base + (as * MB + mblock) * 256u + cb, v);
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {
+                        const float sc = __uint_as_float(v[j]);
+                        if (sc > t3 && cb + j < nvalid) {  // 4-slot sorted insert
+                            const float a0 = fmaxf(t0, sc), b0 = fminf(t0, sc);
+                            const float a1 = fmaxf(t1, b0), b1 = fminf(t1, b0);
+                            const float a2 = fmaxf(t2, b1), b2 = fminf(t2, b1);
+                            t0 = a0, t1 = a1, t2 = a2, t3 = fmaxf(t3, b2);
+                        }
+                    }
+                }
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(tmem_empty + as);
+            }
+            if (live) {
+                float* smp = reinterpret_cast<float*>(a.glists) + (static_cast<size_t>(q) * gridDim.x + blockIdx.x) * 4;
+                smp[0] = t0, smp[1] = t1, smp[2] = t2, smp[3] = t3;
+            }
+        } else {
+        long long t_wait = 0, t_work = 0;  // debug & 8: cycles spent waiting for / draining accumulators
         for (int64_t it = 0; it < my_tiles; ++it) {
             const uint32_t as = static_cast<uint32_t>(it % AS), aph = static_cast<uint32_t>((it / AS) & 1);
+            const long long c0k = clock64();
             mbar_wait(tmem_full + as, aph);
             tc_fence_after();
+            const long long c1k = clock64();
+            t_wait += c1k - c0k;
             const int64_t row0 = ((cluster_id + it * n_clusters) * kCluster + crank) * a.tile_stride * kBN;
             const int nvalid = static_cast<int>(min(static_cast<int64_t>(kBN), a.n_rows - row0));
             for (int cb = 0; cb < kBN; cb += 64) {
@@ -391,7 +430,11 @@ batch_score_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(tmem_empty + as);
+            t_work += clock64() - c1k;
         }
+        if ((a.debug & 8) && blockIdx.x == 0 && lane == 0 && my_tiles > 0)
+            printf("[batch dbg] warp %d: tiles %lld, per tile: wait %lld cyc, drain+scan %lld cyc\n", warp, (long long)my_tiles,
+                   t_wait / my_tiles, t_work / my_tiles);
         // The ring is idle now (every stage was consumed before the last accumulator completed): reuse it to
         // hand each query's 32 keys to a warp, which sorts them (one key per lane) and publishes them.
         uint64_t* keys = reinterpret_cast<uint64_t*>(smem);  // [query][slot]
@@ -409,6 +452,7 @@ batch_score_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
             k = warp_sort_desc(k, lane);
             a.glists[(static_cast<size_t>(q0 + i) * gridDim.x + blockIdx.x) * kBatchKp + lane] = k;  // glists[q][cta][pos]
         }
+        }  // !a.sample
     }
     tc_fence_before();
     __syncthreads();
@@ -645,15 +689,21 @@ batch_score_kernel_2sm(const __grid_constant__ CUtensorMap tmap_q, const __grid_
 }
 
 // ---------------------------------------------------------------- sampling-pass thresholds
-// One CTA per query: merges the per-CTA lists of the sampling pass and keeps the k'-th best approximate score.
-__global__ void __launch_bounds__(kScanThreads, 1) batch_thresholds_kernel(const uint64_t* glists, int nlists, int kp,
-                                                                           uint32_t stage_bytes, float* thr0) {
-    extern __shared__ __align__(128) uint8_t smem[];
-    uint64_t* stage = reinterpret_cast<uint64_t*>(smem);
-    uint64_t* lists = reinterpret_cast<uint64_t*>(smem + stage_bytes);
+// One CTA per query: the sampling pass left 4 best scores per CTA; the k'-th largest of these n values is the score of
+// a real row that at least k' real rows reach, i.e. a lower bound of the k'-th best score over the whole corpus.
+__global__ void __launch_bounds__(256) batch_thresholds_kernel(const float* smp, int n, int kth, float* thr0) {
+    extern __shared__ float vals[];
     const int q = blockIdx.x;
-    merge_global_lists(glists + static_cast<size_t>(q) * nlists * kp, nlists, kp, lists, stage, stage_bytes);
-    if (threadIdx.x == 0) thr0[q] = lists[kp - 1] ? key_score(lists[kp - 1]) : -CUDART_INF_F;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) vals[i] = smp[static_cast<size_t>(q) * n + i];
+    if (threadIdx.x == 0) thr0[q] = -CUDART_INF_F;
+    __syncthreads();
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        const float x = vals[i];
+        if (!(x > -CUDART_INF_F)) continue;
+        int rank = 0;
+        for (int u = 0; u < n; ++u) rank += (vals[u] > x) || (vals[u] == x && u < i);
+        if (rank == kth - 1) thr0[q] = x;
+    }
 }
 
 // ---------------------------------------------------------------- per-query merge + exact rescoring
@@ -813,6 +863,7 @@ int launch_batch_search(const BatchSearchArgs& b, cudaStream_t stream) {
     int nlists = grid;
     a.tile_stride = 1;
     a.thr0 = nullptr;
+    a.sample = 0;
     const float* thr_used = nullptr;
     auto launch_main = [&]() -> cudaError_t {
         if (mblocks == 2) {
@@ -844,15 +895,14 @@ int launch_batch_search(const BatchSearchArgs& b, cudaStream_t stream) {
             int stride = static_cast<int>(n_tiles / (8ll * grid));
             stride = stride > 16 ? 16 : (stride < 2 ? 2 : stride);
             a.tile_stride = stride;
+            a.sample = 1;
             e = launch_main();
             if (e != cudaSuccess) return static_cast<int>(e);
-            const uint32_t stage_bytes = ((static_cast<uint32_t>(grid) * kBatchKp * 8u) + 127u) & ~127u;
-            const size_t tsm = stage_bytes + sizeof(uint64_t) * 2u * kConsumerWarps * kBatchKp;
-            e = cudaFuncSetAttribute(batch_thresholds_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-            if (e != cudaSuccess) return static_cast<int>(e);
-            batch_thresholds_kernel<<<b.nq, kScanThreads, tsm, stream>>>(glists, grid, kBatchKp, stage_bytes, thr0);
+            const int nvals = grid * 4;
+            batch_thresholds_kernel<<<b.nq, 256, nvals * sizeof(float), stream>>>(reinterpret_cast<const float*>(glists), nvals, kBatchKp, thr0);
             e = cudaGetLastError();
             if (e != cudaSuccess) return static_cast<int>(e);
+            a.sample = 0;
             a.tile_stride = 1;
             a.thr0 = thr0;
             thr_used = thr0;

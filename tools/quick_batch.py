@@ -31,3 +31,5 @@ def run(n, d, nq, k, iters=5):
 if __name__ == "__main__":
     run(2000000, 1024, 256, 10)
     run(6000000, 1024, 256, 10, iters=3)
+    run(10000000, 1024, 256, 10, iters=3)
+    run(6000000, 1024, 100, 10, iters=3)
