@@ -207,6 +207,9 @@ ScanArgs base_args(const ragstore* s, int64_t n, int take, int kp) {
     a.k_take = take;
     a.kp = kp;
     a.eps = scan_eps(s->ld, s->dtype);
+    // bf16 store whose exact scores come from fp32 originals (sidecar): the scanned image of a row differs from the
+    // row that is rescored by the bf16 rounding, <= 2^-9 per element -> <= 2^-8 on a cosine (Cauchy-Schwarz + norm)
+    if (s->dtype == RAGSTORE_BF16 && s->raw_used > 0) a.eps += 3.90625e-3f;
     a.sm_count = s->sm_count;
     return a;
 }

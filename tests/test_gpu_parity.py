@@ -488,3 +488,33 @@ def test_save_and_load_round_trip(tmp_path, dtype):
         assert list(idx[0]) == list(eidx) and np.array_equal(sc[0].view(np.uint64), esc.view(np.uint64))
     finally:
         st2.close()
+
+
+BF16_ABS_TOL = 2e-3   # stated tolerance for fp32 embeddings stored lossily as bf16 (north_star: "a stated bf16 tolerance")
+
+
+def test_bf16_store_of_fp32_rows_within_stated_tolerance():
+    """fp32 rows rounded to bf16 at ingest (no sidecar: the default for bf16 stores).  The scan and the rescoring then see
+    the rounded rows, so scores differ from the fp32 reference by the rounding of the stored row: <= 2e-3 absolute on
+    unit vectors (observed ~1e-4), and the hit lists overlap almost entirely.  With the sidecar on, results are exact."""
+    n, d, k = 50000, 768, 10
+    rows = oc.synth_rows(0, n, d, 1234)            # fp32, NOT bf16-representable
+    qs = oc.synth_rows(0, 4, d, 5678)
+    with rb.RagStore(d, n, rb.RAGSTORE_BF16) as st:
+        st.add(rows)
+        assert st.info()["has_sidecar"] == 0 and st.info()["n_inexact_rows"] > 0.99 * n
+        idx, sc, found, flags = st.search(qs, k)
+    overlap = 0
+    for i in range(4):
+        full = oc.score_all(rows, qs[i], n_threads=4)
+        eidx, esc = oc.query(rows, qs[i], k, n_threads=4)
+        assert np.max(np.abs(sc[i] - full[idx[i]])) <= BF16_ABS_TOL      # each returned score vs the reference's for that row
+        assert not (flags[i] & rb.RAGSTORE_HIT_EXACT_ROWS)                # and the result says the rows were stored lossily
+        overlap += len(set(idx[i].tolist()) & set(eidx.tolist()))
+    assert overlap >= 0.8 * 4 * k
+    with rb.RagStore(d, n, rb.RAGSTORE_BF16, 0, rb.RAGSTORE_CREATE_SIDECAR_ON) as st:
+        st.add(rows)
+        idx, sc, found, flags = st.search(qs[0], k)
+        eidx, esc = oc.query(rows, qs[0], k, n_threads=4)
+        # candidates come from the bf16 scan; the exact rescoring uses the original fp32 rows kept in the sidecar
+        assert np.array_equal(sc[0].view(np.uint64), oc.score_all(rows, qs[0], n_threads=4)[idx[0]].view(np.uint64))
