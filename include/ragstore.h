@@ -124,7 +124,9 @@ RAGSTORE_API int ragstore_set_row_blocking(ragstore_t* s, int64_t block_rows, in
  *   out_idx / out_score   n_queries x max(1,top_k); row ids best first, fp64 scores
  *   out_found per query: min(count, max(1,top_k))    out_flags per query: RAGSTORE_HIT_* (may be NULL)
  * Mirrors the reference's corner cases: empty store -> 0 hits; query_dim != dim -> every score is
- * -1, so rows 0..found-1 in insertion order with score -1.0 (RagIndex.cs:126 + stable sort). */
+ * -1, so rows 0..found-1 in insertion order with score -1.0 (RagIndex.cs:126 + stable sort).
+ * Any top_k is accepted; up to 256 hits come from one kernel launch per query, more (up to 8128) from
+ * repeated scans over disjoint candidate ranges.  More than 8128 hits: RAGSTORE_ERR_UNSUPPORTED. */
 RAGSTORE_API int ragstore_search(ragstore_t* s, const float* queries, int n_queries, int query_dim,
                                  int top_k, int64_t* out_idx, double* out_score,
                                  int32_t* out_found, int32_t* out_flags);
@@ -141,7 +143,8 @@ RAGSTORE_API int ragstore_search_coalesced(ragstore_t* s, const float* query, in
 RAGSTORE_API int ragstore_set_coalescing(ragstore_t* s, int window_us, int max_batch);
 
 /* Same work with every buffer already in device memory and no host synchronisation: enqueues on
- * `stream` (a cudaStream_t; NULL = the store's own stream) and returns.  query_dim must equal dim.
+ * `stream` (a cudaStream_t; NULL = the store's own stream) and returns.  query_dim must equal dim; at most
+ * 256 hits per query (min(count, max(1,top_k)) <= 256), because nothing can be read back to decide on more passes.
  * Not re-entrant: one in-flight device search per store (it uses the store's scratch). */
 RAGSTORE_API int ragstore_search_device(ragstore_t* s, const float* d_queries, int n_queries,
                                         int top_k, int64_t* d_idx, double* d_score,

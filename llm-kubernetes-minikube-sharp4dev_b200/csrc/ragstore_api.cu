@@ -10,6 +10,7 @@
 #include <condition_variable>
 #include <cstdio>
 #include <cstring>
+#include <limits>
 #include <mutex>
 #include <string>
 #include <vector>
@@ -52,11 +53,15 @@ struct DeviceGuard {
 
 constexpr int kCtxQueries = 256; // queries per host-search context batch (= one tensor-core launch)
 constexpr int kNumCtx = 4;       // concurrent host searches per store
+constexpr int kMaxPasses = 32;   // top_k > 256 is served by repeated scans of 256 candidates each
+constexpr int kMaxTake = kMaxPasses * kMaxKp - 64;
 
 struct SearchCtx {
     cudaStream_t st = nullptr;
     ScanScratch scratch{};
     uint8_t* batch_scratch = nullptr;  // candidate lists + query operand of the tensor-core path
+    ragstore_cand* d_pass = nullptr;   // top_k > 256: the rescored candidates of up to kMaxPasses scans
+    double* d_bound = nullptr;         // [1] + uint64 last key [1]
     float* d_q = nullptr;
     int64_t* d_idx = nullptr;
     double* d_score = nullptr;
@@ -166,6 +171,8 @@ int alloc_ctx(SearchCtx& c, int ld, int sm_count) {
     int rc = alloc_scratch(c.scratch);
     if (rc) return rc;
     CU_TRY(cudaMalloc(&c.batch_scratch, batch_scratch_bytes(sm_count)));
+    CU_TRY(cudaMalloc(&c.d_pass, sizeof(ragstore_cand) * kMaxPasses * kMaxKp));
+    CU_TRY(cudaMalloc(&c.d_bound, 16));
     const size_t nq = kCtxQueries;
     CU_TRY(cudaMalloc(&c.d_q, nq * ld * sizeof(float)));
     // one block per side: [idx][score][found][flags] packed per call, so the hits come back in ONE copy
@@ -179,6 +186,8 @@ void free_ctx(SearchCtx& c) {
     if (c.st) cudaStreamDestroy(c.st);
     free_scratch(c.scratch);
     cudaFree(c.batch_scratch);
+    cudaFree(c.d_pass);
+    cudaFree(c.d_bound);
     cudaFree(c.d_q);
     cudaFree(c.d_idx);
     cudaFreeHost(c.h_q);
@@ -721,7 +730,7 @@ int ragstore_search(ragstore_t* s, const float* queries, int n_queries, int quer
         }
         return RAGSTORE_OK;
     }
-    if (take > kMaxKp) return fail(RAGSTORE_ERR_UNSUPPORTED, "top_k above 256 is not covered yet");
+    if (take > kMaxTake) return fail(RAGSTORE_ERR_UNSUPPORTED, "more than 8128 hits per query are not covered");
     DeviceGuard g(s->device);
     if (!g.ok) return fail(RAGSTORE_ERR_CUDA, "cudaSetDevice failed");
 
@@ -745,6 +754,66 @@ int ragstore_search(ragstore_t* s, const float* queries, int n_queries, int quer
     } rel{s, ci};
     SearchCtx& c = s->ctxs[ci];
 
+    if (take > kMaxKp) {
+        // More than 256 hits: the candidate lists hold 256 keys, so the scan is repeated.  Pass p collects (and rescores
+        // exactly) the 256 best candidates whose approximate key lies BELOW the worst key of pass p-1; keys are unique
+        // (score bits, row), so the passes partition the corpus in approximate order.  The rescored records of all
+        // passes are then merged by (fp64 score desc, row asc) like the shards of a sharded corpus.
+        const int passes = std::min<int>(kMaxPasses, static_cast<int>((std::min<int64_t>(n, take + 64) + kMaxKp - 1) / kMaxKp));
+        for (int qi = 0; qi < n_queries; ++qi) {
+            memcpy(c.h_q, queries + static_cast<size_t>(qi) * s->dim, s->dim * sizeof(float));
+            CU_TRY(cudaMemcpyAsync(c.d_q, c.h_q, s->dim * sizeof(float), cudaMemcpyHostToDevice, c.st));
+            uint64_t key_below = 0;
+            int32_t flags_all = RAGSTORE_HIT_EXACT_ROWS;
+            double bound_total = 0.0;
+            int done_passes = 0;
+            bool exhausted = false;
+            for (int p = 0; p < passes && !exhausted; ++p) {
+                ScanArgs a = base_args(s, n, kMaxKp, kMaxKp);
+                a.d_query = c.d_q;
+                a.scratch = c.scratch;
+                a.key_below = key_below;
+                a.out_flags = reinterpret_cast<int32_t*>(c.d_idx);   // scratch word, read back below
+                a.out_cand = c.d_pass + static_cast<size_t>(p) * kMaxKp;
+                a.cand_slots = kMaxKp;
+                a.out_bound = c.d_bound;
+                a.out_last_key = reinterpret_cast<uint64_t*>(c.d_bound + 1);
+                s->n_scan_launches.fetch_add(1, std::memory_order_relaxed);
+                const int rc = launch_scan(a, c.st);
+                if (rc) return fail(RAGSTORE_ERR_CUDA, "scan kernel launch", cudaGetErrorString(static_cast<cudaError_t>(rc)));
+                struct { double bound; uint64_t last; } hb{};
+                int32_t hf = 0;
+                CU_TRY(cudaMemcpyAsync(&hb, c.d_bound, 16, cudaMemcpyDeviceToHost, c.st));
+                CU_TRY(cudaMemcpyAsync(&hf, c.d_idx, 4, cudaMemcpyDeviceToHost, c.st));
+                CU_TRY(cudaStreamSynchronize(c.st));
+                flags_all &= hf | ~RAGSTORE_HIT_EXACT_ROWS;
+                bound_total = hb.bound;
+                key_below = hb.last;
+                done_passes = p + 1;
+                exhausted = hb.last == 0ull || hb.bound == -std::numeric_limits<double>::infinity();  // list not full: nothing left
+            }
+            // merge the passes' records; outputs land in the context's packed result block
+            const size_t nh = static_cast<size_t>(take);
+            int64_t* d_idx = c.d_idx;
+            double* d_score = reinterpret_cast<double*>(c.d_idx + nh);
+            int32_t* d_found = reinterpret_cast<int32_t*>(d_score + nh);
+            const int rc = launch_merge_shards(c.d_pass, done_passes, 1, kMaxKp, take, d_idx, d_score, d_found, c.st);
+            if (rc) return fail(RAGSTORE_ERR_CUDA, "merge kernel launch", cudaGetErrorString(static_cast<cudaError_t>(rc)));
+            CU_TRY(cudaMemcpyAsync(c.h_idx, c.d_idx, nh * 16 + 8, cudaMemcpyDeviceToHost, c.st));
+            CU_TRY(cudaStreamSynchronize(c.st));
+            const int32_t found = *reinterpret_cast<int32_t*>(reinterpret_cast<double*>(c.h_idx + nh) + nh);
+            const size_t o = static_cast<size_t>(qi) * req;
+            memcpy(out_idx + o, c.h_idx, sizeof(int64_t) * found);
+            memcpy(out_score + o, reinterpret_cast<double*>(c.h_idx + nh), sizeof(double) * found);
+            out_found[qi] = found;
+            if (out_flags) {
+                const double ek = found > 0 ? out_score[o + found - 1] : 0.0;
+                const bool cert = exhausted || (found == take && ek > bound_total);
+                out_flags[qi] = (flags_all & RAGSTORE_HIT_EXACT_ROWS) | (cert ? RAGSTORE_HIT_CERTIFIED : 0);
+            }
+        }
+        return RAGSTORE_OK;
+    }
     int kp0 = choose_kp(take);
     const int hs = take;  // hits per query in the context buffers (compact: only what is copied back)
     for (int q0 = 0; q0 < n_queries; q0 += kCtxQueries) {

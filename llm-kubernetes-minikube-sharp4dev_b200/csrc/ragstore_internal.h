@@ -40,6 +40,8 @@ struct ScanArgs {
     int k_take;             // min(n_rows, max(1, top_k))
     int kp;                 // candidate list length: power of two in [32, kMaxKp], >= k_take
     float eps;              // bound on |approximate score - reference score| (DESIGN.md "certificate")
+    uint64_t key_below;     // 0 = none; otherwise only candidates with key < key_below are collected (top_k > 256: the
+                            // next 256 candidates after those of the previous pass)
     // scratch
     ScanScratch scratch;
     // outputs (device memory)
@@ -49,6 +51,8 @@ struct ScanArgs {
     int32_t* out_flags;     // [1] RAGSTORE_HIT_*
     ragstore_cand* out_cand;// [cand_slots] shard records, padded with {-inf,-1} (may be null)
     int cand_slots;
+    double* out_bound;      // [1] bound + eps + shrink: no row outside the collected candidates scores above it (may be null)
+    uint64_t* out_last_key; // [1] approximate key of the worst collected candidate, 0 if none (may be null)
     int sm_count;
 };
 

@@ -250,7 +250,7 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
                 const bool valid = r <= last;
                 const float sc = d * rn[valid ? r : last] + 0.0f;  // +0.0f: -0.0 -> +0.0 (the reference never yields -0.0)
                 const uint64_t key = make_key(sc, static_cast<uint32_t>(row0 + r));
-                unsigned m = __ballot_sync(0xffffffffu, valid && key > thr);
+                unsigned m = __ballot_sync(0xffffffffu, valid && key > thr && (a.key_below == 0ull || key < a.key_below));
                 while (m) {  // rare: a row beat the warp's current k'-th best
                     const int src = __ffs(m) - 1;
                     const uint64_t kk = __shfl_sync(0xffffffffu, key, src);
@@ -259,7 +259,7 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
                     if (++cnt == 32) {
                         thr = warp_flush(myL, myB, mybuf, cnt, kp, lane);
                         cnt = 0;
-                        m &= __ballot_sync(0xffffffffu, valid && key > thr);
+                        m &= __ballot_sync(0xffffffffu, valid && key > thr);  // (the key_below test already passed for these)
                     }
                 }
             }

@@ -323,7 +323,8 @@ __device__ __forceinline__ void finalize_candidates(const ScanArgs& a, const Fin
     __syncthreads();
     if (tid == 0) {
         bool cert;
-        if (a.n_rows <= static_cast<int64_t>(kp)) {
+        double bound_total = -CUDART_INF;
+        if (a.n_rows <= static_cast<int64_t>(kp) && a.key_below == 0ull) {
             cert = true;  // every row was rescored
         } else {
             // Rows outside the survivors have approximate score <= bound.  Their reference score is at
@@ -337,7 +338,11 @@ __device__ __forceinline__ void finalize_candidates(const ScanArgs& a, const Fin
                 const double d = sqrt(misc->na) * static_cast<double>(__uint_as_float(*a.min_norm_bits));
                 shrink = 1e-9 / d;  // +inf when the query is zero: then only a full rescore certifies
             }
-            cert = misc->ek > bound + static_cast<double>(a.eps) + shrink;  // false if either side is NaN
+            bound_total = bound + static_cast<double>(a.eps) + shrink;
+            // the list did not fill up and nothing was skipped by an initial threshold: no row was left out below it
+            const bool complete = n_cand < kp && !(f.bound_floor > -CUDART_INF_F);
+            if (complete) bound_total = -CUDART_INF;
+            cert = misc->ek > bound_total || complete;  // false if either side is NaN
             if (misc->na == 0.0) cert = true;  // zero query: every reference score is exactly +0.0 (or NaN, ranked last)
             if (k_take < a.k_take) cert = false;  // fewer survivors than requested hits: nothing to certify against
         }
@@ -346,6 +351,8 @@ __device__ __forceinline__ void finalize_candidates(const ScanArgs& a, const Fin
         if (misc->inexact == 0) flags |= RAGSTORE_HIT_EXACT_ROWS;
         if (a.out_flags) *a.out_flags = flags;
         if (a.out_found) *a.out_found = k_take;
+        if (a.out_bound) *a.out_bound = bound_total;
+        if (a.out_last_key) *a.out_last_key = n_cand > 0 ? lists[n_cand - 1] : 0ull;
         stamp(a, 5);
     }
 }

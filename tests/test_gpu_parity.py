@@ -518,3 +518,29 @@ def test_bf16_store_of_fp32_rows_within_stated_tolerance():
         eidx, esc = oc.query(rows, qs[0], k, n_threads=4)
         # candidates come from the bf16 scan; the exact rescoring uses the original fp32 rows kept in the sidecar
         assert np.array_equal(sc[0].view(np.uint64), oc.score_all(rows, qs[0], n_threads=4)[idx[0]].view(np.uint64))
+
+
+@pytest.mark.parametrize("n,d,k", [(5000, 96, 1000), (280, 64, 300), (3000, 768, 257), (20000, 128, 2000)])
+def test_more_than_256_hits_by_repeated_scans(n, d, k):
+    """QueryAsync takes any topK (RagIndex.cs:59,65).  Above 256 hits the scan is repeated over disjoint ranges of
+    approximate keys and the rescored passes are merged; the result must still be the reference's list."""
+    rows = oc.synth_rows(0, n, d, 21)
+    rows[5] = rows[200 if n > 200 else 3]
+    q = oc.synth_rows(0, 1, d, 22)[0]
+    eidx, esc = oc.query(rows, q, k, n_threads=4)
+    idx, sc, flags, _ = _search(rows, q, k)
+    assert len(idx) == min(n, k)
+    assert list(idx) == list(eidx)
+    assert np.array_equal(sc.view(np.uint64), esc.view(np.uint64))
+    assert flags & rb.RAGSTORE_HIT_CERTIFIED
+
+
+def test_many_identical_rows_across_pass_boundaries():
+    base = oc.synth_rows(0, 1, 64, 5)[0]
+    rows = np.tile(base, (700, 1))
+    rows[650] = -base
+    q = oc.synth_rows(0, 1, 64, 6)[0]
+    idx, sc, flags, _ = _search(rows, q, 400)
+    eidx, esc = oc.query(rows, q, 400)
+    assert list(idx) == list(eidx)          # 400 equal scores: insertion order, through two pass boundaries
+    assert np.array_equal(sc.view(np.uint64), esc.view(np.uint64))
