@@ -228,6 +228,22 @@ def measure_workload(name, args, torch, dist, rb, native, rank, world, dev, do_e
                 qi[0] += 1
                 st.search_device(q, 1, k, d_idx, d_score, d_found, d_flags, stream=ts.cuda_stream)
             launches_per_step = 1
+        elif nqb > 1:
+            # batched + sharded: every shard sweeps its rows once for the whole batch (tensor-core path), the per-query
+            # candidates are all-gathered (nq * k * 16 bytes per rank) and merged, one CTA per query
+            n_q = nqb
+            d_q = torch.empty((n_q, dim), dtype=torch.float32, device="cuda")
+            native.synth_fill_device(d_q, 0, n_q, dim, dim, QUERY_SEED, device=dev, stream=ts.cuda_stream)
+            sh = rb.ShardedSearcher(st, rank, world, rank * rows, max_k=max(k, 1), device=dev)
+            sh.search_batch_device(d_q, nqb, k)          # allocates the batch buffers
+            d_cand, d_all, d_flags = sh._b_cand, sh._b_all, sh.d_flags
+            d_idx, d_score, d_found = sh._b_idx, sh._b_score, sh._b_found
+            d_flags = torch.ones(nqb, dtype=torch.int32, device="cuda")
+
+            def step():
+                qi[0] += 1
+                sh.search_batch_device(d_q, nqb, k)
+            launches_per_step = 4
         else:
             sh = rb.ShardedSearcher(st, rank, world, rank * rows, max_k=max(k, 1), device=dev)
             d_cand, d_all, d_idx, d_score, d_found, d_flags = sh.d_cand, sh.d_all, sh.d_idx, sh.d_score, sh.d_found, sh.d_flags
@@ -250,7 +266,7 @@ def measure_workload(name, args, torch, dist, rb, native, rank, world, dev, do_e
         if nqb > 1:
             res["tensor_tflops"] = 2.0 * nqb * rows * dim * args.steps / (ms * 1e-3) / 1e12
         # dominant kernel: the fused scan; at world == 1 a step IS one launch of it
-        if world == 1:
+        if world == 1 or nqb > 1:
             kern_ms = ms / args.steps
         else:
             qi[0] = 0
@@ -281,7 +297,7 @@ def measure_workload(name, args, torch, dist, rb, native, rank, world, dev, do_e
                       "d2h_bytes_per_step": nqb * (256 * 16 + 8), "ms_per_step": dt / n_e2e * 1e3, "steps": n_e2e,
                       "queries_per_s": nqb * n_e2e / dt,
                       "api": "ragstore_search (C ABI, host buffers, synchronous)"}
-    elif do_e2e:
+    elif do_e2e and nqb == 1:
         # sharded: host query -> every rank's device, hits back to the host on every rank
         hq = d_q.cpu()
         hq_pin = torch.empty(dim, dtype=torch.float32).pin_memory()

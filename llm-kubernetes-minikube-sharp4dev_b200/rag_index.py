@@ -39,12 +39,13 @@ class RagIndex:
     """Drop-in for `class RagIndex` (RagIndex.cs:6): store + brute-force cosine top-k."""
 
     def __init__(self, embedModel: str, embedder: Optional[Callable] = None, *, dim: Optional[int] = None,
-                 capacity_rows: int = 1 << 20, dtype: int = RAGSTORE_F32, device: int = 0):
+                 capacity_rows: int = 1 << 20, dtype: int = RAGSTORE_F32, device: int = 0, coalesce: bool = False):
         self._embedModel = embedModel                       # RagIndex.cs:9,11
         self._embedder = embedder
         self._meta: List[tuple] = []                        # (Id, Source, Text) per row, insertion order
         self._store: Optional[RagStore] = None
         self._dim, self._cap, self._dtype, self._device = dim, capacity_rows, dtype, device
+        self._coalesce = coalesce          # concurrent QueryAsync callers share one corpus sweep (SURVEY 8f N1)
         self.last_flags = None
 
     # -- store side ---------------------------------------------------------------------------
@@ -99,13 +100,27 @@ class RagIndex:
         """QueryAsync after the embedding call (RagIndex.cs:62-66)."""
         if self._store is None or not self._meta:
             return []                                         # empty index -> empty list
-        idx, score, found, flags = self._store.search(np.asarray(q, dtype=np.float32), topK)
-        self.last_flags = int(flags[0])
+        if self._coalesce:
+            idx1, score1, flags1 = self._store.search_coalesced(np.asarray(q, dtype=np.float32), topK)
+            self.last_flags = int(flags1)
+        else:
+            idx, score, found, flags = self._store.search(np.asarray(q, dtype=np.float32), topK)
+            idx1, score1 = idx[0, :int(found[0])], score[0, :int(found[0])]
+            self.last_flags = int(flags[0])
         hits = []
-        for j in range(int(found[0])):
-            Id, Source, Text = self._meta[int(idx[0, j])]
-            hits.append(RagHit(Id, Source, Text, float(score[0, j])))
+        for i, sc in zip(idx1, score1):
+            Id, Source, Text = self._meta[int(i)]
+            hits.append(RagHit(Id, Source, Text, float(sc)))
         return hits
+
+    @staticmethod
+    def Citations(hits: Sequence[RagHit], evidenceMinScore: float = 0.35, bestFactor: float = 0.6) -> List[str]:
+        """The /agent_rag citation rule (Program.cs:125-128): ids of hits with Score >= max(0.35, 0.6 * best)."""
+        from .native import hit_filters
+        if not hits:
+            return []
+        cited, _, _ = hit_filters([h.Score for h in hits], evidenceMinScore, bestFactor)
+        return [h.Id for h, c in zip(hits, cited) if c]
 
     async def QueryAsync(self, query: str, topK: int = 5) -> List[RagHit]:
         """`Task<List<RagHit>> QueryAsync(string query, int topK = 5)` (RagIndex.cs:59)."""

@@ -217,7 +217,14 @@ def test_rag_index_mirror():
     assert [h.Id for h in hits] == [f"doc.md#{i}" for i in eidx]
     assert [h.Score for h in hits] == list(esc)
     assert rb.RagIndex("m").QueryEmbedding(emb["t1"], 3) == []
+    cites = rb.RagIndex.Citations(hits)
+    best = max(h.Score for h in hits)
+    assert cites == [h.Id for h in hits if h.Score >= max(0.35, 0.6 * best)] and cites[0] == "doc.md#7"
     ri.close()
+    rc = rb.RagIndex("nomic-embed-text", embedder=lambda model, text: emb[text], capacity_rows=128, coalesce=True)
+    rc.AddRange([rb.RagChunk(f"doc.md#{i}", "doc.md", f"t{i}", emb[f"t{i}"]) for i in range(40)])
+    assert [h.Id for h in rc.Query("t7", 5)] == [h.Id for h in hits]
+    rc.close()
 
 
 @pytest.mark.parametrize("n,k,dtype", [(5000, 10, 0), (3001, 100, 0), (4000, 100, 1)])
