@@ -11,7 +11,6 @@ constexpr int kConsumerWarps = 8;                       // warps that score rows
 constexpr int kScanThreads = (kConsumerWarps + 1) * 32; // + one producer warp (bulk-copy issue)
 constexpr int kMaxKp = 256;                             // largest candidate list kept per warp/CTA
 constexpr int kMaxCtas = 1024;                          // scratch sizing: CTAs of one scan launch
-constexpr int kMaxBatchQ = 4;                           // queries scored per corpus sweep (GEMV path)
 
 // Scratch one scan launch needs in global memory (beyond inputs/outputs).
 struct ScanScratch {
@@ -58,8 +57,6 @@ struct ScanArgs {
 
 // Enqueues the fused scan + top-k + exact-rescore kernel.  Returns cudaError_t as int.
 int launch_scan(const ScanArgs& a, cudaStream_t stream);
-// One-time per-device kernel attribute set-up (max dynamic shared memory).
-int scan_configure_device();
 
 struct NormaliseArgs {
     const float* src;     // [n_rows][src_ld] fp32 (may alias dst for the fp32 store)

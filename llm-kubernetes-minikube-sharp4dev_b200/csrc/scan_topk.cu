@@ -423,6 +423,4 @@ int launch_scan(const ScanArgs& a, cudaStream_t stream) {
     return dispatch_dv<uint16_t>(a, dv, full, L, grid, stream);
 }
 
-int scan_configure_device() { return 0; }
-
 }  // namespace rag
