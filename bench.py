@@ -273,6 +273,18 @@ def measure_workload(name, args, torch, dist, rb, native, rank, world, dev, do_e
             kern_ms = time_device_steps(torch, dist, 1, lambda: st.search_shard_device(d_q[0], k, d_cand, d_flags, stream=ts.cuda_stream),
                                         max(10, args.steps // 4), 3) / max(10, args.steps // 4)
         res["kernel_ms"] = kern_ms
+        if world == 1:
+            # per-step latency distribution (median and p99), a separate pass with an event between steps
+            n_lat = min(max(args.steps, 20), 400)
+            evs = [torch.cuda.Event(enable_timing=True) for _ in range(n_lat + 1)]
+            evs[0].record()
+            for i in range(n_lat):
+                step()
+                evs[i + 1].record()
+            torch.cuda.synchronize()
+            lat = sorted(evs[i].elapsed_time(evs[i + 1]) for i in range(n_lat))
+            res["latency_ms"] = {"n": n_lat, "min": lat[0], "median": lat[n_lat // 2],
+                                 "p99": lat[min(n_lat - 1, int(n_lat * 0.99))], "max": lat[-1]}
         res["achieved_gbs"] = rows * dim * esz / (kern_ms * 1e-3) / 1e9
         last_q_index = (qi[0] - 1) % n_q
         torch.cuda.synchronize()
@@ -289,13 +301,18 @@ def measure_workload(name, args, torch, dist, rb, native, rank, world, dev, do_e
         for i in range(max(3, args.warmup // 4)):
             st.search(hq_step(i), k)
         n_e2e = max(5, args.steps // 4)
+        per_call = []
         t0 = time.perf_counter()
         for i in range(n_e2e):
+            tc = time.perf_counter()
             idx, sc, found, flags = st.search(hq_step(i), k)
+            per_call.append(time.perf_counter() - tc)
         dt = time.perf_counter() - t0
+        per_call.sort()
         res["e2e"] = {"value": rows * n_e2e / dt, "unit": "vectors/s", "h2d_bytes_per_step": nqb * dim * 4,
                       "d2h_bytes_per_step": nqb * (256 * 16 + 8), "ms_per_step": dt / n_e2e * 1e3, "steps": n_e2e,
                       "queries_per_s": nqb * n_e2e / dt,
+                      "median_ms": per_call[n_e2e // 2] * 1e3, "p99_ms": per_call[min(n_e2e - 1, int(n_e2e * 0.99))] * 1e3,
                       "api": "ragstore_search (C ABI, host buffers, synchronous)"}
     elif do_e2e and nqb == 1:
         # sharded: host query -> every rank's device, hits back to the host on every rank
@@ -517,7 +534,7 @@ def main():
                 peak, _ = measured_peaks()
                 extra[name] = {"desc": r["desc"], "vectors_per_s": r["value"], "queries_per_s": r["queries_per_s"], "ms_per_step": r["ms_per_step"],
                                "achieved_gbs": r["achieved_gbs"], "frac_of_measured_hbm": r["achieved_gbs"] / peak,
-                               "frac_of_8TBs_spec": r["achieved_gbs"] / 8000.0, "steps": sub.steps, "flags": r["flags"]}
+                               "frac_of_8TBs_spec": r["achieved_gbs"] / 8000.0, "steps": sub.steps, "flags": r["flags"], "latency_ms": r.get("latency_ms")}
                 if "e2e" in r:
                     extra[name]["e2e_ms_per_query"] = r["e2e"]["ms_per_step"]
             except Exception as ex:  # an extra must never take the headline down
@@ -562,6 +579,7 @@ def main():
             "gpu_launches": args.steps * r["launches_per_step"],
             "clocks": r["clocks"],
             "parity": r.get("parity"),
+            "latency_ms": r.get("latency_ms"),
             "result_flags": r["flags"],
             "ingest_vectors_per_s": r["ingest_vectors_per_s"],
             "k1_upload_normalise": k1,

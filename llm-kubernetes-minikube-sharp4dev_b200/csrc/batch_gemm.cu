@@ -6,22 +6,26 @@
 // whole batch of queries at once; selection and exact rescoring follow the same rules as the
 // single-query kernel (topk_device.cuh), so the returned hits are the reference's.
 //
-// Shape (B200 / sm_100a), one persistent CTA per SM, 384 threads:
+// Shape (B200 / sm_100a), one persistent CTA per SM, 384 threads, clusters of 2:
 //   warp 0      TMA producer: 2-D tiled bulk tensor copies (cp.async.bulk.tensor, 128B swizzle) of a
-//               128-row corpus tile slice and of the 128/256-query slice into a 3..5-stage ring;
-//   warp 1      MMA issuer: one lane issues tcgen05.mma.cta_group::1.kind::tf32 (M=128 queries, N=128
-//               corpus rows, K=8 per instruction), accumulators in TMEM, double buffered (2 x 256
-//               columns), tcgen05.commit releases ring stages and publishes finished accumulators;
+//               256-row corpus tile slice and (multicast across the cluster) of the 128/256-query slice
+//               into a 4..5-stage ring; one stage = 128 bytes of K per row;
+//   warp 1      MMA issuer: one lane issues tcgen05.mma.cta_group::1 (M = 128 queries, N = 256 corpus
+//               rows; kind::tf32 with K = 8 for fp32 stores, kind::f16 on bf16 operands with K = 16 for
+//               bf16 stores), accumulators in TMEM, tcgen05.commit releases ring stages and publishes
+//               finished accumulators;
 //   warp 2      allocates / frees the 512 TMEM columns;
-//   warps 4-11  epilogue: thread <-> query (TMEM lane), tcgen05.ld of its 128 scores per tile, a
-//               register threshold and a thread-private sorted candidate list in shared memory --
-//               no atomics, no overflow, and the M x N score block is never written anywhere.
+//   warps 4-11  epilogue: thread <-> query (TMEM lane), tcgen05.ld of its 256 scores per tile, a
+//               register threshold and a thread-private candidate list (scores in registers, row ids
+//               in shared memory) -- no atomics, no overflow, and the M x N score block is never
+//               written anywhere.
 // Queries are the M operand on purpose: a TMEM lane then carries ONE query's scores across corpus rows,
 // which is what makes the per-query running top-k thread-private.
-// tf32 products differ from the reference's by up to 2^-9 relative, so this kernel only nominates
+// Reduced-precision products differ from the reference's (tf32: two 10-bit mantissas; bf16 stores: the
+// query is rounded to bf16, the stored rows are used as they are), so this kernel only nominates
 // k' = 32 candidates per query; batch_finalize_kernel re-scores them with the reference's exact
-// fp64 arithmetic and certifies the margin (eps = 2.1e-3); uncertified queries are redone by the
-// fp32 scan kernel (host side, ragstore_api.cu).
+// fp64 arithmetic and certifies the margin (eps ~ 2.1e-3); uncertified queries are redone by the
+// scan kernel (host side, ragstore_api.cu).
 #include <cuda.h>
 
 #include <cstdio>
@@ -111,6 +115,15 @@ __device__ __forceinline__ void mma_tf32(uint32_t tmem_d, uint64_t adesc, uint64
         ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
         : "memory");
 }
+// same with bf16 inputs (kind::f16, K = 16 per instruction)
+__device__ __forceinline__ void mma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
 // 32 lanes x 32 consecutive 32-bit columns: thread i of the warp gets lane (base + i)
 __device__ __forceinline__ void tmem_ld_32x32(uint32_t taddr, uint32_t (&v)[32]) {
     asm volatile(
@@ -140,12 +153,15 @@ __device__ __forceinline__ uint64_t make_sw128_desc(uint32_t smem_addr) {
 
 // instruction descriptor: D fp32, A/B tf32, both K-major, M = 128, N = 128
 constexpr uint32_t kIdescTf32 = (1u << 4) | (2u << 7) | (2u << 10) | ((kBN >> 3) << 17) | ((kBM >> 4) << 24);
+// the same shape for kind::f16 with bf16 A and B (format code 1)
+constexpr uint32_t kIdescBf16 = (1u << 4) | (1u << 7) | (1u << 10) | ((kBN >> 3) << 17) | ((kBM >> 4) << 24);
 
 struct BatchArgs {
     int64_t n_rows;
     int nq;            // real queries in this launch (<= 128 * mblocks)
     int mblocks;       // 1 or 2 blocks of 128 queries
-    int nkb;           // k-blocks of 32 fp32 per row
+    int nkb;           // k-blocks of 128 bytes (32 fp32 / 64 bf16) per row
+    const float* rnorm; // per-row reciprocal norms (bf16 stores: applied to the tensor-core dot products)
     uint64_t* glists;  // [nq][n_ctas][kBatchKp] candidate keys, written by this kernel
     int debug;         // profiling experiments: 1 = epilogue drains without scanning, 2 = no MMA issue
     int tile_stride;   // 1 = every tile; s > 1 = the sampling pass: tiles 0, s, 2s, ...
@@ -207,13 +223,23 @@ __device__ __forceinline__ void tmem_ld_32x16(uint32_t taddr, uint32_t (&v)[16])
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
+// bf16 stores: the smallest raw dot product that could still exceed `thr` once multiplied by a reciprocal norm
+// <= rn_max.  Rounded down with slack, so the test `dot > raw_threshold` never misses a row; a negative threshold
+// (lists still cold) admits everything.
+__device__ __forceinline__ float raw_threshold(float thr, float rn_max) {
+    if (thr < 0.f) return -CUDART_INF_F;
+    return __fdiv_rd(thr, rn_max) * (1.0f - 2.4e-7f);   // thr > 0, rn_max == 0: +inf (nothing passes, all scores are 0)
+}
+
 // ---------------------------------------------------------------- the tensor-core kernel
 // MB = blocks of 128 queries (1 or 2).  Tile = 256 corpus rows: one MMA is M=128 (queries) x N=256 (rows),
 // so MB = 1 double-buffers its accumulator (2 x 256 TMEM columns) while MB = 2 uses all 512 columns for
 // one tile.  Per ring stage a CTA ingests 32 KB of corpus + MB x 16 KB of queries: the L2->SM ingest per
 // corpus byte (1.5x / 2x) is what bounds this kernel (measured ~46 B/clk/SM for 128-byte TMA rows), which
 // is why the tile is as tall as TMEM allows.
-template <int MB>
+// BF = bf16 store: operands are bf16 (64 elements per 128-byte slice), and because such a store keeps rows
+// as given (their norm is 1 only to within bf16 rounding) the epilogue applies the row's reciprocal norm.
+template <int MB, bool BF>
 __global__ void __cluster_dims__(kCluster, 1, 1) __launch_bounds__(kBatchThreads, 1)
 batch_score_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_c,
                    const BatchArgs a, const BatchLayout L) {
@@ -224,6 +250,7 @@ batch_score_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
     const int n_stages = static_cast<int>(L.n_stages);
     constexpr int AS = MB == 1 ? 2 : 1;       // accumulator stages
     constexpr int NQ = kBM * MB;
+    constexpr int KE = BF ? 64 : 32;          // elements per 128-byte K slice
     uint64_t* full = reinterpret_cast<uint64_t*>(smem + L.off_bars);
     uint64_t* empty = full + n_stages;
     uint64_t* tmem_full = empty + n_stages;   // [AS]
@@ -278,8 +305,8 @@ batch_score_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
                     mbar_wait(empty + s, ph ^ 1u);
                     uint8_t* st = smem + static_cast<size_t>(s) * L.stage_bytes;
                     mbar_arrive_expect_tx(full + s, tx);
-                    tma_load_2d_mc(st + q_off, &tmap_q, full + s, kb * 32, static_cast<int>(crank) * q_rows, cmask);
-                    tma_load_2d(st + MB * kOperandBytes, &tmap_c, full + s, kb * 32, row0);
+                    tma_load_2d_mc(st + q_off, &tmap_q, full + s, kb * KE, static_cast<int>(crank) * q_rows, cmask);
+                    tma_load_2d(st + MB * kOperandBytes, &tmap_c, full + s, kb * KE, row0);
                     if (++s == n_stages) {
                         s = 0;
                         ph ^= 1u;
@@ -303,12 +330,17 @@ batch_score_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
                     const uint32_t st = smem_u32(smem + static_cast<size_t>(s) * L.stage_bytes);
                     const uint32_t b_addr = st + MB * kOperandBytes;
 #pragma unroll
-                    for (int k4 = 0; k4 < 4; ++k4) {  // 4 x K=8 tf32 per 128-byte slice
+                    for (int k4 = 0; k4 < 4; ++k4) {  // 4 x (K=8 tf32 | K=16 bf16) = 32 bytes each per 128-byte slice
                         const uint64_t bdesc = make_sw128_desc(b_addr + k4 * 32);
 #pragma unroll
                         for (int m = 0; m < MB; ++m) {
                             const uint64_t adesc = make_sw128_desc(st + m * kOperandBytes + k4 * 32);
-                            if (!(a.debug & 2)) mma_tf32(tmem_base + (as * MB + m) * 256u, adesc, bdesc, kIdescTf32, (kb | k4) != 0);
+                            if (!(a.debug & 2)) {
+                                if (BF)
+                                    mma_bf16(tmem_base + (as * MB + m) * 256u, adesc, bdesc, kIdescBf16, (kb | k4) != 0);
+                                else
+                                    mma_tf32(tmem_base + (as * MB + m) * 256u, adesc, bdesc, kIdescTf32, (kb | k4) != 0);
+                            }
                         }
                     }
                     tc_commit_mc(empty + s, cmask);  // stage reusable (here and in the peers) once these MMAs have read it
@@ -347,16 +379,29 @@ batch_score_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
             float t0 = -CUDART_INF_F, t1 = -CUDART_INF_F, t2 = -CUDART_INF_F, t3 = -CUDART_INF_F;  // t0 >= t1 >= t2 >= t3
             for (int64_t it = 0; it < my_tiles; ++it) {
                 const uint32_t as = static_cast<uint32_t>(it % AS), aph = static_cast<uint32_t>((it / AS) & 1);
-                mbar_wait(tmem_full + as, aph);
-                tc_fence_after();
                 const int64_t row0 = ((cluster_id + it * n_clusters) * kCluster + crank) * a.tile_stride * kBN;
                 const int nvalid = static_cast<int>(min(static_cast<int64_t>(kBN), a.n_rows - row0));
+                // bf16 store: a sampled value only has to be a LOWER bound of a real row's score, so the tile's
+                // smallest / largest reciprocal norm stands in for the row's own
+                float rn_lo = 1.f, rn_hi = 1.f;
+                if (BF) {
+                    float lo = CUDART_INF_F, hi = 0.f;
+                    for (int j = lane; j < nvalid; j += 32) {
+                        const float r = __ldg(a.rnorm + row0 + j);
+                        lo = fminf(lo, r), hi = fmaxf(hi, r);
+                    }
+                    rn_lo = __uint_as_float(__reduce_min_sync(0xffffffffu, __float_as_uint(lo)));
+                    rn_hi = __uint_as_float(__reduce_max_sync(0xffffffffu, __float_as_uint(hi)));
+                }
+                mbar_wait(tmem_full + as, aph);
+                tc_fence_after();
                 for (int cb = 0; cb < kBN; cb += 32) {
                     uint32_t v[32];
                     tmem_ld_32x32(tmem_base + lane_base + (as * MB + mblock) * 256u + cb, v);
 #pragma unroll
                     for (int j = 0; j < 32; ++j) {
-                        const float sc = __uint_as_float(v[j]);
+                        float sc = __uint_as_float(v[j]);
+                        if (BF) sc = sc > 0.f ? sc * rn_lo : sc * rn_hi;
                         if (sc > t3 && cb + j < nvalid) {  // 4-slot sorted insert
                             const float a0 = fmaxf(t0, sc), b0 = fminf(t0, sc);
                             const float a1 = fmaxf(t1, b0), b1 = fminf(t1, b0);
@@ -378,12 +423,22 @@ batch_score_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
         for (int64_t it = 0; it < my_tiles; ++it) {
             const uint32_t as = static_cast<uint32_t>(it % AS), aph = static_cast<uint32_t>((it / AS) & 1);
             const long long c0k = clock64();
+            const int64_t row0 = ((cluster_id + it * n_clusters) * kCluster + crank) * a.tile_stride * kBN;
+            const int nvalid = static_cast<int>(min(static_cast<int64_t>(kBN), a.n_rows - row0));
+            // bf16 store: score = dot * rnorm[row].  The steady-state test compares the raw dot products with
+            // thr / (largest rnorm of the tile), a superset of the rows that can beat thr; only those get the
+            // exact product.  (fetched before the wait so the loads overlap the MMAs)
+            float rn_max = 1.f;
+            if (BF) {
+                float hi = 0.f;
+                for (int j = lane; j < nvalid; j += 32) hi = fmaxf(hi, __ldg(a.rnorm + row0 + j));
+                rn_max = __uint_as_float(__reduce_max_sync(0xffffffffu, __float_as_uint(hi)));
+            }
             mbar_wait(tmem_full + as, aph);
             tc_fence_after();
             const long long c1k = clock64();
             t_wait += c1k - c0k;
-            const int64_t row0 = ((cluster_id + it * n_clusters) * kCluster + crank) * a.tile_stride * kBN;
-            const int nvalid = static_cast<int>(min(static_cast<int64_t>(kBN), a.n_rows - row0));
+            float thr_cmp = BF ? raw_threshold(thr, rn_max) : thr;
             for (int cb = 0; cb < kBN; cb += 64) {
                 // four 16-column loads in flight per wait: the TMEM read latency is paid once per 64 columns
                 uint32_t v[4][16];
@@ -402,7 +457,7 @@ batch_score_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
 #pragma unroll
                     for (int j = 1; j < 16; ++j) mx[u] = fmaxf(mx[u], __uint_as_float(v[u][j]));
                 }
-                const bool hot = live && !(a.debug & 1) && fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3])) > thr;
+                const bool hot = live && !(a.debug & 1) && fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3])) > thr_cmp;
                 unsigned long long mine = 0, any = 0;
                 if (__any_sync(0xffffffffu, hot)) {
                     if (hot) {
@@ -410,7 +465,7 @@ batch_score_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
                         for (int u = 0; u < 4; ++u)
 #pragma unroll
                             for (int j = 0; j < 16; ++j)
-                                mine |= static_cast<unsigned long long>(__uint_as_float(v[u][j]) > thr ? 1u : 0u) << (u * 16 + j);
+                                mine |= static_cast<unsigned long long>(__uint_as_float(v[u][j]) > thr_cmp ? 1u : 0u) << (u * 16 + j);
                     }
                     const unsigned lo = __reduce_or_sync(0xffffffffu, static_cast<unsigned>(mine));
                     const unsigned hi = __reduce_or_sync(0xffffffffu, static_cast<unsigned>(mine >> 32));
@@ -422,9 +477,12 @@ batch_score_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
                     uint32_t one;
                     asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(one) : "r"(tmem_base + lane_base + (as * MB + mblock) * 256u + cb + j) : "memory");
                     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-                    const float sc = __uint_as_float(one);
-                    if (((mine >> j) & 1ull) && sc > thr && cb + j < nvalid)  // rows ascend, so an equal score never displaces
+                    float sc = __uint_as_float(one);
+                    if (BF) sc = cb + j < nvalid ? sc * __ldg(a.rnorm + row0 + cb + j) + 0.0f : -CUDART_INF_F;
+                    if (((mine >> j) & 1ull) && sc > thr && cb + j < nvalid) {  // rows ascend, so an equal score never displaces
                         list_insert(S, minpos, thr, rows, NQ, q, sc, static_cast<uint32_t>(row0 + cb + j));
+                        if (BF) thr_cmp = raw_threshold(thr, rn_max); else thr_cmp = thr;
+                    }
                 }
             }
             tc_fence_before();
@@ -754,14 +812,16 @@ __global__ void __launch_bounds__(kScanThreads, 1) batch_finalize_kernel(const B
 }
 
 // normalised, zero-padded copy of the queries: the tensor-core operand (rows >= nq are zero)
-__global__ void __launch_bounds__(256) prep_queries_kernel(const float* __restrict__ q, float* __restrict__ qhat, int nq,
+// (T = float for fp32 stores; T = uint16_t: rounded to bf16, nearest-even, for bf16 stores)
+template <typename T>
+__global__ void __launch_bounds__(256) prep_queries_kernel(const float* __restrict__ q, T* __restrict__ qhat, int nq,
                                                            int nq_pad, int dim, int ld) {
     const int lane = threadIdx.x & 31;
     const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (row >= nq_pad) return;
-    float* dst = qhat + static_cast<size_t>(row) * ld;
+    T* dst = qhat + static_cast<size_t>(row) * ld;
     if (row >= nq) {
-        for (int i = lane; i < ld; i += 32) dst[i] = 0.f;
+        for (int i = lane; i < ld; i += 32) dst[i] = T(0);
         return;
     }
     const float* src = q + static_cast<size_t>(row) * dim;
@@ -769,7 +829,13 @@ __global__ void __launch_bounds__(256) prep_queries_kernel(const float* __restri
     for (int i = lane; i < dim; i += 32) acc += static_cast<double>(src[i]) * static_cast<double>(src[i]);
     acc = warp_sum(acc);
     const float r = acc > 0.0 ? static_cast<float>(1.0 / sqrt(acc)) : 0.f;
-    for (int i = lane; i < ld; i += 32) dst[i] = i < dim ? src[i] * r : 0.f;
+    for (int i = lane; i < ld; i += 32) {
+        const float x = i < dim ? src[i] * r : 0.f;
+        if (sizeof(T) == 4)
+            dst[i] = static_cast<T>(x);
+        else
+            dst[i] = static_cast<T>(f32_to_bf16_bits(x));
+    }
 }
 
 // ---------------------------------------------------------------- host side
@@ -790,14 +856,16 @@ static PFN_encodeTiled encode_fn() {
     return fn;
 }
 
-static bool make_map_f32(CUtensorMap* m, const void* base, uint64_t rows, uint64_t ld, uint32_t box_rows) {
+// row-major [rows][ld] matrix of fp32 or bf16; a box is 128 bytes of K x box_rows rows
+static bool make_map(CUtensorMap* m, const void* base, uint64_t rows, uint64_t ld, uint32_t box_rows, bool bf16) {
     PFN_encodeTiled enc = encode_fn();
     if (!enc) return false;
+    const uint32_t esz = bf16 ? 2 : 4;
     const cuuint64_t dims[2] = {ld, rows};
-    const cuuint64_t strides[1] = {ld * 4};
-    const cuuint32_t box[2] = {32, box_rows};
+    const cuuint64_t strides[1] = {ld * esz};
+    const cuuint32_t box[2] = {128u / esz, box_rows};
     const cuuint32_t estr[2] = {1, 1};
-    return enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(base), dims, strides, box, estr,
+    return enc(m, bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(base), dims, strides, box, estr,
                CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
@@ -810,7 +878,8 @@ size_t batch_scratch_bytes(int sm_count) {
 
 int launch_batch_search(const BatchSearchArgs& b, cudaStream_t stream) {
     const ScanArgs& s = b.scan;
-    if (s.dtype != RAGSTORE_F32 || b.nq < 1 || b.nq > kBatchMaxQ || s.ld > kBatchMaxLd || s.kp != kBatchKp ||
+    const bool bf = s.dtype == RAGSTORE_BF16;
+    if ((bf && s.ld % 8 != 0) || b.nq < 1 || b.nq > kBatchMaxQ || s.ld > kBatchMaxLd || s.kp != kBatchKp ||
         s.n_rows < 1 || s.n_rows >= 0x7FFF0000ll)
         return static_cast<int>(cudaErrorInvalidValue);
     const int mblocks = b.nq > kBM ? 2 : 1;
@@ -819,21 +888,24 @@ int launch_batch_search(const BatchSearchArgs& b, cudaStream_t stream) {
     float* qhat = reinterpret_cast<float*>(b.scratch + sizeof(uint64_t) * size_t(kBatchMaxQ) * size_t(s.sm_count) * kBatchKp);
     float* thr0 = qhat + size_t(kBatchMaxQ) * size_t(kBatchMaxLd);
 
-    prep_queries_kernel<<<(nq_pad * 32 + 255) / 256, 256, 0, stream>>>(b.d_queries, qhat, b.nq, nq_pad, s.dim, s.ld);
+    if (bf)
+        prep_queries_kernel<uint16_t><<<(nq_pad * 32 + 255) / 256, 256, 0, stream>>>(b.d_queries, reinterpret_cast<uint16_t*>(qhat), b.nq, nq_pad, s.dim, s.ld);
+    else
+        prep_queries_kernel<float><<<(nq_pad * 32 + 255) / 256, 256, 0, stream>>>(b.d_queries, qhat, b.nq, nq_pad, s.dim, s.ld);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return static_cast<int>(e);
 
     CUtensorMap map_q, map_c;
     const char* mode_env = std::getenv("RAGSTORE_BATCH_2SM");
-    const bool pair_maps = mblocks == 2 && mode_env && mode_env[0] == '1';
-    if (!make_map_f32(&map_q, qhat, static_cast<uint64_t>(nq_pad), static_cast<uint64_t>(s.ld), pair_maps ? kBM : nq_pad / kCluster) ||
-        !make_map_f32(&map_c, s.mat, static_cast<uint64_t>(s.n_rows), static_cast<uint64_t>(s.ld), pair_maps ? 128 : kBN))
+    const bool pair_maps = mblocks == 2 && !bf && mode_env && mode_env[0] == '1';
+    if (!make_map(&map_q, qhat, static_cast<uint64_t>(nq_pad), static_cast<uint64_t>(s.ld), pair_maps ? kBM : nq_pad / kCluster, bf) ||
+        !make_map(&map_c, s.mat, static_cast<uint64_t>(s.n_rows), static_cast<uint64_t>(s.ld), pair_maps ? 128 : kBN, bf))
         return static_cast<int>(cudaErrorNotSupported);
 
     const char* mode = std::getenv("RAGSTORE_BATCH_2SM");
     // The CTA-pair (cta_group::2) kernel is correct but measured slower for tf32 (2.9 vs 4.7 TB/s of corpus: the pair's
     // operand exchange paces 4-byte operands), so it is opt-in: RAGSTORE_BATCH_2SM=1.
-    const bool pair = mblocks == 2 && mode && mode[0] == '1';
+    const bool pair = mblocks == 2 && !bf && mode && mode[0] == '1';
     BatchLayout L;
     L.mblocks = mblocks;
     L.stage_bytes = pair ? 2 * kOperandBytes : (mblocks + 2) * kOperandBytes;
@@ -852,7 +924,8 @@ int launch_batch_search(const BatchSearchArgs& b, cudaStream_t stream) {
     a.n_rows = s.n_rows;
     a.nq = b.nq;
     a.mblocks = mblocks;
-    a.nkb = (s.ld + 31) / 32;
+    a.nkb = bf ? (s.ld + 63) / 64 : (s.ld + 31) / 32;
+    a.rnorm = s.rnorm;
     a.glists = glists;
     a.debug = std::getenv("RAGSTORE_BATCH_DEBUG") ? atoi(std::getenv("RAGSTORE_BATCH_DEBUG")) : 0;
     const int64_t n_tiles = (s.n_rows + kBN - 1) / kBN;
@@ -865,17 +938,15 @@ int launch_batch_search(const BatchSearchArgs& b, cudaStream_t stream) {
     a.thr0 = nullptr;
     a.sample = 0;
     const float* thr_used = nullptr;
-    auto launch_main = [&]() -> cudaError_t {
-        if (mblocks == 2) {
-            cudaError_t e2 = cudaFuncSetAttribute(batch_score_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-            if (e2 != cudaSuccess) return e2;
-            batch_score_kernel<2><<<grid, kBatchThreads, L.total, stream>>>(map_q, map_c, a, L);
-        } else {
-            cudaError_t e2 = cudaFuncSetAttribute(batch_score_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-            if (e2 != cudaSuccess) return e2;
-            batch_score_kernel<1><<<grid, kBatchThreads, L.total, stream>>>(map_q, map_c, a, L);
-        }
+    auto launch_as = [&](auto kernel) -> cudaError_t {
+        cudaError_t e2 = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        if (e2 != cudaSuccess) return e2;
+        kernel<<<grid, kBatchThreads, L.total, stream>>>(map_q, map_c, a, L);
         return cudaGetLastError();
+    };
+    auto launch_main = [&]() -> cudaError_t {
+        if (mblocks == 2) return bf ? launch_as(batch_score_kernel<2, true>) : launch_as(batch_score_kernel<2, false>);
+        return bf ? launch_as(batch_score_kernel<1, true>) : launch_as(batch_score_kernel<1, false>);
     };
     if (pair) {
         e = cudaFuncSetAttribute(batch_score_kernel_2sm, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
@@ -890,9 +961,9 @@ int launch_batch_search(const BatchSearchArgs& b, cudaStream_t stream) {
         // sample -- a lower bound of the k'-th best overall -- and the full pass starts from it: only ~32*s rows per
         // query in the WHOLE corpus still beat it.
         const char* tp = std::getenv("RAGSTORE_BATCH_TWOPASS");
-        const bool two_pass = n_tiles >= 32ll * grid && !(tp && tp[0] == '0');
+        const bool two_pass = n_tiles >= 4ll * grid && !(tp && tp[0] == '0');
         if (two_pass) {
-            int stride = static_cast<int>(n_tiles / (8ll * grid));
+            int stride = static_cast<int>(n_tiles / (2ll * grid));   // every CTA still samples >= 2 tiles
             stride = stride > 16 ? 16 : (stride < 2 ? 2 : stride);
             a.tile_stride = stride;
             a.sample = 1;
@@ -918,7 +989,7 @@ int launch_batch_search(const BatchSearchArgs& b, cudaStream_t stream) {
     f.thr0 = thr_used;
     f.nlists = nlists;
     f.out_stride = b.out_stride;
-    f.row_bytes = static_cast<uint32_t>(s.ld) * 4u;
+    f.row_bytes = static_cast<uint32_t>(s.ld) * (bf ? 2u : 4u);
     f.qpad = static_cast<uint32_t>(s.ld);
     const uint32_t fixed = f.qpad * 4u + sizeof(uint64_t) * 2u * kConsumerWarps * s.kp + sizeof(ScanMisc) + 256u;
     uint32_t ring = 200u * 1024u - fixed;
@@ -928,9 +999,15 @@ int launch_batch_search(const BatchSearchArgs& b, cudaStream_t stream) {
     if (ring < lists_need && lists_need + fixed <= 200u * 1024u) ring = lists_need;
     f.ring_bytes = (ring + 127u) & ~127u;
     const size_t fin_smem = f.ring_bytes + fixed;
-    e = cudaFuncSetAttribute(batch_finalize_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-    if (e != cudaSuccess) return static_cast<int>(e);
-    batch_finalize_kernel<float><<<b.nq, kScanThreads, fin_smem, stream>>>(f);
+    if (bf) {
+        e = cudaFuncSetAttribute(batch_finalize_kernel<uint16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        if (e != cudaSuccess) return static_cast<int>(e);
+        batch_finalize_kernel<uint16_t><<<b.nq, kScanThreads, fin_smem, stream>>>(f);
+    } else {
+        e = cudaFuncSetAttribute(batch_finalize_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        if (e != cudaSuccess) return static_cast<int>(e);
+        batch_finalize_kernel<float><<<b.nq, kScanThreads, fin_smem, stream>>>(f);
+    }
     return static_cast<int>(cudaGetLastError());
 }
 

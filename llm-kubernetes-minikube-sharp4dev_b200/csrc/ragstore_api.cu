@@ -223,11 +223,20 @@ ScanArgs base_args(const ragstore* s, int64_t n, int take, int kp) {
     return a;
 }
 
-// tf32 products (10-bit mantissas, both operands) + fp32 accumulation vs the reference's score
-constexpr float kBatchEps = 2.1e-3f;
+// fp32 store: tf32 products (10-bit mantissas, both operands) + fp32 accumulation vs the reference's score.
+// bf16 store: the stored rows enter exactly and the row norm is applied, so only the query's rounding to bf16
+// (<= 2^-9 relative per element -> <= 2^-9 on a cosine, Cauchy-Schwarz) and the fp32 accumulation remain; when
+// exact scores come from fp32 originals (sidecar) the stored image itself is another 2^-8 away, as in base_args.
+float batch_eps(const ragstore* s) {
+    if (s->dtype == RAGSTORE_F32) return 2.1e-3f;
+    float e = 1.953125e-3f + static_cast<float>(s->ld) * 2.4e-7f + 2e-5f;
+    if (s->raw_used > 0) e += 3.90625e-3f;
+    return e;
+}
 
 bool batch_eligible(const ragstore* s, int64_t n, int nq, int kp) {
-    return s->dtype == RAGSTORE_F32 && nq >= kBatchMinQ && n >= kBatchMinRows && kp == 32 && s->ld <= kBatchMaxLd;
+    return nq >= kBatchMinQ && n >= kBatchMinRows && kp == 32 && s->ld <= kBatchMaxLd &&
+           (s->dtype == RAGSTORE_F32 || s->ld % 8 == 0);
 }
 
 // One tensor-core launch for up to kBatchMaxQ queries (outputs laid out with `stride` hits per query).
@@ -235,7 +244,7 @@ int run_batch(const ragstore* s, int64_t n, int take, const float* d_q, int nq, 
               int32_t* d_found, int32_t* d_flags, int stride, uint8_t* scratch, cudaStream_t st) {
     BatchSearchArgs b{};
     b.scan = base_args(s, n, take, 32);
-    b.scan.eps = kBatchEps;
+    b.scan.eps = batch_eps(s);
     b.scan.out_idx = d_idx;
     b.scan.out_score = d_score;
     b.scan.out_found = d_found;
@@ -650,7 +659,7 @@ int ragstore_search_shard_batch_device(ragstore_t* s, const float* d_queries, in
             const int nq = std::min(kBatchMaxQ, n_queries - q0);
             BatchSearchArgs b{};
             b.scan = base_args(s, n, take, 32);
-            b.scan.eps = kBatchEps;
+            b.scan.eps = batch_eps(s);
             b.scan.out_flags = d_flags ? d_flags + q0 : nullptr;
             b.scan.out_cand = d_out + static_cast<size_t>(q0) * req;
             b.scan.cand_slots = req;

@@ -596,3 +596,50 @@ def test_single_pass_and_two_pass_batched_agree(monkeypatch):
         st2.add_device(buf, n, d)
         one = st2.search(qs[5], k)
     assert list(one[0][0]) == list(b[0][5]) and np.array_equal(one[1][0].view(np.uint64), b[1][5].view(np.uint64))
+
+
+@pytest.mark.parametrize("n,d,nq,k", [(20000, 768, 32, 10), (30000, 1024, 200, 10), (12345, 200, 130, 5), (8000, 64, 256, 10)])
+def test_batched_queries_on_bf16_store(n, d, nq, k):
+    """bf16 stores take the tensor-core path too (kind::f16 on bf16 operands, the query rounded to bf16, the row's
+    reciprocal norm applied in the epilogue); the exact rescoring still makes the hits the oracle's on the stored rows."""
+    rows = oc.synth_rows(0, n, d, 1234, round_bf16=True)
+    qs = oc.synth_rows(0, nq, d, 5678)
+    with rb.RagStore(d, n, rb.RAGSTORE_BF16) as st:
+        st.add(rows, prenormalised=True)
+        idx, sc, found, flags = st.search(qs, k)
+        info = st.info()
+    assert info["n_inexact_rows"] == 0
+    assert info["batch_launches"] >= (nq + 255) // 256
+    for i in range(nq):
+        eidx, esc = oc.query(rows, qs[i], k, n_threads=4)
+        assert list(idx[i, :found[i]]) == list(eidx), i
+        assert np.array_equal(sc[i, :found[i]].view(np.uint64), esc.view(np.uint64)), i
+        assert flags[i] & rb.RAGSTORE_HIT_CERTIFIED
+    assert info["scan_launches"] <= max(2, nq // 4)
+
+
+@pytest.mark.parametrize("sidecar", [False, True])
+def test_batched_bf16_store_of_unnormalised_fp32_rows(sidecar):
+    """Rows of arbitrary length, rounded to bf16 at ingest: the batched path must return what the single-query scan of
+    the same store returns (identical ids and scores), and with the sidecar the scores are the reference's on the fp32
+    originals."""
+    n, d, nq, k = 30000, 768, 48, 10
+    rng = np.random.default_rng(5)
+    rows = oc.synth_rows(0, n, d, 1234) * rng.uniform(0.05, 30.0, size=(n, 1)).astype(np.float32)
+    qs = oc.synth_rows(0, nq, d, 5678) * np.float32(3.0)
+    flags_create = rb.RAGSTORE_CREATE_SIDECAR_ON if sidecar else rb.RAGSTORE_CREATE_SIDECAR_OFF
+    with rb.RagStore(d, n, rb.RAGSTORE_BF16, 0, flags_create) as st:
+        st.add(rows)
+        idx, sc, found, flags = st.search(qs, k)
+        launches = st.info()["batch_launches"]
+        one = [st.search(qs[i], k) for i in range(nq)]
+    assert launches >= 1
+    for i in range(nq):
+        assert np.array_equal(idx[i], one[i][0][0]), i
+        assert np.array_equal(sc[i].view(np.uint64), one[i][1][0].view(np.uint64)), i
+    if sidecar:
+        for i in range(0, nq, 8):
+            full = oc.score_all(rows, qs[i], n_threads=4)
+            eidx, esc = oc.query(rows, qs[i], k, n_threads=4)
+            assert list(idx[i]) == list(eidx)
+            assert np.array_equal(sc[i].view(np.uint64), full[idx[i]].view(np.uint64))
