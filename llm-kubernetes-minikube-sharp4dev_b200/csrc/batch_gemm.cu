@@ -961,10 +961,12 @@ int launch_batch_search(const BatchSearchArgs& b, cudaStream_t stream) {
         // sample -- a lower bound of the k'-th best overall -- and the full pass starts from it: only ~32*s rows per
         // query in the WHOLE corpus still beat it.
         const char* tp = std::getenv("RAGSTORE_BATCH_TWOPASS");
-        const bool two_pass = n_tiles >= 4ll * grid && !(tp && tp[0] == '0');
+        const bool two_pass = !(tp && tp[0] == '0');
         if (two_pass) {
-            int stride = static_cast<int>(n_tiles / (2ll * grid));   // every CTA still samples >= 2 tiles
-            stride = stride > 16 ? 16 : (stride < 2 ? 2 : stride);
+            // small corpora: stride 1, i.e. the "sample" is a full (cheap: 4 registers per thread, no lists) sweep --
+            // still far cheaper than filling cold lists column by column (~200 us per CTA for 256 queries)
+            int stride = static_cast<int>(n_tiles / (2ll * grid));   // every CTA samples >= 2 tiles when it can
+            stride = stride > 16 ? 16 : (stride < 1 ? 1 : stride);
             a.tile_stride = stride;
             a.sample = 1;
             e = launch_main();

@@ -29,6 +29,10 @@ def run(n, d, nq, k, iters=5, bf16=False):
     st.close()
 
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "small":
+        run(40000, 768, 256, 10, iters=3)
+        run(40000, 768, 64, 10, iters=3)
+        sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "sizes":
         for n in (40000, 150000, 500000, 1000000, 2000000, 4000000):
             run(n, 1024, 256, 10, iters=5)
