@@ -73,6 +73,7 @@ class ClockSampler:
 
     def __init__(self, index, enabled=True):
         self.samples, self.reasons, self.max_mhz, self._stop = [], set(), None, threading.Event()
+        self.power, self.power_limit = [], None
         self.nv = None
         if not enabled:          # only rank 0 polls NVML: N processes hammering its global lock perturb each other
             self.t = None
@@ -83,6 +84,10 @@ class ClockSampler:
             self.nv = pynvml
             self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
             self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            try:
+                self.power_limit = pynvml.nvmlDeviceGetEnforcedPowerLimit(self.h) / 1000.0
+            except Exception:
+                self.power_limit = None
         except Exception:
             self.nv = None
         self.t = threading.Thread(target=self._run, daemon=True)
@@ -98,6 +103,10 @@ class ClockSampler:
                 for k, bit in names.items():
                     if r & bit:
                         self.reasons.add(k)
+            except Exception:
+                pass
+            try:
+                self.power.append(nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0)
             except Exception:
                 pass
             time.sleep(0.02)
@@ -116,7 +125,11 @@ class ClockSampler:
         if not self.samples:
             return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": ["unavailable"]}
         s = sorted(self.samples)
-        return {"sm_mhz": s[len(s) // 2], "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(s)}
+        out = {"sm_mhz": s[len(s) // 2], "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(s)}
+        if self.power:
+            p = sorted(self.power)
+            out.update({"power_w_median": p[len(p) // 2], "power_w_max": p[-1], "power_limit_w": self.power_limit})
+        return out
 
 
 def run_reference(args, rank, world):
@@ -221,7 +234,7 @@ def measure_workload(name, args, torch, dist, rb, native, rank, world, dev, do_e
             def step():
                 qi[0] += 1
                 st.search_device(d_q, nqb, k, d_idx, d_score, d_found, d_flags, stream=ts.cuda_stream)
-            launches_per_step = 3      # normalise queries, tcgen05 scoring, per-query finalize
+            launches_per_step = 5      # normalise queries, threshold pass (tcgen05) + thresholds, full pass (tcgen05), per-query finalize
         elif world == 1:
             def step():
                 q = d_q[qi[0] % n_q]
@@ -243,7 +256,7 @@ def measure_workload(name, args, torch, dist, rb, native, rank, world, dev, do_e
             def step():
                 qi[0] += 1
                 sh.search_batch_device(d_q, nqb, k)
-            launches_per_step = 4
+            launches_per_step = 6      # the five batched-search launches of the shard + the merge kernel (NCCL all-gather not counted)
         else:
             sh = rb.ShardedSearcher(st, rank, world, rank * rows, max_k=max(k, 1), device=dev)
             d_cand, d_all, d_idx, d_score, d_found, d_flags = sh.d_cand, sh.d_all, sh.d_idx, sh.d_score, sh.d_found, sh.d_flags

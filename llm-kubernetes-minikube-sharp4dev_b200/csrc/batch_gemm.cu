@@ -231,6 +231,122 @@ __device__ __forceinline__ float raw_threshold(float thr, float rn_max) {
     return __fdiv_rd(thr, rn_max) * (1.0f - 2.4e-7f);   // thr > 0, rn_max == 0: +inf (nothing passes, all scores are 0)
 }
 
+// ---------------------------------------------------------------- epilogue pieces shared by both kernels
+// smallest / largest reciprocal norm of a tile's valid rows (bf16 stores; fp32 stores keep unit rows: 1, 1)
+template <bool BF>
+__device__ __forceinline__ void tile_rnorm_range(const float* rnorm, int64_t row0, int nvalid, int lane, float& rn_lo, float& rn_hi) {
+    rn_lo = 1.f, rn_hi = 1.f;
+    if (BF) {
+        float lo = CUDART_INF_F, hi = 0.f;
+        for (int j = lane; j < nvalid; j += 32) {
+            const float r = __ldg(rnorm + row0 + j);
+            lo = fminf(lo, r), hi = fmaxf(hi, r);
+        }
+        rn_lo = __uint_as_float(__reduce_min_sync(0xffffffffu, __float_as_uint(lo)));
+        rn_hi = __uint_as_float(__reduce_max_sync(0xffffffffu, __float_as_uint(hi)));
+    }
+}
+
+// Sampling pass, one finished 256-row accumulator at TMEM address `tacc` (this warp's lanes): fold the thread's query's
+// scores into its 4 best (t0 >= t1 >= t2 >= t3).  bf16 store: a sampled value only has to be a LOWER bound of a real
+// row's score, so the tile's smallest / largest reciprocal norm stands in for the row's own.
+template <bool BF>
+__device__ __forceinline__ void sample_tile(uint32_t tacc, int nvalid, float rn_lo, float rn_hi, float& t0, float& t1, float& t2,
+                                            float& t3) {
+    for (int cb = 0; cb < kBN; cb += 32) {
+        uint32_t v[32];
+        tmem_ld_32x32(tacc + cb, v);
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+            float sc = __uint_as_float(v[j]);
+            if (BF) sc = sc > 0.f ? sc * rn_lo : sc * rn_hi;
+            if (sc > t3 && cb + j < nvalid) {  // 4-slot sorted insert
+                const float a0 = fmaxf(t0, sc), b0 = fminf(t0, sc);
+                const float a1 = fmaxf(t1, b0), b1 = fminf(t1, b0);
+                const float a2 = fmaxf(t2, b1), b2 = fminf(t2, b1);
+                t0 = a0, t1 = a1, t2 = a2, t3 = fmaxf(t3, b2);
+            }
+        }
+    }
+}
+
+// Main pass, one finished 256-row accumulator: feed the thread's candidate list.
+// bf16 store: score = dot * rnorm[row].  The steady-state test compares the raw dot products with thr / (largest rnorm
+// of the tile), a superset of the rows that can beat thr; only those get the exact product.
+template <bool BF>
+__device__ __forceinline__ void scan_tile(uint32_t tacc, int64_t row0, int nvalid, float rn_max, const float* rnorm, bool active,
+                                          float (&S)[kBatchKp], int& minpos, float& thr, uint32_t* rows, int NQ, int q) {
+    float thr_cmp = BF ? raw_threshold(thr, rn_max) : thr;
+    for (int cb = 0; cb < kBN; cb += 64) {
+        // four 16-column loads in flight per wait: the TMEM read latency is paid once per 64 columns
+        uint32_t v[4][16];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) tmem_ld_32x16_nowait(tacc + cb + u * 16, v[u]);
+        tmem_ld_wait();
+        // Hits are rare once the lists have warmed up.  Steady state: one max over the 64 scores and one vote; the
+        // per-column mask is built only when some lane of the warp has a score above its threshold; the warp then
+        // revisits only the marked columns (one-column TMEM load) and the lanes concerned insert.  One copy of the
+        // insert code keeps the loop in the I-cache.
+        float mx[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            mx[u] = __uint_as_float(v[u][0]);
+#pragma unroll
+            for (int j = 1; j < 16; ++j) mx[u] = fmaxf(mx[u], __uint_as_float(v[u][j]));
+        }
+        const bool hot = active && fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3])) > thr_cmp;
+        unsigned long long mine = 0, any = 0;
+        if (__any_sync(0xffffffffu, hot)) {
+            if (hot) {
+#pragma unroll
+                for (int u = 0; u < 4; ++u)
+#pragma unroll
+                    for (int j = 0; j < 16; ++j)
+                        mine |= static_cast<unsigned long long>(__uint_as_float(v[u][j]) > thr_cmp ? 1u : 0u) << (u * 16 + j);
+            }
+            const unsigned lo = __reduce_or_sync(0xffffffffu, static_cast<unsigned>(mine));
+            const unsigned hi = __reduce_or_sync(0xffffffffu, static_cast<unsigned>(mine >> 32));
+            any = (static_cast<unsigned long long>(hi) << 32) | lo;
+        }
+        while (any) {
+            const int j = __ffsll(static_cast<long long>(any)) - 1;
+            any &= any - 1;
+            uint32_t one;
+            asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(one) : "r"(tacc + cb + j) : "memory");
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+            float sc = __uint_as_float(one);
+            if (BF) sc = cb + j < nvalid ? sc * __ldg(rnorm + row0 + cb + j) + 0.0f : -CUDART_INF_F;
+            if (((mine >> j) & 1ull) && sc > thr && cb + j < nvalid) {  // rows ascend, so an equal score never displaces
+                list_insert(S, minpos, thr, rows, NQ, q, sc, static_cast<uint32_t>(row0 + cb + j));
+                thr_cmp = BF ? raw_threshold(thr, rn_max) : thr;
+            }
+        }
+    }
+}
+
+// End of the main pass.  The ring is idle (every stage was consumed before the last accumulator completed): reuse it
+// to hand each query's 32 keys to a warp, which sorts them (one key per lane) and publishes them as
+// glists[query][list_id][pos].  `ql` = the thread's query within this CTA (0 .. NQ-1), `qg0` = global index of the
+// CTA's first query; called by all 4 * NQ / 128 epilogue warps.
+__device__ __forceinline__ void publish_lists(uint8_t* smem, const float (&S)[kBatchKp], const uint32_t* rows, int NQ, int ql, int qg0,
+                                              int nq, uint64_t* glists, int nlists, int list_id, int lane) {
+    uint64_t* keys = reinterpret_cast<uint64_t*>(smem);  // [query][slot]
+    named_bar_sync(2, NQ);
+#pragma unroll
+    for (int p = 0; p < kBatchKp; ++p) {
+        const uint32_t r = rows[p * NQ + ql];
+        keys[ql * kBatchKp + p] = (S[p] > -CUDART_INF_F && r != 0xFFFFFFFFu) ? make_key(S[p] + 0.0f, r) : 0ull;
+    }
+    __syncwarp();
+    const int ql0 = ql & ~31;
+    const int n_live = max(0, min(32, nq - (qg0 + ql0)));
+    for (int i = 0; i < n_live; ++i) {
+        uint64_t k = keys[(ql0 + i) * kBatchKp + lane];
+        k = warp_sort_desc(k, lane);
+        glists[(static_cast<size_t>(qg0 + ql0 + i) * nlists + list_id) * kBatchKp + lane] = k;
+    }
+}
+
 // ---------------------------------------------------------------- the tensor-core kernel
 // MB = blocks of 128 queries (1 or 2).  Tile = 256 corpus rows: one MMA is M=128 (queries) x N=256 (rows),
 // so MB = 1 double-buffers its accumulator (2 x 256 TMEM columns) while MB = 2 uses all 512 columns for
@@ -373,6 +489,7 @@ batch_score_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
             for (int p = 0; p < kBatchKp; ++p) S[p] = floor0;
             thr = floor0;
         }
+        const uint32_t tacc0 = tmem_base + lane_base + mblock * 256u;
         if (a.sample) {
             // Sampling pass: only thresholds are wanted, so a thread keeps just its 4 best scores (registers, no row
             // ids, no lists): the warm-up that makes list maintenance expensive costs almost nothing here.
@@ -381,35 +498,11 @@ batch_score_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
                 const uint32_t as = static_cast<uint32_t>(it % AS), aph = static_cast<uint32_t>((it / AS) & 1);
                 const int64_t row0 = ((cluster_id + it * n_clusters) * kCluster + crank) * a.tile_stride * kBN;
                 const int nvalid = static_cast<int>(min(static_cast<int64_t>(kBN), a.n_rows - row0));
-                // bf16 store: a sampled value only has to be a LOWER bound of a real row's score, so the tile's
-                // smallest / largest reciprocal norm stands in for the row's own
-                float rn_lo = 1.f, rn_hi = 1.f;
-                if (BF) {
-                    float lo = CUDART_INF_F, hi = 0.f;
-                    for (int j = lane; j < nvalid; j += 32) {
-                        const float r = __ldg(a.rnorm + row0 + j);
-                        lo = fminf(lo, r), hi = fmaxf(hi, r);
-                    }
-                    rn_lo = __uint_as_float(__reduce_min_sync(0xffffffffu, __float_as_uint(lo)));
-                    rn_hi = __uint_as_float(__reduce_max_sync(0xffffffffu, __float_as_uint(hi)));
-                }
+                float rn_lo, rn_hi;
+                tile_rnorm_range<BF>(a.rnorm, row0, nvalid, lane, rn_lo, rn_hi);  // before the wait: overlaps the MMAs
                 mbar_wait(tmem_full + as, aph);
                 tc_fence_after();
-                for (int cb = 0; cb < kBN; cb += 32) {
-                    uint32_t v[32];
-                    tmem_ld_32x32(tmem_base + lane_base + (as * MB + mblock) * 256u + cb, v);
-#pragma unroll
-                    for (int j = 0; j < 32; ++j) {
-                        float sc = __uint_as_float(v[j]);
-                        if (BF) sc = sc > 0.f ? sc * rn_lo : sc * rn_hi;
-                        if (sc > t3 && cb + j < nvalid) {  // 4-slot sorted insert
-                            const float a0 = fmaxf(t0, sc), b0 = fminf(t0, sc);
-                            const float a1 = fmaxf(t1, b0), b1 = fminf(t1, b0);
-                            const float a2 = fmaxf(t2, b1), b2 = fminf(t2, b1);
-                            t0 = a0, t1 = a1, t2 = a2, t3 = fmaxf(t3, b2);
-                        }
-                    }
-                }
+                sample_tile<BF>(tacc0 + as * MB * 256u, nvalid, rn_lo, rn_hi, t0, t1, t2, t3);
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(tmem_empty + as);
@@ -419,98 +512,29 @@ batch_score_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
                 smp[0] = t0, smp[1] = t1, smp[2] = t2, smp[3] = t3;
             }
         } else {
-        long long t_wait = 0, t_work = 0;  // debug & 8: cycles spent waiting for / draining accumulators
-        for (int64_t it = 0; it < my_tiles; ++it) {
-            const uint32_t as = static_cast<uint32_t>(it % AS), aph = static_cast<uint32_t>((it / AS) & 1);
-            const long long c0k = clock64();
-            const int64_t row0 = ((cluster_id + it * n_clusters) * kCluster + crank) * a.tile_stride * kBN;
-            const int nvalid = static_cast<int>(min(static_cast<int64_t>(kBN), a.n_rows - row0));
-            // bf16 store: score = dot * rnorm[row].  The steady-state test compares the raw dot products with
-            // thr / (largest rnorm of the tile), a superset of the rows that can beat thr; only those get the
-            // exact product.  (fetched before the wait so the loads overlap the MMAs)
-            float rn_max = 1.f;
-            if (BF) {
-                float hi = 0.f;
-                for (int j = lane; j < nvalid; j += 32) hi = fmaxf(hi, __ldg(a.rnorm + row0 + j));
-                rn_max = __uint_as_float(__reduce_max_sync(0xffffffffu, __float_as_uint(hi)));
+            long long t_wait = 0, t_work = 0;  // debug & 8: cycles spent waiting for / draining accumulators
+            for (int64_t it = 0; it < my_tiles; ++it) {
+                const uint32_t as = static_cast<uint32_t>(it % AS), aph = static_cast<uint32_t>((it / AS) & 1);
+                const long long c0k = clock64();
+                const int64_t row0 = ((cluster_id + it * n_clusters) * kCluster + crank) * a.tile_stride * kBN;
+                const int nvalid = static_cast<int>(min(static_cast<int64_t>(kBN), a.n_rows - row0));
+                float rn_lo, rn_max;
+                tile_rnorm_range<BF>(a.rnorm, row0, nvalid, lane, rn_lo, rn_max);
+                mbar_wait(tmem_full + as, aph);
+                tc_fence_after();
+                const long long c1k = clock64();
+                t_wait += c1k - c0k;
+                scan_tile<BF>(tacc0 + as * MB * 256u, row0, nvalid, rn_max, a.rnorm, live && !(a.debug & 1), S, minpos, thr, rows, NQ, q);
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(tmem_empty + as);
+                t_work += clock64() - c1k;
             }
-            mbar_wait(tmem_full + as, aph);
-            tc_fence_after();
-            const long long c1k = clock64();
-            t_wait += c1k - c0k;
-            float thr_cmp = BF ? raw_threshold(thr, rn_max) : thr;
-            for (int cb = 0; cb < kBN; cb += 64) {
-                // four 16-column loads in flight per wait: the TMEM read latency is paid once per 64 columns
-                uint32_t v[4][16];
-#pragma unroll
-                for (int u = 0; u < 4; ++u) tmem_ld_32x16_nowait(tmem_base + lane_base + (as * MB + mblock) * 256u + cb + u * 16, v[u]);
-                tmem_ld_wait();
-                // Hits are rare once the lists have warmed up.  Each lane marks the columns whose score beats ITS
-                // threshold; the warp then revisits only the marked columns (one-column TMEM load) and the lanes
-                // concerned insert.  One copy of the insert code keeps the loop in the I-cache.
-                // steady state: one max over the 64 scores and one vote; the per-column mask is built only when some
-                // lane of the warp actually has a score above its threshold
-                float mx[4];
-#pragma unroll
-                for (int u = 0; u < 4; ++u) {
-                    mx[u] = __uint_as_float(v[u][0]);
-#pragma unroll
-                    for (int j = 1; j < 16; ++j) mx[u] = fmaxf(mx[u], __uint_as_float(v[u][j]));
-                }
-                const bool hot = live && !(a.debug & 1) && fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3])) > thr_cmp;
-                unsigned long long mine = 0, any = 0;
-                if (__any_sync(0xffffffffu, hot)) {
-                    if (hot) {
-#pragma unroll
-                        for (int u = 0; u < 4; ++u)
-#pragma unroll
-                            for (int j = 0; j < 16; ++j)
-                                mine |= static_cast<unsigned long long>(__uint_as_float(v[u][j]) > thr_cmp ? 1u : 0u) << (u * 16 + j);
-                    }
-                    const unsigned lo = __reduce_or_sync(0xffffffffu, static_cast<unsigned>(mine));
-                    const unsigned hi = __reduce_or_sync(0xffffffffu, static_cast<unsigned>(mine >> 32));
-                    any = (static_cast<unsigned long long>(hi) << 32) | lo;
-                }
-                while (any) {
-                    const int j = __ffsll(static_cast<long long>(any)) - 1;
-                    any &= any - 1;
-                    uint32_t one;
-                    asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(one) : "r"(tmem_base + lane_base + (as * MB + mblock) * 256u + cb + j) : "memory");
-                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-                    float sc = __uint_as_float(one);
-                    if (BF) sc = cb + j < nvalid ? sc * __ldg(a.rnorm + row0 + cb + j) + 0.0f : -CUDART_INF_F;
-                    if (((mine >> j) & 1ull) && sc > thr && cb + j < nvalid) {  // rows ascend, so an equal score never displaces
-                        list_insert(S, minpos, thr, rows, NQ, q, sc, static_cast<uint32_t>(row0 + cb + j));
-                        if (BF) thr_cmp = raw_threshold(thr, rn_max); else thr_cmp = thr;
-                    }
-                }
-            }
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(tmem_empty + as);
-            t_work += clock64() - c1k;
+            if ((a.debug & 8) && blockIdx.x == 0 && lane == 0 && my_tiles > 0)
+                printf("[batch dbg] warp %d: tiles %lld, per tile: wait %lld cyc, drain+scan %lld cyc\n", warp, (long long)my_tiles,
+                       t_wait / my_tiles, t_work / my_tiles);
+            publish_lists(smem, S, rows, NQ, q, 0, a.nq, a.glists, static_cast<int>(gridDim.x), static_cast<int>(blockIdx.x), lane);
         }
-        if ((a.debug & 8) && blockIdx.x == 0 && lane == 0 && my_tiles > 0)
-            printf("[batch dbg] warp %d: tiles %lld, per tile: wait %lld cyc, drain+scan %lld cyc\n", warp, (long long)my_tiles,
-                   t_wait / my_tiles, t_work / my_tiles);
-        // The ring is idle now (every stage was consumed before the last accumulator completed): reuse it to
-        // hand each query's 32 keys to a warp, which sorts them (one key per lane) and publishes them.
-        uint64_t* keys = reinterpret_cast<uint64_t*>(smem);  // [query][slot]
-        named_bar_sync(2, 128 * MB);
-#pragma unroll
-        for (int p = 0; p < kBatchKp; ++p) {
-            const uint32_t r = rows[p * NQ + q];
-            keys[q * kBatchKp + p] = (S[p] > -CUDART_INF_F && r != 0xFFFFFFFFu) ? make_key(S[p] + 0.0f, r) : 0ull;
-        }
-        __syncwarp();
-        const int q0 = (warp - kEpiWarp0) * 32;
-        const int n_live = max(0, min(32, a.nq - q0));
-        for (int i = 0; i < n_live; ++i) {
-            uint64_t k = keys[(q0 + i) * kBatchKp + lane];
-            k = warp_sort_desc(k, lane);
-            a.glists[(static_cast<size_t>(q0 + i) * gridDim.x + blockIdx.x) * kBatchKp + lane] = k;  // glists[q][cta][pos]
-        }
-        }  // !a.sample
     }
     tc_fence_before();
     __syncthreads();
@@ -528,7 +552,7 @@ batch_score_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
 // 256 rows of the pair, i.e. half the L2->SM bytes per corpus row of the single-CTA kernel, and its
 // TMEM holds 128 queries x 256 rows = 256 columns, so the accumulator is double buffered and the
 // epilogue of tile t overlaps the MMAs of tile t+1.
-// Barriers: both CTAs' TMA loads complete on the LEADER's full barrier; the leader's MMA lane commits
+// Barriers: both CTAs' TMA loads complete on the LEADER's full barrier (armed by the leader alone); the leader's MMA lane commits
 // (multicast) to both CTAs' empty / tmem_full barriers; both epilogues arrive on the leader's tmem_empty.
 constexpr int kPairThreads = 256;   // warp0 TMA, warp1 MMA (leader), warp2 TMEM, warp3 idle, warps 4-7 epilogue
 constexpr uint32_t kIdescTf32Pair = (1u << 4) | (2u << 7) | (2u << 10) | ((256u >> 3) << 17) | ((256u >> 4) << 24);
@@ -582,6 +606,17 @@ __device__ __forceinline__ void mma_tf32_2sm(uint32_t tmem_d, uint64_t adesc, ui
         : "memory");
 }
 
+__device__ __forceinline__ void mma_bf16_2sm(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+constexpr uint32_t kIdescBf16Pair = (1u << 4) | (1u << 7) | (1u << 10) | ((256u >> 3) << 17) | ((256u >> 4) << 24);
+
+template <bool BF>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPairThreads, 1)
 batch_score_kernel_2sm(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_c,
                        const BatchArgs a, const BatchLayout L) {
@@ -599,13 +634,15 @@ batch_score_kernel_2sm(const __grid_constant__ CUtensorMap tmap_q, const __grid_
 
     const uint32_t crank = cluster_ctarank();
     const bool leader = crank == 0;
-    const int64_t n_ptiles = (a.n_rows + kBN - 1) / kBN;  // pair tiles of 256 rows
+    constexpr int KE = BF ? 64 : 32;
+    const int64_t all_ptiles = (a.n_rows + kBN - 1) / kBN;  // pair tiles of 256 rows
+    const int64_t n_ptiles = (all_ptiles + a.tile_stride - 1) / a.tile_stride;  // tiles this launch visits
     const int64_t n_pairs = gridDim.x / 2, pair_id = blockIdx.x / 2;
     const int64_t my_tiles = n_ptiles > pair_id ? (n_ptiles - pair_id + n_pairs - 1) / n_pairs : 0;
 
     if (tid == 0) {
         for (int s = 0; s < n_stages; ++s) {
-            mbar_init(full + s, 2);   // leader's expect_tx arrival + the peer's arrival
+            mbar_init(full + s, 1);   // the leader's expect_tx arrival (covers the bytes of both CTAs)
             mbar_init(empty + s, 1);  // the leader's multicast commit
         }
         for (int s = 0; s < 2; ++s) {
@@ -632,16 +669,17 @@ batch_score_kernel_2sm(const __grid_constant__ CUtensorMap tmap_q, const __grid_
             int s = 0;
             uint32_t ph = 0;
             for (int64_t it = 0; it < my_tiles; ++it) {
-                const int row0 = static_cast<int>((pair_id + it * n_pairs) * kBN + crank * 128);
+                const int row0 = static_cast<int>((pair_id + it * n_pairs) * a.tile_stride * kBN + crank * 128);
                 for (int kb = 0; kb < a.nkb; ++kb) {
                     mbar_wait(empty + s, ph ^ 1u);
                     uint8_t* st = smem + static_cast<size_t>(s) * L.stage_bytes;
-                    if (leader)
-                        mbar_arrive_expect_tx(full + s, 4u * kOperandBytes);  // both CTAs' A and B halves
-                    else
-                        mbar_arrive_cluster(full + s, 0);
-                    tma_load_2d_2sm(st, &tmap_q, full + s, kb * 32, static_cast<int>(crank) * kBM);
-                    tma_load_2d_2sm(st + kOperandBytes, &tmap_c, full + s, kb * 32, row0);
+                    // Only the leader arms the barrier, with the bytes of both CTAs.  The peer's copies may land first:
+                    // they can only be issued after the leader's MMA lane released this stage, i.e. after the barrier's
+                    // previous phase completed, and the phase cannot complete before the leader's own arrival.  (A
+                    // per-stage remote arrive with cluster-scope release semantics cost the peer ~1500 cycles per stage.)
+                    if (leader) mbar_arrive_expect_tx(full + s, 4u * kOperandBytes);
+                    tma_load_2d_2sm(st, &tmap_q, full + s, kb * KE, static_cast<int>(crank) * kBM);
+                    tma_load_2d_2sm(st + kOperandBytes, &tmap_c, full + s, kb * KE, row0);
                     if (++s == n_stages) {
                         s = 0;
                         ph ^= 1u;
@@ -667,7 +705,12 @@ batch_score_kernel_2sm(const __grid_constant__ CUtensorMap tmap_q, const __grid_
                     for (int k4 = 0; k4 < 4; ++k4) {
                         const uint64_t adesc = make_sw128_desc(st + k4 * 32);
                         const uint64_t bdesc = make_sw128_desc(st + kOperandBytes + k4 * 32);
-                        if (!(a.debug & 2)) mma_tf32_2sm(tmem_base + as * 256u, adesc, bdesc, kIdescTf32Pair, (kb | k4) != 0);
+                        if (!(a.debug & 2)) {
+                            if (BF)
+                                mma_bf16_2sm(tmem_base + as * 256u, adesc, bdesc, kIdescBf16Pair, (kb | k4) != 0);
+                            else
+                                mma_tf32_2sm(tmem_base + as * 256u, adesc, bdesc, kIdescTf32Pair, (kb | k4) != 0);
+                        }
                     }
                     tc_commit_2sm_mc(empty + s, 0x3);  // both CTAs may refill the stage once these MMAs are done
                     if (++s == n_stages) {
@@ -690,51 +733,46 @@ batch_score_kernel_2sm(const __grid_constant__ CUtensorMap tmap_q, const __grid_
         for (int p = 0; p < kBatchKp; ++p) S[p] = -CUDART_INF_F;
         float thr = -CUDART_INF_F;
         int minpos = 0;
+        const float floor0 = (a.thr0 && live) ? nextafterf(a.thr0[q], -CUDART_INF_F) : -CUDART_INF_F;  // see batch_score_kernel
+        if (floor0 > -CUDART_INF_F) {
+#pragma unroll
+            for (int p = 0; p < kBatchKp; ++p) S[p] = floor0;
+            thr = floor0;
+        }
+        float t0 = -CUDART_INF_F, t1 = -CUDART_INF_F, t2 = -CUDART_INF_F, t3 = -CUDART_INF_F;  // sampling pass: 4 best
+        long long t_wait = 0, t_work = 0;
         for (int64_t it = 0; it < my_tiles; ++it) {
             const uint32_t as = static_cast<uint32_t>(it & 1), aph = static_cast<uint32_t>((it >> 1) & 1);
+            const long long c0k = clock64();
+            const int64_t row0 = (pair_id + it * n_pairs) * a.tile_stride * kBN;
+            const int nvalid = static_cast<int>(min(static_cast<int64_t>(kBN), a.n_rows - row0));
+            float rn_lo, rn_hi;
+            tile_rnorm_range<BF>(a.rnorm, row0, nvalid, lane, rn_lo, rn_hi);
             mbar_wait(tmem_full + as, aph);
             tc_fence_after();
-            const int64_t row0 = (pair_id + it * n_pairs) * kBN;
-            const int nvalid = static_cast<int>(min(static_cast<int64_t>(kBN), a.n_rows - row0));
-            for (int c0 = 0; c0 < kBN; c0 += 16) {
-                uint32_t v[16];
-                tmem_ld_32x16(tmem_base + lane_base + as * 256u + c0, v);
-                unsigned mine = 0;
-                if (live && !(a.debug & 1)) {
-#pragma unroll
-                    for (int j = 0; j < 16; ++j) mine |= (__uint_as_float(v[j]) > thr ? 1u : 0u) << j;
-                }
-                unsigned any = __reduce_or_sync(0xffffffffu, mine);
-                while (any) {
-                    const int j = __ffs(any) - 1;
-                    any &= any - 1;
-                    uint32_t one;
-                    asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(one) : "r"(tmem_base + lane_base + as * 256u + c0 + j) : "memory");
-                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-                    const float sc = __uint_as_float(one);
-                    if (((mine >> j) & 1u) && sc > thr && c0 + j < nvalid)
-                        list_insert(S, minpos, thr, rows, NQL, ql, sc, static_cast<uint32_t>(row0 + c0 + j));
-                }
-            }
+            const long long c1k = clock64();
+            t_wait += c1k - c0k;
+            const uint32_t tacc = tmem_base + lane_base + as * 256u;
+            if (a.sample)
+                sample_tile<BF>(tacc, nvalid, rn_lo, rn_hi, t0, t1, t2, t3);
+            else
+                scan_tile<BF>(tacc, row0, nvalid, rn_hi, a.rnorm, live && !(a.debug & 1), S, minpos, thr, rows, NQL, ql);
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive_cluster(tmem_empty + as, 0);
+            t_work += clock64() - c1k;
         }
-        uint64_t* keys = reinterpret_cast<uint64_t*>(smem);  // [local query][slot]; the ring is idle now
-        named_bar_sync(2, 128);
-#pragma unroll
-        for (int p = 0; p < kBatchKp; ++p) {
-            const uint32_t r = rows[p * NQL + ql];
-            keys[ql * kBatchKp + p] = (S[p] > -CUDART_INF_F && r != 0xFFFFFFFFu) ? make_key(S[p] + 0.0f, r) : 0ull;
-        }
-        __syncwarp();
-        const int ql0 = (warp - kEpiWarp0) * 32;
-        const int qg0 = static_cast<int>(crank) * kBM + ql0;
-        const int n_live = max(0, min(32, a.nq - qg0));
-        for (int i = 0; i < n_live; ++i) {
-            uint64_t k = keys[(ql0 + i) * kBatchKp + lane];
-            k = warp_sort_desc(k, lane);
-            a.glists[(static_cast<size_t>(qg0 + i) * n_pairs + pair_id) * kBatchKp + lane] = k;  // glists[q][pair][pos]
+        if ((a.debug & 8) && blockIdx.x == 0 && lane == 0 && my_tiles > 0)
+            printf("[batch dbg pair] warp %d: tiles %lld, per tile: wait %lld cyc, drain+scan %lld cyc\n", warp, (long long)my_tiles,
+                   t_wait / my_tiles, t_work / my_tiles);
+        if (a.sample) {
+            if (live) {
+                float* smp = reinterpret_cast<float*>(a.glists) + (static_cast<size_t>(q) * n_pairs + pair_id) * 4;
+                smp[0] = t0, smp[1] = t1, smp[2] = t2, smp[3] = t3;
+            }
+        } else {
+            publish_lists(smem, S, rows, NQL, ql, static_cast<int>(crank) * kBM, a.nq, a.glists, static_cast<int>(n_pairs),
+                          static_cast<int>(pair_id), lane);
         }
     }
     tc_fence_before();
@@ -897,15 +935,16 @@ int launch_batch_search(const BatchSearchArgs& b, cudaStream_t stream) {
 
     CUtensorMap map_q, map_c;
     const char* mode_env = std::getenv("RAGSTORE_BATCH_2SM");
-    const bool pair_maps = mblocks == 2 && !bf && mode_env && mode_env[0] == '1';
+    const bool pair_maps = mblocks == 2 && !(mode_env && mode_env[0] == '0');
     if (!make_map(&map_q, qhat, static_cast<uint64_t>(nq_pad), static_cast<uint64_t>(s.ld), pair_maps ? kBM : nq_pad / kCluster, bf) ||
         !make_map(&map_c, s.mat, static_cast<uint64_t>(s.n_rows), static_cast<uint64_t>(s.ld), pair_maps ? 128 : kBN, bf))
         return static_cast<int>(cudaErrorNotSupported);
 
     const char* mode = std::getenv("RAGSTORE_BATCH_2SM");
-    // The CTA-pair (cta_group::2) kernel is correct but measured slower for tf32 (2.9 vs 4.7 TB/s of corpus: the pair's
-    // operand exchange paces 4-byte operands), so it is opt-in: RAGSTORE_BATCH_2SM=1.
-    const bool pair = mblocks == 2 && !bf && mode && mode[0] == '1';
+    // 129..256 queries: the CTA-pair (cta_group::2) kernel by default -- half the shared-memory fill per corpus row and a
+    // double-buffered accumulator; measured equal to 4 % faster than the single-CTA kernel on fp32 stores (both sit at
+    // the power-capped tensor rate) and 4-15 % faster on bf16 stores and small corpora.  RAGSTORE_BATCH_2SM=0 opts out.
+    const bool pair = mblocks == 2 && !(mode && mode[0] == '0');
     BatchLayout L;
     L.mblocks = mblocks;
     L.stage_bytes = pair ? 2 * kOperandBytes : (mblocks + 2) * kOperandBytes;
@@ -914,6 +953,10 @@ int launch_batch_search(const BatchSearchArgs& b, cudaStream_t stream) {
     const uint32_t budget = 227u * 1024u - 1024u /*alignment slack*/ - lists_bytes - 512u;
     L.n_stages = budget / L.stage_bytes;
     if (L.n_stages > 8) L.n_stages = 8;
+    if (const char* se = std::getenv("RAGSTORE_BATCH_STAGES")) {   // experiments only
+        const uint32_t v = static_cast<uint32_t>(atoi(se));
+        if (v >= 2 && v < L.n_stages) L.n_stages = v;
+    }
     if (L.n_stages < 2 || L.n_stages * L.stage_bytes < keys_bytes) return static_cast<int>(cudaErrorInvalidConfiguration);
     L.off_bars = L.n_stages * L.stage_bytes;
     L.off_tmem = L.off_bars + 8u * (2u * L.n_stages + 4u);
@@ -933,7 +976,7 @@ int launch_batch_search(const BatchSearchArgs& b, cudaStream_t stream) {
     int grid = static_cast<int>(n_units < s.sm_count ? n_units : s.sm_count);
     grid = (grid + kCluster - 1) / kCluster * kCluster;          // whole clusters
     if (grid > s.sm_count) grid = s.sm_count / kCluster * kCluster;
-    int nlists = grid;
+    const int nlists = pair ? grid / 2 : grid;
     a.tile_stride = 1;
     a.thr0 = nullptr;
     a.sample = 0;
@@ -944,17 +987,18 @@ int launch_batch_search(const BatchSearchArgs& b, cudaStream_t stream) {
         kernel<<<grid, kBatchThreads, L.total, stream>>>(map_q, map_c, a, L);
         return cudaGetLastError();
     };
+    auto launch_pair = [&](auto kernel) -> cudaError_t {
+        cudaError_t e2 = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        if (e2 != cudaSuccess) return e2;
+        kernel<<<grid, kPairThreads, L.total, stream>>>(map_q, map_c, a, L);
+        return cudaGetLastError();
+    };
     auto launch_main = [&]() -> cudaError_t {
+        if (pair) return bf ? launch_pair(batch_score_kernel_2sm<true>) : launch_pair(batch_score_kernel_2sm<false>);
         if (mblocks == 2) return bf ? launch_as(batch_score_kernel<2, true>) : launch_as(batch_score_kernel<2, false>);
         return bf ? launch_as(batch_score_kernel<1, true>) : launch_as(batch_score_kernel<1, false>);
     };
-    if (pair) {
-        e = cudaFuncSetAttribute(batch_score_kernel_2sm, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-        if (e != cudaSuccess) return static_cast<int>(e);
-        batch_score_kernel_2sm<<<grid, kPairThreads, L.total, stream>>>(map_q, map_c, a, L);
-        nlists = grid / 2;
-        e = cudaGetLastError();
-    } else {
+    {
         // Two passes on large corpora.  The cost of the fused top-k is the list warm-up: each CTA sees only 1/148 of
         // the rows, so its thresholds rise slowly and ~1000 ln(tiles) insert events per warp stall the accumulator
         // drain.  A sampling pass over every s-th tile (same kernel) gives, per query, the k'-th best score of the
@@ -965,13 +1009,13 @@ int launch_batch_search(const BatchSearchArgs& b, cudaStream_t stream) {
         if (two_pass) {
             // small corpora: stride 1, i.e. the "sample" is a full (cheap: 4 registers per thread, no lists) sweep --
             // still far cheaper than filling cold lists column by column (~200 us per CTA for 256 queries)
-            int stride = static_cast<int>(n_tiles / (2ll * grid));   // every CTA samples >= 2 tiles when it can
+            int stride = static_cast<int>(n_tiles / (2ll * nlists));   // every CTA (pair) samples >= 2 tiles when it can
             stride = stride > 16 ? 16 : (stride < 1 ? 1 : stride);
             a.tile_stride = stride;
             a.sample = 1;
             e = launch_main();
             if (e != cudaSuccess) return static_cast<int>(e);
-            const int nvals = grid * 4;
+            const int nvals = nlists * 4;
             batch_thresholds_kernel<<<b.nq, 256, nvals * sizeof(float), stream>>>(reinterpret_cast<const float*>(glists), nvals, kBatchKp, thr0);
             e = cudaGetLastError();
             if (e != cudaSuccess) return static_cast<int>(e);

@@ -553,14 +553,16 @@ def test_many_identical_rows_across_pass_boundaries():
     assert np.array_equal(sc.view(np.uint64), esc.view(np.uint64))
 
 
-def test_cta_pair_kernel_variant(monkeypatch):
-    """The opt-in cta_group::2 variant of the batched kernel (RAGSTORE_BATCH_2SM=1) must give the same hits."""
-    monkeypatch.setenv("RAGSTORE_BATCH_2SM", "1")
+@pytest.mark.parametrize("pair,dtype", [("1", 0), ("0", 0), ("1", 1), ("0", 1)])
+def test_cta_pair_and_single_cta_kernel_variants(monkeypatch, pair, dtype):
+    """129..256 queries run on the cta_group::2 kernel by default; RAGSTORE_BATCH_2SM=0 selects the single-CTA kernel
+    (all 512 TMEM columns for one tile).  Both must give the oracle's hits, on fp32 and bf16 stores."""
+    monkeypatch.setenv("RAGSTORE_BATCH_2SM", pair)
     n, d, nq, k = 20000, 768, 200, 10
-    rows = oc.synth_rows(0, n, d, 1234)
+    rows = oc.synth_rows(0, n, d, 1234, round_bf16=bool(dtype))
     qs = oc.synth_rows(0, nq, d, 5678)
-    with rb.RagStore(d, n) as st:
-        st.add(rows)
+    with rb.RagStore(d, n, rb.RAGSTORE_BF16 if dtype else rb.RAGSTORE_F32) as st:
+        st.add(rows, prenormalised=bool(dtype))
         idx, sc, found, flags = st.search(qs, k)
         assert st.info()["batch_launches"] >= 1
     for i in range(0, nq, 7):
