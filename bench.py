@@ -577,7 +577,7 @@ def main():
                        "rescoring": "exact fp64 (reference arithmetic) for k' >= k candidates inside the same launch"},
             "roofline": {"bound": "hbm", "achieved": r["achieved_gbs"], "peak": peak, "unit": "GB/s", "frac": r["achieved_gbs"] / peak,
                          "traffic": traffic, "peak_source": peak_src, "frac_of_8TBs_spec": r["achieved_gbs"] / 8000.0,
-                         "kernel": "batch_score_kernel (+prep, +finalize; whole step timed)" if r.get("queries_per_step", 1) > 1 else "scan_topk_kernel",
+                         "kernel": "batch_score_kernel_2sm (threshold pass + full pass; prep, thresholds and finalize included: whole step timed)" if r.get("queries_per_step", 1) > 1 else "scan_topk_kernel",
                          "kernel_ms": r["kernel_ms"],
                          "algorithmic_bytes_per_launch": r["rows_per_gpu"] * r["dim"] * (4 if r["storage"] == "f32" else 2)},
             "tensor": ({"achieved_tflops": r["tensor_tflops"], "kind": "tf32 (tcgen05.mma kind::tf32, fp32 accumulate in TMEM)",
@@ -585,7 +585,7 @@ def main():
                         "peak_source": measured_tensor_peaks()[2],
                         "frac_of_tf32_burst": r["tensor_tflops"] / (measured_tensor_peaks()[0] / 2),
                         "frac_of_tf32_sustained": r["tensor_tflops"] / (measured_tensor_peaks()[1] / 2),
-                        "note": "tf32 peak taken as half the measured bf16 cuBLAS rate; this kernel runs inside a long step (power-capped clocks), so the sustained figure is the fair denominator; the step is bound by L2->SM ingest, see DESIGN.md K3",
+                        "note": "tf32 peak taken as half the measured bf16 cuBLAS rate; this kernel runs inside a long step (power-capped clocks), so the sustained figure is the fair denominator; the step is bound by L2->SM ingest and by power (SM clock ~1.27 GHz under this load), see DESIGN.md K3",
                         "certified_fraction": r.get("certified_fraction")} if "tensor_tflops" in r else None),
             "cpu_baseline": r.get("cpu_baseline"),
             "e2e": {k: v for k, v in r.get("e2e", {}).items()} if "e2e" in r else None,
