@@ -247,7 +247,7 @@ def measure_workload(name, args, torch, dist, rb, native, rank, world, dev, do_e
             n_q = nqb
             d_q = torch.empty((n_q, dim), dtype=torch.float32, device="cuda")
             native.synth_fill_device(d_q, 0, n_q, dim, dim, QUERY_SEED, device=dev, stream=ts.cuda_stream)
-            sh = rb.ShardedSearcher(st, rank, world, rank * rows, max_k=max(k, 1), device=dev)
+            sh = rb.ShardedSearcher(st, rank, world, rank * rows, max_k=max(k, 1), device=dev, exchange=args.exchange, max_queries=nqb)
             sh.search_batch_device(d_q, nqb, k)          # allocates the batch buffers
             d_cand, d_all, d_flags = sh._b_cand, sh._b_all, sh.d_flags
             d_idx, d_score, d_found = sh._b_idx, sh._b_score, sh._b_found
@@ -258,20 +258,24 @@ def measure_workload(name, args, torch, dist, rb, native, rank, world, dev, do_e
                 sh.search_batch_device(d_q, nqb, k)
             launches_per_step = 6      # the five batched-search launches of the shard + the merge kernel (NCCL all-gather not counted)
         else:
-            sh = rb.ShardedSearcher(st, rank, world, rank * rows, max_k=max(k, 1), device=dev)
+            sh = rb.ShardedSearcher(st, rank, world, rank * rows, max_k=max(k, 1), device=dev, exchange=args.exchange, max_queries=1)
             d_cand, d_all, d_idx, d_score, d_found, d_flags = sh.d_cand, sh.d_all, sh.d_idx, sh.d_score, sh.d_found, sh.d_flags
 
             def step():
                 q = d_q[qi[0] % n_q]
                 qi[0] += 1
-                sh.search_device(q, k)      # shard scan -> NCCL all-gather (world * k * 16 B) -> merge kernel
+                sh.search_device(q, k)      # shard scan -> exchange (peer-memory kernel, or NCCL all-gather + merge kernel)
             launches_per_step = 2
 
         with ClockSampler(dev, enabled=(rank == 0)) as clk:
             ms = time_device_steps(torch, dist, world, step, args.steps, args.warmup)
         clocks = clk.summary()
         total_rows = rows * world
-        res = {"ms_per_step": ms / args.steps, "value": total_rows * args.steps / (ms * 1e-3), "clocks": clocks,
+        exchange_used = None
+        if world > 1:
+            exchange_used = "p2p: one kernel per rank over IPC-mapped peer memory (csrc/exchange.cu)" if sh.peer is not None else \
+                ("nccl all-gather + merge kernel" + (" (p2p requested but peers could not be mapped)" if args.exchange == "p2p" else ""))
+        res = {"ms_per_step": ms / args.steps, "value": total_rows * args.steps / (ms * 1e-3), "clocks": clocks, "exchange": exchange_used,
                "ingest_vectors_per_s": rows / ingest_s, "launches_per_step": launches_per_step,
                "rows_per_gpu": rows, "dim": dim, "top_k": k, "storage": dtype, "desc": desc}
         res["queries_per_s"] = nqb * args.steps / (ms * 1e-3)
@@ -338,9 +342,7 @@ def measure_workload(name, args, torch, dist, rb, native, rank, world, dev, do_e
             def e2e_step(i):
                 hq_pin.copy_(hq[i % n_q])
                 d_q1.copy_(hq_pin, non_blocking=True)
-                st.search_shard_device(d_q1, k, d_cand, d_flags, stream=ts.cuda_stream)
-                dist.all_gather_into_tensor(d_all, d_cand)
-                native.merge_shards_device(d_all, world, k, k, d_idx, d_score, d_found, device=dev, stream=ts.cuda_stream)
+                sh.search_device(d_q1, k)
                 h_idx.copy_(d_idx, non_blocking=True)
                 h_sc.copy_(d_score, non_blocking=True)
                 ts.synchronize()
@@ -356,7 +358,7 @@ def measure_workload(name, args, torch, dist, rb, native, rank, world, dev, do_e
             dt = float(dt.item())
         res["e2e"] = {"value": rows * world * n_e2e / dt, "unit": "vectors/s", "h2d_bytes_per_step": dim * 4,
                       "d2h_bytes_per_step": k * 16, "ms_per_step": dt / n_e2e * 1e3, "steps": n_e2e,
-                      "api": "host query -> search_shard_device + NCCL all-gather + merge_shards_device -> host hits, per rank"}
+                      "api": "host query -> ShardedSearcher.search_device (shard scan + exchange + merge) -> host hits, per rank"}
 
     # CPU baseline + parity check against the oracle (rank 0, N = 1 only)
     if do_cpu and world == 1 and rank == 0:
@@ -496,6 +498,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="config2", choices=sorted(WORKLOADS) + ["config5"])
     ap.add_argument("--rows", type=int, default=0, help="override rows per GPU")
+    ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"],
+                    help="N > 1: how the per-shard hits meet -- one peer-memory kernel per rank (default) or NCCL all-gather + merge kernel")
     ap.add_argument("--pinned", action="store_true", help="config5: the application's batches live in page-locked memory")
     ap.add_argument("--no-extra", action="store_true", help="skip the extra target10m / config1 measurements")
     args = ap.parse_args()
@@ -572,7 +576,7 @@ def main():
             "dtype": "f32" if r["storage"] == "f32" else "bf16 storage, f32 accumulate", "data": "synthetic",
             "queries_per_s": r["queries_per_s"],
             "config": {"workload": args.workload, "desc": r["desc"], "rows_per_gpu": r["rows_per_gpu"], "total_rows": r["rows_per_gpu"] * world,
-                       "dim": r["dim"], "top_k": r["top_k"], "storage": r["storage"], "parallelism": f"row-sharded x{world}" if world > 1 else "single GPU",
+                       "dim": r["dim"], "top_k": r["top_k"], "storage": r["storage"], "parallelism": f"row-sharded x{world}" if world > 1 else "single GPU", "exchange": r.get("exchange"),
                        "l2": "corpus shard is larger than L2 (no flush needed)" if r["rows_per_gpu"] * r["dim"] * (4 if r["storage"] == "f32" else 2) > 512e6 else "L2-resident workload: latency config, HBM fraction not meaningful",
                        "rescoring": "exact fp64 (reference arithmetic) for k' >= k candidates inside the same launch"},
             "roofline": {"bound": "hbm", "achieved": r["achieved_gbs"], "peak": peak, "unit": "GB/s", "frac": r["achieved_gbs"] / peak,

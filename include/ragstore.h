@@ -177,6 +177,31 @@ RAGSTORE_API int ragstore_merge_shards_device(const ragstore_cand* d_gathered, i
                                               double* d_score, int32_t* d_found, int device,
                                               void* stream);
 
+/* Row-sharded search, steps "all-gather" and 2 fused into one launch over peer memory (one process per GPU
+ * on one node, GPUs with peer access -- NVLink / NVSwitch).  Every rank owns an INBOX; a call stores this
+ * rank's records into every rank's inbox, waits for everybody else's, and merges -- no NCCL call and no
+ * host round trip on the query path.  Replaces, for the sharded form of RagIndex.QueryAsync
+ * (RagIndex.cs:59-67), the host-side all-gather between ragstore_search_shard*_device and
+ * ragstore_merge_shards*_device; results are identical.
+ *   create   allocates the inbox for at most max_queries queries and max_records records
+ *            (n_queries * per_shard) per call and writes the RAGSTORE_EXCHANGE_HANDLE_BYTES-byte handle
+ *            that peers need; the caller moves the handles between the processes (any transport).
+ *   connect  all_handles = world handles in rank order (own one included); maps the peers' inboxes.
+ *   merge    d_mine = this rank's n_queries x per_shard records (what ragstore_search_shard*_device
+ *            wrote); outputs as ragstore_merge_shards_batch_device; d_status (n_queries, may be null)
+ *            receives 0, or 1 when a peer's records did not arrive within 5 s (results then invalid).
+ *            Collective: every rank must make the same sequence of calls with the same n_queries and
+ *            per_shard, each rank on one stream of its own. */
+#define RAGSTORE_EXCHANGE_HANDLE_BYTES 64
+typedef struct ragstore_exchange ragstore_exchange_t;
+RAGSTORE_API int ragstore_exchange_create(int device, int world, int rank, int max_records, int max_queries,
+                                          ragstore_exchange_t** out, void* handle_out);
+RAGSTORE_API int ragstore_exchange_connect(ragstore_exchange_t* x, const void* all_handles);
+RAGSTORE_API int ragstore_exchange_merge(ragstore_exchange_t* x, const ragstore_cand* d_mine, int n_queries,
+                                         int per_shard, int top_k, int64_t* d_idx, double* d_score,
+                                         int32_t* d_found, int32_t* d_status, void* stream);
+RAGSTORE_API int ragstore_exchange_destroy(ragstore_exchange_t* x);
+
 /* No counterpart in the reference: an extra search entry point for hosts that are not allowed to
  * allocate device memory -- a server that gave all of HBM to its own arena at start-up, or a request
  * thread that cannot afford the device-wide synchronisation and driver locks of cudaMalloc/cudaFree.

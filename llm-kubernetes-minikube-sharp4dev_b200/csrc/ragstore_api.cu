@@ -93,6 +93,10 @@ float scan_eps(int dim_ld, int dtype) {
 
 }  // namespace
 
+namespace rag {
+int api_fail(int code, const char* what, const char* detail) { return fail(code, what, detail); }
+}  // namespace rag
+
 struct ragstore {
     int device = 0, dim = 0, ld = 0, dtype = 0, sm_count = 0;
     int64_t capacity = 0;

@@ -94,6 +94,9 @@ int launch_batch_search(const BatchSearchArgs& b, cudaStream_t stream);
 int launch_synth(float* d_out, int64_t row0, int64_t n_rows, int dim, int64_t ld, uint64_t seed,
                  int round_bf16, cudaStream_t stream);
 
+// records `what[: detail]` as the calling thread's ragstore_last_error text and returns `code` (ragstore_api.cu)
+int api_fail(int code, const char* what, const char* detail = nullptr);
+
 int launch_merge_shards(const ragstore_cand* d_gathered, int n_shards, int n_queries, int per_shard, int k_take,
                         int64_t* d_idx, double* d_score, int32_t* d_found, cudaStream_t stream);
 

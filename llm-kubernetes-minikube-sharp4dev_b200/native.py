@@ -59,6 +59,10 @@ def lib():
             "ragstore_search_shard_batch_device": (C.c_int, [vp, vp, C.c_int, C.c_int, vp, vp, vp]),
             "ragstore_merge_shards_batch_device": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, vp, vp, C.c_int, vp]),
             "ragstore_merge_shards_device": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, vp, vp, vp, C.c_int, vp]),
+            "ragstore_exchange_create": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(vp), vp]),
+            "ragstore_exchange_connect": (C.c_int, [vp, vp]),
+            "ragstore_exchange_merge": (C.c_int, [vp, vp, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp, vp]),
+            "ragstore_exchange_destroy": (C.c_int, [vp]),
             "ragstore_info": (C.c_int, [vp, i64p, C.c_int]),
             "ragstore_search_noalloc": (C.c_int, [vp, vp, C.c_int64, C.c_int, C.c_int, vp, C.c_int, vp, vp, vp, vp, C.c_int, vp]),
             "ragstore_noalloc_scratch_bytes": (C.c_int64, []),
@@ -251,6 +255,42 @@ def merge_shards_batch_device(d_gathered, n_shards: int, n_queries: int, per_sha
                               device: int = 0, stream: int = 0):
     check(lib().ragstore_merge_shards_batch_device(_ptr(d_gathered), n_shards, n_queries, per_shard, int(top_k), _ptr(d_idx),
                                                    _ptr(d_score), _ptr(d_found), device, C.c_void_p(stream)))
+
+
+EXCHANGE_HANDLE_BYTES = 64
+
+
+class PeerExchange:
+    """This rank's end of the peer-memory exchange (ragstore_exchange_*): an inbox every peer writes into directly.
+    `handle` (64 bytes) must reach every rank; `connect(all_handles)` takes them back in rank order."""
+
+    def __init__(self, device: int, world: int, rank: int, max_records: int, max_queries: int = 1):
+        self._h = C.c_void_p()
+        buf = C.create_string_buffer(EXCHANGE_HANDLE_BYTES)
+        check(lib().ragstore_exchange_create(device, world, rank, max_records, max_queries, C.byref(self._h), buf))
+        self.handle = buf.raw
+        self.world, self.rank, self.device = world, rank, device
+        self.max_records, self.max_queries = max_records, max_queries
+
+    def connect(self, all_handles: bytes):
+        if len(all_handles) != self.world * EXCHANGE_HANDLE_BYTES:
+            raise ValueError("all_handles must hold world x 64 bytes, in rank order")
+        check(lib().ragstore_exchange_connect(self._h, C.c_char_p(all_handles)))
+
+    def merge(self, d_mine, n_queries: int, per_shard: int, top_k: int, d_idx, d_score, d_found, d_status=None, stream: int = 0):
+        check(lib().ragstore_exchange_merge(self._h, _ptr(d_mine), n_queries, per_shard, int(top_k), _ptr(d_idx), _ptr(d_score),
+                                            _ptr(d_found), _ptr(d_status), C.c_void_p(stream)))
+
+    def close(self):
+        if self._h:
+            lib().ragstore_exchange_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 def synth_fill_device(d_out, row0: int, n_rows: int, dim: int, ld: int, seed: int, round_bf16: bool = False, device: int = 0, stream: int = 0):

@@ -1,8 +1,13 @@
 """Row-sharded search across the GPUs of one node: one process per GPU, each owning a
-contiguous block of rows; a query is scored by every shard, each shard's exactly-rescored top-k is
-all-gathered (k * 16 bytes per rank, NCCL over NVLink) and every rank merges the G * k records on its GPU.
+contiguous block of rows; a query is scored by every shard, each shard's exactly-rescored top-k
+(k * 16 bytes per rank) reaches every rank, and every rank merges the G * k records on its GPU.
 The order (score desc, global id asc) is what a single RagIndex over the whole corpus returns
-(reference Helpers/RagIndex.cs:64-65)."""
+(reference Helpers/RagIndex.cs:64-65).
+
+Two forms of the exchange:
+  * "p2p"  -- one kernel per rank stores its records into every peer's inbox over NVLink, waits for the peers' flags
+              and merges (csrc/exchange.cu): no NCCL call and one launch on the query path;
+  * "nccl" -- torch.distributed.all_gather_into_tensor + the merge kernel (also what tests inject a fake into)."""
 from __future__ import annotations
 
 from typing import Callable, Optional, Tuple
@@ -23,12 +28,20 @@ def gather_layout(world: int, k: int) -> Tuple[int, int]:
     return per, per * world
 
 
+def _current_stream_handle(torch) -> int:
+    """cudaStream_t of torch's current stream.  The C ABI reads NULL as "the store's own stream", so torch's default
+    stream (handle 0) is passed as cudaStreamLegacy (0x1): scan, exchange and merge must share ONE stream."""
+    h = torch.cuda.current_stream().cuda_stream
+    return h if h else 1
+
+
 class ShardedSearcher:
     """One shard (a RagStore on this rank's GPU) + the exchange.  `all_gather(out, inp)` defaults to
     torch.distributed.all_gather_into_tensor; tests inject their own."""
 
     def __init__(self, store, rank: int, world: int, row_base: int, max_k: int = 256,
-                 all_gather: Optional[Callable] = None, device: Optional[int] = None):
+                 all_gather: Optional[Callable] = None, device: Optional[int] = None, exchange: str = "nccl",
+                 max_queries: int = 256):
         import torch
         from . import native
         self.torch, self.native = torch, native
@@ -46,6 +59,43 @@ class ShardedSearcher:
             import torch.distributed as dist
             all_gather = dist.all_gather_into_tensor
         self._all_gather = all_gather
+        self.peer = None
+        self.d_status = torch.zeros(max_queries, dtype=torch.int32, device="cuda")
+        if exchange == "p2p":
+            self.peer = self._connect_peers(max_k, max_queries)
+        elif exchange != "nccl":
+            raise ValueError("exchange must be 'p2p' or 'nccl'")
+
+    def _connect_peers(self, max_k: int, max_queries: int):
+        """Create this rank's inbox, swap the 64-byte IPC handles (one all-gather at set-up time), map the peers.
+        Returns None -- on EVERY rank -- when any rank cannot map its peers, so that all ranks fall back together."""
+        torch, native = self.torch, self.native
+        px, ok = None, 1
+        try:
+            px = native.PeerExchange(self.device, self.world, self.rank, max_records=max_k * max_queries, max_queries=max_queries)
+            mine = torch.frombuffer(bytearray(px.handle), dtype=torch.uint8).cuda()
+        except native.RagStoreError:
+            ok, mine = 0, torch.zeros(native.EXCHANGE_HANDLE_BYTES, dtype=torch.uint8, device="cuda")
+        if self.world > 1:
+            import torch.distributed as dist
+            everyone = torch.zeros(self.world * native.EXCHANGE_HANDLE_BYTES, dtype=torch.uint8, device="cuda")
+            dist.all_gather_into_tensor(everyone, mine)
+            handles = bytes(everyone.cpu().numpy().tobytes())
+        else:
+            handles = bytes(mine.cpu().numpy().tobytes())
+        if ok:
+            try:
+                px.connect(handles)
+            except native.RagStoreError:
+                ok = 0
+        if self.world > 1:
+            import torch.distributed as dist
+            flag = torch.tensor([ok], dtype=torch.int32, device="cuda")
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+            ok = int(flag.item())
+        if not ok and px is not None:
+            px.close()
+        return px if ok else None
 
     def search_device(self, d_query, k: int):
         """Enqueue shard search -> all-gather -> merge on the current torch stream; results stay on the device
@@ -53,9 +103,12 @@ class ShardedSearcher:
         req = max(1, int(k))
         if req > self.max_k:
             raise ValueError("k above max_k")
-        stream = self.torch.cuda.current_stream().cuda_stream
+        stream = _current_stream_handle(self.torch)
         per, total = gather_layout(self.world, req)
         self.store.search_shard_device(d_query, k, self.d_cand, self.d_flags, stream=stream)
+        if self.peer is not None:
+            self.peer.merge(self.d_cand, 1, req, k, self.d_idx, self.d_score, self.d_found, self.d_status, stream=stream)
+            return
         if self.world > 1:
             self._all_gather(self.d_all[:total], self.d_cand[:per])
             src = self.d_all
@@ -76,8 +129,11 @@ class ShardedSearcher:
             self._b_score = torch.zeros(n_queries * req, dtype=torch.float64, device="cuda")
             self._b_found = torch.zeros(n_queries, dtype=torch.int32, device="cuda")
             self._b_cap = need
-        stream = torch.cuda.current_stream().cuda_stream
+        stream = _current_stream_handle(torch)
         self.store.search_shard_batch_device(d_queries, n_queries, k, self._b_cand, None, stream=stream)
+        if self.peer is not None and n_queries <= self.peer.max_queries and n_queries * req <= self.peer.max_records:
+            self.peer.merge(self._b_cand, n_queries, req, k, self._b_idx, self._b_score, self._b_found, self.d_status, stream=stream)
+            return self._b_idx[: n_queries * req].view(n_queries, req), self._b_score[: n_queries * req].view(n_queries, req), self._b_found[:n_queries]
         if self.world > 1:
             self._all_gather(self._b_all[: self.world * need], self._b_cand[:need])
             src = self._b_all
@@ -90,5 +146,7 @@ class ShardedSearcher:
     def search(self, d_query, k: int):
         self.search_device(d_query, k)
         self.torch.cuda.current_stream().synchronize()
+        if self.peer is not None and int(self.d_status[0].item()) != 0:
+            raise RuntimeError("peer exchange timed out: a rank did not publish its hits within 5 s")
         n = int(self.d_found.item())
         return self.d_idx[:n].cpu().numpy(), self.d_score[:n].cpu().numpy()

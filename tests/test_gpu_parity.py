@@ -645,3 +645,41 @@ def test_batched_bf16_store_of_unnormalised_fp32_rows(sidecar):
             eidx, esc = oc.query(rows, qs[i], k, n_threads=4)
             assert list(idx[i]) == list(eidx)
             assert np.array_equal(sc[i].view(np.uint64), full[idx[i]].view(np.uint64))
+
+
+def test_peer_exchange_single_rank_equals_merge_kernel():
+    """world = 1: the peer-memory exchange kernel degenerates to publish-to-self + merge and must give exactly what the
+    merge kernel gives on the same records (two calls in a row: both inbox slots)."""
+    import torch
+    from ragstore_b200 import native
+    nq, per, k = 37, 10, 10
+    rng = np.random.default_rng(3)
+    for call in range(3):
+        rec = np.zeros(nq * per, dtype=[("score", "<f8"), ("id", "<i8")])
+        rec["score"] = np.round(rng.standard_normal(nq * per), 2)          # ties on purpose
+        rec["id"] = rng.permutation(nq * per)
+        rec["id"][::7] = -1                                                # padding records
+        d_rec = torch.from_numpy(rec.view(np.uint8).copy()).cuda()
+        outs = []
+        if call == 0:
+            px = native.PeerExchange(0, 1, 0, max_records=nq * per, max_queries=nq)
+            px.connect(px.handle)
+        for which in ("exchange", "merge"):
+            idx = torch.full((nq, k), -7, dtype=torch.int64, device="cuda")
+            sc = torch.zeros((nq, k), dtype=torch.float64, device="cuda")
+            fnd = torch.zeros(nq, dtype=torch.int32, device="cuda")
+            status = torch.full((nq,), 9, dtype=torch.int32, device="cuda")
+            if which == "exchange":
+                px.merge(d_rec, nq, per, k, idx, sc, fnd, status)
+            else:
+                native.merge_shards_batch_device(d_rec, 1, nq, per, k, idx, sc, fnd)
+            torch.cuda.synchronize()
+            if which == "exchange":
+                assert int(status.abs().sum().item()) == 0
+            outs.append((idx.cpu().numpy(), sc.cpu().numpy(), fnd.cpu().numpy()))
+        assert np.array_equal(outs[0][2], outs[1][2])
+        for q in range(nq):
+            n = outs[0][2][q]
+            assert np.array_equal(outs[0][0][q, :n], outs[1][0][q, :n])
+            assert np.array_equal(outs[0][1][q, :n].view(np.uint64), outs[1][1][q, :n].view(np.uint64))
+    px.close()
