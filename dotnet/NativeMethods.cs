@@ -22,6 +22,26 @@ namespace Minimal_RAG.Helpers
                                                                              long* outIdx, double* outScore, int* outFound, int* outFlags);
         [LibraryImport(Lib)] public static unsafe partial int ragstore_last_error(byte* buf, int len);
 
+        // one query per call, coalesced with concurrent callers into one corpus sweep (SURVEY 8(f) N1)
+        [LibraryImport(Lib)] public static unsafe partial int ragstore_search_coalesced(IntPtr store, float* query, int queryDim, int topK,
+                                                                                       long* outIdx, double* outScore, int* outFound, int* outFlags);
+        [LibraryImport(Lib)] public static partial int ragstore_set_coalescing(IntPtr store, int windowUs, int maxBatch);
+        // Program.cs:77-89,125-128 in one call: citation mask, best score, low-score flag (N2)
+        [LibraryImport(Lib)] public static unsafe partial int ragstore_hit_filters(double* scores, int found, double evidenceMinScore, double bestFactor,
+                                                                                  double lowScoreFloor, byte* outCited, out double best, out int lowScore);
+        // store image on disk (N3)
+        [LibraryImport(Lib, StringMarshalling = StringMarshalling.Utf8)] public static partial int ragstore_save(IntPtr store, string path);
+        [LibraryImport(Lib, StringMarshalling = StringMarshalling.Utf8)] public static partial int ragstore_load(string path, int device, long capacityRows, out IntPtr store);
+        // row-sharded hosts (one process per GPU): per-shard hits, then the peer-memory exchange + merge in one launch
+        [LibraryImport(Lib)] public static partial int ragstore_set_row_base(IntPtr store, long rowBase);
+        [LibraryImport(Lib)] public static partial int ragstore_search_shard_device(IntPtr store, IntPtr dQuery, int topK, IntPtr dOut, IntPtr dFlags, IntPtr stream);
+        [LibraryImport(Lib)] public static unsafe partial int ragstore_exchange_create(int device, int world, int rank, int maxRecords, int maxQueries,
+                                                                                      out IntPtr exchange, byte* handleOut /* 64 bytes */);
+        [LibraryImport(Lib)] public static unsafe partial int ragstore_exchange_connect(IntPtr exchange, byte* allHandles /* world x 64 bytes, rank order */);
+        [LibraryImport(Lib)] public static partial int ragstore_exchange_merge(IntPtr exchange, IntPtr dMine, int nQueries, int perShard, int topK,
+                                                                              IntPtr dIdx, IntPtr dScore, IntPtr dFound, IntPtr dStatus, IntPtr stream);
+        [LibraryImport(Lib)] public static partial int ragstore_exchange_destroy(IntPtr exchange);
+
         public static unsafe void Check(int rc)
         {
             if (rc == 0) return;
