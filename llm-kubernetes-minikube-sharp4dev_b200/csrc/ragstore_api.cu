@@ -840,12 +840,18 @@ int ragstore_search(ragstore_t* s, const float* queries, int n_queries, int quer
             c.h_found = reinterpret_cast<int32_t*>(c.h_score + nh);
             c.h_flags = c.h_found + nq;
         }
-        memcpy(c.h_q, queries + static_cast<size_t>(q0) * s->dim, static_cast<size_t>(nq) * s->dim * sizeof(float));
-        CU_TRY(cudaMemcpyAsync(c.d_q, c.h_q, static_cast<size_t>(nq) * s->dim * sizeof(float), cudaMemcpyHostToDevice, c.st));
-        std::vector<int> todo(nq);
-        for (int i = 0; i < nq; ++i) todo[i] = i;
         int kp = kp0;
         bool batch_pass = batch_eligible(s, n, nq, kp0);
+        // Scan launches carry their query inside the kernel's parameter block (rows of up to kParamQueryMax elements):
+        // no staging copy, no host->device copy command in front of the kernel.  The tensor-core pass reads all
+        // queries from device memory, so a batch is uploaded as before.
+        const bool q_in_params = !batch_pass && s->dim <= kParamQueryMax;
+        if (!q_in_params) {
+            memcpy(c.h_q, queries + static_cast<size_t>(q0) * s->dim, static_cast<size_t>(nq) * s->dim * sizeof(float));
+            CU_TRY(cudaMemcpyAsync(c.d_q, c.h_q, static_cast<size_t>(nq) * s->dim * sizeof(float), cudaMemcpyHostToDevice, c.st));
+        }
+        std::vector<int> todo(nq);
+        for (int i = 0; i < nq; ++i) todo[i] = i;
         while (!todo.empty()) {
             if (batch_pass) {
                 // first pass on the tensor cores; queries whose margin the tf32 scores cannot certify are
@@ -854,20 +860,25 @@ int ragstore_search(ragstore_t* s, const float* queries, int n_queries, int quer
                                          c.batch_scratch, c.st);
                 if (rc) return fail(RAGSTORE_ERR_CUDA, "batched search launch", cudaGetErrorString(static_cast<cudaError_t>(rc)));
             }
+            // Scan launches write their few hits STRAIGHT into the page-locked host block (device-addressable under
+            // unified addressing): k * 16 bytes of posted PCIe writes by the kernel's last CTA instead of a
+            // device->host copy command behind the kernel -- one driver call and one DMA round trip less per search.
+            const bool direct = !batch_pass;
             for (int i : todo) {
                 if (batch_pass) break;
                 ScanArgs a = base_args(s, n, take, kp);
-                a.d_query = c.d_q + static_cast<size_t>(i) * s->dim;
+                a.d_query = q_in_params ? nullptr : c.d_q + static_cast<size_t>(i) * s->dim;
                 a.scratch = c.scratch;
-                a.out_idx = c.d_idx + static_cast<size_t>(i) * hs;
-                a.out_score = c.d_score + static_cast<size_t>(i) * hs;
-                a.out_found = c.d_found + i;
-                a.out_flags = c.d_flags + i;
+                a.out_idx = c.h_idx + static_cast<size_t>(i) * hs;
+                a.out_score = c.h_score + static_cast<size_t>(i) * hs;
+                a.out_found = c.h_found + i;
+                a.out_flags = c.h_flags + i;
                 s->n_scan_launches.fetch_add(1, std::memory_order_relaxed);
-                const int rc = launch_scan(a, c.st);
+                const int rc = launch_scan(a, c.st, q_in_params ? queries + static_cast<size_t>(q0 + i) * s->dim : nullptr);
                 if (rc) return fail(RAGSTORE_ERR_CUDA, "scan kernel launch", cudaGetErrorString(static_cast<cudaError_t>(rc)));
             }
-            CU_TRY(cudaMemcpyAsync(c.h_idx, c.d_idx, static_cast<size_t>(nq) * hs * 16 + static_cast<size_t>(nq) * 8, cudaMemcpyDeviceToHost, c.st));
+            if (!direct)
+                CU_TRY(cudaMemcpyAsync(c.h_idx, c.d_idx, static_cast<size_t>(nq) * hs * 16 + static_cast<size_t>(nq) * 8, cudaMemcpyDeviceToHost, c.st));
             CU_TRY(cudaStreamSynchronize(c.st));
             std::vector<int> again;
             for (int i : todo) {

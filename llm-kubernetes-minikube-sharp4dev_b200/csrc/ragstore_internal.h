@@ -56,7 +56,10 @@ struct ScanArgs {
 };
 
 // Enqueues the fused scan + top-k + exact-rescore kernel.  Returns cudaError_t as int.
-int launch_scan(const ScanArgs& a, cudaStream_t stream);
+// h_query: when not null (and dim <= kParamQueryMax, a.d_query == nullptr) the raw query travels inside the kernel's
+// parameter block instead of device memory: a host caller then needs no host->device copy before the launch.
+constexpr int kParamQueryMax = 1024;
+int launch_scan(const ScanArgs& a, cudaStream_t stream, const float* h_query = nullptr);
 
 struct NormaliseArgs {
     const float* src;     // [n_rows][src_ld] fp32 (may alias dst for the fp32 store)

@@ -29,6 +29,8 @@
 
 #include <cstdlib>
 
+#include <cstring>
+
 #include "topk_device.cuh"
 
 namespace rag {
@@ -133,8 +135,14 @@ __device__ __forceinline__ float group_dot(const uint8_t* const (&p)[kGroup], co
 }
 
 // ---------------------------------------------------------------- the kernel
+// A raw query carried in the kernel's parameter block (see launch_scan): used when a.d_query is null.
+struct QueryParam {
+    float v[kParamQueryMax];
+};
+
 template <typename T, int DV, bool FULL>
-__global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanArgs a, const ScanLayout L) {
+__global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanArgs a, const ScanLayout L,
+                                                                    const __grid_constant__ QueryParam qp) {
     extern __shared__ __align__(128) uint8_t smem[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     constexpr int QV = Elem<T>::kQV;
@@ -195,8 +203,9 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
     } else {
         // ---------------- consumers: query prologue (overlaps the first tiles already in flight)
         double part = 0.0;
+        const float* qsrc = a.d_query ? a.d_query : qp.v;
         for (int i = tid; i < static_cast<int>(L.qpad); i += kConsumerWarps * 32) {
-            const float v = i < a.dim ? a.d_query[i] : 0.f;
+            const float v = i < a.dim ? qsrc[i] : 0.f;
             qraw[i] = v;
             part += static_cast<double>(v) * static_cast<double>(v);
         }
@@ -377,33 +386,36 @@ static bool make_layout(const ScanArgs& a, int dv, ScanLayout& L) {
 }
 
 template <typename T, int DV, bool FULL>
-static int launch_one(const ScanArgs& a, const ScanLayout& L, int grid, cudaStream_t stream) {
+static int launch_one(const ScanArgs& a, const ScanLayout& L, int grid, cudaStream_t stream, const QueryParam& qp) {
     auto kfn = scan_topk_kernel<T, DV, FULL>;
     cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     if (e != cudaSuccess) return static_cast<int>(e);
-    kfn<<<grid, kScanThreads, L.total, stream>>>(a, L);
+    kfn<<<grid, kScanThreads, L.total, stream>>>(a, L, qp);
     return static_cast<int>(cudaGetLastError());
 }
 
 template <typename T, int DV>
-static int launch_full(const ScanArgs& a, const ScanLayout& L, int grid, cudaStream_t st, bool full) {
-    return full ? launch_one<T, DV, true>(a, L, grid, st) : launch_one<T, DV, false>(a, L, grid, st);
+static int launch_full(const ScanArgs& a, const ScanLayout& L, int grid, cudaStream_t st, bool full, const QueryParam& qp) {
+    return full ? launch_one<T, DV, true>(a, L, grid, st, qp) : launch_one<T, DV, false>(a, L, grid, st, qp);
 }
 
 template <typename T>
-static int dispatch_dv(const ScanArgs& a, int dv, bool full, const ScanLayout& L, int grid, cudaStream_t st) {
+static int dispatch_dv(const ScanArgs& a, int dv, bool full, const ScanLayout& L, int grid, cudaStream_t st, const QueryParam& qp) {
     switch (dv) {
-        case 1: return launch_full<T, 1>(a, L, grid, st, full);
-        case 2: return launch_full<T, 2>(a, L, grid, st, full);
-        case 3: return launch_full<T, 3>(a, L, grid, st, full);
-        case 4: return launch_full<T, 4>(a, L, grid, st, full);
-        case 6: return launch_full<T, 6>(a, L, grid, st, full);
-        case 8: return launch_full<T, 8>(a, L, grid, st, full);
-        default: return launch_one<T, 0, false>(a, L, grid, st);
+        case 1: return launch_full<T, 1>(a, L, grid, st, full, qp);
+        case 2: return launch_full<T, 2>(a, L, grid, st, full, qp);
+        case 3: return launch_full<T, 3>(a, L, grid, st, full, qp);
+        case 4: return launch_full<T, 4>(a, L, grid, st, full, qp);
+        case 6: return launch_full<T, 6>(a, L, grid, st, full, qp);
+        case 8: return launch_full<T, 8>(a, L, grid, st, full, qp);
+        default: return launch_one<T, 0, false>(a, L, grid, st, qp);
     }
 }
 
-int launch_scan(const ScanArgs& a, cudaStream_t stream) {
+int launch_scan(const ScanArgs& a, cudaStream_t stream, const float* h_query) {
+    if ((a.d_query == nullptr) != (h_query != nullptr) || (h_query && a.dim > kParamQueryMax)) return static_cast<int>(cudaErrorInvalidValue);
+    QueryParam qp;  // left as it is unless the query travels in it: the launch copies the block either way
+    if (h_query) memcpy(qp.v, h_query, sizeof(float) * static_cast<size_t>(a.dim));
     if (a.n_rows <= 0 || a.n_rows >= 0xFFFFFFFFll || a.kp < 32 || a.kp > kMaxKp || (a.kp & (a.kp - 1)) ||
         a.k_take < 1 || a.k_take > a.kp)
         return static_cast<int>(cudaErrorInvalidValue);
@@ -419,8 +431,8 @@ int launch_scan(const ScanArgs& a, cudaStream_t stream) {
     const int64_t n_tiles = (a.n_rows + L.rows_per_tile - 1) / L.rows_per_tile;
     int grid = static_cast<int>(n_tiles < a.sm_count ? n_tiles : a.sm_count);
     if (grid > kMaxCtas) grid = kMaxCtas;
-    if (a.dtype == RAGSTORE_F32) return dispatch_dv<float>(a, dv, full, L, grid, stream);
-    return dispatch_dv<uint16_t>(a, dv, full, L, grid, stream);
+    if (a.dtype == RAGSTORE_F32) return dispatch_dv<float>(a, dv, full, L, grid, stream, qp);
+    return dispatch_dv<uint16_t>(a, dv, full, L, grid, stream, qp);
 }
 
 }  // namespace rag

@@ -203,6 +203,26 @@ class RagStore:
                                     found.ctypes.data_as(C.POINTER(C.c_int32)), flags.ctypes.data_as(C.POINTER(C.c_int32))))
         return idx, score, found, flags
 
+    def search_call(self, n_queries: int, top_k: int):
+        """Preallocated form of `search`, the way a compiled host uses the ABI (buffers pinned once, reused per request):
+        returns (call, idx, score, found, flags); `call(q)` takes a C-contiguous float32 array of n_queries x dim, runs
+        ragstore_search into the four arrays and returns nothing.  Per-call Python work is one ctypes call."""
+        req = max(1, int(top_k))
+        idx = np.full((n_queries, req), -1, dtype=np.int64)
+        score = np.full((n_queries, req), np.nan, dtype=np.float64)
+        found = np.zeros(n_queries, dtype=np.int32)
+        flags = np.zeros(n_queries, dtype=np.int32)
+        fn, h, dim, k = lib().ragstore_search, self._h, self.dim, int(top_k)
+        p_idx, p_sc = idx.ctypes.data_as(C.POINTER(C.c_int64)), score.ctypes.data_as(C.POINTER(C.c_double))
+        p_fnd, p_flg = found.ctypes.data_as(C.POINTER(C.c_int32)), flags.ctypes.data_as(C.POINTER(C.c_int32))
+        f32p = C.POINTER(C.c_float)
+
+        def call(q: np.ndarray):
+            rc = fn(h, C.cast(q.ctypes.data, f32p), n_queries, dim, k, p_idx, p_sc, p_fnd, p_flg)
+            if rc:
+                check(rc)
+        return call, idx, score, found, flags
+
     def search_coalesced(self, query: np.ndarray, top_k: int):
         """One query per call; concurrent callers share a corpus sweep (ragstore_search_coalesced)."""
         q = np.ascontiguousarray(query, dtype=np.float32).reshape(-1)
