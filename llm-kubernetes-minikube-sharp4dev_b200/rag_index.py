@@ -39,13 +39,18 @@ class RagIndex:
     """Drop-in for `class RagIndex` (RagIndex.cs:6): store + brute-force cosine top-k."""
 
     def __init__(self, embedModel: str, embedder: Optional[Callable] = None, *, dim: Optional[int] = None,
-                 capacity_rows: int = 1 << 20, dtype: int = RAGSTORE_F32, device: int = 0, coalesce: bool = False):
+                 capacity_rows: int = 1 << 20, dtype: int = RAGSTORE_F32, device: int = 0, coalesce: bool = False,
+                 batch_embedder: Optional[Callable] = None, embed_batch: int = 64):
         self._embedModel = embedModel                       # RagIndex.cs:9,11
         self._embedder = embedder
         self._meta: List[tuple] = []                        # (Id, Source, Text) per row, insertion order
         self._store: Optional[RagStore] = None
         self._dim, self._cap, self._dtype, self._device = dim, capacity_rows, dtype, device
         self._coalesce = coalesce          # concurrent QueryAsync callers share one corpus sweep (SURVEY 8f N1)
+        # SURVEY 8f N4: `batch_embedder(model, [texts]) -> [embeddings]` -- the array form of the embed endpoint that
+        # Embedder.cs:19 already sends for one text -- turns one HTTP round trip per chunk (RagIndex.cs:42-50) into one
+        # per `embed_batch` chunks; the rows then reach the device as one ragstore_add batch either way.
+        self._batch_embedder, self._embed_batch = batch_embedder, max(1, int(embed_batch))
         self.last_flags = None
 
     # -- store side ---------------------------------------------------------------------------
@@ -75,14 +80,35 @@ class RagIndex:
     async def BuildFromChunksAsync(self, items, logger=None):
         """The tail of BuildFromFolderAsync (RagIndex.cs:42-50): embed each cleaned chunk and store it.
         `items` yields (file_name, source_path, clean_text); ids follow `"{file}#{i}"` per file."""
-        counters, batch = {}, []
+        counters, batch, pending = {}, [], []
+
+        async def flush():
+            if not pending:
+                return
+            r = self._batch_embedder(self._embedModel, [t for _, _, t in pending])
+            if inspect.isawaitable(r):
+                r = await r
+            if len(r) != len(pending):
+                raise RuntimeError("Embedding batch returned a different number of vectors")   # cf. Embedder.cs:28
+            for (cid, source, text), emb in zip(pending, r):
+                batch.append(RagChunk(cid, source, text, np.asarray(emb, dtype=np.float32)))
+            pending.clear()
+
         for file_name, source, text in items:
             if text is None or not str(text).strip():
                 continue                                      # :45
-            emb = await self._embed(text)                     # :47
             i = counters.get(file_name, 0)
             counters[file_name] = i + 1
-            batch.append(RagChunk(f"{file_name}#{i}", source, text, emb))   # :48
+            cid = f"{file_name}#{i}"
+            if self._batch_embedder is not None:
+                pending.append((cid, source, text))
+                if len(pending) >= self._embed_batch:
+                    await flush()
+            else:
+                emb = await self._embed(text)                 # :47
+                batch.append(RagChunk(cid, source, text, emb))   # :48
+        if self._batch_embedder is not None:
+            await flush()
         self.AddRange(batch)
         if logger is not None:
             logger.info("[RAG] Totale chunks indicizzati: %d", self.Count)   # :55

@@ -225,6 +225,24 @@ def test_rag_index_mirror():
     rc.AddRange([rb.RagChunk(f"doc.md#{i}", "doc.md", f"t{i}", emb[f"t{i}"]) for i in range(40)])
     assert [h.Id for h in rc.Query("t7", 5)] == [h.Id for h in hits]
     rc.close()
+    # ingest through BuildFromChunksAsync: one embed call per chunk (RagIndex.cs:47) and the batched embedder (8f N4)
+    # must build the same index, ids "{file}#{i}" per file, blank chunks skipped (:45)
+    import asyncio
+    items = [("a.md" if i % 3 else "b.md", "/k/x.md", f"t{i}" if i != 5 else "  ") for i in range(40)]
+    calls = []
+
+    def many(model, texts):
+        calls.append(len(texts))
+        return [emb[t] for t in texts]
+    one = rb.RagIndex("m", embedder=lambda model, text: emb[text], capacity_rows=128)
+    bat = rb.RagIndex("m", embedder=lambda model, text: emb[text], batch_embedder=many, embed_batch=16, capacity_rows=128)
+    asyncio.run(one.BuildFromChunksAsync(items))
+    asyncio.run(bat.BuildFromChunksAsync(items))
+    assert one.Count == bat.Count == 39 and calls == [16, 16, 7]
+    h1, h2 = one.Query("t7", 6), bat.Query("t7", 6)
+    assert [(h.Id, h.Source, h.Text, h.Score) for h in h1] == [(h.Id, h.Source, h.Text, h.Score) for h in h2]
+    assert h1[0].Text == "t7" and h1[0].Id.endswith("#" + str(sum(1 for i in range(7) if (i % 3 != 0) == (7 % 3 != 0) and i != 5)))
+    one.close(), bat.close()
 
 
 @pytest.mark.parametrize("n,k,dtype", [(5000, 10, 0), (3001, 100, 0), (4000, 100, 1)])
