@@ -25,6 +25,20 @@ __global__ void k_f2f(double* out, long long* cyc, const float* in, int n) {
     out[threadIdx.x] = acc;
     if (threadIdx.x == 0) cyc[blockIdx.x] = t1 - t0;
 }
+// the same chain with only `active` lanes of each warp alive: does the F2F cost scale with the lanes in use?
+__global__ void k_f2f_lanes(double* out, long long* cyc, const float* in, int n, int active) {
+    double acc = 0;
+    float f = in[threadIdx.x];
+    if ((int)(threadIdx.x & 31) >= active) return;
+    long long t0 = clock64();
+    for (int i = 0; i < n; i += 8) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { acc = __dadd_rn(acc, (double)f); f = __fmul_rn(f, 1.0001f); }
+    }
+    long long t1 = clock64();
+    out[threadIdx.x] = acc;
+    if (threadIdx.x == 0) cyc[blockIdx.x] = t1 - t0;
+}
 __global__ void k_f2f_only(double* out, long long* cyc, const float* in, int n) {
     double a0 = 0, a1 = 0, a2 = 0, a3 = 0;
     float f = in[threadIdx.x];
@@ -59,6 +73,13 @@ int main() {
         k_f2f_only<<<1, 32 * warps>>>(out, cyc, in, n);
         cudaMemcpy(&h, cyc, 8, cudaMemcpyDeviceToHost);
         printf("4 independent (F2F + DADD) chains: warps=%d  %.2f cycles/op\n", warps, (double)h / n);
+    }
+    for (int warps : {1, 3, 9}) {
+        for (int active : {32, 16, 8, 4, 1}) {
+            k_f2f_lanes<<<1, 32 * warps>>>(out, cyc, in, n, active);
+            cudaMemcpy(&h, cyc, 8, cudaMemcpyDeviceToHost);
+            printf("DADD chain + F2F + FMUL per op: warps=%d active lanes per warp=%d  %.2f cycles/op\n", warps, active, (double)h / n);
+        }
     }
     printf("%s\n", cudaGetErrorString(cudaDeviceSynchronize()));
     return 0;
