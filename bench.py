@@ -423,6 +423,8 @@ def run_streaming(args, torch, dist, rb, native, rank, world, dev):
     n_batches = max(1, total // B // world)                 # batches appended by THIS rank
     st = rb.RagStore(dim, n_batches * B, rb.RAGSTORE_F32, dev)
     st.set_row_blocking(B, world, rank)
+    if not args.no_reserve:
+        st.reserve_rows(n_batches * B)      # HBM for the announced capacity mapped at start-up, not inside the stream
     ts = torch.cuda.Stream()
     with torch.cuda.stream(ts):
         d_batch = torch.empty((B, dim), dtype=torch.float32, device="cuda")
@@ -432,10 +434,17 @@ def run_streaming(args, torch, dist, rb, native, rank, world, dev):
         del d_batch
         d_q = torch.empty((QB, dim), dtype=torch.float32, device="cuda")
         native.synth_fill_device(d_q, 0, QB, dim, dim, QUERY_SEED, device=dev, stream=ts.cuda_stream)
-        sh = rb.ShardedSearcher(st, rank, world, 0, max_k=k, device=dev)
+        local_only = bool(os.environ.get("BENCH_STREAM_LOCAL"))    # experiment: no exchange between the ranks
+        sh = rb.ShardedSearcher(st, rank, 1 if local_only else world, 0, max_k=k, device=dev)
         st.add(h_batch)                                      # first batch in before serving starts (also warms up)
-        for _ in range(2):
+        for _ in range(3):
+            # the serving loop below, once, outside the timed region: NCCL sets its connections up lazily per collective
+            # (device-wide allocations and mappings that stall the ingest stream as well)
+            wflag = torch.zeros(1, dtype=torch.int32, device="cuda")
+            if world > 1 and not local_only:
+                dist.all_reduce(wflag, op=dist.ReduceOp.MIN)
             sh.search_batch_device(d_q, QB, k)
+            ts.synchronize()
         torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
@@ -443,9 +452,12 @@ def run_streaming(args, torch, dist, rb, native, rank, world, dev):
         t_ingest = [0.0]
 
         def writer():
+            torch.cuda.set_device(dev)      # CUDA's current device is per thread; a new thread starts on device 0
             t0 = time.perf_counter()
-            for _ in range(n_batches - 1):
-                st.add(h_batch)
+            # one native call for the whole stream of batches (ragstore_add_many): every batch is still uploaded,
+            # normalised and published on its own, but the producer loop does not compete for the Python GIL with the
+            # serving loop of this process -- that contention, not the device, bounded earlier multi-GPU runs
+            st.add_many([h_batch] * (n_batches - 1))
             t_ingest[0] = time.perf_counter() - t0
             stop.set()
 
@@ -454,16 +466,29 @@ def run_streaming(args, torch, dist, rb, native, rank, world, dev):
         t0 = time.perf_counter()
         w.start()
         with ClockSampler(dev, enabled=(rank == 0)) as clk:
+            trace = [0.0, 0.0, 0.0, 0.0] if os.environ.get("BENCH_STREAM_TRACE") else None
             while True:
                 # every rank must agree on when to stop: the flag is reduced with the batch
+                ta = time.perf_counter()
                 flag = torch.tensor([1 if stop.is_set() else 0], dtype=torch.int32, device="cuda")
-                if world > 1:
+                if world > 1 and not local_only:
                     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+                tb = time.perf_counter()
                 sh.search_batch_device(d_q, QB, k)
+                tc = time.perf_counter()
                 ts.synchronize()
+                td = time.perf_counter()
                 qbatches += 1
-                if int(flag.item()) == 1:
+                done = int(flag.item()) == 1
+                if trace is not None:
+                    te = time.perf_counter()
+                    for i, v in enumerate((tb - ta, tc - tb, td - tc, te - td)):
+                        trace[i] += v
+                if done:
                     break
+            if trace is not None and rank == 0:
+                print("[stream trace] per iteration ms: flag+all_reduce %.2f, enqueue search %.2f, stream sync %.2f, flag read %.2f" %
+                      tuple(1e3 * v / qbatches for v in trace), file=sys.stderr, flush=True)
         w.join()
         t_serve = time.perf_counter() - t0
         tt = torch.tensor([t_ingest[0], t_serve], dtype=torch.float64, device="cuda")
@@ -481,6 +506,7 @@ def run_streaming(args, torch, dist, rb, native, rank, world, dev):
                "config": {"workload": "config5", "desc": c["desc"], "rows_total": n_batches * B * world, "rows_per_gpu": n_batches * B,
                           "dim": dim, "top_k": k, "batch_rows": B, "queries_per_batch": QB, "parallelism": f"block-cyclic x{world}",
                           "start": "one batch per GPU preloaded, the rest appended during the timed region",
+                          "device_memory": "mapped on demand during the appends" if args.no_reserve else "mapped for the whole capacity before the timed region (ragstore_reserve_rows)",
                           "host_batches": "page-locked (direct PCIe copy)" if args.pinned else "pageable (staged through the library's pinned ring)"},
                "roofline": {"bound": "pcie (host->device copy of the appended rows; not an HBM or tensor bound)",
                             "achieved": rows_streamed * dim * 4 / t_ing / 1e9 / world, "peak": 64.0, "unit": "GB/s per GPU",
@@ -505,6 +531,7 @@ def main():
     ap.add_argument("--rows", type=int, default=0, help="override rows per GPU")
     ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"],
                     help="N > 1: how the per-shard hits meet -- one peer-memory kernel per rank (default) or NCCL all-gather + merge kernel")
+    ap.add_argument("--no-reserve", action="store_true", help="config5: let appends map device memory on demand")
     ap.add_argument("--pinned", action="store_true", help="config5: the application's batches live in page-locked memory")
     ap.add_argument("--no-extra", action="store_true", help="skip the extra target10m / config1 measurements")
     args = ap.parse_args()

@@ -14,6 +14,9 @@
  *   Program.cs:326-327           RagChunk(float[] Embedding) / RagHit(double Score)
  *                                                                         -> fp32 in, fp64 score out
  *
+ * Threads: CUDA's current device is per thread.  Every call switches to the store's device and back when the calling
+ * thread is on another one; call from a thread already on the store's device to avoid that cost (it is measurable:
+ * DESIGN.md 4b).
  * Conventions: plain C types only; every call returns an int status (0 = RAGSTORE_OK) and never
  * unwinds across the boundary; the caller owns every in/out buffer; the library owns device
  * memory; handles are opaque.  INTEGRATION.md shows the P/Invoke declarations a maintainer
@@ -101,6 +104,19 @@ RAGSTORE_API int ragstore_destroy(ragstore_t* s);
  * overlap with searches; a search sees a prefix of the appended rows. */
 RAGSTORE_API int ragstore_add(ragstore_t* s, const float* rows, int64_t n_rows, int row_dim,
                               uint32_t flags, int64_t* out_first_row);
+
+/* Scatter-gather form of ragstore_add: appends n_blocks host (or device, per `flags`) blocks of block_rows[b] rows each,
+ * in order, exactly as n_blocks calls would -- every block becomes visible to searches as soon as it is in, and
+ * out_first_row receives the row id of the first row of block 0.  For hosts that queue up embedding responses
+ * (RagIndex.cs:42-50 produces one row at a time) and want one native call per flush. */
+RAGSTORE_API int ragstore_add_many(ragstore_t* s, const float* const* blocks, const int64_t* block_rows, int n_blocks,
+                                   int row_dim, uint32_t flags, int64_t* out_first_row);
+
+/* Maps device memory for the first n_rows rows now instead of as they arrive (like List<T>.Capacity for the reference's
+ * `_chunks`, RagIndex.cs:8).  Optional: appends map memory on demand, in geometrically growing steps; a server that
+ * knows its corpus size calls this once at start-up so that no append ever pays for page-table work (which is a
+ * device-wide operation and, on hosts with several GPUs in peer-to-peer contact, stalls running searches too). */
+RAGSTORE_API int ragstore_reserve_rows(ragstore_t* s, int64_t n_rows);
 
 /* Replaces `_chunks.Count` (RagIndex.cs:55). */
 RAGSTORE_API int ragstore_count(ragstore_t* s, int64_t* out_rows);

@@ -109,7 +109,12 @@ struct DeviceScope {
     bool ok = false;
     explicit DeviceScope(int dev) {
         if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
-        ok = cudaSetDevice(dev) == cudaSuccess;
+        if (prev == dev) {
+            prev = -1;  // already there: nothing to switch, nothing to restore
+            ok = true;
+        } else {
+            ok = cudaSetDevice(dev) == cudaSuccess;
+        }
     }
     ~DeviceScope() {
         if (prev >= 0) cudaSetDevice(prev);

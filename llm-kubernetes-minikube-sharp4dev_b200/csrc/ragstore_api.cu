@@ -44,7 +44,12 @@ struct DeviceGuard {
     bool ok = false;
     explicit DeviceGuard(int dev) {
         if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
-        ok = cudaSetDevice(dev) == cudaSuccess;
+        if (prev == dev) {
+            prev = -1;  // already there: nothing to switch, nothing to restore
+            ok = true;
+        } else {
+            ok = cudaSetDevice(dev) == cudaSuccess;
+        }
     }
     ~DeviceGuard() {
         if (prev >= 0) cudaSetDevice(prev);
@@ -232,7 +237,11 @@ ScanArgs base_args(const ragstore* s, int64_t n, int take, int kp) {
 // (<= 2^-9 relative per element -> <= 2^-9 on a cosine, Cauchy-Schwarz) and the fp32 accumulation remain; when
 // exact scores come from fp32 originals (sidecar) the stored image itself is another 2^-8 away, as in base_args.
 float batch_eps(const ragstore* s) {
-    if (s->dtype == RAGSTORE_F32) return 2.1e-3f;
+    if (s->dtype == RAGSTORE_F32) {
+        const char* tr = std::getenv("RAGSTORE_BATCH_TRUNC");
+        if (tr && tr[0] == '1' && s->ld % 8 == 0) return 6.0e-3f;   // experiment: truncated-bf16 corpus + bf16 query
+        return 2.1e-3f;
+    }
     float e = 1.953125e-3f + static_cast<float>(s->ld) * 2.4e-7f + 2e-5f;
     if (s->raw_used > 0) e += 3.90625e-3f;
     return e;
@@ -403,6 +412,37 @@ int ragstore_set_row_blocking(ragstore_t* s, int64_t block_rows, int n_shards, i
     s->row_block = block_rows;
     s->row_nshards = n_shards;
     s->row_shard = shard_index;
+    return RAGSTORE_OK;
+}
+
+int ragstore_add_many(ragstore_t* s, const float* const* blocks, const int64_t* block_rows, int n_blocks, int row_dim,
+                      uint32_t flags, int64_t* out_first_row) {
+    if (!s || n_blocks < 0 || (n_blocks > 0 && (!blocks || !block_rows)))
+        return fail(RAGSTORE_ERR_INVALID, "ragstore_add_many: null/negative argument");
+    for (int b = 0; b < n_blocks; ++b) {
+        int64_t first = 0;
+        const int rc = ragstore_add(s, blocks[b], block_rows[b], row_dim, flags, &first);   // publishes block b before b + 1 starts
+        if (rc) return rc;
+        if (b == 0 && out_first_row) *out_first_row = first;
+    }
+    if (n_blocks == 0 && out_first_row) *out_first_row = s->count.load(std::memory_order_acquire);
+    return RAGSTORE_OK;
+}
+
+int ragstore_reserve_rows(ragstore_t* s, int64_t n_rows) {
+    if (!s || n_rows < 0) return fail(RAGSTORE_ERR_INVALID, "ragstore_reserve_rows: bad argument");
+    if (n_rows > s->capacity) return fail(RAGSTORE_ERR_CAPACITY, "ragstore_reserve_rows: above the capacity fixed at create");
+    std::lock_guard<std::mutex> lk(s->add_mu);
+    DeviceGuard g(s->device);
+    if (!g.ok) return fail(RAGSTORE_ERR_CUDA, "cudaSetDevice failed");
+    const size_t upto = static_cast<size_t>(n_rows);
+    const size_t upto4 = ((upto + 3) & ~size_t(3)) + 64;
+    int vr = s->mat_buf.ensure(upto * s->ld * s->elem_size(), false, s->ingest_stream);
+    if (!vr) vr = s->rnorm_buf.ensure(upto4 * sizeof(float), true, s->ingest_stream);
+    if (!vr) vr = s->exact_buf.ensure(upto4, true, s->ingest_stream);
+    if (!vr && s->raw_slot) vr = s->slot_buf.ensure(upto4 * sizeof(int32_t), true, s->ingest_stream);
+    if (vr) return fail(RAGSTORE_ERR_CUDA, "ragstore_reserve_rows: mapping device memory", cudaGetErrorString(static_cast<cudaError_t>(vr)));
+    CU_TRY(cudaStreamSynchronize(s->ingest_stream));
     return RAGSTORE_OK;
 }
 

@@ -46,6 +46,8 @@ def lib():
             "ragstore_destroy": (C.c_int, [vp]),
             "ragstore_add": (C.c_int, [vp, vp, C.c_int64, C.c_int, C.c_uint32, i64p]),
             "ragstore_count": (C.c_int, [vp, i64p]),
+            "ragstore_reserve_rows": (C.c_int, [vp, C.c_int64]),
+            "ragstore_add_many": (C.c_int, [vp, C.POINTER(vp), i64p, C.c_int, C.c_int, C.c_uint32, i64p]),
             "ragstore_set_row_base": (C.c_int, [vp, C.c_int64]),
             "ragstore_search": (C.c_int, [vp, f32p, C.c_int, C.c_int, C.c_int, i64p, f64p, i32p, i32p]),
             "ragstore_hit_filters": (C.c_int, [f64p, C.c_int, C.c_double, C.c_double, C.c_double, C.POINTER(C.c_uint8), f64p, i32p]),
@@ -108,6 +110,25 @@ class RagStore:
             self._h = C.c_void_p()
             check(lib().ragstore_create(dim, dtype, capacity_rows, device, flags, C.byref(self._h)))
         self.dim, self.dtype, self.device, self.capacity = dim, dtype, device, capacity_rows
+
+    def add_many(self, blocks, prenormalised: bool = False) -> int:
+        """Append a list of C-contiguous float32 host arrays (rows x dim each) with ONE native call; each block is
+        published as soon as it is in.  Returns the row id of the first appended row."""
+        arrs = [np.ascontiguousarray(b, dtype=np.float32) for b in blocks]
+        for a in arrs:
+            if a.ndim != 2 or a.shape[1] != self.dim:
+                raise ValueError("every block must be rows x dim")
+        n = len(arrs)
+        ptrs = (C.c_void_p * max(1, n))(*[a.ctypes.data for a in arrs])
+        rows = (C.c_int64 * max(1, n))(*[a.shape[0] for a in arrs])
+        first = C.c_int64(0)
+        flags = RAGSTORE_ADD_HOST | (RAGSTORE_ADD_PRENORMALISED if prenormalised else 0)
+        check(lib().ragstore_add_many(self._h, ptrs, rows, n, self.dim, flags, C.byref(first)))
+        return first.value
+
+    def reserve_rows(self, n_rows: int):
+        """Map device memory for the first n_rows rows now (appends otherwise map on demand)."""
+        check(lib().ragstore_reserve_rows(self._h, int(n_rows)))
 
     def save(self, path: str):
         check(lib().ragstore_save(self._h, path.encode()))

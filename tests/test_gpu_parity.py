@@ -701,3 +701,25 @@ def test_peer_exchange_single_rank_equals_merge_kernel():
             assert np.array_equal(outs[0][0][q, :n], outs[1][0][q, :n])
             assert np.array_equal(outs[0][1][q, :n].view(np.uint64), outs[1][1][q, :n].view(np.uint64))
     px.close()
+
+
+def test_add_many_and_reserve_rows_equal_repeated_adds():
+    """ragstore_add_many == the same blocks appended one call at a time (ids, results); ragstore_reserve_rows changes
+    nothing observable and rejects more than the capacity."""
+    d, k = 96, 7
+    blocks = [oc.synth_rows(i * 1000, n, d, 1234) for i, n in enumerate((300, 1, 4097, 50))]
+    q = oc.synth_rows(0, 1, d, 5678)[0]
+    total = sum(b.shape[0] for b in blocks)
+    with rb.RagStore(d, total) as a, rb.RagStore(d, total) as b:
+        b.reserve_rows(total)
+        with pytest.raises(rb.RagStoreError):
+            b.reserve_rows(total + 1)
+        first = b.add_many(blocks)
+        for blk in blocks:
+            a.add(blk)
+        assert first == 0 and a.count() == b.count() == total
+        assert b.add_many([]) == total
+        ra, rb_ = a.search(q, k), b.search(q, k)
+    assert np.array_equal(ra[0], rb_[0]) and np.array_equal(ra[1].view(np.uint64), rb_[1].view(np.uint64))
+    eidx, esc = oc.query(np.concatenate(blocks), q, k)
+    assert list(ra[0][0]) == list(eidx) and np.array_equal(ra[1][0].view(np.uint64), esc.view(np.uint64))
