@@ -29,6 +29,10 @@ namespace Minimal_RAG.Helpers
         // Program.cs:77-89,125-128 in one call: citation mask, best score, low-score flag (N2)
         [LibraryImport(Lib)] public static unsafe partial int ragstore_hit_filters(double* scores, int found, double evidenceMinScore, double bestFactor,
                                                                                   double lowScoreFloor, byte* outCited, out double best, out int lowScore);
+        // capacity planning and scatter-gather appends (RagIndex.cs:8,48: List<T>.Capacity / AddRange)
+        [LibraryImport(Lib)] public static partial int ragstore_reserve_rows(IntPtr store, long nRows);
+        [LibraryImport(Lib)] public static unsafe partial int ragstore_add_many(IntPtr store, float** blocks, long* blockRows, int nBlocks, int rowDim,
+                                                                               uint flags, out long firstRow);
         // store image on disk (N3)
         [LibraryImport(Lib, StringMarshalling = StringMarshalling.Utf8)] public static partial int ragstore_save(IntPtr store, string path);
         [LibraryImport(Lib, StringMarshalling = StringMarshalling.Utf8)] public static partial int ragstore_load(string path, int device, long capacityRows, out IntPtr store);
