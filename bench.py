@@ -338,14 +338,18 @@ def measure_workload(name, args, torch, dist, rb, native, rank, world, dev, do_e
         res["e2e_top_idx"] = [int(x) for x in idx[0, :found[0]]]
     elif do_e2e and nqb == 1:
         # sharded: host query -> every rank's device, hits back to the host on every rank
-        hq = d_q.cpu()
+        hq_rows = [np.ascontiguousarray(r) for r in d_q.cpu().numpy()]
+        host_path = sh.peer is not None and dim <= 1024
         hq_pin = torch.empty(dim, dtype=torch.float32).pin_memory()
         h_idx = torch.empty(k, dtype=torch.int64).pin_memory()
         h_sc = torch.empty(k, dtype=torch.float64).pin_memory()
         d_q1 = torch.empty(dim, dtype=torch.float32, device="cuda")
         with torch.cuda.stream(ts):
             def e2e_step(i):
-                hq_pin.copy_(hq[i % n_q])
+                if host_path:
+                    sh.search_host(hq_rows[i % n_q], k)     # query in the kernel parameters, hits written to page-locked memory
+                    return
+                hq_pin.copy_(torch.from_numpy(hq_rows[i % n_q]))
                 d_q1.copy_(hq_pin, non_blocking=True)
                 sh.search_device(d_q1, k)
                 h_idx.copy_(d_idx, non_blocking=True)
@@ -363,7 +367,9 @@ def measure_workload(name, args, torch, dist, rb, native, rank, world, dev, do_e
             dt = float(dt.item())
         res["e2e"] = {"value": rows * world * n_e2e / dt, "unit": "vectors/s", "h2d_bytes_per_step": dim * 4,
                       "d2h_bytes_per_step": k * 16, "ms_per_step": dt / n_e2e * 1e3, "steps": n_e2e,
-                      "api": "host query -> ShardedSearcher.search_device (shard scan + exchange + merge) -> host hits, per rank"}
+                      "api": ("ShardedSearcher.search_host: ragstore_search_shard_hostq (query in the kernel parameters) + ragstore_exchange_merge writing "
+                              "into page-locked host memory; two launches and one stream wait per rank") if host_path else
+                             "host query -> ShardedSearcher.search_device (shard scan + exchange + merge) -> host hits, per rank"}
 
     # CPU baseline + parity check against the oracle (rank 0, N = 1 only)
     if do_cpu and world == 1 and rank == 0:

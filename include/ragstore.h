@@ -172,6 +172,13 @@ RAGSTORE_API int ragstore_search_device(ragstore_t* s, const float* d_queries, i
 RAGSTORE_API int ragstore_search_shard_device(ragstore_t* s, const float* d_query, int top_k,
                                               ragstore_cand* d_out, int32_t* d_flags, void* stream);
 
+/* Step 1 with the query still in HOST memory (any host memory; read before the call returns): it travels inside the
+ * kernel's parameter block, so a rank that receives the query from its host process needs no host->device copy in
+ * front of the launch.  dim <= 1024.  With the outputs of ragstore_exchange_merge pointed at page-locked host memory
+ * a sharded query is two launches and one stream wait per rank, end to end. */
+RAGSTORE_API int ragstore_search_shard_hostq(ragstore_t* s, const float* h_query, int top_k,
+                                             ragstore_cand* d_out, int32_t* d_flags, void* stream);
+
 /* Batched form of step 1: n_queries queries at once (tensor-core path when eligible); d_out holds
  * n_queries x max(1,top_k) records, query-major. */
 RAGSTORE_API int ragstore_search_shard_batch_device(ragstore_t* s, const float* d_queries, int n_queries,

@@ -654,9 +654,13 @@ int ragstore_search_device(ragstore_t* s, const float* d_queries, int n_queries,
     return RAGSTORE_OK;
 }
 
-int ragstore_search_shard_device(ragstore_t* s, const float* d_query, int top_k, ragstore_cand* d_out,
-                                 int32_t* d_flags, void* stream) {
-    if (!s || !d_query || !d_out) return fail(RAGSTORE_ERR_INVALID, "ragstore_search_shard_device: null argument");
+// one shard's rescored top-k as records; the query comes from device memory (d_query) or, inside the kernel's
+// parameter block, from host memory (h_query)
+static int search_shard_impl(ragstore_t* s, const float* d_query, const float* h_query, int top_k, ragstore_cand* d_out,
+                             int32_t* d_flags, void* stream) {
+    if (!s || (!d_query && !h_query) || !d_out) return fail(RAGSTORE_ERR_INVALID, "ragstore_search_shard: null argument");
+    if (h_query && s->dim > kParamQueryMax)
+        return fail(RAGSTORE_ERR_UNSUPPORTED, "ragstore_search_shard_hostq: rows above 1024 elements need the query in device memory");
     DeviceGuard g(s->device);
     cudaStream_t st = stream ? static_cast<cudaStream_t>(stream) : s->dev_stream;
     const int64_t n = s->count.load(std::memory_order_acquire);
@@ -679,9 +683,21 @@ int ragstore_search_shard_device(ragstore_t* s, const float* d_query, int top_k,
     a.out_cand = d_out;
     a.cand_slots = req;
     s->n_scan_launches.fetch_add(1, std::memory_order_relaxed);
-    const int rc = launch_scan(a, st);
+    const int rc = launch_scan(a, st, h_query);
     if (rc) return fail(RAGSTORE_ERR_CUDA, "scan kernel launch", cudaGetErrorString(static_cast<cudaError_t>(rc)));
     return RAGSTORE_OK;
+}
+
+int ragstore_search_shard_device(ragstore_t* s, const float* d_query, int top_k, ragstore_cand* d_out,
+                                 int32_t* d_flags, void* stream) {
+    if (!d_query) return fail(RAGSTORE_ERR_INVALID, "ragstore_search_shard_device: null argument");
+    return search_shard_impl(s, d_query, nullptr, top_k, d_out, d_flags, stream);
+}
+
+int ragstore_search_shard_hostq(ragstore_t* s, const float* h_query, int top_k, ragstore_cand* d_out,
+                                int32_t* d_flags, void* stream) {
+    if (!h_query) return fail(RAGSTORE_ERR_INVALID, "ragstore_search_shard_hostq: null argument");
+    return search_shard_impl(s, nullptr, h_query, top_k, d_out, d_flags, stream);
 }
 
 int ragstore_search_shard_batch_device(ragstore_t* s, const float* d_queries, int n_queries, int top_k, ragstore_cand* d_out,

@@ -57,6 +57,7 @@ def lib():
             "ragstore_set_coalescing": (C.c_int, [vp, C.c_int, C.c_int]),
             "ragstore_search_device": (C.c_int, [vp, vp, C.c_int, C.c_int, vp, vp, vp, vp, vp]),
             "ragstore_search_shard_device": (C.c_int, [vp, vp, C.c_int, vp, vp, vp]),
+            "ragstore_search_shard_hostq": (C.c_int, [vp, vp, C.c_int, vp, vp, vp]),
             "ragstore_set_row_blocking": (C.c_int, [vp, C.c_int64, C.c_int, C.c_int]),
             "ragstore_search_shard_batch_device": (C.c_int, [vp, vp, C.c_int, C.c_int, vp, vp, vp]),
             "ragstore_merge_shards_batch_device": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, vp, vp, C.c_int, vp]),
@@ -266,6 +267,11 @@ class RagStore:
 
     def search_shard_device(self, d_query, top_k: int, d_cand, d_flags=None, stream: int = 0):
         check(lib().ragstore_search_shard_device(self._h, _ptr(d_query), int(top_k), _ptr(d_cand), _ptr(d_flags), C.c_void_p(stream)))
+
+    def search_shard_hostq(self, h_query: np.ndarray, top_k: int, d_cand, d_flags=None, stream: int = 0):
+        """Shard search with the query in host memory (C-contiguous float32 of `dim` values); it rides in the kernel parameters."""
+        check(lib().ragstore_search_shard_hostq(self._h, C.c_void_p(h_query.ctypes.data), int(top_k), _ptr(d_cand), _ptr(d_flags),
+                                                C.c_void_p(stream)))
 
 
 def search_noalloc(d_matrix, d_rnorm, n_rows: int, dim: int, dtype: int, d_query, top_k: int, d_idx, d_score, d_found,

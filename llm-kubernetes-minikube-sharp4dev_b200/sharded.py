@@ -117,6 +117,35 @@ class ShardedSearcher:
         self.native.merge_shards_device(src, self.world, req, k, self.d_idx, self.d_score, self.d_found,
                                         device=self.device, stream=stream)
 
+    def search_host(self, h_query, k: int):
+        """Host query in, host hits out (what a host process serving requests does): the query rides in the scan
+        kernel's parameter block, the exchange kernel writes the merged hits into page-locked host memory; one stream
+        wait.  Needs the peer-memory exchange (or world == 1) and dim <= 1024.  Returns (idx, score) numpy views that
+        the next call overwrites."""
+        torch = self.torch
+        req = max(1, int(k))
+        if req > self.max_k:
+            raise ValueError("k above max_k")
+        if self.peer is None:
+            raise RuntimeError("search_host needs exchange='p2p'")
+        if getattr(self, "_h_idx", None) is None:
+            self._h_idx = torch.zeros(self.max_k, dtype=torch.int64).pin_memory()
+            self._h_score = torch.zeros(self.max_k, dtype=torch.float64).pin_memory()
+            self._h_meta = torch.zeros(2, dtype=torch.int32).pin_memory()          # [found, status]
+            self._h_np = (self._h_idx.numpy(), self._h_score.numpy(), self._h_meta.numpy())   # views of the same memory
+            self._h_ptr = (self._h_idx.data_ptr(), self._h_score.data_ptr(), self._h_meta.data_ptr(), self._h_meta.data_ptr() + 4)
+        cur = torch.cuda.current_stream()
+        stream = cur.cuda_stream or 1
+        p_idx, p_sc, p_found, p_status = self._h_ptr
+        self.store.search_shard_hostq(h_query, k, self.d_cand, self.d_flags, stream=stream)
+        self.peer.merge(self.d_cand, 1, req, k, p_idx, p_sc, p_found, p_status, stream=stream)
+        cur.synchronize()
+        np_idx, np_sc, np_meta = self._h_np
+        if np_meta[1] != 0:
+            raise RuntimeError("peer exchange timed out: a rank did not publish its hits within 5 s")
+        n = int(np_meta[0])
+        return np_idx[:n], np_sc[:n]
+
     def search_batch_device(self, d_queries, n_queries: int, k: int):
         """Batched form (tensor-core path on each shard): returns device tensors (idx [nq, k], score, found)."""
         torch = self.torch

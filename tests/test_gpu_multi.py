@@ -34,6 +34,11 @@ def _worker(rank, world, port, n_total, d, k, nq, out_dir):
             for i in range(6):                      # consecutive calls: both inbox slots, several times
                 idx, sc = sh.search(qs[i], k)
                 single.append((idx.copy(), sc.copy()))
+            if mode == "p2p":                       # host query in (kernel parameters), host hits out (page-locked memory)
+                hq = np.ascontiguousarray(qs.cpu().numpy())
+                for i in range(6):
+                    hidx, hsc = sh.search_host(hq[i], k)
+                    assert np.array_equal(hidx, single[i][0]) and np.array_equal(hsc.view(np.uint64), single[i][1].view(np.uint64))
             bi, bs, bf = sh.search_batch_device(qs, nq, k)
             torch.cuda.synchronize()
             assert int(sh.d_status.abs().sum().item()) == 0
