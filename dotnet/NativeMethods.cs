@@ -39,6 +39,7 @@ namespace Minimal_RAG.Helpers
         // row-sharded hosts (one process per GPU): per-shard hits, then the peer-memory exchange + merge in one launch
         [LibraryImport(Lib)] public static partial int ragstore_set_row_base(IntPtr store, long rowBase);
         [LibraryImport(Lib)] public static partial int ragstore_search_shard_device(IntPtr store, IntPtr dQuery, int topK, IntPtr dOut, IntPtr dFlags, IntPtr stream);
+        [LibraryImport(Lib)] public static unsafe partial int ragstore_search_shard_hostq(IntPtr store, float* hostQuery, int topK, IntPtr dOut, IntPtr dFlags, IntPtr stream);
         [LibraryImport(Lib)] public static unsafe partial int ragstore_exchange_create(int device, int world, int rank, int maxRecords, int maxQueries,
                                                                                       out IntPtr exchange, byte* handleOut /* 64 bytes */);
         [LibraryImport(Lib)] public static unsafe partial int ragstore_exchange_connect(IntPtr exchange, byte* allHandles /* world x 64 bytes, rank order */);
