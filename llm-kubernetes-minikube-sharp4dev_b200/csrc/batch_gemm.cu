@@ -162,7 +162,6 @@ struct BatchArgs {
     int mblocks;       // 1 or 2 blocks of 128 queries
     int nkb;           // k-blocks of 128 bytes (32 fp32 / 64 bf16) per row
     const float* rnorm; // per-row reciprocal norms (bf16 stores: applied to the tensor-core dot products)
-    int c_step, c_off;  // corpus tensor-map coordinate of k-block kb: kb * c_step + c_off (elements of the map's type)
     uint64_t* glists;  // [nq][n_ctas][kBatchKp] candidate keys, written by this kernel
     int debug;         // profiling experiments: 1 = epilogue drains without scanning, 2 = no MMA issue
     int tile_stride;   // 1 = every tile; s > 1 = the sampling pass: tiles 0, s, 2s, ...
@@ -423,7 +422,7 @@ batch_score_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
                     uint8_t* st = smem + static_cast<size_t>(s) * L.stage_bytes;
                     mbar_arrive_expect_tx(full + s, tx);
                     tma_load_2d_mc(st + q_off, &tmap_q, full + s, kb * KE, static_cast<int>(crank) * q_rows, cmask);
-                    tma_load_2d(st + MB * kOperandBytes, &tmap_c, full + s, kb * a.c_step + a.c_off, row0);
+                    tma_load_2d(st + MB * kOperandBytes, &tmap_c, full + s, kb * KE, row0);
                     if (++s == n_stages) {
                         s = 0;
                         ph ^= 1u;
@@ -683,7 +682,7 @@ batch_score_kernel_2sm(const __grid_constant__ CUtensorMap tmap_q, const __grid_
                     // per-stage remote arrive with cluster-scope release semantics cost the peer ~1500 cycles per stage.)
                     if (leader) mbar_arrive_expect_tx(full + s, 4u * kOperandBytes);
                     tma_load_2d_2sm(st, &tmap_q, full + s, kb * KE, static_cast<int>(crank) * kBM);
-                    tma_load_2d_2sm(st + kOperandBytes, &tmap_c, full + s, kb * a.c_step + a.c_off, row0);
+                    tma_load_2d_2sm(st + kOperandBytes, &tmap_c, full + s, kb * KE, row0);
                     if (++s == n_stages) {
                         s = 0;
                         ph ^= 1u;
@@ -912,22 +911,6 @@ static bool make_map(CUtensorMap* m, const void* base, uint64_t rows, uint64_t l
                CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
-// The UPPER HALVES of a row-major fp32 matrix as a bf16 matrix: the map sees 16-bit elements and walks them with an
-// element stride of 2; coordinate 1 of a row is the upper half of its first float (little endian).  What lands in
-// shared memory is each value truncated to bf16 -- 64 of them per 128-byte swizzle row -- so the tensor cores can run
-// kind::f16 on an fp32 store without a second copy of the corpus.
-static bool make_map_upper_halves(CUtensorMap* m, const void* base, uint64_t rows, uint64_t ld, uint32_t box_rows) {
-    PFN_encodeTiled enc = encode_fn();
-    if (!enc) return false;
-    const cuuint64_t dims[2] = {2 * ld, rows};
-    const cuuint64_t strides[1] = {ld * 4};
-    const cuuint32_t box[2] = {128, box_rows};
-    const cuuint32_t estr[2] = {2, 1};
-    return enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
-               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
-}
-
 size_t batch_scratch_bytes(int sm_count) {
     return sizeof(uint64_t) * size_t(kBatchMaxQ) * size_t(sm_count) * kBatchKp   // candidate lists
            + sizeof(float) * size_t(kBatchMaxQ) * size_t(kBatchMaxLd)           // normalised query operand
@@ -936,10 +919,7 @@ size_t batch_scratch_bytes(int sm_count) {
 
 int launch_batch_search(const BatchSearchArgs& b, cudaStream_t stream) {
     const ScanArgs& s = b.scan;
-    const bool bf_store = s.dtype == RAGSTORE_BF16;
-    const char* tr_env = std::getenv("RAGSTORE_BATCH_TRUNC");
-    const bool trunc = !bf_store && tr_env && tr_env[0] == '1' && s.ld % 8 == 0;   // experiment: bf16 operands from fp32 upper halves
-    const bool bf = bf_store || trunc;   // operand type of the tensor-core pass
+    const bool bf = s.dtype == RAGSTORE_BF16;
     if ((bf && s.ld % 8 != 0) || b.nq < 1 || b.nq > kBatchMaxQ || s.ld > kBatchMaxLd || s.kp != kBatchKp ||
         s.n_rows < 1 || s.n_rows >= 0x7FFF0000ll)
         return static_cast<int>(cudaErrorInvalidValue);
@@ -960,8 +940,7 @@ int launch_batch_search(const BatchSearchArgs& b, cudaStream_t stream) {
     const char* mode_env = std::getenv("RAGSTORE_BATCH_2SM");
     const bool pair_maps = mblocks == 2 && !(mode_env && mode_env[0] == '0');
     if (!make_map(&map_q, qhat, static_cast<uint64_t>(nq_pad), static_cast<uint64_t>(s.ld), pair_maps ? kBM : nq_pad / kCluster, bf) ||
-        !(trunc ? make_map_upper_halves(&map_c, s.mat, static_cast<uint64_t>(s.n_rows), static_cast<uint64_t>(s.ld), pair_maps ? 128 : kBN)
-                : make_map(&map_c, s.mat, static_cast<uint64_t>(s.n_rows), static_cast<uint64_t>(s.ld), pair_maps ? 128 : kBN, bf)))
+        !make_map(&map_c, s.mat, static_cast<uint64_t>(s.n_rows), static_cast<uint64_t>(s.ld), pair_maps ? 128 : kBN, bf))
         return static_cast<int>(cudaErrorNotSupported);
 
     const char* mode = std::getenv("RAGSTORE_BATCH_2SM");
@@ -993,8 +972,6 @@ int launch_batch_search(const BatchSearchArgs& b, cudaStream_t stream) {
     a.mblocks = mblocks;
     a.nkb = bf ? (s.ld + 63) / 64 : (s.ld + 31) / 32;
     a.rnorm = s.rnorm;
-    a.c_step = trunc ? 128 : (bf ? 64 : 32);
-    a.c_off = trunc ? 1 : 0;
     a.glists = glists;
     a.debug = std::getenv("RAGSTORE_BATCH_DEBUG") ? atoi(std::getenv("RAGSTORE_BATCH_DEBUG")) : 0;
     const int64_t n_tiles = (s.n_rows + kBN - 1) / kBN;
@@ -1061,7 +1038,7 @@ int launch_batch_search(const BatchSearchArgs& b, cudaStream_t stream) {
     f.thr0 = thr_used;
     f.nlists = nlists;
     f.out_stride = b.out_stride;
-    f.row_bytes = static_cast<uint32_t>(s.ld) * (bf_store ? 2u : 4u);
+    f.row_bytes = static_cast<uint32_t>(s.ld) * (bf ? 2u : 4u);
     f.qpad = static_cast<uint32_t>(s.ld);
     const uint32_t fixed = f.qpad * 4u + sizeof(uint64_t) * 2u * kConsumerWarps * s.kp + sizeof(ScanMisc) + 256u;
     uint32_t ring = 200u * 1024u - fixed;
@@ -1071,7 +1048,7 @@ int launch_batch_search(const BatchSearchArgs& b, cudaStream_t stream) {
     if (ring < lists_need && lists_need + fixed <= 200u * 1024u) ring = lists_need;
     f.ring_bytes = (ring + 127u) & ~127u;
     const size_t fin_smem = f.ring_bytes + fixed;
-    if (bf_store) {
+    if (bf) {
         e = cudaFuncSetAttribute(batch_finalize_kernel<uint16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
         if (e != cudaSuccess) return static_cast<int>(e);
         batch_finalize_kernel<uint16_t><<<b.nq, kScanThreads, fin_smem, stream>>>(f);

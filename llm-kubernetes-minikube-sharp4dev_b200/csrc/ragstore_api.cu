@@ -237,11 +237,7 @@ ScanArgs base_args(const ragstore* s, int64_t n, int take, int kp) {
 // (<= 2^-9 relative per element -> <= 2^-9 on a cosine, Cauchy-Schwarz) and the fp32 accumulation remain; when
 // exact scores come from fp32 originals (sidecar) the stored image itself is another 2^-8 away, as in base_args.
 float batch_eps(const ragstore* s) {
-    if (s->dtype == RAGSTORE_F32) {
-        const char* tr = std::getenv("RAGSTORE_BATCH_TRUNC");
-        if (tr && tr[0] == '1' && s->ld % 8 == 0) return 6.0e-3f;   // experiment: truncated-bf16 corpus + bf16 query
-        return 2.1e-3f;
-    }
+    if (s->dtype == RAGSTORE_F32) return 2.1e-3f;
     float e = 1.953125e-3f + static_cast<float>(s->ld) * 2.4e-7f + 2e-5f;
     if (s->raw_used > 0) e += 3.90625e-3f;
     return e;
