@@ -36,7 +36,11 @@ def _seq_sum64(prod32: np.ndarray) -> np.ndarray:
     np.sum is pairwise and would NOT match the reference)."""
     if prod32.shape[1] == 0:
         return np.zeros(prod32.shape[0], dtype=np.float64)
-    return np.cumsum(prod32.astype(np.float64), axis=1)[:, -1]
+    # `double dot = 0; dot += p0; ...` (:127-132): the accumulator STARTS at +0.0, so a run of -0.0 products sums to
+    # +0.0 (np.cumsum alone would start at p0 and keep -0.0); adding +0.0 afterwards restores exactly that:
+    # x + (+0.0) == x for every x except -0.0, which becomes +0.0 -- and a sequential sum can only end at -0.0 when
+    # every term was -0.0.
+    return np.cumsum(prod32.astype(np.float64), axis=1)[:, -1] + 0.0
 
 
 def score_all(rows: np.ndarray, q: np.ndarray, chunk: int = 4096) -> np.ndarray:

@@ -723,3 +723,31 @@ def test_add_many_and_reserve_rows_equal_repeated_adds():
     assert np.array_equal(ra[0], rb_[0]) and np.array_equal(ra[1].view(np.uint64), rb_[1].view(np.uint64))
     eidx, esc = oc.query(np.concatenate(blocks), q, k)
     assert list(ra[0][0]) == list(eidx) and np.array_equal(ra[1][0].view(np.uint64), esc.view(np.uint64))
+
+
+@pytest.mark.parametrize("seed", range(16))
+def test_wild_values_match_oracle(seed):
+    """Rows and queries far from unit length, spanning 50 orders of magnitude, with zeros, duplicates, denormals and a
+    few NaN / inf entries: indices and scores must still be the oracle's, bit for bit (sidecar keeps the originals)."""
+    rng = np.random.default_rng(1000 + seed)
+    n, d, k = int(rng.integers(40, 400)), int(rng.integers(3, 70)), int(rng.integers(1, 40))
+    if seed >= 12:                                                      # many CTAs, real nomination
+        n, d = int(rng.integers(5000, 20000)), int(rng.integers(64, 200))
+    rows = rng.standard_normal((n, d)).astype(np.float32)
+    rows *= (10.0 ** rng.uniform(-25, 18, size=(n, 1))).astype(np.float32)
+    rows[rng.integers(0, n, 5)] = 0.0                                   # zero rows
+    rows[rng.integers(0, n)] = rows[rng.integers(0, n)]                 # a duplicate
+    rows[rng.integers(0, n), rng.integers(0, d)] = np.float32(1e-42)    # a denormal element
+    if seed % 3 == 0:
+        rows[rng.integers(0, n), rng.integers(0, d)] = np.nan
+    if seed % 4 == 0:
+        rows[rng.integers(0, n), rng.integers(0, d)] = np.inf
+    q = (rng.standard_normal(d) * 10.0 ** rng.uniform(-10, 10)).astype(np.float32)
+    with np.errstate(all="ignore"):
+        eidx, esc = oc.query(rows, q, k, n_threads=2)
+    idx, sc, flags, info = _search(rows, q, k)
+    assert len(idx) == len(eidx)
+    same_scores = all((a == b) or (math.isnan(a) and math.isnan(b)) for a, b in zip(sc, esc))
+    assert same_scores, (sc, esc)
+    # rows with equal (or NaN) scores may only be ordered by index, like the oracle
+    assert list(idx) == list(eidx)

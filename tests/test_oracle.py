@@ -99,3 +99,46 @@ def test_unit_rows_survive_renormalisation_exactly():
     rows = oc.synth_rows(0, 20000, 768, 1234)
     n2 = (rows.astype(np.float64) ** 2).sum(axis=1)
     assert np.all((1.0 / np.sqrt(n2)).astype(np.float32) == np.float32(1.0))
+
+
+# ---- property fuzz: the two restatements (C, numpy) and the plain Python loop must agree bit for bit on arbitrary
+# float32 inputs (specials included), and the selection must have the reference's shape (RagIndex.cs:64-66)
+from hypothesis import given, settings, strategies as hst  # noqa: E402
+
+_f32 = hst.one_of(
+    hst.floats(width=32, allow_nan=True, allow_infinity=True),
+    hst.sampled_from([0.0, -0.0, 1.0, -1.0, 1e-45, -1e-45, 1.17549435e-38, 3.4028235e38, 1e-20, 1e20, 0.1, 1 / 3]))
+
+
+@settings(max_examples=150, deadline=None)
+@given(hst.data())
+def test_fuzz_restatements_agree_and_selection_is_well_formed(data):
+    d = data.draw(hst.integers(1, 24))
+    n = data.draw(hst.integers(0, 12))
+    k = data.draw(hst.integers(-2, 16))
+    flat = data.draw(hst.lists(_f32, min_size=(n + 1) * d, max_size=(n + 1) * d))
+    arr = np.asarray(flat, dtype=np.float32).reshape(n + 1, d)
+    q, rows = arr[0], np.ascontiguousarray(arr[1:])
+    with np.errstate(all="ignore"):
+        ci, cs = oc.query(rows, q, k)
+        ni, ns = onp.query(rows, q, k)
+    assert list(ci) == list(ni)
+    assert np.array_equal(np.asarray(cs).view(np.uint64) | 0, np.asarray(ns).view(np.uint64) | 0) or \
+        all((a == b and math.copysign(1, a) == math.copysign(1, b)) or (math.isnan(a) and math.isnan(b)) for a, b in zip(cs, ns))
+    assert len(ci) == min(n, max(1, k))
+    with np.errstate(all="ignore"):
+        full = [onp.cosine_py(q, rows[r]) for r in range(n)]
+    for r, s in zip(ci, cs):
+        assert (full[r] == s) or (math.isnan(full[r]) and math.isnan(s))
+    # order: score descending under double.CompareTo (NaN below everything, +0 == -0), ties by lower row index
+    def key(r):
+        s = full[r]
+        return (0, 0.0, r) if math.isnan(s) else (1, s, -r)
+    order = sorted(range(n), key=key, reverse=True)
+    def same_rank(a, b):
+        return (math.isnan(full[a]) and math.isnan(full[b])) or full[a] == full[b]
+    for pos, r in enumerate(ci):
+        assert same_rank(r, order[pos]), (pos, r, order[pos])
+    for a, b in zip(ci, ci[1:]):
+        if same_rank(a, b):
+            assert a < b
