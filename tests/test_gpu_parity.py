@@ -751,3 +751,31 @@ def test_wild_values_match_oracle(seed):
     assert same_scores, (sc, esc)
     # rows with equal (or NaN) scores may only be ordered by index, like the oracle
     assert list(idx) == list(eidx)
+
+
+@pytest.mark.parametrize("dtype", [0, 1])
+def test_wild_values_through_the_batched_path(dtype):
+    """The same kind of input through the tensor-core path (32 queries at once): rows of wildly different lengths are
+    normalised at ingest, originals kept in the sidecar, so the hits must equal the single-query path's, which the test
+    above pins to the oracle."""
+    rng = np.random.default_rng(77 + dtype)
+    n, d, nq, k = 20000, 128, 32, 10
+    rows = rng.standard_normal((n, d)).astype(np.float32)
+    rows *= (10.0 ** rng.uniform(-12, 12, size=(n, 1))).astype(np.float32)
+    rows[rng.integers(0, n, 20)] = 0.0
+    rows[100] = rows[7]
+    qs = (rng.standard_normal((nq, d)) * 10.0 ** rng.uniform(-5, 5, size=(nq, 1))).astype(np.float32)
+    flags_create = rb.RAGSTORE_CREATE_SIDECAR_ON
+    with rb.RagStore(d, n, rb.RAGSTORE_BF16 if dtype else rb.RAGSTORE_F32, 0, flags_create) as st:
+        st.add(rows)
+        idx, sc, found, flags = st.search(qs, k)
+        assert st.info()["batch_launches"] >= 1
+        for i in range(nq):
+            i1, s1, f1, _ = st.search(qs[i], k)
+            assert np.array_equal(idx[i], i1[0]), i
+            assert np.array_equal(sc[i].view(np.uint64), s1[0].view(np.uint64)), i
+    for i in range(0, nq, 5):
+        with np.errstate(all="ignore"):
+            eidx, esc = oc.query(rows, qs[i], k, n_threads=4)
+        assert list(idx[i]) == list(eidx), i
+        assert np.array_equal(sc[i].view(np.uint64), esc.view(np.uint64)), i
