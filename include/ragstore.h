@@ -150,7 +150,7 @@ RAGSTORE_API int ragstore_search(ragstore_t* s, const float* queries, int n_quer
 /* the reference serves /rag/search and /agent_rag concurrently from one singleton index
  * (Program.cs:43,62,106), each request scanning the whole list on its own thread-pool thread.  This entry
  * point takes ONE query per call, like QueryAsync, but callers that arrive within a short window are
- * answered by one sweep of the corpus (the batched tensor-core path from 16 callers up).  Same results as
+ * answered by one sweep of the corpus (the batched tensor-core path, from 2-3 callers up).  Same results as
  * ragstore_search; thread-safe; blocks until this caller's hits are ready. */
 RAGSTORE_API int ragstore_search_coalesced(ragstore_t* s, const float* query, int query_dim, int top_k,
                                            int64_t* out_idx, double* out_score, int32_t* out_found,

@@ -12,6 +12,7 @@
 #include <cstring>
 #include <limits>
 #include <mutex>
+#include <cmath>
 #include <string>
 #include <vector>
 
@@ -243,9 +244,25 @@ float batch_eps(const ragstore* s) {
     return e;
 }
 
+// nq scans (one corpus sweep each + ~28 us of fixed cost) against one tensor-core batch (~62 us of fixed cost in its
+// five launches, one sweep, and the threshold pass over 1/stride of the corpus -- a whole second sweep on corpora too
+// small to sample).  Measured on B200 (tools/quick_smallbatch.py): 10k x 768: scans 29 us per query, batch 67-77 us for
+// 2..15 queries; 4M x 768: 15 queries 27.2 ms as scans, 1.91 ms as one batch.  The batch wins from 2 queries on
+// corpora of ~1 GB up and from 3 on small ones.  RAGSTORE_BATCH_MINQ=<n> replaces the model by "at least n queries".
 bool batch_eligible(const ragstore* s, int64_t n, int nq, int kp) {
-    return nq >= kBatchMinQ && n >= kBatchMinRows && kp == 32 && s->ld <= kBatchMaxLd &&
-           (s->dtype == RAGSTORE_F32 || s->ld % 8 == 0);
+    if (nq < kBatchMinQ || n < kBatchMinRows || kp != 32 || s->ld > kBatchMaxLd || (s->dtype != RAGSTORE_F32 && s->ld % 8 != 0))
+        return false;
+    static const int forced_min = [] {
+        const char* e = std::getenv("RAGSTORE_BATCH_MINQ");
+        return e ? atoi(e) : 0;
+    }();
+    if (forced_min > 0) return nq >= forced_min;
+    const double bytes = static_cast<double>(n) * s->ld * (s->dtype == RAGSTORE_F32 ? 4.0 : 2.0);
+    const double t_scan = 28e-6 + bytes / 6.6e12;
+    const double tiles_per_cta = static_cast<double>(n) / 256.0 / (s->sm_count > 0 ? s->sm_count : 148);
+    const double stride = std::min(16.0, std::max(1.0, std::floor(tiles_per_cta / 2.0)));
+    const double t_batch = 62e-6 + (1.0 + 1.0 / stride) * bytes / (nq <= 128 ? 6.2e12 : 4.5e12);
+    return nq * t_scan > t_batch;
 }
 
 // One tensor-core launch for up to kBatchMaxQ queries (outputs laid out with `stride` hits per query).

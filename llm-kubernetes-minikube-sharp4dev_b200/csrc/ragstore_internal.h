@@ -81,7 +81,7 @@ int launch_normalise(const NormaliseArgs& a, cudaStream_t stream);
 
 // ---- batched (tensor-core) path, batch_gemm.cu
 constexpr int kBatchMaxQ = 256;    // queries per launch (two 128-row MMA blocks)
-constexpr int kBatchMinQ = 16;     // below this the per-query scan kernel is used
+constexpr int kBatchMinQ = 2;      // one query always takes the scan kernel; from 2 up a cost model decides (ragstore_api.cu)
 constexpr int kBatchMaxLd = 4096;  // padded row length covered by the query operand buffer
 constexpr int64_t kBatchMinRows = 4096;
 struct BatchSearchArgs {

@@ -779,3 +779,21 @@ def test_wild_values_through_the_batched_path(dtype):
             eidx, esc = oc.query(rows, qs[i], k, n_threads=4)
         assert list(idx[i]) == list(eidx), i
         assert np.array_equal(sc[i].view(np.uint64), esc.view(np.uint64)), i
+
+
+@pytest.mark.parametrize("n,nq", [(300000, 2), (20000, 3), (20000, 7)])
+def test_few_queries_at_once_take_one_sweep(n, nq):
+    """From 2-3 queries up one tensor-core sweep is cheaper than a scan per query (cost model in batch_eligible); the hits
+    stay the oracle's."""
+    d, k = 256, 10
+    rows = oc.synth_rows(0, n, d, 1234)
+    qs = oc.synth_rows(0, nq, d, 5678)
+    with rb.RagStore(d, n) as st:
+        st.add(rows)
+        idx, sc, found, flags = st.search(qs, k)
+        info = st.info()
+    assert info["batch_launches"] >= 1
+    for i in range(nq):
+        eidx, esc = oc.query(rows, qs[i], k, n_threads=4)
+        assert list(idx[i]) == list(eidx), i
+        assert np.array_equal(sc[i].view(np.uint64), esc.view(np.uint64)), i
