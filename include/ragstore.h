@@ -155,7 +155,8 @@ RAGSTORE_API int ragstore_search(ragstore_t* s, const float* queries, int n_quer
 RAGSTORE_API int ragstore_search_coalesced(ragstore_t* s, const float* query, int query_dim, int top_k,
                                            int64_t* out_idx, double* out_score, int32_t* out_found,
                                            int32_t* out_flags);
-/* window_us: how long the first caller waits for company (default 150); max_batch: queries per sweep. */
+/* window_us: how long every batch's first caller waits for company (default 0: nobody waits; callers that arrive while
+ * a batch is executing form the next batch by themselves).  max_batch: queries per sweep (default 256). */
 RAGSTORE_API int ragstore_set_coalescing(ragstore_t* s, int window_us, int max_batch);
 
 /* Same work with every buffer already in device memory and no host synchronisation: enqueues on

@@ -149,7 +149,7 @@ struct ragstore {
     std::condition_variable co_cv;
     std::vector<Pending*> co_queue;
     bool co_leader = false;
-    int co_window_us = 150, co_max_batch = 256;
+    int co_window_us = 0, co_max_batch = 256;
     ScanScratch dev_scratch{};
     uint8_t* dev_batch_scratch = nullptr;
     std::vector<SearchCtx> ctxs;
@@ -1145,9 +1145,14 @@ int ragstore_search_coalesced(ragstore_t* s, const float* query, int query_dim, 
     std::vector<double> sbuf;
     std::vector<int32_t> fbuf, gbuf;
     while (!s->co_queue.empty()) {
-        // give concurrent callers a short window to join the batch
-        const auto deadline = std::chrono::steady_clock::now() + std::chrono::microseconds(s->co_window_us);
-        s->co_cv.wait_until(lk, deadline, [&] { return static_cast<int>(s->co_queue.size()) >= s->co_max_batch; });
+        // Batches form by themselves: whoever arrives while a batch is executing is queued and taken, all together, by
+        // the next one, so by default nobody waits (a lone caller on an idle store runs at once).  A window set with
+        // ragstore_set_coalescing makes every batch's first caller wait that long for company: larger batches, at the
+        // price of that much latency (measured with 16 closed-loop clients on 10k x 768: 2.9 -> 10.3 queries per sweep).
+        if (s->co_window_us > 0) {
+            const auto deadline = std::chrono::steady_clock::now() + std::chrono::microseconds(s->co_window_us);
+            s->co_cv.wait_until(lk, deadline, [&] { return static_cast<int>(s->co_queue.size()) >= s->co_max_batch; });
+        }
         const int nb = std::min<int>(static_cast<int>(s->co_queue.size()), s->co_max_batch);
         std::vector<ragstore::Pending*> batch(s->co_queue.begin(), s->co_queue.begin() + nb);
         s->co_queue.erase(s->co_queue.begin(), s->co_queue.begin() + nb);
@@ -1160,7 +1165,7 @@ int ragstore_search_coalesced(ragstore_t* s, const float* query, int query_dim, 
         fbuf.resize(nb);
         gbuf.resize(nb);
         for (int i = 0; i < nb; ++i) memcpy(qbuf.data() + static_cast<size_t>(i) * s->dim, batch[i]->q, sizeof(float) * s->dim);
-        // one sweep of the corpus for the whole batch (tensor-core path from 16 queries up)
+        // one sweep of the corpus for the whole batch (tensor-core path from 2-3 queries up)
         const int rc = ragstore_search(s, qbuf.data(), nb, s->dim, kmax, ibuf.data(), sbuf.data(), fbuf.data(), gbuf.data());
         const std::string err = rc ? g_err : std::string();
         for (int i = 0; i < nb; ++i) {
