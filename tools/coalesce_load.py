@@ -39,7 +39,7 @@ def run(n, d, threads, seconds=1.0, window=None):
     i1 = st.info()
     total = sum(counts)
     sweeps = (i1["batch_launches"] - i0["batch_launches"]) + (i1["scan_launches"] - i0["scan_launches"])
-    print(f"n={n} d={d} threads={threads} window={'adaptive' if window is None else window}: {total/dt:.0f} queries/s, "
+    print(f"n={n} d={d} threads={threads} window={'default (0)' if window is None else window}: {total/dt:.0f} queries/s, "
           f"mean latency {sum(lat)/max(total,1)*1e3:.3f} ms, {total/max(sweeps,1):.1f} queries per corpus sweep", flush=True)
     st.close()
 
