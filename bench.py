@@ -46,6 +46,20 @@ BATCH_QUERIES = {"config3": 256}   # queries per step for the batched (tensor-co
 CORPUS_SEED, QUERY_SEED = 1234, 5678
 
 
+def cpu_model():
+    """(model name, logical cores) of the host the CPU baseline runs on."""
+    name = "unknown"
+    try:
+        with open("/proc/cpuinfo") as f:
+            for line in f:
+                if line.lower().startswith("model name"):
+                    name = line.split(":", 1)[1].strip()
+                    break
+    except OSError:
+        pass
+    return name, os.cpu_count()
+
+
 def measured_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -155,7 +169,7 @@ def run_reference(args, rank, world):
            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32 products, f64 accumulate",
            "data": "synthetic", "queries_per_s": args.steps / dt * (rows / sample_rows) ** -1 if rows else None,
            "config": {"workload": args.workload, "desc": desc, "rows_per_gpu": rows, "dim": dim, "top_k": k, "storage": dtype},
-           "cpu_baseline": {"value": v, "unit": "vectors/s", "cores": cores, "kind": "port",
+           "cpu_baseline": {"value": v, "unit": "vectors/s", "cores": cores, "kind": "port", "cpu": cpu_model()[0], "host_cores": cpu_model()[1],
                             "sample": f"one query per step over the first {sample_rows} rows of the workload, all {cores} host threads (row-parallel, per-row arithmetic unchanged)"},
            "e2e": {"value": v, "unit": "vectors/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
            "gpu_launches": 0,
@@ -383,7 +397,7 @@ def measure_workload(name, args, torch, dist, rb, native, rank, world, dev, do_e
             eidx, esc = oc.query(corpus, q, k, n_threads=1)
             t_used += time.perf_counter() - t0
             reps += 1
-        res["cpu_baseline"] = {"value": sample_rows * reps / t_used, "unit": "vectors/s", "cores": 1, "kind": "port",
+        res["cpu_baseline"] = {"value": sample_rows * reps / t_used, "unit": "vectors/s", "cores": 1, "kind": "port", "cpu": cpu_model()[0], "host_cores": cpu_model()[1],
                                "sample": f"{reps} single-thread queries over the first {sample_rows} rows of the workload "
                                          "(oracle/ragindex_oracle.c; the reference's LINQ pipeline is single-threaded)"}
         if sample_rows == rows:
