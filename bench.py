@@ -46,6 +46,28 @@ BATCH_QUERIES = {"config3": 256}   # queries per step for the batched (tensor-co
 CORPUS_SEED, QUERY_SEED = 1234, 5678
 
 
+_REAL_STDOUT = None
+
+
+def quiet_stdout():
+    """Libraries (NCCL prints its version banner from C) must not add lines to stdout: the contract is ONE JSON line.
+    File descriptor 1 is pointed at stderr for the run; emit() writes the line to the original stdout."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(obj):
+    line = (json.dumps(obj) + "\n").encode()
+    sys.stdout.flush()
+    if _REAL_STDOUT is None:
+        os.write(1, line)
+    else:
+        os.write(_REAL_STDOUT, line)
+
+
 def cpu_model():
     """(model name, logical cores) of the host the CPU baseline runs on."""
     name = "unknown"
@@ -174,7 +196,7 @@ def run_reference(args, rank, world):
            "e2e": {"value": v, "unit": "vectors/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
            "gpu_launches": 0,
            "note": "the reference is C# (net9.0); no dotnet toolchain here, so this arm times oracle/ragindex_oracle.c, the CPU restatement of RagIndex.cs:59-67,124-135"}
-    print(json.dumps(out), flush=True)
+    emit(out)
 
 
 def fill_store(st, native, torch, rows, dim, dtype, row0, chunk=1 << 18):
@@ -556,6 +578,7 @@ def main():
     ap.add_argument("--no-extra", action="store_true", help="skip the extra target10m / config1 measurements")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
+    quiet_stdout()
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -580,7 +603,7 @@ def main():
     if args.workload == "config5":
         out = run_streaming(args, torch, dist, rb, native, rank, world, local)
         if rank == 0:
-            print(json.dumps(out), flush=True)
+            emit(out)
         if world > 1:
             dist.destroy_process_group()
         return
@@ -654,7 +677,7 @@ def main():
             "k1_upload_normalise": k1,
             "extra": extra,
         }
-        print(json.dumps(out), flush=True)
+        emit(out)
     if world > 1:
         dist.destroy_process_group()
 
