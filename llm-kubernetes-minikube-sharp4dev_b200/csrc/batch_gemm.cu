@@ -1013,7 +1013,12 @@ int launch_batch_search(const BatchSearchArgs& b, cudaStream_t stream) {
             // small corpora: stride 1, i.e. the "sample" is a full (cheap: 4 registers per thread, no lists) sweep --
             // still far cheaper than filling cold lists column by column (~200 us per CTA for 256 queries)
             int stride = static_cast<int>(n_tiles / (2ll * nlists));   // every CTA (pair) samples >= 2 tiles when it can
-            stride = stride > 16 ? 16 : (stride < 1 ? 1 : stride);
+            static const int stride_max = [] {
+                const char* e = std::getenv("RAGSTORE_BATCH_STRIDE_MAX");   // experiments
+                const int v = e ? atoi(e) : 0;
+                return v >= 1 ? v : 32;
+            }();
+            stride = stride > stride_max ? stride_max : (stride < 1 ? 1 : stride);
             a.tile_stride = stride;
             a.sample = 1;
             e = launch_main();
