@@ -57,6 +57,9 @@ def kat():
     add("topk_negative_gives_one", [[1, 0], [0, 1]], [1, 0], -7, [0], [one], "Math.Max(1, topK) (:65)")
     add("topk_larger_than_n", [[1, 0], [0, 1]], [1, 0], 10, [0, 1], [one, 0.0], "Take(k) over N<k rows returns N")
     add("empty_index", [], [1, 0], 5, [], [], "no chunks -> empty list (Program.cs:74,117)")
+    add("negative_zero_products_sum_to_plus_zero", [[-1.0, -2.0], [3.0, 4.0]], [0.0, 0.0], 2, [0, 1], [0.0, 0.0],
+        "every product of row 0 is -0.0f, but the accumulator starts at +0.0 (`double dot = 0`, :127) and +0.0 + -0.0 = +0.0; "
+        "na = 0 -> +0.0 / 1e-9 = +0.0 with a POSITIVE sign for both rows (found by the fuzz test in tests/test_oracle.py)")
     add("zero_row_scores_plus_zero", [[0, 0], [1, 0], [0, 0]], [1, 0], 3, [1, 0, 2], [one, 0.0, 0.0],
         "0/(0+1e-9) = +0.0 exactly (:134)")
     add("zero_query", [[1, 0], [0, 1], [1, 1]], [0, 0], 2, [0, 1], [0.0, 0.0], "all scores +0.0 -> insertion order")
