@@ -7,13 +7,15 @@ on N B200s of one node.  One JSON line on stdout (rank 0).
 A "step" is one pass of the hot path over one batch of synthetic input: ONE query scored against the
 whole device-resident corpus shard(s) + fused top-k + exact rescoring (+ all-gather/merge for N > 1).
 Workloads (BASELINE.json configs):
-  config1   10k x 768 fp32, top-5       (the reference's own CPU-runnable case; L2-resident, latency-bound)
-  config2   1M  x 768 fp32, top-10      <- default at N = 1 (configs[1], the one `metric` is quoted on)
-  target10m 10M x 768 fp32, top-10      (north_star target; also measured as `extra.target10m` by default)
-  config4   bf16 x 768, top-100, 12.5M rows per GPU (100M over 8), NCCL all-gather merge
-  config3   10M x 1024 fp32, 256 queries per step, top-10: the tcgen05/TMEM tf32 GEMM path (single GPU)
+  target10m 10M x 768 fp32, top-10      <- default at N = 1: north_star's stated target (>= 85 % of HBM on 1 GPU)
+  config4   bf16 x 768, top-100, 12.5M rows per GPU (100M over 8)  <- default at N > 1: north_star's sharded corpus
+  config1   10k x 768 fp32, top-5       (the reference's own CPU-runnable case; L2-resident, latency-bound)   } measured as
+  config2   1M  x 768 fp32, top-10      (configs[1])                                                          } `extra.*`
+  config3   10M x 1024 fp32, 256 queries per step, top-10: the tcgen05/TMEM GEMM path (single GPU)            } at N = 1
   config5   streaming: 64k-row host batches appended while 1k-query batches are served (any N; block-cyclic)
 N > 1 runs the chosen workload row-sharded with the per-GPU shard size fixed (weak scaling).
+Every line carries `parity`: the GPU hits of query 0 (config3: 8 of the 256 queries) against the CPU oracle run over the
+WHOLE corpus of that line (rows regenerated from the counter hash chunk by chunk on the host, every rank its own shard).
 
 value   = corpus vectors scanned per second, whole job, inputs resident in HBM when the clock starts
 e2e     = the same through the reference-facing C-ABI call with HOST buffers (query H2D, hits D2H inside)
@@ -168,6 +170,69 @@ class ClockSampler:
         return out
 
 
+def default_workload(world):
+    """north_star's two stated targets: 10M x 768 fp32 on one GPU; the 100M x 768 bf16 top-100 corpus sharded over N."""
+    return "target10m" if world == 1 else "config4"
+
+
+def config_dict(name, world, rows_override=0):
+    """The `config` object of the JSON line.  Built in ONE place so that our arm and the reference arm describe the
+    workload with the same keys and values."""
+    rows, dim, dtype, k, desc = WORKLOADS[name]
+    if rows_override:
+        rows = rows_override
+    esz = 4 if dtype == "f32" else 2
+    return {"workload": name, "desc": desc, "rows_per_gpu": rows, "total_rows": rows * world, "dim": dim, "top_k": k, "storage": dtype,
+            "queries_per_step": BATCH_QUERIES.get(name, 1) if world == 1 else 1,
+            "parallelism": f"row-sharded x{world}" if world > 1 else "single GPU",
+            "l2": "corpus shard is larger than L2 (no flush needed)" if rows * dim * esz > 512e6 else
+                  "L2-resident workload: latency config, HBM fraction not meaningful"}
+
+
+def oracle_topk_streamed(row0, n_rows, dim, bf16, queries, k, n_threads, id_base=None, chunk_rows=250_000):
+    """CPU oracle over rows [row0, row0 + n_rows) of the synthetic corpus WITHOUT holding them all: the rows are
+    regenerated from the counter hash chunk by chunk (oracle/ragindex_oracle.c:rag_synth_rows, bit-identical to the
+    device generator), every chunk is scored with the reference's arithmetic (rag_oracle_query) and the per-chunk hit
+    lists are merged under the reference's order (score descending, lower row first).  Returns [(ids, scores)] per
+    query; ids are global (id_base + position in the range; id_base defaults to row0)."""
+    import numpy as np
+    from oracle import oracle_c as oc
+    if id_base is None:
+        id_base = row0
+    best = [(np.zeros(0, dtype=np.int64), np.zeros(0, dtype=np.float64)) for _ in queries]
+    for c0 in range(0, n_rows, chunk_rows):
+        m = min(chunk_rows, n_rows - c0)
+        rows = oc.synth_rows(row0 + c0, m, dim, CORPUS_SEED, round_bf16=bf16, n_threads=n_threads)
+        for qi, q in enumerate(queries):
+            idx, sc = oc.query(rows, q, k, n_threads=n_threads)
+            ids = np.concatenate([best[qi][0], idx + (id_base + c0)])
+            scs = np.concatenate([best[qi][1], sc])
+            order = np.lexsort((ids, -scs))[:max(1, k)]     # synthetic scores are finite: plain descending order
+            best[qi] = (ids[order], scs[order])
+        del rows
+    return best
+
+
+def merge_hit_lists(lists, k):
+    """Merge per-shard (ids, scores) lists into the global top-k, (score desc, id asc)."""
+    import numpy as np
+    ids = np.concatenate([l[0] for l in lists])
+    scs = np.concatenate([l[1] for l in lists])
+    order = np.lexsort((ids, -scs))[:max(1, k)]
+    return ids[order], scs[order]
+
+
+def compare_hits(gpu_idx, gpu_score, ora_idx, ora_score):
+    import numpy as np
+    gi, gs = np.asarray(gpu_idx, dtype=np.int64), np.asarray(gpu_score, dtype=np.float64)
+    oi, os_ = np.asarray(ora_idx, dtype=np.int64), np.asarray(ora_score, dtype=np.float64)
+    same_len = gi.shape == oi.shape
+    ok_idx = bool(same_len and np.array_equal(gi, oi))
+    ok_sc = bool(same_len and np.array_equal(gs.view(np.uint64), os_.view(np.uint64)))
+    rel = float(np.max(np.abs(gs - os_) / np.maximum(np.abs(os_), 1e-300))) if same_len and gi.size else None
+    return ok_idx, ok_sc, rel
+
+
 def run_reference(args, rank, world):
     """--impl reference: the CPU restatement of RagIndex.QueryAsync (oracle/) with all host threads."""
     if rank != 0:
@@ -175,6 +240,8 @@ def run_reference(args, rank, world):
     import numpy as np
     from oracle import oracle_c as oc
     rows, dim, dtype, k, desc = WORKLOADS[args.workload]
+    if args.rows:
+        rows = args.rows
     cores = os.cpu_count() or 1
     sample_rows = min(rows, 1_000_000)     # bounded sample of the workload: the first 1M rows
     corpus = oc.synth_rows(0, sample_rows, dim, CORPUS_SEED, round_bf16=(dtype == "bf16"))
@@ -190,7 +257,7 @@ def run_reference(args, rank, world):
            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32 products, f64 accumulate",
            "data": "synthetic", "queries_per_s": args.steps / dt * (rows / sample_rows) ** -1 if rows else None,
-           "config": {"workload": args.workload, "desc": desc, "rows_per_gpu": rows, "dim": dim, "top_k": k, "storage": dtype},
+           "config": config_dict(args.workload, max(world, args.gpus), args.rows),
            "cpu_baseline": {"value": v, "unit": "vectors/s", "cores": cores, "kind": "port", "cpu": cpu_model()[0], "host_cores": cpu_model()[1],
                             "sample": f"one query per step over the first {sample_rows} rows of the workload, all {cores} host threads (row-parallel, per-row arithmetic unchanged)"},
            "e2e": {"value": v, "unit": "vectors/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -235,7 +302,7 @@ def time_device_steps(torch, dist, world, step_fn, steps, warmup):
     return ms
 
 
-def measure_workload(name, args, torch, dist, rb, native, rank, world, dev, do_e2e=True, do_cpu=True):
+def measure_workload(name, args, torch, dist, rb, native, rank, world, dev, do_e2e=True, do_cpu=True, do_parity=True):
     import numpy as np
     rows, dim, dtype, k, desc = WORKLOADS[name]
     if args.rows:
@@ -356,7 +423,7 @@ def measure_workload(name, args, torch, dist, rb, native, rank, world, dev, do_e
         call, idx, sc, found, flags = st.search_call(nqb, k)
         for i in range(max(3, args.warmup // 4)):
             call(hq_step(i))
-        n_e2e = max(5, args.steps // 4)
+        n_e2e = max(100, args.steps // 4)     # >= 100 calls whatever --steps says: a p99 of five samples is not a p99
         per_call = []
         t0 = time.perf_counter()
         for i in range(n_e2e):
@@ -394,7 +461,7 @@ def measure_workload(name, args, torch, dist, rb, native, rank, world, dev, do_e
             for i in range(3):
                 e2e_step(i)
             dist.barrier()
-            n_e2e = max(20, args.steps // 4)
+            n_e2e = max(100, args.steps // 4)
             t0 = time.perf_counter()
             for i in range(n_e2e):
                 e2e_step(i)
@@ -407,27 +474,72 @@ def measure_workload(name, args, torch, dist, rb, native, rank, world, dev, do_e
                               "into page-locked host memory; two launches and one stream wait per rank") if host_path else
                              "host query -> ShardedSearcher.search_device (shard scan + exchange + merge) -> host hits, per rank"}
 
-    # CPU baseline + parity check against the oracle (rank 0, N = 1 only)
+    # CPU baseline (rank 0, N = 1 only): the oracle, one thread, on a bounded sample of the workload
     if do_cpu and world == 1 and rank == 0:
         from oracle import oracle_c as oc
         sample_rows = min(rows, 1_000_000)
         corpus = oc.synth_rows(0, sample_rows, dim, CORPUS_SEED, round_bf16=(dtype == "bf16"))
-        q = oc.synth_rows(0 if nqb > 1 else res["last_query_index"], 1, dim, QUERY_SEED)[0]
+        q = oc.synth_rows(0, 1, dim, QUERY_SEED)[0]
         reps, t_used = 0, 0.0
         while t_used < 8.0 and reps < 50:
             t0 = time.perf_counter()
-            eidx, esc = oc.query(corpus, q, k, n_threads=1)
+            oc.query(corpus, q, k, n_threads=1)
             t_used += time.perf_counter() - t0
             reps += 1
+        del corpus
         res["cpu_baseline"] = {"value": sample_rows * reps / t_used, "unit": "vectors/s", "cores": 1, "kind": "port", "cpu": cpu_model()[0], "host_cores": cpu_model()[1],
                                "sample": f"{reps} single-thread queries over the first {sample_rows} rows of the workload "
                                          "(oracle/ragindex_oracle.c; the reference's LINQ pipeline is single-threaded)"}
-        if sample_rows == rows:
-            ok_idx = [int(i) for i in eidx] == res["top_idx"]
-            ok_sc = [float(s) for s in esc] == res["top_score"]
-            res["parity"] = {"checked": "full corpus vs oracle", "indices_bit_exact": ok_idx, "scores_bit_exact": ok_sc}
+
+    # Parity at the REAL size, inside the line: the GPU hits against the CPU oracle over the whole corpus of this run.
+    # The oracle regenerates the rows from the counter hash chunk by chunk (never all resident); at N > 1 every rank
+    # scores its own shard with the host cores it is entitled to and rank 0 merges the per-shard lists.
+    if do_parity:
+        import numpy as np
+        t_par = time.perf_counter()
+        threads = max(1, (os.cpu_count() or 1) // world)
+        n_check = 1 if (nqb == 1 or world > 1) else min(8, nqb)
+        hq_par = np.ascontiguousarray(d_q[:n_check].cpu().numpy())   # the very floats the GPU searched with
+        with torch.cuda.stream(ts):
+            if world == 1:
+                p_idx = torch.zeros((max(nqb, 1), k), dtype=torch.int64, device="cuda")
+                p_sc = torch.zeros((max(nqb, 1), k), dtype=torch.float64, device="cuda")
+                p_found = torch.zeros(max(nqb, 1), dtype=torch.int32, device="cuda")
+                p_flags = torch.zeros(max(nqb, 1), dtype=torch.int32, device="cuda")
+                st.search_device(d_q[:nqb] if nqb > 1 else d_q[0], nqb, k, p_idx, p_sc, p_found, p_flags, stream=ts.cuda_stream)
+                ts.synchronize()
+                g_idx, g_sc = p_idx[:n_check].cpu().numpy(), p_sc[:n_check].cpu().numpy()
+                g_flags = p_flags[:n_check].cpu().numpy()
+            else:
+                sh.search_device(d_q[0], k)
+                ts.synchronize()
+                nf = int(sh.d_found.item())
+                g_idx, g_sc = sh.d_idx[:nf].cpu().numpy()[None, :], sh.d_score[:nf].cpu().numpy()[None, :]
+                g_flags = sh.d_flags.cpu().numpy()
+        mine = oracle_topk_streamed(rank * rows, rows, dim, dtype == "bf16", list(hq_par), k, threads)
+        if world > 1:
+            # fixed-size exchange of the per-shard oracle lists (k ids + k scores per rank) through the process group
+            o_ids = torch.full((k,), -1, dtype=torch.int64, device="cuda")
+            o_scs = torch.full((k,), float("-inf"), dtype=torch.float64, device="cuda")
+            n_m = len(mine[0][0])
+            o_ids[:n_m] = torch.from_numpy(mine[0][0]).cuda()
+            o_scs[:n_m] = torch.from_numpy(mine[0][1]).cuda()
+            all_ids = torch.empty(world * k, dtype=torch.int64, device="cuda")
+            all_scs = torch.empty(world * k, dtype=torch.float64, device="cuda")
+            dist.all_gather_into_tensor(all_ids, o_ids)
+            dist.all_gather_into_tensor(all_scs, o_scs)
+            ai, asc = all_ids.cpu().numpy(), all_scs.cpu().numpy()
+            keep = ai >= 0
+            oracle_hits = [merge_hit_lists([(ai[keep], asc[keep])], k)]
         else:
-            res["parity"] = {"checked": "not at this size in bench (see tests/ for properties and oracle checks)"}
+            oracle_hits = mine
+        oks = [compare_hits(g_idx[i], g_sc[i], oracle_hits[i][0], oracle_hits[i][1]) for i in range(n_check)]
+        res["parity"] = {"checked": f"{n_check} quer{'y' if n_check == 1 else 'ies'} x the full corpus of this run ({rows * world} rows) vs the CPU oracle "
+                                    "(oracle/ragindex_oracle.c), rows regenerated chunk by chunk" + (", every rank its own shard" if world > 1 else ""),
+                         "indices_bit_exact": all(o[0] for o in oks), "scores_bit_exact": all(o[1] for o in oks),
+                         "max_rel_score_err": max((o[2] or 0.0) for o in oks), "queries_checked": n_check, "rows_checked": rows * world,
+                         "gpu_flags": [int(x) for x in g_flags.reshape(-1)[:n_check]], "oracle_threads_per_rank": threads,
+                         "seconds": time.perf_counter() - t_par}
     st.close()
     return res
 
@@ -563,19 +675,34 @@ def run_streaming(args, torch, dist, rb, native, rank, world, dev):
     return out
 
 
+def tensor_block(r):
+    burst, sust, src = measured_tensor_peaks()
+    bf = r["storage"] != "f32" or r.get("operands") == "bf16"
+    div = 1.0 if bf else 2.0    # tf32 runs at half the bf16 rate on the tensor pipe
+    return {"achieved_tflops": r["tensor_tflops"],
+            "kind": "bf16 (tcgen05.mma kind::f16, fp32 accumulate in TMEM)" if bf else "tf32 (tcgen05.mma kind::tf32, fp32 accumulate in TMEM)",
+            "peak_tflops_bf16_burst": burst, "peak_tflops_bf16_sustained": sust, "peak_source": src,
+            "frac_of_burst": r["tensor_tflops"] / (burst / div), "frac_of_sustained": r["tensor_tflops"] / (sust / div),
+            "note": "tf32 peak taken as half the measured bf16 cuBLAS rate; the kernel runs inside a long step (power-capped clocks), so the "
+                    "sustained figure is the fair denominator; see DESIGN.md K3",
+            "certified_fraction": r.get("certified_fraction")}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=400)
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="config2", choices=sorted(WORKLOADS) + ["config5"])
+    ap.add_argument("--workload", default=None, choices=sorted(WORKLOADS) + ["config5"],
+                    help="default: target10m at N = 1, config4 at N > 1 (north_star's two stated targets)")
     ap.add_argument("--rows", type=int, default=0, help="override rows per GPU")
     ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"],
                     help="N > 1: how the per-shard hits meet -- one peer-memory kernel per rank (default) or NCCL all-gather + merge kernel")
     ap.add_argument("--no-reserve", action="store_true", help="config5: let appends map device memory on demand")
     ap.add_argument("--pinned", action="store_true", help="config5: the application's batches live in page-locked memory")
-    ap.add_argument("--no-extra", action="store_true", help="skip the extra target10m / config1 measurements")
+    ap.add_argument("--no-extra", action="store_true", help="skip the extra config1 / config2 / config3 measurements")
+    ap.add_argument("--no-parity", action="store_true", help="skip the full-corpus oracle check (profiling runs)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     quiet_stdout()
@@ -583,6 +710,9 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.workload is None:
+        # the reference arm may be started without torchrun: --gpus then says which line it is the partner of
+        args.workload = default_workload(max(world, args.gpus) if args.impl == "reference" else world)
 
     if args.impl == "reference":
         run_reference(args, rank, world)
@@ -607,7 +737,7 @@ def main():
         if world > 1:
             dist.destroy_process_group()
         return
-    main_res = measure_workload(args.workload, args, torch, dist, rb, native, rank, world, local)
+    main_res = measure_workload(args.workload, args, torch, dist, rb, native, rank, world, local, do_parity=not args.no_parity)
     k1 = None
     if world == 1 and not args.no_extra:
         try:
@@ -616,21 +746,26 @@ def main():
             k1 = {"error": repr(ex)[:200]}
     extra = {}
     if world == 1 and not args.no_extra and not args.rows:
-        for name in ("config1", "target10m"):
+        peak, _ = measured_peaks()
+        for name in ("config2", "config1", "config3", "target10m"):
             if name == args.workload:
                 continue
             try:
                 sub = argparse.Namespace(**vars(args))
-                sub.steps = max(50, args.steps // 4) if name == "target10m" else args.steps
-                r = measure_workload(name, sub, torch, dist, rb, native, rank, world, local, do_e2e=(name == "config1"), do_cpu=False)
-                peak, _ = measured_peaks()
+                sub.steps = max(100, args.steps) if name in ("config1", "config2") else max(50, min(args.steps, 200))
+                sub.warmup = max(args.warmup, 5)
+                r = measure_workload(name, sub, torch, dist, rb, native, rank, world, local, do_e2e=(name != "target10m"), do_cpu=False,
+                                     do_parity=not args.no_parity)
                 extra[name] = {"desc": r["desc"], "vectors_per_s": r["value"], "queries_per_s": r["queries_per_s"], "ms_per_step": r["ms_per_step"],
                                "achieved_gbs": r["achieved_gbs"], "frac_of_measured_hbm": r["achieved_gbs"] / peak,
-                               "frac_of_8TBs_spec": r["achieved_gbs"] / 8000.0, "steps": sub.steps, "flags": r["flags"], "latency_ms": r.get("latency_ms")}
+                               "frac_of_8TBs_spec": r["achieved_gbs"] / 8000.0, "steps": sub.steps, "flags": r["flags"], "latency_ms": r.get("latency_ms"),
+                               "clocks": r["clocks"], "parity": r.get("parity"), "certified_fraction": r.get("certified_fraction")}
                 if "e2e" in r:
-                    extra[name]["e2e_ms_per_query"] = r["e2e"]["ms_per_step"]
+                    extra[name]["e2e"] = r["e2e"]
+                if "tensor_tflops" in r:
+                    extra[name]["tensor"] = tensor_block(r)
             except Exception as ex:  # an extra must never take the headline down
-                extra[name] = {"error": repr(ex)[:200]}
+                extra[name] = {"error": repr(ex)[:300]}
 
     if rank == 0:
         peak, peak_src = measured_peaks()
@@ -643,29 +778,24 @@ def main():
                     traffic = json.load(f).get(f"{args.workload}:{r['rows_per_gpu']}")
             except Exception:
                 traffic = None
+        batched = r.get("queries_per_step", 1) > 1
         out = {
-            "metric": "corpus vectors scanned/sec (single query, top-k)" if r.get("queries_per_step", 1) == 1 else "corpus vectors scanned/sec (per sweep of a 256-query batch, top-k)",
+            "metric": "corpus vectors scanned/sec (single query, top-k)" if not batched else "corpus vectors scanned/sec (per sweep of a 256-query batch, top-k)",
             "value": r["value"], "unit": "vectors/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_per_step"],
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32" if r["storage"] == "f32" else "bf16 storage, f32 accumulate", "data": "synthetic",
             "queries_per_s": r["queries_per_s"],
-            "config": {"workload": args.workload, "desc": r["desc"], "rows_per_gpu": r["rows_per_gpu"], "total_rows": r["rows_per_gpu"] * world,
-                       "dim": r["dim"], "top_k": r["top_k"], "storage": r["storage"], "parallelism": f"row-sharded x{world}" if world > 1 else "single GPU", "exchange": r.get("exchange"),
-                       "l2": "corpus shard is larger than L2 (no flush needed)" if r["rows_per_gpu"] * r["dim"] * (4 if r["storage"] == "f32" else 2) > 512e6 else "L2-resident workload: latency config, HBM fraction not meaningful",
-                       "rescoring": "exact fp64 (reference arithmetic) for k' >= k candidates inside the same launch"},
+            "config": config_dict(args.workload, world, args.rows),
+            "exchange": r.get("exchange"),
+            "rescoring": "exact fp64 (reference arithmetic) for k' >= k candidates inside the same launch",
             "roofline": {"bound": "hbm", "achieved": r["achieved_gbs"], "peak": peak, "unit": "GB/s", "frac": r["achieved_gbs"] / peak,
                          "traffic": traffic, "peak_source": peak_src, "frac_of_8TBs_spec": r["achieved_gbs"] / 8000.0,
-                         "kernel": "batch_score_kernel_2sm (threshold pass + full pass; prep, thresholds and finalize included: whole step timed)" if r.get("queries_per_step", 1) > 1 else "scan_topk_kernel",
+                         "kernel": "batch_score_kernel_2sm (threshold pass + full pass; prep, thresholds and finalize included: whole step timed)" if batched else "scan_topk_kernel",
                          "kernel_ms": r["kernel_ms"],
-                         "algorithmic_bytes_per_launch": r["rows_per_gpu"] * r["dim"] * (4 if r["storage"] == "f32" else 2)},
-            "tensor": ({"achieved_tflops": r["tensor_tflops"], "kind": "tf32 (tcgen05.mma kind::tf32, fp32 accumulate in TMEM)",
-                        "peak_tflops_bf16_burst": measured_tensor_peaks()[0], "peak_tflops_bf16_sustained": measured_tensor_peaks()[1],
-                        "peak_source": measured_tensor_peaks()[2],
-                        "frac_of_tf32_burst": r["tensor_tflops"] / (measured_tensor_peaks()[0] / 2),
-                        "frac_of_tf32_sustained": r["tensor_tflops"] / (measured_tensor_peaks()[1] / 2),
-                        "note": "tf32 peak taken as half the measured bf16 cuBLAS rate; this kernel runs inside a long step (power-capped clocks), so the sustained figure is the fair denominator; the step is bound by L2->SM ingest and by power (SM clock ~1.27 GHz under this load), see DESIGN.md K3",
-                        "certified_fraction": r.get("certified_fraction")} if "tensor_tflops" in r else None),
+                         "algorithmic_bytes_per_launch": r["rows_per_gpu"] * r["dim"] * (4 if r["storage"] == "f32" else 2),
+                         "note": "peak = measured read+write copy bandwidth; a read-only stream can exceed it, so both denominators are given"},
+            "tensor": tensor_block(r) if "tensor_tflops" in r else None,
             "cpu_baseline": r.get("cpu_baseline"),
             "e2e": {k: v for k, v in r.get("e2e", {}).items()} if "e2e" in r else None,
             "gpu_launches": args.steps * r["launches_per_step"],

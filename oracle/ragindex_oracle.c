@@ -203,22 +203,25 @@ static inline float bf16_round_f32(float x)
 void rag_synth_rows(float *out, int64_t row0, int64_t n_rows, int64_t dim, int64_t ld,
                     uint64_t seed, int round_bf16)
 {
+    /* the samples of a row are drawn once and kept (same values as drawing them again for the second pass) */
+    int32_t *smp = (int32_t *)malloc(sizeof(int32_t) * (size_t)(dim > 0 ? dim : 1));
     for (int64_t r = 0; r < n_rows; r++) {
         uint64_t row_key = splitmix64(seed + 0x632BE59BD9B4E019ull * (uint64_t)(row0 + r + 1));
         int64_t n2 = 0;
         for (int64_t c = 0; c < dim; c++) {
-            int64_t s = synth_sample(row_key, c);
+            int64_t s = smp[c] = synth_sample(row_key, c);
             n2 += s * s;
         }
         double norm = sqrt((double)n2);
         float *o = out + r * ld;
         for (int64_t c = 0; c < dim; c++) {
-            double v = n2 ? (double)synth_sample(row_key, c) / norm : 0.0;
+            double v = n2 ? (double)smp[c] / norm : 0.0;
             float f = (float)v;
             o[c] = round_bf16 ? bf16_round_f32(f) : f;
         }
         for (int64_t c = dim; c < ld; c++) o[c] = 0.0f;
     }
+    free(smp);
 }
 
 typedef struct { float *out; int64_t row0, n, dim, ld; uint64_t seed; int bf; } synth_job;
