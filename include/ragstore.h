@@ -231,15 +231,17 @@ RAGSTORE_API int ragstore_exchange_destroy(ragstore_exchange_t* x);
  * thread that cannot afford the device-wide synchronisation and driver locks of cudaMalloc/cudaFree.
  * It runs the same scan + top-k + exact-rescoring launch as ragstore_search_device on buffers the
  * caller owns, and calls no cudaMalloc, cudaFree or other allocating routine, ever.
- *   d_matrix  n_rows x dim, row-major, fp32 or bf16 (dtype), rows a multiple of 16 bytes, unit norm
+ *   d_matrix  n_rows x dim, row-major, fp32 or bf16 (dtype), rows a multiple of 16 bytes, unit norm (RAGSTORE_HIT_CERTIFIED
+ *             is computed for rows of norm >= 1/2; shorter rows are still rescored exactly, but the flag may over-promise)
  *   d_rnorm   reciprocal norm of each stored row, fp32, readable up to the next multiple of 4 rows
  *   d_query   dim raw fp32 values;  outputs as ragstore_search_device for one query
  * The kernel's scratch (per-CTA candidate lists + a ticket) lives in a fixed array inside the
  * library image: ragstore_noalloc_scratch_bytes() (about 321 KB) is held on every GPU that loads the
  * library, until the process exits.  Limits that follow from the fixed size: top_k <= 256 and at most
  * 160 SMs; beyond them the call returns RAGSTORE_ERR_UNSUPPORTED and says why.
- * The first call on each device resolves the array's device address; make that first call before any
- * stream capture begins.  All calls share the one array: it keeps the previous call's contents (the
+ * The first call on each device resolves the array's device address, and -- CUDA loads modules lazily by default -- may
+ * make the driver load the kernel for that dtype / row width together with the array itself; make one call per device
+ * and per matrix shape at start-up, before any stream capture begins and before the arena takes the last of HBM.  All calls share the one array: it keeps the previous call's contents (the
  * call clears the ticket it needs zeroed, in stream order), and two calls whose kernels overlap on the
  * same GPU race on it -- issue them on one stream, or otherwise order them.
  * Errors of this entry point are reported by ragstore_noalloc_last_error(). */
@@ -274,10 +276,16 @@ RAGSTORE_API int ragstore_last_error(char* buf, int buf_len);
 /* Library/ABI version (major*1000 + minor). */
 RAGSTORE_API int ragstore_version(void);
 
+/* The RAGSTORE_BATCH_* environment knobs (kernel-variant experiments) are read once, at first use; tests
+ * that switch them inside one process call this afterwards. */
+RAGSTORE_API int ragstore_debug_reload_env(void);
+
 /* Store facts for tests and the bench: fills up to n of
  * [dim, ld (padded row length), dtype, count, capacity, n_inexact_rows, device, sm_count,
  *  has_sidecar, sidecar_rows, matrix_bytes_mapped, uses_vmm, scan_launches, batch_launches,
- *  last_add_kernel_ns (device time of the upload/normalise launches of the last ragstore_add)]. */
+ *  last_add_kernel_ns (device time of the upload/normalise launches of the last ragstore_add),
+ *  scratch_overlaps (scan launches that found their scratch in use by another launch: a caller broke the
+ *  "one in-flight device search per store" rule of ragstore_search_device; results of such launches are garbage)]. */
 RAGSTORE_API int ragstore_info(ragstore_t* s, int64_t* out, int n);
 
 /* Profiling aid: %globaltimer (ns) at the phase boundaries of the store's most recent

@@ -30,8 +30,19 @@
 
 #include <cstdio>
 #include <cstdlib>
+#include <mutex>
+#include <set>
+#include <utility>
 
 #include "topk_device.cuh"
+
+// In-kernel cycle counters of the epilogue (RAGSTORE_BATCH_DEBUG=8 prints them) are compiled in only with
+// -DRAGSTORE_BATCH_PROFILE (make EXTRA=-DRAGSTORE_BATCH_PROFILE): the production kernels carry no clock reads and no printf.
+#ifdef RAGSTORE_BATCH_PROFILE
+#define RAG_PROF(...) __VA_ARGS__
+#else
+#define RAG_PROF(...)
+#endif
 
 namespace rag {
 
@@ -512,27 +523,26 @@ batch_score_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
                 smp[0] = t0, smp[1] = t1, smp[2] = t2, smp[3] = t3;
             }
         } else {
-            long long t_wait = 0, t_work = 0;  // debug & 8: cycles spent waiting for / draining accumulators
+            RAG_PROF(long long t_wait = 0, t_work = 0;)  // cycles spent waiting for / draining accumulators
             for (int64_t it = 0; it < my_tiles; ++it) {
                 const uint32_t as = static_cast<uint32_t>(it % AS), aph = static_cast<uint32_t>((it / AS) & 1);
-                const long long c0k = clock64();
+                RAG_PROF(const long long c0k = clock64();)
                 const int64_t row0 = ((cluster_id + it * n_clusters) * kCluster + crank) * a.tile_stride * kBN;
                 const int nvalid = static_cast<int>(min(static_cast<int64_t>(kBN), a.n_rows - row0));
                 float rn_lo, rn_max;
                 tile_rnorm_range<BF>(a.rnorm, row0, nvalid, lane, rn_lo, rn_max);
                 mbar_wait(tmem_full + as, aph);
                 tc_fence_after();
-                const long long c1k = clock64();
-                t_wait += c1k - c0k;
+                RAG_PROF(const long long c1k = clock64(); t_wait += c1k - c0k;)
                 scan_tile<BF>(tacc0 + as * MB * 256u, row0, nvalid, rn_max, a.rnorm, live && !(a.debug & 1), S, minpos, thr, rows, NQ, q);
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(tmem_empty + as);
-                t_work += clock64() - c1k;
+                RAG_PROF(t_work += clock64() - c1k;)
             }
-            if ((a.debug & 8) && blockIdx.x == 0 && lane == 0 && my_tiles > 0)
+            RAG_PROF(if ((a.debug & 8) && blockIdx.x == 0 && lane == 0 && my_tiles > 0)
                 printf("[batch dbg] warp %d: tiles %lld, per tile: wait %lld cyc, drain+scan %lld cyc\n", warp, (long long)my_tiles,
-                       t_wait / my_tiles, t_work / my_tiles);
+                       t_wait / my_tiles, t_work / my_tiles);)
             publish_lists(smem, S, rows, NQ, q, 0, a.nq, a.glists, static_cast<int>(gridDim.x), static_cast<int>(blockIdx.x), lane);
         }
     }
@@ -743,18 +753,17 @@ batch_score_kernel_2sm(const __grid_constant__ CUtensorMap tmap_q, const __grid_
             thr = floor0;
         }
         float t0 = -CUDART_INF_F, t1 = -CUDART_INF_F, t2 = -CUDART_INF_F, t3 = -CUDART_INF_F;  // sampling pass: 4 best
-        long long t_wait = 0, t_work = 0;
+        RAG_PROF(long long t_wait = 0, t_work = 0;)
         for (int64_t it = 0; it < my_tiles; ++it) {
             const uint32_t as = static_cast<uint32_t>(it & 1), aph = static_cast<uint32_t>((it >> 1) & 1);
-            const long long c0k = clock64();
+            RAG_PROF(const long long c0k = clock64();)
             const int64_t row0 = (pair_id + it * n_pairs) * a.tile_stride * kBN;
             const int nvalid = static_cast<int>(min(static_cast<int64_t>(kBN), a.n_rows - row0));
             float rn_lo, rn_hi;
             tile_rnorm_range<BF>(a.rnorm, row0, nvalid, lane, rn_lo, rn_hi);
             mbar_wait(tmem_full + as, aph);
             tc_fence_after();
-            const long long c1k = clock64();
-            t_wait += c1k - c0k;
+            RAG_PROF(const long long c1k = clock64(); t_wait += c1k - c0k;)
             const uint32_t tacc = tmem_base + lane_base + as * 256u;
             if (a.sample)
                 sample_tile<BF>(tacc, nvalid, rn_lo, rn_hi, t0, t1, t2, t3);
@@ -763,11 +772,11 @@ batch_score_kernel_2sm(const __grid_constant__ CUtensorMap tmap_q, const __grid_
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive_cluster_relaxed(tmem_empty + as, 0);
-            t_work += clock64() - c1k;
+            RAG_PROF(t_work += clock64() - c1k;)
         }
-        if ((a.debug & 8) && blockIdx.x == 0 && lane == 0 && my_tiles > 0)
+        RAG_PROF(if ((a.debug & 8) && blockIdx.x == 0 && lane == 0 && my_tiles > 0)
             printf("[batch dbg pair] warp %d: tiles %lld, per tile: wait %lld cyc, drain+scan %lld cyc\n", warp, (long long)my_tiles,
-                   t_wait / my_tiles, t_work / my_tiles);
+                   t_wait / my_tiles, t_work / my_tiles);)
         if (a.sample) {
             if (live) {
                 float* smp = reinterpret_cast<float*>(a.glists) + (static_cast<size_t>(q) * n_pairs + pair_id) * 4;
@@ -911,6 +920,46 @@ static bool make_map(CUtensorMap* m, const void* base, uint64_t rows, uint64_t l
                CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
+// Shared-memory opt-in of a kernel: per function and per device, so done once for each pair instead of per launch.
+template <typename K>
+static cudaError_t opt_in_smem(K kernel) {
+    static std::mutex mu;
+    static std::set<std::pair<const void*, int>> done;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    const std::pair<const void*, int> key(reinterpret_cast<const void*>(kernel), dev);
+    std::lock_guard<std::mutex> lk(mu);
+    if (done.count(key)) return cudaSuccess;
+    const cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e == cudaSuccess) done.insert(key);
+    return e;
+}
+
+// Experiment knobs (environment), read ONCE -- five getenv calls per launch were measurable on the latency path.
+// ragstore_debug_reload_env() re-reads them (tests switch kernel variants at run time).
+struct BatchKnobs {
+    bool no_pair = false, no_twopass = false;
+    int stages = 0, debug = 0, stride_max = 32;
+    void load() {
+        const char* e;
+        no_pair = (e = std::getenv("RAGSTORE_BATCH_2SM")) && e[0] == '0';
+        no_twopass = (e = std::getenv("RAGSTORE_BATCH_TWOPASS")) && e[0] == '0';
+        stages = (e = std::getenv("RAGSTORE_BATCH_STAGES")) ? atoi(e) : 0;
+        debug = (e = std::getenv("RAGSTORE_BATCH_DEBUG")) ? atoi(e) : 0;
+        const int v = (e = std::getenv("RAGSTORE_BATCH_STRIDE_MAX")) ? atoi(e) : 0;
+        stride_max = v >= 1 ? v : 32;
+    }
+};
+static BatchKnobs& knobs() {
+    static BatchKnobs k = [] {
+        BatchKnobs b;
+        b.load();
+        return b;
+    }();
+    return k;
+}
+void batch_reload_env() { knobs().load(); }
+
 size_t batch_scratch_bytes(int sm_count) {
     return sizeof(uint64_t) * size_t(kBatchMaxQ) * size_t(sm_count) * kBatchKp   // candidate lists
            + sizeof(float) * size_t(kBatchMaxQ) * size_t(kBatchMaxLd)           // normalised query operand
@@ -937,17 +986,16 @@ int launch_batch_search(const BatchSearchArgs& b, cudaStream_t stream) {
     if (e != cudaSuccess) return static_cast<int>(e);
 
     CUtensorMap map_q, map_c;
-    const char* mode_env = std::getenv("RAGSTORE_BATCH_2SM");
-    const bool pair_maps = mblocks == 2 && !(mode_env && mode_env[0] == '0');
+    const BatchKnobs& kn = knobs();
+    const bool pair_maps = mblocks == 2 && !kn.no_pair;
     if (!make_map(&map_q, qhat, static_cast<uint64_t>(nq_pad), static_cast<uint64_t>(s.ld), pair_maps ? kBM : nq_pad / kCluster, bf) ||
         !make_map(&map_c, s.mat, static_cast<uint64_t>(s.n_rows), static_cast<uint64_t>(s.ld), pair_maps ? 128 : kBN, bf))
         return static_cast<int>(cudaErrorNotSupported);
 
-    const char* mode = std::getenv("RAGSTORE_BATCH_2SM");
     // 129..256 queries: the CTA-pair (cta_group::2) kernel by default -- half the shared-memory fill per corpus row and a
     // double-buffered accumulator; measured equal to 4 % faster than the single-CTA kernel on fp32 stores (both sit at
     // the power-capped tensor rate) and 4-15 % faster on bf16 stores and small corpora.  RAGSTORE_BATCH_2SM=0 opts out.
-    const bool pair = mblocks == 2 && !(mode && mode[0] == '0');
+    const bool pair = pair_maps;
     BatchLayout L;
     L.mblocks = mblocks;
     L.stage_bytes = pair ? 2 * kOperandBytes : (mblocks + 2) * kOperandBytes;
@@ -956,10 +1004,7 @@ int launch_batch_search(const BatchSearchArgs& b, cudaStream_t stream) {
     const uint32_t budget = 227u * 1024u - 1024u /*alignment slack*/ - lists_bytes - 512u;
     L.n_stages = budget / L.stage_bytes;
     if (L.n_stages > 8) L.n_stages = 8;
-    if (const char* se = std::getenv("RAGSTORE_BATCH_STAGES")) {   // experiments only
-        const uint32_t v = static_cast<uint32_t>(atoi(se));
-        if (v >= 2 && v < L.n_stages) L.n_stages = v;
-    }
+    if (kn.stages >= 2 && static_cast<uint32_t>(kn.stages) < L.n_stages) L.n_stages = static_cast<uint32_t>(kn.stages);   // experiments only
     if (L.n_stages < 2 || L.n_stages * L.stage_bytes < keys_bytes) return static_cast<int>(cudaErrorInvalidConfiguration);
     L.off_bars = L.n_stages * L.stage_bytes;
     L.off_tmem = L.off_bars + 8u * (2u * L.n_stages + 4u);
@@ -973,7 +1018,7 @@ int launch_batch_search(const BatchSearchArgs& b, cudaStream_t stream) {
     a.nkb = bf ? (s.ld + 63) / 64 : (s.ld + 31) / 32;
     a.rnorm = s.rnorm;
     a.glists = glists;
-    a.debug = std::getenv("RAGSTORE_BATCH_DEBUG") ? atoi(std::getenv("RAGSTORE_BATCH_DEBUG")) : 0;
+    a.debug = kn.debug;
     const int64_t n_tiles = (s.n_rows + kBN - 1) / kBN;
     const int64_t n_units = pair ? 2 * n_tiles : n_tiles;       // CTAs that have work
     int grid = static_cast<int>(n_units < s.sm_count ? n_units : s.sm_count);
@@ -985,13 +1030,13 @@ int launch_batch_search(const BatchSearchArgs& b, cudaStream_t stream) {
     a.sample = 0;
     const float* thr_used = nullptr;
     auto launch_as = [&](auto kernel) -> cudaError_t {
-        cudaError_t e2 = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        cudaError_t e2 = opt_in_smem(kernel);
         if (e2 != cudaSuccess) return e2;
         kernel<<<grid, kBatchThreads, L.total, stream>>>(map_q, map_c, a, L);
         return cudaGetLastError();
     };
     auto launch_pair = [&](auto kernel) -> cudaError_t {
-        cudaError_t e2 = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        cudaError_t e2 = opt_in_smem(kernel);
         if (e2 != cudaSuccess) return e2;
         kernel<<<grid, kPairThreads, L.total, stream>>>(map_q, map_c, a, L);
         return cudaGetLastError();
@@ -1007,17 +1052,12 @@ int launch_batch_search(const BatchSearchArgs& b, cudaStream_t stream) {
         // drain.  A sampling pass over every s-th tile (same kernel) gives, per query, the k'-th best score of the
         // sample -- a lower bound of the k'-th best overall -- and the full pass starts from it: only ~32*s rows per
         // query in the WHOLE corpus still beat it.
-        const char* tp = std::getenv("RAGSTORE_BATCH_TWOPASS");
-        const bool two_pass = !(tp && tp[0] == '0');
+        const bool two_pass = !kn.no_twopass;
         if (two_pass) {
             // small corpora: stride 1, i.e. the "sample" is a full (cheap: 4 registers per thread, no lists) sweep --
             // still far cheaper than filling cold lists column by column (~200 us per CTA for 256 queries)
             int stride = static_cast<int>(n_tiles / (2ll * nlists));   // every CTA (pair) samples >= 2 tiles when it can
-            static const int stride_max = [] {
-                const char* e = std::getenv("RAGSTORE_BATCH_STRIDE_MAX");   // experiments
-                const int v = e ? atoi(e) : 0;
-                return v >= 1 ? v : 32;
-            }();
+            const int stride_max = kn.stride_max;   // experiments
             stride = stride > stride_max ? stride_max : (stride < 1 ? 1 : stride);
             a.tile_stride = stride;
             a.sample = 1;
@@ -1054,11 +1094,11 @@ int launch_batch_search(const BatchSearchArgs& b, cudaStream_t stream) {
     f.ring_bytes = (ring + 127u) & ~127u;
     const size_t fin_smem = f.ring_bytes + fixed;
     if (bf) {
-        e = cudaFuncSetAttribute(batch_finalize_kernel<uint16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        e = opt_in_smem(batch_finalize_kernel<uint16_t>);
         if (e != cudaSuccess) return static_cast<int>(e);
         batch_finalize_kernel<uint16_t><<<b.nq, kScanThreads, fin_smem, stream>>>(f);
     } else {
-        e = cudaFuncSetAttribute(batch_finalize_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        e = opt_in_smem(batch_finalize_kernel<float>);
         if (e != cudaSuccess) return static_cast<int>(e);
         batch_finalize_kernel<float><<<b.nq, kScanThreads, fin_smem, stream>>>(f);
     }

@@ -138,6 +138,11 @@ int ragstore_search_noalloc(const void* d_matrix, const float* d_rnorm, int64_t 
         const int dv = ((dim + per_chunk - 1) / per_chunk + 31) / 32;
         a.eps = static_cast<float>((dv * per_chunk + 16) * 5.9604644775390625e-08);
     }
+    // Certificate: the store-backed entry points know the smallest row norm they ever ingested and charge the reference's
+    // "+1e-9" (RagIndex.cs:134) with it.  Here the rows are the caller's and unit norm by contract, so the term is charged
+    // for rows no shorter than 1/2 -- 2e-9 / |q| -- which covers any rounding of a unit row with a wide margin.  A caller
+    // that passes shorter rows still gets correctly rescored hits; only RAGSTORE_HIT_CERTIFIED may then promise too much.
+    a.min_norm_assumed = 0.5f;
     a.scratch.ticket = reinterpret_cast<unsigned int*>(pd.scratch);
     a.scratch.stamps = reinterpret_cast<unsigned long long*>(pd.scratch + 64);
     a.scratch.cta_lists = reinterpret_cast<uint64_t*>(pd.scratch + 256);

@@ -161,6 +161,13 @@ struct ragstore {
 
 namespace {
 
+// host mirror of global_row_id() (topk_device.cuh)
+int64_t host_global_row_id(const ragstore* s, int64_t local) {
+    if (s->row_block <= 0) return s->row_base + local;
+    const int64_t blk = local / s->row_block, off = local % s->row_block;
+    return s->row_base + (blk * s->row_nshards + s->row_shard) * s->row_block + off;
+}
+
 int alloc_scratch(ScanScratch& s) {
     uint8_t* p = nullptr;
     CU_TRY(cudaMalloc(&p, kScanScratchBytes));
@@ -287,7 +294,12 @@ int run_batch(const ragstore* s, int64_t n, int take, const float* d_q, int nq, 
 
 extern "C" {
 
-int ragstore_version(void) { return 1000; }
+int ragstore_version(void) { return 1001; }
+
+int ragstore_debug_reload_env(void) {
+    batch_reload_env();
+    return RAGSTORE_OK;
+}
 
 int ragstore_last_error(char* buf, int buf_len) {
     if (!buf || buf_len <= 0) return 0;
@@ -602,10 +614,22 @@ int ragstore_info(ragstore_t* s, int64_t* out, int n) {
     DeviceGuard g(s->device);
     unsigned long long inexact = 0;
     CU_TRY(cudaMemcpy(&inexact, s->d_inexact, sizeof(inexact), cudaMemcpyDeviceToHost));
-    const int64_t v[15] = {s->dim, s->ld, s->dtype, s->count.load(), s->capacity, static_cast<int64_t>(inexact), s->device, s->sm_count,
+    int64_t overlaps = 0;
+    if (n > 15) {  // launches that found their scratch in use by another launch (misuse of the device entry points)
+        unsigned int w = 0;
+        CU_TRY(cudaMemcpy(&w, s->dev_scratch.ticket + 2, sizeof(w), cudaMemcpyDeviceToHost));
+        overlaps += w;
+        for (auto& c : s->ctxs) {
+            if (!c.scratch.ticket) continue;
+            CU_TRY(cudaMemcpy(&w, c.scratch.ticket + 2, sizeof(w), cudaMemcpyDeviceToHost));
+            overlaps += w;
+        }
+    }
+    const int64_t v[16] = {s->dim, s->ld, s->dtype, s->count.load(), s->capacity, static_cast<int64_t>(inexact), s->device, s->sm_count,
                            s->raw_slot ? 1 : 0, s->raw_used, static_cast<int64_t>(s->mat_buf.mapped()), s->mat_buf.uses_vmm() ? 1 : 0,
-                           s->n_scan_launches.load(), s->n_batch_launches.load(), static_cast<int64_t>(s->last_add_kernel_us * 1000.0)};
-    for (int i = 0; i < n && i < 15; ++i) out[i] = v[i];
+                           s->n_scan_launches.load(), s->n_batch_launches.load(), static_cast<int64_t>(s->last_add_kernel_us * 1000.0),
+                           overlaps};
+    for (int i = 0; i < n && i < 16; ++i) out[i] = v[i];
     return RAGSTORE_OK;
 }
 
@@ -804,7 +828,9 @@ int ragstore_search(ragstore_t* s, const float* queries, int n_queries, int quer
         // RagIndex.cs:126: every Cosine returns -1; the stable sort keeps insertion order
         for (int q = 0; q < n_queries; ++q) {
             for (int j = 0; j < take; ++j) {
-                out_idx[static_cast<size_t>(q) * req + j] = s->row_base + j;
+                // the shard's first rows in insertion order; under block-cyclic dealing their GLOBAL ids (the merge of
+                // all shards' answers then yields the corpus' first rows, as the reference's stable sort does)
+                out_idx[static_cast<size_t>(q) * req + j] = host_global_row_id(s, j);
                 out_score[static_cast<size_t>(q) * req + j] = -1.0;
             }
             out_found[q] = take;
@@ -1067,6 +1093,24 @@ int ragstore_load(const char* path, int device, int64_t capacity_rows, ragstore_
         fclose(f);
         return fail(RAGSTORE_ERR_INVALID, "ragstore_load: not a ragstore image (version 1)");
     }
+    {   // nothing in the header is trusted before it is checked against itself and against the file's size
+        const bool dt_ok = h.dtype == RAGSTORE_F32 || h.dtype == RAGSTORE_BF16;
+        const int align = h.dtype == RAGSTORE_F32 ? 4 : 8;
+        bool ok = dt_ok && h.dim > 0 && h.dim <= (1 << 20) && h.ld == (h.dim + align - 1) / align * align && h.raw_ld == (h.dim + 3) / 4 * 4 &&
+                  h.count >= 0 && h.count < 0xFFFFFFFFll && (h.has_sidecar == 0 || h.has_sidecar == 1) && h.sidecar_rows >= 0 &&
+                  h.sidecar_rows <= h.count && h.inexact_rows >= 0 && h.inexact_rows <= h.count && (h.has_sidecar || h.sidecar_rows == 0);
+        if (ok) {
+            const uint64_t n = static_cast<uint64_t>(h.count), esz = h.dtype == RAGSTORE_F32 ? 4 : 2;
+            uint64_t want = sizeof(SaveHeader) + n * static_cast<uint64_t>(h.ld) * esz + n * 4 + n;
+            if (h.has_sidecar) want += n * 4 + static_cast<uint64_t>(h.sidecar_rows) * static_cast<uint64_t>(h.raw_ld) * 4;
+            long here = ftell(f);
+            ok = fseek(f, 0, SEEK_END) == 0 && static_cast<uint64_t>(ftell(f)) == want && fseek(f, here, SEEK_SET) == 0;
+        }
+        if (!ok) {
+            fclose(f);
+            return fail(RAGSTORE_ERR_INVALID, "ragstore_load: header is inconsistent (counts, layout or file size do not agree)");
+        }
+    }
     const int64_t cap = std::max<int64_t>(std::max<int64_t>(capacity_rows, h.count), 1);
     ragstore_t* s = nullptr;
     int rc = ragstore_create(h.dim, h.dtype, cap, device, h.has_sidecar ? RAGSTORE_CREATE_SIDECAR_ON : RAGSTORE_CREATE_SIDECAR_OFF, &s);
@@ -1125,26 +1169,40 @@ int ragstore_set_coalescing(ragstore_t* s, int window_us, int max_batch) {
     return RAGSTORE_OK;
 }
 
+// Which search path a request of `req` hits takes: requests are only batched with their own kind, so that one caller's
+// large top_k cannot push everybody else off the tensor-core path (or hand them its error).
+static int coalesce_class(int req) {
+    if (req > kMaxKp) return 2;              // repeated scans (top_k above 256)
+    return choose_kp(req) == 32 ? 0 : 1;     // 0: candidate lists of 32 (tensor-core path from 2-3 callers up); 1: wider lists
+}
+
 int ragstore_search_coalesced(ragstore_t* s, const float* query, int query_dim, int top_k, int64_t* out_idx, double* out_score,
                               int32_t* out_found, int32_t* out_flags) {
     if (!s || !query || !out_idx || !out_score || !out_found) return fail(RAGSTORE_ERR_INVALID, "ragstore_search_coalesced: null argument");
     if (query_dim != s->dim)  // the -1 corner case needs no GPU work: answer it directly
         return ragstore_search(s, query, 1, query_dim, top_k, out_idx, out_score, out_found, out_flags);
+    const int req = top_k < 1 ? 1 : top_k;
+    // refused before it is queued: an unservable request must not reach (and fail) a batch it shares with others
+    if (std::min<int64_t>(s->count.load(std::memory_order_acquire), req) > kMaxTake)
+        return fail(RAGSTORE_ERR_UNSUPPORTED, "more than 8128 hits per query are not covered");
     ragstore::Pending me{query, top_k, out_idx, out_score, out_found, out_flags};
     std::unique_lock<std::mutex> lk(s->co_mu);
     s->co_queue.push_back(&me);
-    if (s->co_leader) {
-        s->co_cv.notify_all();  // lets a waiting leader see that its batch has grown
-        s->co_cv.wait(lk, [&] { return me.done; });
-        if (me.status) g_err = me.err;
-        return me.status;
-    }
-    s->co_leader = true;  // this caller runs batches until the queue is empty
+    s->co_cv.notify_all();  // lets a leader that waits for company see that its batch has grown
     std::vector<float> qbuf;
     std::vector<int64_t> ibuf;
     std::vector<double> sbuf;
     std::vector<int32_t> fbuf, gbuf;
-    while (!s->co_queue.empty()) {
+    // Leadership is held for ONE batch at a time.  Whoever finds no batch running while its own request is still pending
+    // runs the next batch (the oldest request's kind), then steps down and wakes the others: a caller whose hits are in
+    // returns at once, and under sustained load the queue is served by whoever is waiting -- nobody is kept past its own
+    // answer, however many clients keep re-entering.
+    while (!me.done) {
+        if (s->co_leader) {
+            s->co_cv.wait(lk, [&] { return me.done || !s->co_leader; });
+            continue;
+        }
+        s->co_leader = true;
         // Batches form by themselves: whoever arrives while a batch is executing is queued and taken, all together, by
         // the next one, so by default nobody waits (a lone caller on an idle store runs at once).  A window set with
         // ragstore_set_coalescing makes every batch's first caller wait that long for company: larger batches, at the
@@ -1153,9 +1211,16 @@ int ragstore_search_coalesced(ragstore_t* s, const float* query, int query_dim, 
             const auto deadline = std::chrono::steady_clock::now() + std::chrono::microseconds(s->co_window_us);
             s->co_cv.wait_until(lk, deadline, [&] { return static_cast<int>(s->co_queue.size()) >= s->co_max_batch; });
         }
-        const int nb = std::min<int>(static_cast<int>(s->co_queue.size()), s->co_max_batch);
-        std::vector<ragstore::Pending*> batch(s->co_queue.begin(), s->co_queue.begin() + nb);
-        s->co_queue.erase(s->co_queue.begin(), s->co_queue.begin() + nb);
+        const int cls = coalesce_class(s->co_queue.front()->top_k < 1 ? 1 : s->co_queue.front()->top_k);
+        std::vector<ragstore::Pending*> batch, rest;
+        for (auto* p : s->co_queue) {
+            if (static_cast<int>(batch.size()) < s->co_max_batch && coalesce_class(p->top_k < 1 ? 1 : p->top_k) == cls)
+                batch.push_back(p);
+            else
+                rest.push_back(p);
+        }
+        s->co_queue.swap(rest);
+        const int nb = static_cast<int>(batch.size());
         lk.unlock();
         int kmax = 1;
         for (auto* p : batch) kmax = std::max(kmax, p->top_k);
@@ -1184,9 +1249,9 @@ int ragstore_search_coalesced(ragstore_t* s, const float* query, int query_dim, 
         }
         lk.lock();
         for (auto* p : batch) p->done = true;
+        s->co_leader = false;
         s->co_cv.notify_all();
     }
-    s->co_leader = false;
     lk.unlock();
     if (me.status) g_err = me.err;
     return me.status;

@@ -15,7 +15,8 @@ constexpr int kMaxCtas = 1024;                          // scratch sizing: CTAs 
 // Scratch one scan launch needs in global memory (beyond inputs/outputs).
 struct ScanScratch {
     uint64_t* cta_lists;   // [kMaxCtas * kMaxKp] per-CTA candidate keys
-    unsigned int* ticket;  // [1] "last CTA done" counter, self-resetting
+    unsigned int* ticket;  // [1] "last CTA done" counter, self-resetting; ticket[1] = in-use flag, ticket[2] = number of
+                           // launches that found the scratch already in use (two searches overlapping on one scratch)
     unsigned long long* stamps;  // [8] %globaltimer at the phase boundaries of the last launch (profiling aid)
 };
 constexpr size_t kScanScratchBytes = sizeof(uint64_t) * size_t(kMaxCtas) * kMaxKp + 256;
@@ -29,6 +30,8 @@ struct ScanArgs {
     const float* raw_rows;  // [n_slots][raw_ld] original fp32 rows of the inexactly stored ones (sidecar)
     int raw_ld;
     const uint32_t* min_norm_bits;  // fp32 bits of the smallest non-zero original row norm (may be null)
+    float min_norm_assumed;         // used when min_norm_bits is null: the caller's promise about the smallest row norm
+                                    // (0 = no promise: the certificate then ignores the reference's +1e-9 term)
     int64_t n_rows;
     int dim, ld, dtype;
     int64_t row_base;
@@ -93,6 +96,7 @@ struct BatchSearchArgs {
 };
 size_t batch_scratch_bytes(int sm_count);
 int launch_batch_search(const BatchSearchArgs& b, cudaStream_t stream);
+void batch_reload_env();   // re-reads the RAGSTORE_BATCH_* experiment knobs (otherwise read once)
 
 int launch_synth(float* d_out, int64_t row0, int64_t n_rows, int dim, int64_t ld, uint64_t seed,
                  int round_bf16, cudaStream_t stream);

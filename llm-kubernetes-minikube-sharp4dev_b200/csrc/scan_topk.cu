@@ -27,6 +27,7 @@
 // HBM traffic: every stored element is read exactly once (d * sizeof(elem) + 4 bytes per row).
 #include <math_constants.h>
 
+#include <atomic>
 #include <cstdlib>
 
 #include <cstring>
@@ -164,7 +165,11 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
     const uint8_t* mat = static_cast<const uint8_t*>(a.mat);
 
     if (tid == 0) {
-        if (blockIdx.x == 0) stamp(a, 0);
+        if (blockIdx.x == 0) {
+            stamp(a, 0);
+            // two launches overlapping on one scratch corrupt each other's lists silently: count it (ragstore_info)
+            if (atomicExch(a.scratch.ticket + 1, 1u) != 0u) atomicAdd(a.scratch.ticket + 2, 1u);
+        }
         for (int s = 0; s < n_stages; ++s) {
             mbar_init(full + s, 1);
             mbar_init(empty + s, 1);  // one consumer warp drains a tile
@@ -320,6 +325,7 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
     f.nlists = static_cast<int>(gridDim.x);
     f.bound_floor = -CUDART_INF_F;
     finalize_candidates<T>(a, f);
+    if (tid == 0) atomicExch(a.scratch.ticket + 1, 0u);  // scratch free again
 }
 
 // ---------------------------------------------------------------- host side
@@ -365,7 +371,8 @@ static bool make_layout(const ScanArgs& a, int dv, ScanLayout& L) {
     L.stage_bytes = (L.tile_bytes + R * 4u + 127u) & ~127u;
     L.n_stages = best_ns;
     L.n_consumers = best_ns < kConsumerWarps ? best_ns : kConsumerWarps;
-    L.no_hint = std::getenv("RAGSTORE_SCAN_NOHINT") ? 1u : 0u;
+    static const uint32_t no_hint = std::getenv("RAGSTORE_SCAN_NOHINT") ? 1u : 0u;   // experiments; read once
+    L.no_hint = no_hint;
     uint32_t off = L.n_stages * L.stage_bytes;
     L.off_bars = off;
     off += bars_bytes;
@@ -388,8 +395,16 @@ static bool make_layout(const ScanArgs& a, int dv, ScanLayout& L) {
 template <typename T, int DV, bool FULL>
 static int launch_one(const ScanArgs& a, const ScanLayout& L, int grid, cudaStream_t stream, const QueryParam& qp) {
     auto kfn = scan_topk_kernel<T, DV, FULL>;
-    cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-    if (e != cudaSuccess) return static_cast<int>(e);
+    // the shared-memory opt-in is per function AND per device: done once for each (bit = device ordinal), not per launch
+    static std::atomic<uint64_t> opted_in{0};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    const uint64_t bit = 1ull << (dev & 63);
+    if (!(opted_in.load(std::memory_order_acquire) & bit)) {
+        cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        if (e != cudaSuccess) return static_cast<int>(e);
+        opted_in.fetch_or(bit, std::memory_order_release);
+    }
     kfn<<<grid, kScanThreads, L.total, stream>>>(a, L, qp);
     return static_cast<int>(cudaGetLastError());
 }

@@ -334,8 +334,9 @@ __device__ __forceinline__ void finalize_candidates(const ScanArgs& a, const Fin
             double bound = lists[kp - 1] ? static_cast<double>(key_score(lists[kp - 1])) : -CUDART_INF;
             if (static_cast<double>(f.bound_floor) > bound) bound = static_cast<double>(f.bound_floor);
             double shrink = 0.0;
-            if (a.min_norm_bits) {
-                const double d = sqrt(misc->na) * static_cast<double>(__uint_as_float(*a.min_norm_bits));
+            if (a.min_norm_bits || a.min_norm_assumed > 0.f) {
+                const double mn = a.min_norm_bits ? static_cast<double>(__uint_as_float(*a.min_norm_bits)) : static_cast<double>(a.min_norm_assumed);
+                const double d = sqrt(misc->na) * mn;
                 shrink = 1e-9 / d;  // +inf when the query is zero: then only a full rescore certifies
             }
             bound_total = bound + static_cast<double>(a.eps) + shrink;
@@ -343,7 +344,14 @@ __device__ __forceinline__ void finalize_candidates(const ScanArgs& a, const Fin
             const bool complete = n_cand < kp && !(f.bound_floor > -CUDART_INF_F);
             if (complete) bound_total = -CUDART_INF;
             cert = misc->ek > bound_total || complete;  // false if either side is NaN
-            if (misc->na == 0.0) cert = true;  // zero query: every reference score is exactly +0.0 (or NaN, ranked last)
+            if (misc->na == 0.0) {
+                // All-zero query: every reference score is exactly +0.0 (or NaN, ranked last), any k rows in index order
+                // are right.  A NON-zero query whose fp32 squares all flush to zero (|q_i| < ~3e-23) also has na == 0,
+                // but the reference then ranks by dot / 1e-9, which the cosine scan knows nothing about: not certified.
+                bool all_zero = true;
+                for (int i = 0; i < a.dim; ++i) all_zero = all_zero && (qraw[i] == 0.0f);
+                cert = all_zero;
+            }
             if (k_take < a.k_take) cert = false;  // fewer survivors than requested hits: nothing to certify against
         }
         int32_t flags = 0;

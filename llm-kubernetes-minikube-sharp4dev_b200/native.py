@@ -67,6 +67,7 @@ def lib():
             "ragstore_exchange_merge": (C.c_int, [vp, vp, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp, vp]),
             "ragstore_exchange_destroy": (C.c_int, [vp]),
             "ragstore_info": (C.c_int, [vp, i64p, C.c_int]),
+            "ragstore_debug_reload_env": (C.c_int, []),
             "ragstore_search_noalloc": (C.c_int, [vp, vp, C.c_int64, C.c_int, C.c_int, vp, C.c_int, vp, vp, vp, vp, C.c_int, vp]),
             "ragstore_noalloc_scratch_bytes": (C.c_int64, []),
             "ragstore_noalloc_last_error": (C.c_char_p, []),
@@ -193,10 +194,11 @@ class RagStore:
                                                        C.c_void_p(stream)))
 
     def info(self) -> dict:
-        v = (C.c_int64 * 15)()
-        check(lib().ragstore_info(self._h, v, 15))
+        v = (C.c_int64 * 16)()
+        check(lib().ragstore_info(self._h, v, 16))
         keys = ["dim", "ld", "dtype", "count", "capacity", "n_inexact_rows", "device", "sm_count",
-                "has_sidecar", "sidecar_rows", "matrix_bytes_mapped", "uses_vmm", "scan_launches", "batch_launches", "last_add_kernel_ns"]
+                "has_sidecar", "sidecar_rows", "matrix_bytes_mapped", "uses_vmm", "scan_launches", "batch_launches", "last_add_kernel_ns",
+                "scratch_overlaps"]
         return dict(zip(keys, list(v)))
 
     def debug_stamps(self):

@@ -573,11 +573,22 @@ def test_many_identical_rows_across_pass_boundaries():
     assert np.array_equal(sc.view(np.uint64), esc.view(np.uint64))
 
 
+@pytest.fixture
+def knob(monkeypatch):
+    """Sets a RAGSTORE_BATCH_* experiment knob for one test: the library reads them once, so it is told to re-read."""
+    def set_(name, value):
+        monkeypatch.setenv(name, value)
+        rb.lib().ragstore_debug_reload_env()
+    yield set_
+    monkeypatch.undo()
+    rb.lib().ragstore_debug_reload_env()
+
+
 @pytest.mark.parametrize("pair,dtype", [("1", 0), ("0", 0), ("1", 1), ("0", 1)])
-def test_cta_pair_and_single_cta_kernel_variants(monkeypatch, pair, dtype):
+def test_cta_pair_and_single_cta_kernel_variants(knob, pair, dtype):
     """129..256 queries run on the cta_group::2 kernel by default; RAGSTORE_BATCH_2SM=0 selects the single-CTA kernel
     (all 512 TMEM columns for one tile).  Both must give the oracle's hits, on fp32 and bf16 stores."""
-    monkeypatch.setenv("RAGSTORE_BATCH_2SM", pair)
+    knob("RAGSTORE_BATCH_2SM", pair)
     n, d, nq, k = 20000, 768, 200, 10
     rows = oc.synth_rows(0, n, d, 1234, round_bf16=bool(dtype))
     qs = oc.synth_rows(0, nq, d, 5678)
@@ -591,7 +602,7 @@ def test_cta_pair_and_single_cta_kernel_variants(monkeypatch, pair, dtype):
         assert np.array_equal(sc[i].view(np.uint64), esc.view(np.uint64)), i
 
 
-def test_single_pass_and_two_pass_batched_agree(monkeypatch):
+def test_single_pass_and_two_pass_batched_agree(knob):
     """Large enough for the sampling pass (>= 32 tiles per CTA): results with and without it must be identical."""
     import torch
     from ragstore_b200 import native
@@ -603,9 +614,9 @@ def test_single_pass_and_two_pass_batched_agree(monkeypatch):
         st.add_device(buf, n, d)
         del buf
         qs = oc.synth_rows(0, nq, d, 77)
-        monkeypatch.setenv("RAGSTORE_BATCH_TWOPASS", "0")
+        knob("RAGSTORE_BATCH_TWOPASS", "0")
         a = st.search(qs, k)
-        monkeypatch.setenv("RAGSTORE_BATCH_TWOPASS", "1")
+        knob("RAGSTORE_BATCH_TWOPASS", "1")
         b = st.search(qs, k)
     assert np.array_equal(a[0], b[0]) and np.array_equal(a[1].view(np.uint64), b[1].view(np.uint64))
     assert (b[3] & rb.RAGSTORE_HIT_CERTIFIED).all()
@@ -799,3 +810,91 @@ def test_few_queries_at_once_take_one_sweep(n, nq):
         eidx, esc = oc.query(rows, qs[i], k, n_threads=4)
         assert list(idx[i]) == list(eidx), i
         assert np.array_equal(sc[i].view(np.uint64), esc.view(np.uint64)), i
+
+
+def test_dim_mismatch_under_block_cyclic_ids():
+    """query_dim != dim scores every row -1 (RagIndex.cs:126), so the stable sort returns the FIRST rows.  On a shard of a
+    block-cyclic corpus those are the shard's first rows under their GLOBAL ids; merging the shards' answers by
+    (score desc, id asc) then yields the corpus' first k rows, as one RagIndex would."""
+    d, block, world, k = 16, 4, 3, 6
+    stores = [rb.RagStore(d, 64) for _ in range(world)]
+    try:
+        lists = []
+        for r, st in enumerate(stores):
+            st.set_row_blocking(block, world, r)
+            st.add(oc.synth_rows(100 * r, 12, d, 5))
+            idx, sc, found, _ = st.search(np.ones(d - 1, dtype=np.float32), k)
+            assert found[0] == k and (sc[0] == -1.0).all()
+            # local rows 0..5 of shard r: blocks 0 and 1 of that shard = global blocks r and world + r
+            want = [(0 * world + r) * block + j for j in range(block)] + [(1 * world + r) * block + j for j in range(k - block)]
+            assert list(idx[0]) == want
+            lists.append(idx[0])
+        merged = sorted(int(x) for l in lists for x in l)[:k]
+        assert merged == list(range(k))
+    finally:
+        for st in stores:
+            st.close()
+
+
+def test_load_rejects_inconsistent_headers(tmp_path):
+    """ragstore_load checks the header against itself and against the file size before it trusts any count in it."""
+    import struct
+    d, n = 32, 100
+    path = str(tmp_path / "s.rag")
+    with rb.RagStore(d, n) as st:
+        st.add(oc.synth_rows(0, n, d, 9))
+        st.save(path)
+    good = open(path, "rb").read()
+    rb.RagStore.load(path).close()
+    def bad(mutate):
+        b = bytearray(good)
+        mutate(b)
+        p = str(tmp_path / "bad.rag")
+        open(p, "wb").write(bytes(b))
+        with pytest.raises(rb.RagStoreError) as ei:
+            rb.RagStore.load(p)
+        assert ei.value.code == 1
+    # header layout: magic[8], version, dim, ld, dtype, has_sidecar, raw_ld (int32 x 6), min_norm_bits, pad (u32 x 2), count, inexact, sidecar (int64 x 3)
+    bad(lambda b: struct.pack_into("<q", b, 40, -5))                 # negative count
+    bad(lambda b: struct.pack_into("<q", b, 40, n + 1000))           # count beyond the file
+    bad(lambda b: struct.pack_into("<q", b, 56, n + 1))              # more sidecar rows than rows
+    bad(lambda b: struct.pack_into("<i", b, 16, 48))                 # ld that does not follow from dim
+    bad(lambda b: b.extend(b"\0" * 7))                               # trailing bytes
+
+
+def test_closed_loop_clients_all_return_from_coalesced_search():
+    """16 clients that re-enter ragstore_search_coalesced as soon as they are answered: leadership changes hands after
+    every batch, so each call returns once its own hits are in -- nobody is kept serving the others' traffic."""
+    import threading
+    import time
+    n, d, nthreads, rounds = 20000, 256, 16, 40
+    rows = oc.synth_rows(0, n, d, 3)
+    qs = oc.synth_rows(0, nthreads, d, 4)
+    expect = [oc.query(rows, qs[i], 5 if i % 4 else 120, n_threads=2) for i in range(nthreads)]   # mixed kinds: top-5 and top-120
+    worst = [0.0] * nthreads
+    errors = []
+    with rb.RagStore(d, n) as st:
+        st.add(rows)
+        st.search(qs[:4], 5)     # warm-up: kernels loaded before latencies are looked at
+        t_start = time.perf_counter()
+
+        def client(i):
+            k = 5 if i % 4 else 120
+            for _ in range(rounds):
+                t0 = time.perf_counter()
+                idx, sc, _ = st.search_coalesced(qs[i], k)
+                worst[i] = max(worst[i], time.perf_counter() - t0)
+                if list(idx) != list(expect[i][0]) or not np.array_equal(sc.view(np.uint64), expect[i][1].view(np.uint64)):
+                    errors.append(i)
+
+        ts = [threading.Thread(target=client, args=(i,)) for i in range(nthreads)]
+        for t in ts:
+            t.start()
+        for t in ts:
+            t.join(timeout=120)
+        assert not any(t.is_alive() for t in ts), "a closed-loop client never returned"
+        total = time.perf_counter() - t_start
+        assert st.info()["scratch_overlaps"] == 0
+    assert not errors
+    # no single call may take a sizeable part of the whole run (the old leader served every batch until the queue emptied)
+    assert max(worst) < max(0.25, total / 4), (max(worst), total)

@@ -70,3 +70,28 @@ def test_noalloc_rejects_sizes_beyond_its_fixed_scratch():
     with pytest.raises(rb.RagStoreError):
         native.search_noalloc(m, rn, 8, 62, rb.RAGSTORE_F32, q, 5, idx, sc, fnd)   # rows not a multiple of 16 bytes
     assert 300_000 < rb.lib().ragstore_noalloc_scratch_bytes() < 400_000
+
+
+def test_noalloc_tiny_query_negative_scores_against_the_oracle():
+    """A query of norm 1e-6 whose scores are all negative is where the reference's `+1e-9` (RagIndex.cs:134) moves scores
+    the most.  The hits must be the oracle's, bit for bit, and the no-allocation entry point -- which cannot know the
+    corpus' smallest row norm and assumes 1/2 -- must never claim a certificate that the store-backed entry point,
+    which does know it, withholds.  Run on a second stream as well: the fixed scratch belongs to no stream."""
+    import torch
+    from oracle import oracle_c as oc
+    n, dim, k = 30000, 768, 10
+    rows = np.abs(oc.synth_rows(0, n, dim, 4321))          # unit norm, all components >= 0
+    q = -np.abs(oc.synth_rows(0, 1, dim, 8765)[0]) * np.float32(1e-6)
+    eidx, esc = oc.query(rows, q, k, n_threads=4)
+    assert (esc < 0).all()
+    with rb.RagStore(dim, n, rb.RAGSTORE_F32) as st:
+        st.add(rows)
+        assert st.info()["sidecar_rows"] == 0
+        mat_ptr, rn_ptr, _ = st.device_views()
+        dq = torch.from_numpy(q).cuda()
+        for stream in (torch.cuda.Stream(), torch.cuda.Stream()):
+            (i0, s0, f0, g0), (i1, s1, f1, g1) = _both(st, mat_ptr, rn_ptr, n, dim, rb.RAGSTORE_F32, dq, k, stream)
+            for i, s, f in ((i0, s0, f0), (i1, s1, f1)):
+                assert f == k and list(i[:k]) == list(eidx)
+                assert np.array_equal(s[:k].view(np.uint64), esc.view(np.uint64))
+            assert (g1 & rb.RAGSTORE_HIT_CERTIFIED) <= (g0 & rb.RAGSTORE_HIT_CERTIFIED)
