@@ -29,9 +29,11 @@ def f32(x):
 def kat():
     cases = []
 
-    def add(name, rows, q, k, idx, scores, why):
+    def add(name, rows, q, k, idx, scores, why, pins=None):
         cases.append(dict(name=name, rows=rows, query=q, top_k=k, expect_idx=idx,
                           expect_score=scores, why=why))
+        if pins:   # which of the C#-specific facts the equivalence argument rests on this case exercises
+            cases[-1]["pins_csharp_fact"] = pins
 
     one = 1.0 / (1.0 * 1.0 + EPS)
     add("onehot_orthogonal", [[1, 0, 0], [0, 1, 0], [0, 0, 1]], [0, 1, 0], 3,
@@ -52,6 +54,7 @@ def kat():
     order = sorted(range(4), key=lambda i: (-sc[i], i))
     c["expect_idx"], c["expect_score"] = order, [sc[i] for i in order]
     assert order.index(0) < order.index(2)
+    c["pins_csharp_fact"] = "System.Linq ordering is stable; Take(k) after it keeps the first k in source order among equal keys"
 
     add("topk_zero_gives_one", [[1, 0], [0, 1]], [0, 1], 0, [1], [one], "Math.Max(1, topK) (:65)")
     add("topk_negative_gives_one", [[1, 0], [0, 1]], [1, 0], -7, [0], [one], "Math.Max(1, topK) (:65)")
@@ -74,12 +77,29 @@ def kat():
     t = 1.0 + 2.0 ** -12
     p = 1.0 + 2.0 ** -11          # fp32(t*t): exact 1+2^-11+2^-24 ties-to-even -> 1+2^-11
     add("fp32_product_rounding", [[t]], [t], 1, [0], [p / (math.sqrt(p) * math.sqrt(p) + EPS)],
-        "a[i]*b[i] is rounded to fp32 BEFORE widening (:130); an fp64 product would give 1+2^-11+2^-24")
+        "a[i]*b[i] is rounded to fp32 BEFORE widening (:130); an fp64 product would give 1+2^-11+2^-24",
+        pins="float * float is evaluated in fp32 on .NET (x64 RyuJIT), then widened by `+=` into the double accumulator")
     big = 2.0 ** 30
     na_ = (2.0 ** 60 + 1.0) + 2.0 ** 60     # sequential fp64: 2^60+1 -> 2^60, then +2^60 -> 2^61
     add("sequential_fp64_order", [[big, 1.0, big]], [big, 1.0, -big], 1, [0],
         [0.0 / (math.sqrt(na_) * math.sqrt(na_) + EPS)],
-        "dot: (2^60 + 1) rounds to 2^60 in fp64, then -2^60 -> 0 exactly; any other order gives 1")
+        "dot: (2^60 + 1) rounds to 2^60 in fp64, then -2^60 -> 0 exactly; any other order gives 1",
+        pins="the loop adds in index order into ONE fp64 accumulator (no vectorisation, no reassociation)")
+    # four terms, so that a pairwise tree ((t0+t1)+(t2+t3)) and the sequential loop (((t0+t1)+t2)+t3) disagree:
+    # products 1, 2^60, -2^60, 1.  sequential: 1+2^60 -> 2^60; -2^60 -> 0; +1 -> 1.   pairwise: 2^60 + (-2^60 + 1 -> -2^60) = 0
+    n4 = ((1.0 + 2.0 ** 60) + 2.0 ** 60) + 1.0          # na = nb, sequential: 2^60, 2^61, 2^61
+    add("sequential_not_pairwise_sum", [[1.0, big, -big, 1.0]], [1.0, big, big, 1.0], 1, [0],
+        [1.0 / (math.sqrt(n4) * math.sqrt(n4) + EPS)],
+        "dot = ((1 + 2^60) - 2^60) + 1 = 1 when summed in index order; a pairwise (SIMD-style) tree gives 0",
+        pins="the loop adds in index order into ONE fp64 accumulator (no vectorisation, no reassociation)")
+    # stability: eight bit-identical rows among others, fewer requested than there are duplicates.  An unstable
+    # selection (heap, quickselect, parallel partial sort) returns SOME five of the eight; LINQ returns the first five.
+    dup = [0.6, 0.8]
+    rows_st = [[1, 0], dup, [0, 1], dup, dup, [-1, 0], dup, dup, [0.8, 0.6], dup, dup, dup]
+    sc_dup = cos_formula(dup, dup)
+    add("stable_sort_first_of_many_equal_keys", rows_st, dup, 5, [1, 3, 4, 6, 7], [sc_dup] * 5,
+        "OrderByDescending is a STABLE sort (:64): equal keys keep source order, so Take(5) is the five lowest-numbered duplicates",
+        pins="System.Linq ordering is stable; Take(k) after it keeps the first k in source order among equal keys")
     add("scale_invariance", [[3, 4], [0.75, 1.0], [300, 400]], [3, 4], 3, None, None,
         "positive scaling leaves cosine unchanged up to rounding; equal-score rows keep index order")
     c = cases[-1]

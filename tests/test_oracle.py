@@ -142,3 +142,58 @@ def test_fuzz_restatements_agree_and_selection_is_well_formed(data):
     for a, b in zip(ci, ci[1:]):
         if same_rank(a, b):
             assert a < b
+
+
+# ---- the day-one check for anyone with a .NET SDK: dotnet/GoldenDump runs the reference's own compiled assembly on the
+# inputs of kat_v1.json / synth_v1.json and writes its answers to tests/golden/from_dotnet/.  When those files exist the
+# oracle must equal them bit for bit -- that is what turns "parity unpinned" into "pinned".
+_FROM_DOTNET = os.path.join(GOLD, "from_dotnet")
+_UNPINNED = ("parity unpinned: tests/golden/from_dotnet/ is absent -- the reference (C#, net9.0) could not run where this "
+             "repository was written; generate it with `dotnet run --project dotnet/GoldenDump` (see that file's header)")
+
+
+def _bits(x):
+    return format(np.float64(x).view(np.uint64).item(), "016x")
+
+
+@pytest.mark.skipif(not os.path.exists(os.path.join(_FROM_DOTNET, "kat_v1.json")), reason=_UNPINNED)
+def test_from_dotnet_known_answers_equal_the_oracle_bit_for_bit():
+    with open(os.path.join(_FROM_DOTNET, "kat_v1.json")) as f:
+        ref = {c["name"]: c for c in json.load(f)}
+    for case in _load("kat_v1.json"):
+        r = ref[case["name"]]
+        rows, q = _rows(case), np.asarray(case["query"], dtype=np.float32)
+        for mod in (oc, onp):
+            idx, sc = mod.query(rows, q, case["top_k"])
+            assert [int(i) for i in idx] == r["expect_idx"], case["name"]
+            got, want = [_bits(s) for s in sc], r["expect_score_bits"]
+            # NaN payloads may differ between runtimes; everything else must match to the bit
+            assert all(g == w or (math.isnan(s) and int(w, 16) & 0x7FF0000000000000 == 0x7FF0000000000000) for g, w, s in zip(got, want, sc)), case["name"]
+        for r_i in range(rows.shape[0]):
+            c = oc.cosine(q, rows[r_i])
+            w = r["cosine_bits_all_rows"][r_i]
+            assert _bits(c) == w or math.isnan(c), (case["name"], r_i)
+
+
+@pytest.mark.skipif(not os.path.exists(os.path.join(_FROM_DOTNET, "synth_v1.json")), reason=_UNPINNED)
+def test_from_dotnet_seeded_queries_equal_the_oracle_bit_for_bit():
+    with open(os.path.join(_FROM_DOTNET, "synth_v1.json")) as f:
+        ref = json.load(f)["queries"]
+    for c, r in zip(_load("synth_v1.json")["queries"], ref):
+        assert (c["n"], c["dim"], c["top_k"]) == (r["n"], r["dim"], r["top_k"])
+        corpus, q = _corpus(c)
+        idx, sc = oc.query(corpus, q, c["top_k"])
+        assert [int(i) for i in idx] == r["expect_idx"]
+        assert [_bits(s) for s in sc] == r["expect_score_bits"]
+
+
+def test_every_csharp_fact_the_equivalence_rests_on_has_a_named_case():
+    """The oracle equals the C# only if three facts about .NET hold.  Each is exercised by at least one
+    known-answer case that would come out differently if the fact did not hold -- so the moment GoldenDump runs, a wrong
+    assumption shows up as a failing named case rather than as noise in a large corpus."""
+    facts = {c.get("pins_csharp_fact") for c in _load("kat_v1.json")} - {None}
+    assert any("fp32" in f for f in facts)
+    assert any("index order" in f for f in facts)
+    assert any("stable" in f for f in facts)
+    names = {c["name"] for c in _load("kat_v1.json")}
+    assert {"fp32_product_rounding", "sequential_fp64_order", "sequential_not_pairwise_sum", "stable_sort_first_of_many_equal_keys"} <= names
