@@ -91,6 +91,21 @@ typedef struct ragstore_cand {
 RAGSTORE_API int ragstore_create(int dim, int dtype, int64_t capacity_rows, int device,
                                  uint32_t flags, ragstore_t** out);
 
+/* The same store over several GPUs of THIS process, behind the same handle.  The reference's index is one object in one
+ * process -- a DI singleton (Program.cs:35,43) that every handler queries (Program.cs:72,116) -- so a corpus larger than
+ * one GPU (100M x 768) must still be one `RagIndex` holding one handle.  ragstore_add deals the rows to the
+ * devices in blocks of block_rows (0 = 65536), round-robin, in insertion order, and a row's id stays its place in that
+ * order (RagIndex.cs:48); ragstore_search launches every shard's scan from the calling thread on per-device streams,
+ * the shards store their rescored hits straight into the first device's memory (peer access over NVLink; the copy
+ * engine where there is none) and one merge kernel there returns the hits in the order a single index would
+ * (RagIndex.cs:64-65).  ragstore_add, ragstore_add_many, ragstore_reserve_rows, ragstore_count, ragstore_search (any
+ * top_k up to 8128, batches on the tensor cores of every device), ragstore_search_coalesced, ragstore_info and
+ * ragstore_destroy accept the handle; the per-device entry points (ragstore_search_device, ragstore_search_shard_*,
+ * ragstore_device_views, ragstore_set_row_*) return RAGSTORE_ERR_INVALID and ragstore_save RAGSTORE_ERR_UNSUPPORTED.
+ * A device may be listed more than once (several shards on one GPU). */
+RAGSTORE_API int ragstore_create_sharded(int dim, int dtype, int64_t capacity_rows, const int* devices, int n_devices,
+                                         int64_t block_rows, uint32_t flags, ragstore_t** out);
+
 RAGSTORE_API int ragstore_destroy(ragstore_t* s);
 
 /* ---- store side --------------------------------------------------------------------------- */

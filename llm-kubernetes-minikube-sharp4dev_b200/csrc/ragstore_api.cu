@@ -16,8 +16,7 @@
 #include <string>
 #include <vector>
 
-#include "ragstore_internal.h"
-#include "vmm_buffer.h"
+#include "store_impl.h"
 
 using namespace rag;
 
@@ -40,46 +39,9 @@ int fail(int code, const char* what, const char* detail = nullptr) {
         if (e__ != cudaSuccess) return fail(RAGSTORE_ERR_CUDA, #expr, cudaGetErrorString(e__)); \
     } while (0)
 
-struct DeviceGuard {
-    int prev = -1;
-    bool ok = false;
-    explicit DeviceGuard(int dev) {
-        if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
-        if (prev == dev) {
-            prev = -1;  // already there: nothing to switch, nothing to restore
-            ok = true;
-        } else {
-            ok = cudaSetDevice(dev) == cudaSuccess;
-        }
-    }
-    ~DeviceGuard() {
-        if (prev >= 0) cudaSetDevice(prev);
-    }
-};
+}  // namespace
 
-constexpr int kCtxQueries = 256; // queries per host-search context batch (= one tensor-core launch)
-constexpr int kNumCtx = 4;       // concurrent host searches per store
-constexpr int kMaxPasses = 32;   // top_k > 256 is served by repeated scans of 256 candidates each
-constexpr int kMaxTake = kMaxPasses * kMaxKp - 64;
-
-struct SearchCtx {
-    cudaStream_t st = nullptr;
-    ScanScratch scratch{};
-    uint8_t* batch_scratch = nullptr;  // candidate lists + query operand of the tensor-core path
-    ragstore_cand* d_pass = nullptr;   // top_k > 256: the rescored candidates of up to kMaxPasses scans
-    double* d_bound = nullptr;         // [1] + uint64 last key [1]
-    float* d_q = nullptr;
-    int64_t* d_idx = nullptr;
-    double* d_score = nullptr;
-    int32_t* d_found = nullptr;
-    int32_t* d_flags = nullptr;
-    float* h_q = nullptr;  // pinned mirrors
-    int64_t* h_idx = nullptr;
-    double* h_score = nullptr;
-    int32_t* h_found = nullptr;
-    int32_t* h_flags = nullptr;
-};
-
+namespace rag {
 int choose_kp(int take) {
     // candidate list = requested hits + a safety margin that the certificate can use
     const int want = take + (take / 4 > 8 ? take / 4 : 8);
@@ -97,67 +59,12 @@ float scan_eps(int dim_ld, int dtype) {
     return static_cast<float>((terms + 16) * 5.9604644775390625e-08);
 }
 
-}  // namespace
+}  // namespace rag
 
 namespace rag {
 int api_fail(int code, const char* what, const char* detail) { return fail(code, what, detail); }
 }  // namespace rag
 
-struct ragstore {
-    int device = 0, dim = 0, ld = 0, dtype = 0, sm_count = 0;
-    int64_t capacity = 0;
-    std::atomic<int64_t> count{0};
-    int64_t row_base = 0;
-    int64_t row_block = 0;
-    int row_nshards = 1, row_shard = 0;
-    mutable std::atomic<int64_t> n_scan_launches{0}, n_batch_launches{0};  // kernel launches issued by searches
-    VmmBuffer mat_buf, rnorm_buf, exact_buf, slot_buf, raw_buf;  // address-stable, grown on demand
-    void* mat = nullptr;
-    float* rnorm = nullptr;
-    uint8_t* exact = nullptr;
-    int32_t* raw_slot = nullptr;   // null when the store keeps no sidecar
-    float* raw_rows = nullptr;
-    int raw_ld = 0;
-    int64_t raw_used = 0;          // sidecar rows in use (host copy, refreshed after every add)
-    int64_t inexact_rows = 0;      // rows stored inexactly (host copy, refreshed after every add)
-    unsigned long long* d_inexact = nullptr;  // [0] inexact rows, then [1] raw_count (u32), [2] min_norm_bits (u32)
-    unsigned int* d_raw_count = nullptr;
-    uint32_t* d_min_norm = nullptr;
-    cudaStream_t ingest_stream = nullptr;
-    cudaStream_t dev_stream = nullptr;
-    std::mutex add_mu;
-    float* d_stage = nullptr;      // device staging (bf16 stores fed from the host), two chunks
-    size_t stage_floats = 0;
-    float* h_stage[2] = {nullptr, nullptr};   // pinned host staging, one per pipeline slot
-    cudaEvent_t ingest_ev[2] = {nullptr, nullptr};
-    cudaEvent_t k1_ev0[2] = {nullptr, nullptr}, k1_ev1[2] = {nullptr, nullptr};  // bracket the K1 launches (profiling aid)
-    double last_add_kernel_us = 0.0;
-    unsigned long long* h_counters = nullptr; // pinned: per slot [inexact rows, sidecar rows]
-    // coalescing of concurrent single-query callers (ragstore_search_coalesced)
-    struct Pending {
-        const float* q;
-        int top_k;
-        int64_t* idx;
-        double* score;
-        int32_t* found;
-        int32_t* flags;
-        int status = 0;
-        bool done = false;
-        std::string err;
-    };
-    std::mutex co_mu;
-    std::condition_variable co_cv;
-    std::vector<Pending*> co_queue;
-    bool co_leader = false;
-    int co_window_us = 0, co_max_batch = 256;
-    ScanScratch dev_scratch{};
-    uint8_t* dev_batch_scratch = nullptr;
-    std::vector<SearchCtx> ctxs;
-    std::vector<int> free_ctx;
-    std::mutex ctx_mu;
-    std::condition_variable ctx_cv;
-    size_t elem_size() const { return dtype == RAGSTORE_F32 ? 4 : 2; }
-};
 
 namespace {
 
@@ -211,6 +118,10 @@ void free_ctx(SearchCtx& c) {
     cudaFreeHost(c.h_idx);
     c = SearchCtx{};
 }
+
+}  // namespace
+
+namespace rag {
 
 ScanArgs base_args(const ragstore* s, int64_t n, int take, int kp) {
     ScanArgs a{};
@@ -271,6 +182,26 @@ bool batch_eligible(const ragstore* s, int64_t n, int nq, int kp) {
     const double t_batch = 62e-6 + (1.0 + 1.0 / stride) * bytes / (nq <= 128 ? 6.2e12 : 4.5e12);
     return nq * t_scan > t_batch;
 }
+
+int acquire_ctx(ragstore* s) {
+    std::unique_lock<std::mutex> lk(s->ctx_mu);
+    s->ctx_cv.wait(lk, [&] { return !s->free_ctx.empty(); });
+    const int ci = s->free_ctx.back();
+    s->free_ctx.pop_back();
+    return ci;
+}
+
+void release_ctx(ragstore* s, int ci) {
+    {
+        std::lock_guard<std::mutex> lk(s->ctx_mu);
+        s->free_ctx.push_back(ci);
+    }
+    s->ctx_cv.notify_one();
+}
+
+}  // namespace rag
+
+namespace {
 
 // One tensor-core launch for up to kBatchMaxQ queries (outputs laid out with `stride` hits per query).
 int run_batch(const ragstore* s, int64_t n, int take, const float* d_q, int nq, int64_t* d_idx, double* d_score,
@@ -394,6 +325,7 @@ int ragstore_create(int dim, int dtype, int64_t capacity_rows, int device, uint3
 
 int ragstore_destroy(ragstore_t* s) {
     if (!s) return RAGSTORE_OK;
+    if (s->sharded || !s->shards.empty()) return sharded_destroy(s);
     DeviceGuard g(s->device);
     cudaDeviceSynchronize();
     for (auto& c : s->ctxs) free_ctx(c);
@@ -427,6 +359,7 @@ int ragstore_count(ragstore_t* s, int64_t* out_rows) {
 
 int ragstore_set_row_base(ragstore_t* s, int64_t row_base) {
     if (!s || row_base < 0) return fail(RAGSTORE_ERR_INVALID, "ragstore_set_row_base: bad argument");
+    if (s && s->sharded) return fail(RAGSTORE_ERR_INVALID, "ragstore_set_row_base: per-device entry point, not available on a multi-device handle (ragstore_create_sharded)");
     s->row_base = row_base;
     return RAGSTORE_OK;
 }
@@ -434,6 +367,7 @@ int ragstore_set_row_base(ragstore_t* s, int64_t row_base) {
 int ragstore_set_row_blocking(ragstore_t* s, int64_t block_rows, int n_shards, int shard_index) {
     if (!s || block_rows < 0 || n_shards < 1 || shard_index < 0 || shard_index >= n_shards)
         return fail(RAGSTORE_ERR_INVALID, "ragstore_set_row_blocking: bad argument");
+    if (s && s->sharded) return fail(RAGSTORE_ERR_INVALID, "ragstore_set_row_blocking: per-device entry point, not available on a multi-device handle (ragstore_create_sharded)");
     s->row_block = block_rows;
     s->row_nshards = n_shards;
     s->row_shard = shard_index;
@@ -457,6 +391,7 @@ int ragstore_add_many(ragstore_t* s, const float* const* blocks, const int64_t* 
 int ragstore_reserve_rows(ragstore_t* s, int64_t n_rows) {
     if (!s || n_rows < 0) return fail(RAGSTORE_ERR_INVALID, "ragstore_reserve_rows: bad argument");
     if (n_rows > s->capacity) return fail(RAGSTORE_ERR_CAPACITY, "ragstore_reserve_rows: above the capacity fixed at create");
+    if (s->sharded) return sharded_reserve_rows(s, n_rows);
     std::lock_guard<std::mutex> lk(s->add_mu);
     DeviceGuard g(s->device);
     if (!g.ok) return fail(RAGSTORE_ERR_CUDA, "cudaSetDevice failed");
@@ -474,6 +409,7 @@ int ragstore_reserve_rows(ragstore_t* s, int64_t n_rows) {
 int ragstore_add(ragstore_t* s, const float* rows, int64_t n_rows, int row_dim, uint32_t flags, int64_t* out_first_row) {
     if (!s || (!rows && n_rows > 0) || n_rows < 0) return fail(RAGSTORE_ERR_INVALID, "ragstore_add: null/negative argument");
     if (row_dim != s->dim) return fail(RAGSTORE_ERR_INVALID, "ragstore_add: row_dim differs from the store's dim");
+    if (s->sharded) return sharded_add(s, rows, n_rows, flags, out_first_row);
     std::lock_guard<std::mutex> lk(s->add_mu);
     const int64_t first = s->count.load(std::memory_order_acquire);
     if (out_first_row) *out_first_row = first;
@@ -611,6 +547,7 @@ int ragstore_add(ragstore_t* s, const float* rows, int64_t n_rows, int row_dim, 
 
 int ragstore_info(ragstore_t* s, int64_t* out, int n) {
     if (!s || !out) return fail(RAGSTORE_ERR_INVALID, "ragstore_info: null argument");
+    if (s->sharded) return sharded_info(s, out, n);
     DeviceGuard g(s->device);
     unsigned long long inexact = 0;
     CU_TRY(cudaMemcpy(&inexact, s->d_inexact, sizeof(inexact), cudaMemcpyDeviceToHost));
@@ -635,6 +572,7 @@ int ragstore_info(ragstore_t* s, int64_t* out, int n) {
 
 int ragstore_debug_stamps(ragstore_t* s, uint64_t* out, int n) {
     if (!s || !out) return fail(RAGSTORE_ERR_INVALID, "ragstore_debug_stamps: null argument");
+    if (s && s->sharded) return fail(RAGSTORE_ERR_INVALID, "ragstore_debug_stamps: per-device entry point, not available on a multi-device handle (ragstore_create_sharded)");
     DeviceGuard g(s->device);
     uint64_t v[8] = {0};
     CU_TRY(cudaMemcpy(v, s->dev_scratch.stamps, sizeof(v), cudaMemcpyDeviceToHost));
@@ -644,6 +582,7 @@ int ragstore_debug_stamps(ragstore_t* s, uint64_t* out, int n) {
 
 int ragstore_device_views(ragstore_t* s, void** d_matrix, float** d_rnorm, uint8_t** d_exact) {
     if (!s) return fail(RAGSTORE_ERR_INVALID, "ragstore_device_views: null store");
+    if (s && s->sharded) return fail(RAGSTORE_ERR_INVALID, "ragstore_device_views: per-device entry point, not available on a multi-device handle (ragstore_create_sharded)");
     if (d_matrix) *d_matrix = s->mat;
     if (d_rnorm) *d_rnorm = s->rnorm;
     if (d_exact) *d_exact = s->exact;
@@ -653,6 +592,7 @@ int ragstore_device_views(ragstore_t* s, void** d_matrix, float** d_rnorm, uint8
 int ragstore_search_device(ragstore_t* s, const float* d_queries, int n_queries, int top_k, int64_t* d_idx,
                            double* d_score, int32_t* d_found, int32_t* d_flags, void* stream) {
     if (!s || !d_queries || n_queries < 0 || !d_idx || !d_score) return fail(RAGSTORE_ERR_INVALID, "ragstore_search_device: null argument");
+    if (s && s->sharded) return fail(RAGSTORE_ERR_INVALID, "ragstore_search_device: per-device entry point, not available on a multi-device handle (ragstore_create_sharded)");
     DeviceGuard g(s->device);
     cudaStream_t st = stream ? static_cast<cudaStream_t>(stream) : s->dev_stream;
     const int64_t n = s->count.load(std::memory_order_acquire);
@@ -696,6 +636,7 @@ int ragstore_search_device(ragstore_t* s, const float* d_queries, int n_queries,
 static int search_shard_impl(ragstore_t* s, const float* d_query, const float* h_query, int top_k, ragstore_cand* d_out,
                              int32_t* d_flags, void* stream) {
     if (!s || (!d_query && !h_query) || !d_out) return fail(RAGSTORE_ERR_INVALID, "ragstore_search_shard: null argument");
+    if (s && s->sharded) return fail(RAGSTORE_ERR_INVALID, "ragstore_search_shard: per-device entry point, not available on a multi-device handle (ragstore_create_sharded)");
     if (h_query && s->dim > kParamQueryMax)
         return fail(RAGSTORE_ERR_UNSUPPORTED, "ragstore_search_shard_hostq: rows above 1024 elements need the query in device memory");
     DeviceGuard g(s->device);
@@ -740,6 +681,7 @@ int ragstore_search_shard_hostq(ragstore_t* s, const float* h_query, int top_k, 
 int ragstore_search_shard_batch_device(ragstore_t* s, const float* d_queries, int n_queries, int top_k, ragstore_cand* d_out,
                                        int32_t* d_flags, void* stream) {
     if (!s || !d_queries || !d_out || n_queries < 1) return fail(RAGSTORE_ERR_INVALID, "ragstore_search_shard_batch_device: bad argument");
+    if (s && s->sharded) return fail(RAGSTORE_ERR_INVALID, "ragstore_search_shard_batch_device: per-device entry point, not available on a multi-device handle (ragstore_create_sharded)");
     DeviceGuard g(s->device);
     cudaStream_t st = stream ? static_cast<cudaStream_t>(stream) : s->dev_stream;
     const int64_t n = s->count.load(std::memory_order_acquire);
@@ -812,9 +754,17 @@ int ragstore_merge_shards_device(const ragstore_cand* d_gathered, int n_shards, 
 
 int ragstore_search(ragstore_t* s, const float* queries, int n_queries, int query_dim, int top_k, int64_t* out_idx,
                     double* out_score, int32_t* out_found, int32_t* out_flags) {
+    return rag::search_host_limited(s, -1, queries, n_queries, query_dim, top_k, out_idx, out_score, out_found, out_flags);
+}
+
+}  // extern "C"
+
+int rag::search_host_limited(ragstore* s, int64_t n_limit, const float* queries, int n_queries, int query_dim, int top_k, int64_t* out_idx,
+                             double* out_score, int32_t* out_found, int32_t* out_flags) {
     if (!s || n_queries < 0 || (n_queries > 0 && (!queries || !out_idx || !out_score || !out_found)))
         return fail(RAGSTORE_ERR_INVALID, "ragstore_search: null argument");
-    const int64_t n = s->count.load(std::memory_order_acquire);  // snapshot: a prefix of the appended rows
+    int64_t n = s->count.load(std::memory_order_acquire);  // snapshot: a prefix of the appended rows
+    if (n_limit >= 0 && n_limit < n) n = n_limit;
     const int req = top_k < 1 ? 1 : top_k;                       // Math.Max(1, topK)
     const int take = static_cast<int>(std::min<int64_t>(n, req));
     if (n == 0 || n_queries == 0) {
@@ -839,26 +789,15 @@ int ragstore_search(ragstore_t* s, const float* queries, int n_queries, int quer
         return RAGSTORE_OK;
     }
     if (take > kMaxTake) return fail(RAGSTORE_ERR_UNSUPPORTED, "more than 8128 hits per query are not covered");
+    if (s->sharded) return sharded_search(s, queries, n_queries, top_k, out_idx, out_score, out_found, out_flags);
     DeviceGuard g(s->device);
     if (!g.ok) return fail(RAGSTORE_ERR_CUDA, "cudaSetDevice failed");
 
-    int ci;
-    {
-        std::unique_lock<std::mutex> lk(s->ctx_mu);
-        s->ctx_cv.wait(lk, [&] { return !s->free_ctx.empty(); });
-        ci = s->free_ctx.back();
-        s->free_ctx.pop_back();
-    }
+    const int ci = acquire_ctx(s);
     struct Release {
         ragstore* s;
         int ci;
-        ~Release() {
-            {
-                std::lock_guard<std::mutex> lk(s->ctx_mu);
-                s->free_ctx.push_back(ci);
-            }
-            s->ctx_cv.notify_one();
-        }
+        ~Release() { release_ctx(s, ci); }
     } rel{s, ci};
     SearchCtx& c = s->ctxs[ci];
 
@@ -998,6 +937,8 @@ int ragstore_search(ragstore_t* s, const float* queries, int n_queries, int quer
     return RAGSTORE_OK;
 }
 
+extern "C" {
+
 int ragstore_hit_filters(const double* scores, int found, double evidence_min_score, double best_factor,
                          double low_score_floor, uint8_t* out_cited, double* out_best, int32_t* out_low_score) {
     if (found < 0 || (found > 0 && !scores)) return fail(RAGSTORE_ERR_INVALID, "ragstore_hit_filters: bad argument");
@@ -1048,6 +989,7 @@ int copy_in(FILE* f, void* d_dst, size_t bytes, void* h_pin, size_t pin_bytes) {
 
 int ragstore_save(ragstore_t* s, const char* path) {
     if (!s || !path) return fail(RAGSTORE_ERR_INVALID, "ragstore_save: null argument");
+    if (s->sharded) return fail(RAGSTORE_ERR_UNSUPPORTED, "ragstore_save: a multi-device handle is not saved as one image yet");
     std::lock_guard<std::mutex> lk(s->add_mu);  // no append while the image is written
     DeviceGuard g(s->device);
     FILE* f = fopen(path, "wb");

@@ -43,6 +43,7 @@ def lib():
             "ragstore_version": (C.c_int, []),
             "ragstore_last_error": (C.c_int, [C.c_char_p, C.c_int]),
             "ragstore_create": (C.c_int, [C.c_int, C.c_int, C.c_int64, C.c_int, C.c_uint32, C.POINTER(vp)]),
+            "ragstore_create_sharded": (C.c_int, [C.c_int, C.c_int, C.c_int64, C.POINTER(C.c_int), C.c_int, C.c_int64, C.c_uint32, C.POINTER(vp)]),
             "ragstore_destroy": (C.c_int, [vp]),
             "ragstore_add": (C.c_int, [vp, vp, C.c_int64, C.c_int, C.c_uint32, i64p]),
             "ragstore_count": (C.c_int, [vp, i64p]),
@@ -112,6 +113,16 @@ class RagStore:
             self._h = C.c_void_p()
             check(lib().ragstore_create(dim, dtype, capacity_rows, device, flags, C.byref(self._h)))
         self.dim, self.dtype, self.device, self.capacity = dim, dtype, device, capacity_rows
+
+    @classmethod
+    def create_sharded(cls, dim: int, capacity_rows: int, devices, dtype: int = RAGSTORE_F32, block_rows: int = 0, flags: int = 0) -> "RagStore":
+        """One handle over several GPUs of this process (ragstore_create_sharded): same add/search/count calls."""
+        devs = (C.c_int * len(devices))(*[int(d) for d in devices])
+        h = C.c_void_p()
+        check(lib().ragstore_create_sharded(dim, dtype, capacity_rows, devs, len(devices), block_rows, flags, C.byref(h)))
+        st = cls(dim, capacity_rows, dtype, int(devices[0]), _handle=h)
+        st.devices = [int(d) for d in devices]
+        return st
 
     def add_many(self, blocks, prenormalised: bool = False) -> int:
         """Append a list of C-contiguous float32 host arrays (rows x dim each) with ONE native call; each block is

@@ -44,6 +44,19 @@ int main(void) {
     if (ragstore_search(st, q, 1, 2, 3, idx, score, &found, &flags)) return fail("search dim mismatch");
     if (found != 3 || idx[0] != 0 || idx[2] != 2 || score[0] != -1.0) return fail("dim mismatch semantics");
     if (ragstore_destroy(st)) return fail("destroy");
+    /* the same corpus behind ONE handle over two shards (the same GPU listed twice when the box has only one):
+     * blocks of 2 rows are dealt round-robin, ids stay insertion order, the answer is the same */
+    {
+        const int devices[2] = {0, 0};
+        if (ragstore_create_sharded(3, RAGSTORE_F32, 16, devices, 2, 2, RAGSTORE_CREATE_DEFAULT, &st)) return fail("create_sharded");
+        if (ragstore_add(st, &rows[0][0], 3, 3, RAGSTORE_ADD_HOST, &first) || first != 0) return fail("sharded add 1");
+        if (ragstore_add(st, &rows[3][0], 1, 3, RAGSTORE_ADD_HOST, &first) || first != 3) return fail("sharded add 2");
+        if (ragstore_count(st, &count) || count != 4) return fail("sharded count");
+        if (ragstore_search(st, q, 1, 3, 4, idx, score, &found, &flags)) return fail("sharded search");
+        if (found != 4 || idx[0] != 3 || idx[1] != 1 || idx[2] != 0 || idx[3] != 2) return fail("sharded order");
+        if (score[0] != s3 || score[1] != s1 || score[2] != 0.0 || score[3] != 0.0) return fail("sharded scores");
+        if (ragstore_destroy(st)) return fail("sharded destroy");
+    }
     printf("abi_smoke ok\n");
     return 0;
 }

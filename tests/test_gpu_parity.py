@@ -898,3 +898,83 @@ def test_closed_loop_clients_all_return_from_coalesced_search():
     assert not errors
     # no single call may take a sizeable part of the whole run (the old leader served every batch until the queue emptied)
     assert max(worst) < max(0.25, total / 4), (max(worst), total)
+
+
+# ---------------------------------------------------------------- one handle over several devices (ragstore_create_sharded)
+def _sharded_devices(n):
+    """The driver's test box has one GPU: listing it several times makes several shards on one device, which exercises
+    the same dealing, per-shard limits, cross-stream events and merge as distinct devices do (tests/test_gpu_multi.py
+    runs the same cases over real peers)."""
+    import torch
+    g = torch.cuda.device_count()
+    return [i % g for i in range(n)]
+
+
+@pytest.mark.parametrize("n,d,k,shards,block,dtype", [(5000, 96, 10, 2, 64, 0), (3001, 64, 100, 3, 100, 0), (4000, 128, 7, 4, 1000, 1),
+                                                      (50, 32, 10, 3, 16, 0), (9000, 64, 300, 2, 256, 0)])
+def test_sharded_handle_matches_oracle(n, d, k, shards, block, dtype):
+    """One RagIndex, one handle (Program.cs:35,43), rows dealt over several shards: appends in uneven pieces, single
+    queries, small batches, k beyond one launch -- always the oracle's hits over the whole corpus, bit for bit."""
+    bf = dtype == 1
+    rows = oc.synth_rows(0, n, d, 21, round_bf16=bf)
+    rows[7] = rows[42]                      # a tie across shards: the lower GLOBAL id must win
+    rows[n - 3] = rows[42]
+    qs = oc.synth_rows(0, 5, d, 22)
+    st = rb.RagStore.create_sharded(d, n, _sharded_devices(shards), dtype=rb.RAGSTORE_BF16 if bf else rb.RAGSTORE_F32, block_rows=block)
+    try:
+        cuts = [0, 1, block - 1, block + 3, n // 2, n]
+        cuts = sorted(set(min(max(c, 0), n) for c in cuts))
+        for a, b in zip(cuts, cuts[1:]):
+            first = st.add(rows[a:b], prenormalised=bf)
+            assert first == a
+            assert st.count() == b
+            # a search between appends sees exactly the prefix
+            idx, sc, found, flags = st.search(qs[0], k)
+            eidx, esc = oc.query(rows[:b], qs[0], k, n_threads=2)
+            assert list(idx[0, :found[0]]) == list(eidx), (a, b)
+            assert np.array_equal(sc[0, :found[0]].view(np.uint64), esc.view(np.uint64))
+        idx, sc, found, flags = st.search(qs, k)      # a small batch
+        for i in range(len(qs)):
+            eidx, esc = oc.query(rows, qs[i], k, n_threads=2)
+            assert found[i] == len(eidx) and list(idx[i, :found[i]]) == list(eidx), i
+            assert np.array_equal(sc[i, :found[i]].view(np.uint64), esc.view(np.uint64)), i
+            assert flags[i] & rb.RAGSTORE_HIT_EXACT_ROWS
+        idx, sc, found, _ = st.search(np.ones(d - 1, dtype=np.float32), 4)      # RagIndex.cs:126 on the global order
+        assert list(idx[0, :found[0]]) == list(range(min(4, n))) and (sc[0, :found[0]] == -1.0).all()
+        info = st.info()
+        assert info["count"] == n and info["scratch_overlaps"] == 0
+        with pytest.raises(rb.RagStoreError):
+            st.device_views()
+    finally:
+        st.close()
+
+
+def test_sharded_handle_batches_take_the_tensor_core_path():
+    n, d, nq, k = 40000, 256, 96, 10
+    rows = oc.synth_rows(0, n, d, 31)
+    qs = oc.synth_rows(0, nq, d, 32)
+    st = rb.RagStore.create_sharded(d, n, _sharded_devices(2), block_rows=4096)
+    try:
+        st.add(rows)
+        idx, sc, found, flags = st.search(qs, k)
+        assert st.info()["batch_launches"] >= 2          # one per shard
+        for i in range(0, nq, 5):
+            eidx, esc = oc.query(rows, qs[i], k, n_threads=4)
+            assert list(idx[i]) == list(eidx), i
+            assert np.array_equal(sc[i].view(np.uint64), esc.view(np.uint64)), i
+            assert flags[i] & rb.RAGSTORE_HIT_CERTIFIED
+        # concurrent single-query callers through the coalescing entry point, on the sharded handle
+        import threading
+        out = [None] * 12
+        def ask(i):
+            out[i] = st.search_coalesced(qs[i], 5)
+        ts = [threading.Thread(target=ask, args=(i,)) for i in range(12)]
+        for t in ts:
+            t.start()
+        for t in ts:
+            t.join()
+        for i in range(12):
+            eidx, esc = oc.query(rows, qs[i], 5, n_threads=2)
+            assert list(out[i][0]) == list(eidx) and np.array_equal(out[i][1].view(np.uint64), esc.view(np.uint64))
+    finally:
+        st.close()
