@@ -39,6 +39,8 @@ class ShardedSearcher:
     """One shard (a RagStore on this rank's GPU) + the exchange.  `all_gather(out, inp)` defaults to
     torch.distributed.all_gather_into_tensor; tests inject their own."""
 
+    WIDE_K = 200    # a request for 200 hits makes every shard keep its widest candidate lists (256 keys)
+
     def __init__(self, store, rank: int, world: int, row_base: int, max_k: int = 256,
                  all_gather: Optional[Callable] = None, device: Optional[int] = None, exchange: str = "nccl",
                  max_queries: int = 256):
@@ -49,12 +51,14 @@ class ShardedSearcher:
         self.device = torch.cuda.current_device() if device is None else device
         store.set_row_base(row_base)
         self.max_k = max_k
+        max_k = max(max_k, self.WIDE_K)      # room for the wide redo of an uncertified query (search_batch)
         self.d_cand = torch.zeros(max_k * CAND_BYTES, dtype=torch.uint8, device="cuda")
         self.d_all = torch.zeros(world * max_k * CAND_BYTES, dtype=torch.uint8, device="cuda")
         self.d_idx = torch.zeros(max_k, dtype=torch.int64, device="cuda")
         self.d_score = torch.zeros(max_k, dtype=torch.float64, device="cuda")
         self.d_found = torch.zeros(1, dtype=torch.int32, device="cuda")
         self.d_flags = torch.zeros(1, dtype=torch.int32, device="cuda")
+        self.last_flags = None      # RAGSTORE_HIT_* of the last synchronous search, ANDed over all shards
         if all_gather is None:
             import torch.distributed as dist
             all_gather = dist.all_gather_into_tensor
@@ -72,7 +76,7 @@ class ShardedSearcher:
         torch, native = self.torch, self.native
         px, ok = None, 1
         try:
-            px = native.PeerExchange(self.device, self.world, self.rank, max_records=max_k * max_queries, max_queries=max_queries)
+            px = native.PeerExchange(self.device, self.world, self.rank, max_records=max(max_k * max_queries, self.WIDE_K), max_queries=max_queries)
             mine = torch.frombuffer(bytearray(px.handle), dtype=torch.uint8).cuda()
         except native.RagStoreError:
             ok, mine = 0, torch.zeros(native.EXCHANGE_HANDLE_BYTES, dtype=torch.uint8, device="cuda")
@@ -101,7 +105,7 @@ class ShardedSearcher:
         """Enqueue shard search -> all-gather -> merge on the current torch stream; results stay on the device
         (self.d_idx / d_score / d_found).  Every rank ends with the same global top-k."""
         req = max(1, int(k))
-        if req > self.max_k:
+        if req > max(self.max_k, self.WIDE_K):
             raise ValueError("k above max_k")
         stream = _current_stream_handle(self.torch)
         per, total = gather_layout(self.world, req)
@@ -144,10 +148,47 @@ class ShardedSearcher:
         if np_meta[1] != 0:
             raise RuntimeError("peer exchange timed out: a rank did not publish its hits within 5 s")
         n = int(np_meta[0])
+        self.last_flags = int(self.global_flags(self.d_flags)[0])
         return np_idx[:n], np_sc[:n]
 
+    def global_flags(self, d_flags):
+        """RAGSTORE_HIT_* bits ANDed over all shards (a collective when world > 1): a result is certified / exact only if
+        every shard's part of it is.  Returns a host numpy array."""
+        f = d_flags.clone()
+        if self.world > 1:
+            import torch.distributed as dist
+            dist.all_reduce(f, op=dist.ReduceOp.BAND)
+        return f.cpu().numpy()
+
+    def search_batch(self, d_queries, n_queries: int, k: int):
+        """Synchronous batched search WITH the certificate handled: queries that some shard's tensor-core pass could not
+        certify (tf32 / bf16 scores, eps ~2e-3) are run again through the fp32 scan on every shard, as ragstore_search does
+        on a single store; what is still uncertified comes back with the flag clear.  Returns host arrays
+        (idx [nq, k], score [nq, k], found [nq], flags [nq])."""
+        torch = self.torch
+        req = max(1, int(k))
+        bi, bs, bf = self.search_batch_device(d_queries, n_queries, k)
+        torch.cuda.current_stream().synchronize()
+        if self.peer is not None and int(self.d_status[:n_queries].abs().sum().item()) != 0:
+            raise RuntimeError("peer exchange timed out: a rank did not publish its hits within 5 s")
+        flags = self.global_flags(self._b_flags[:n_queries])
+        idx, sc, found = bi.cpu().numpy().copy(), bs.cpu().numpy().copy(), bf.cpu().numpy().copy()
+        for q in range(n_queries):
+            if flags[q] & 1:
+                continue
+            # every rank sees the same ANDed flags, so every rank takes this branch for the same queries.  Asking for
+            # WIDE_K hits runs the fp32 scan with 256-key candidate lists on every shard; the first k of that answer
+            # are the top k (the order is total), certified by a far wider margin.
+            i1, s1 = self.search(d_queries[q], max(req, self.WIDE_K))
+            m = min(len(i1), req)
+            idx[q, :m], sc[q, :m], found[q] = i1[:m], s1[:m], m
+            flags[q] = self.last_flags
+        return idx, sc, found, flags
+
     def search_batch_device(self, d_queries, n_queries: int, k: int):
-        """Batched form (tensor-core path on each shard): returns device tensors (idx [nq, k], score, found)."""
+        """Batched form (tensor-core path on each shard): returns device tensors (idx [nq, k], score, found).  The
+        per-shard RAGSTORE_HIT_* flags of this rank land in self._b_flags; global_flags() combines them across ranks
+        (search_batch does, and redoes what is uncertified)."""
         torch = self.torch
         req = max(1, int(k))
         need = n_queries * req * CAND_BYTES
@@ -157,9 +198,10 @@ class ShardedSearcher:
             self._b_idx = torch.zeros(n_queries * req, dtype=torch.int64, device="cuda")
             self._b_score = torch.zeros(n_queries * req, dtype=torch.float64, device="cuda")
             self._b_found = torch.zeros(n_queries, dtype=torch.int32, device="cuda")
+            self._b_flags = torch.zeros(n_queries, dtype=torch.int32, device="cuda")
             self._b_cap = need
         stream = _current_stream_handle(torch)
-        self.store.search_shard_batch_device(d_queries, n_queries, k, self._b_cand, None, stream=stream)
+        self.store.search_shard_batch_device(d_queries, n_queries, k, self._b_cand, self._b_flags, stream=stream)
         if self.peer is not None and n_queries <= self.peer.max_queries and n_queries * req <= self.peer.max_records:
             self.peer.merge(self._b_cand, n_queries, req, k, self._b_idx, self._b_score, self._b_found, self.d_status, stream=stream)
             return self._b_idx[: n_queries * req].view(n_queries, req), self._b_score[: n_queries * req].view(n_queries, req), self._b_found[:n_queries]
@@ -178,4 +220,5 @@ class ShardedSearcher:
         if self.peer is not None and int(self.d_status[0].item()) != 0:
             raise RuntimeError("peer exchange timed out: a rank did not publish its hits within 5 s")
         n = int(self.d_found.item())
+        self.last_flags = int(self.global_flags(self.d_flags)[0])
         return self.d_idx[:n].cpu().numpy(), self.d_score[:n].cpu().numpy()
