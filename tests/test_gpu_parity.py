@@ -978,3 +978,30 @@ def test_sharded_handle_batches_take_the_tensor_core_path():
             assert list(out[i][0]) == list(eidx) and np.array_equal(out[i][1].view(np.uint64), esc.view(np.uint64))
     finally:
         st.close()
+
+
+def test_sharded_handle_redoes_queries_a_shard_could_not_certify():
+    """Rows crowding around a query closer than the tensor-core pass can tell apart: some shard's certificate fails, that
+    shard's part of the query is run again with the widest candidate lists, and the merged answer is still the oracle's."""
+    n, d, k, nq = 24000, 256, 10, 16
+    rows = oc.synth_rows(0, n, d, 1234)
+    q0 = oc.synth_rows(0, 1, d, 5678)[0].astype(np.float64)
+    for j in range(220):
+        eps = 0.014 if j < 20 else 0.045
+        r = 97 * j + 11
+        v = q0 + eps * rows[r].astype(np.float64)
+        rows[r] = (v / np.linalg.norm(v)).astype(np.float32)
+    qs = oc.synth_rows(0, nq, d, 5678)
+    st = rb.RagStore.create_sharded(d, n, _sharded_devices(2), block_rows=500)
+    try:
+        st.add(rows)
+        idx, sc, found, flags = st.search(qs, k)
+        info = st.info()
+        assert info["batch_launches"] >= 2 and info["scan_launches"] >= 1      # the redo went through the scan kernel
+        for i in range(nq):
+            eidx, esc = oc.query(rows, qs[i], k, n_threads=4)
+            assert list(idx[i]) == list(eidx), i
+            assert np.array_equal(sc[i].view(np.uint64), esc.view(np.uint64)), i
+            assert flags[i] & rb.RAGSTORE_HIT_CERTIFIED, i
+    finally:
+        st.close()
