@@ -515,7 +515,7 @@ def measure_workload(name, args, torch, dist, rb, native, rank, world, dev, do_e
                 ts.synchronize()
                 nf = int(sh.d_found.item())
                 g_idx, g_sc = sh.d_idx[:nf].cpu().numpy()[None, :], sh.d_score[:nf].cpu().numpy()[None, :]
-                g_flags = sh.global_flags(sh.d_flags)     # certified / exact only if every shard's part is
+                g_flags = sh.global_flags(sh.d_flags, sh.d_gflags)     # certified / exact only if every shard's part is
         mine = oracle_topk_streamed(rank * rows, rows, dim, dtype == "bf16", list(hq_par), k, threads)
         if world > 1:
             # fixed-size exchange of the per-shard oracle lists (k ids + k scores per rank) through the process group

@@ -239,6 +239,12 @@ RAGSTORE_API int ragstore_exchange_connect(ragstore_exchange_t* x, const void* a
 RAGSTORE_API int ragstore_exchange_merge(ragstore_exchange_t* x, const ragstore_cand* d_mine, int n_queries,
                                          int per_shard, int top_k, int64_t* d_idx, double* d_score,
                                          int32_t* d_found, int32_t* d_status, void* stream);
+/* The same with the certificate: d_my_flags (n_queries, may be null = both bits) are this rank's RAGSTORE_HIT_* bits as
+ * written by ragstore_search_shard*_device; they travel with the records, and d_flags (n_queries, may be null) receives
+ * the AND over all ranks -- a merged result is certified / exact only if every shard's part of it is. */
+RAGSTORE_API int ragstore_exchange_merge_flags(ragstore_exchange_t* x, const ragstore_cand* d_mine, const int32_t* d_my_flags,
+                                               int n_queries, int per_shard, int top_k, int64_t* d_idx, double* d_score,
+                                               int32_t* d_found, int32_t* d_flags, int32_t* d_status, void* stream);
 RAGSTORE_API int ragstore_exchange_destroy(ragstore_exchange_t* x);
 
 /* No counterpart in the reference: an extra search entry point for hosts that are not allowed to

@@ -43,10 +43,12 @@ __device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long
 __global__ void __launch_bounds__(256) exchange_merge_kernel(const ExchangeView v, const ragstore_cand* __restrict__ mine, int n_queries,
                                                              int per_shard, int k_req, unsigned long long seq,
                                                              unsigned long long timeout_ns, int64_t* out_idx, double* out_score,
-                                                             int32_t* out_found, int32_t* out_status) {
+                                                             int32_t* out_found, int32_t* out_status, const int32_t* __restrict__ my_flags,
+                                                             int32_t* out_flags) {
     extern __shared__ __align__(16) uint8_t sm[];
     __shared__ int n_valid;
     __shared__ int timed_out;
+    __shared__ int all_flags;
     const int tid = threadIdx.x;
     const int slot = static_cast<int>(seq & 1ull);
     const size_t rec_base = (static_cast<size_t>(slot) * v.world + v.rank) * v.max_records;   // my block in every inbox
@@ -62,28 +64,34 @@ __global__ void __launch_bounds__(256) exchange_merge_kernel(const ExchangeView 
     }
     __threadfence_system();
     __syncthreads();
+    // The arrival word carries, below the sequence number, this rank's RAGSTORE_HIT_* bits for the query: a result is
+    // certified / exact only if every shard's part of it is, so the certificate travels with the hits.
     for (int q = blockIdx.x; q < n_queries; q += gridDim.x)
-        if (tid < v.world) st_release_sys(v.flag[tid] + flag_base + q, seq);
+        if (tid < v.world) st_release_sys(v.flag[tid] + flag_base + q, (seq << 2) | static_cast<unsigned long long>((my_flags ? my_flags[q] : 3) & 3));
 
     // ---- wait for every rank's records of a query, then rank them
     const ragstore_cand* inbox = v.rec[v.rank] + static_cast<size_t>(slot) * v.world * v.max_records;
-    const unsigned long long* my_flags = v.flag[v.rank] + static_cast<size_t>(slot) * v.world * v.max_queries;
+    const unsigned long long* inbox_flags = v.flag[v.rank] + static_cast<size_t>(slot) * v.world * v.max_queries;
     for (int q = blockIdx.x; q < n_queries; q += gridDim.x) {
-        if (tid == 0) timed_out = 0;
+        if (tid == 0) timed_out = 0, all_flags = 3;
         __syncthreads();
         if (tid < v.world) {
-            const unsigned long long* f = my_flags + static_cast<size_t>(tid) * v.max_queries + q;
+            const unsigned long long* f = inbox_flags + static_cast<size_t>(tid) * v.max_queries + q;
             const unsigned long long t0 = globaltimer_ns();
-            while (ld_acquire_sys(f) != seq) {
+            unsigned long long w;
+            while (((w = ld_acquire_sys(f)) >> 2) != seq) {
                 if (globaltimer_ns() - t0 > timeout_ns) {
                     timed_out = 1;
+                    w = 0;
                     break;
                 }
                 __nanosleep(64);
             }
+            atomicAnd(&all_flags, static_cast<int>(w & 3ull));
         }
         __syncthreads();
         if (tid == 0 && out_status) out_status[q] = timed_out;
+        if (tid == 0 && out_flags) out_flags[q] = all_flags;
         merge_query_block<true>(inbox, static_cast<size_t>(v.max_records), v.world, q, per_shard, k_req, out_idx, out_score, out_found, sm,
                           &n_valid);
     }
@@ -194,6 +202,12 @@ int ragstore_exchange_connect(ragstore_exchange_t* x, const void* all_handles) {
 
 int ragstore_exchange_merge(ragstore_exchange_t* x, const ragstore_cand* d_mine, int n_queries, int per_shard, int top_k,
                             int64_t* d_idx, double* d_score, int32_t* d_found, int32_t* d_status, void* stream) {
+    return ragstore_exchange_merge_flags(x, d_mine, nullptr, n_queries, per_shard, top_k, d_idx, d_score, d_found, nullptr, d_status, stream);
+}
+
+int ragstore_exchange_merge_flags(ragstore_exchange_t* x, const ragstore_cand* d_mine, const int32_t* d_my_flags, int n_queries,
+                                  int per_shard, int top_k, int64_t* d_idx, double* d_score, int32_t* d_found, int32_t* d_flags,
+                                  int32_t* d_status, void* stream) {
     if (!x || !d_mine || !d_idx || !d_score || !d_found) return api_fail(RAGSTORE_ERR_INVALID, "ragstore_exchange_merge: null argument");
     if (!x->connected) return api_fail(RAGSTORE_ERR_INVALID, "ragstore_exchange_merge: call ragstore_exchange_connect first");
     const int req = top_k < 1 ? 1 : top_k;
@@ -211,7 +225,7 @@ int ragstore_exchange_merge(ragstore_exchange_t* x, const ragstore_cand* d_mine,
     const unsigned long long seq = ++x->seq;
     exchange_merge_kernel<<<grid, 256, smem, static_cast<cudaStream_t>(stream)>>>(x->view, d_mine, n_queries, per_shard, req, seq,
                                                                                   5000000000ull /* 5 s */, d_idx, d_score, d_found,
-                                                                                  d_status);
+                                                                                  d_status, d_my_flags, d_flags);
     const cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return api_fail(RAGSTORE_ERR_CUDA, "ragstore_exchange_merge: launch", cudaGetErrorString(e));
     return RAGSTORE_OK;

@@ -66,6 +66,7 @@ def lib():
             "ragstore_exchange_create": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(vp), vp]),
             "ragstore_exchange_connect": (C.c_int, [vp, vp]),
             "ragstore_exchange_merge": (C.c_int, [vp, vp, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp, vp]),
+            "ragstore_exchange_merge_flags": (C.c_int, [vp, vp, vp, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp, vp, vp]),
             "ragstore_exchange_destroy": (C.c_int, [vp]),
             "ragstore_info": (C.c_int, [vp, i64p, C.c_int]),
             "ragstore_debug_reload_env": (C.c_int, []),
@@ -337,9 +338,11 @@ class PeerExchange:
             raise ValueError("all_handles must hold world x 64 bytes, in rank order")
         check(lib().ragstore_exchange_connect(self._h, C.c_char_p(all_handles)))
 
-    def merge(self, d_mine, n_queries: int, per_shard: int, top_k: int, d_idx, d_score, d_found, d_status=None, stream: int = 0):
-        check(lib().ragstore_exchange_merge(self._h, _ptr(d_mine), n_queries, per_shard, int(top_k), _ptr(d_idx), _ptr(d_score),
-                                            _ptr(d_found), _ptr(d_status), C.c_void_p(stream)))
+    def merge(self, d_mine, n_queries: int, per_shard: int, top_k: int, d_idx, d_score, d_found, d_status=None, stream: int = 0,
+              d_my_flags=None, d_flags=None):
+        """d_my_flags: this rank's per-query RAGSTORE_HIT_* bits; d_flags receives their AND over all ranks."""
+        check(lib().ragstore_exchange_merge_flags(self._h, _ptr(d_mine), _ptr(d_my_flags), n_queries, per_shard, int(top_k), _ptr(d_idx),
+                                                  _ptr(d_score), _ptr(d_found), _ptr(d_flags), _ptr(d_status), C.c_void_p(stream)))
 
     def close(self):
         if self._h:

@@ -58,6 +58,7 @@ class ShardedSearcher:
         self.d_score = torch.zeros(max_k, dtype=torch.float64, device="cuda")
         self.d_found = torch.zeros(1, dtype=torch.int32, device="cuda")
         self.d_flags = torch.zeros(1, dtype=torch.int32, device="cuda")
+        self.d_gflags = torch.zeros(1, dtype=torch.int32, device="cuda")    # d_flags ANDed over all shards (peer exchange)
         self.last_flags = None      # RAGSTORE_HIT_* of the last synchronous search, ANDed over all shards
         if all_gather is None:
             import torch.distributed as dist
@@ -111,7 +112,8 @@ class ShardedSearcher:
         per, total = gather_layout(self.world, req)
         self.store.search_shard_device(d_query, k, self.d_cand, self.d_flags, stream=stream)
         if self.peer is not None:
-            self.peer.merge(self.d_cand, 1, req, k, self.d_idx, self.d_score, self.d_found, self.d_status, stream=stream)
+            self.peer.merge(self.d_cand, 1, req, k, self.d_idx, self.d_score, self.d_found, self.d_status, stream=stream,
+                            d_my_flags=self.d_flags, d_flags=self.d_gflags)
             return
         if self.world > 1:
             self._all_gather(self.d_all[:total], self.d_cand[:per])
@@ -135,29 +137,35 @@ class ShardedSearcher:
         if getattr(self, "_h_idx", None) is None:
             self._h_idx = torch.zeros(self.max_k, dtype=torch.int64).pin_memory()
             self._h_score = torch.zeros(self.max_k, dtype=torch.float64).pin_memory()
-            self._h_meta = torch.zeros(2, dtype=torch.int32).pin_memory()          # [found, status]
+            self._h_meta = torch.zeros(4, dtype=torch.int32).pin_memory()          # [found, status, flags ANDed over the shards]
             self._h_np = (self._h_idx.numpy(), self._h_score.numpy(), self._h_meta.numpy())   # views of the same memory
             self._h_ptr = (self._h_idx.data_ptr(), self._h_score.data_ptr(), self._h_meta.data_ptr(), self._h_meta.data_ptr() + 4)
         cur = torch.cuda.current_stream()
         stream = cur.cuda_stream or 1
         p_idx, p_sc, p_found, p_status = self._h_ptr
         self.store.search_shard_hostq(h_query, k, self.d_cand, self.d_flags, stream=stream)
-        self.peer.merge(self.d_cand, 1, req, k, p_idx, p_sc, p_found, p_status, stream=stream)
+        self.peer.merge(self.d_cand, 1, req, k, p_idx, p_sc, p_found, p_status, stream=stream,
+                        d_my_flags=self.d_flags, d_flags=self._h_meta.data_ptr() + 8)
         cur.synchronize()
         np_idx, np_sc, np_meta = self._h_np
         if np_meta[1] != 0:
             raise RuntimeError("peer exchange timed out: a rank did not publish its hits within 5 s")
         n = int(np_meta[0])
-        self.last_flags = int(self.global_flags(self.d_flags)[0])
+        self.last_flags = int(np_meta[2])
         return np_idx[:n], np_sc[:n]
 
-    def global_flags(self, d_flags):
-        """RAGSTORE_HIT_* bits ANDed over all shards (a collective when world > 1): a result is certified / exact only if
-        every shard's part of it is.  Returns a host numpy array."""
+    def global_flags(self, d_flags, d_gflags=None):
+        """RAGSTORE_HIT_* bits ANDed over all shards: a result is certified / exact only if every shard's part of it is.
+        With the peer exchange the AND was formed inside the exchange kernel (d_gflags); with NCCL it is one more small
+        collective here (a bitwise AND is a MIN per bit).  Returns a host numpy array."""
+        if self.peer is not None and d_gflags is not None:
+            return d_gflags.cpu().numpy()
         f = d_flags.clone()
         if self.world > 1:
             import torch.distributed as dist
-            dist.all_reduce(f, op=dist.ReduceOp.BAND)
+            bits = self.torch.stack([f & 1, (f >> 1) & 1])
+            dist.all_reduce(bits, op=dist.ReduceOp.MIN)
+            f = bits[0] | (bits[1] << 1)
         return f.cpu().numpy()
 
     def search_batch(self, d_queries, n_queries: int, k: int):
@@ -171,7 +179,7 @@ class ShardedSearcher:
         torch.cuda.current_stream().synchronize()
         if self.peer is not None and int(self.d_status[:n_queries].abs().sum().item()) != 0:
             raise RuntimeError("peer exchange timed out: a rank did not publish its hits within 5 s")
-        flags = self.global_flags(self._b_flags[:n_queries])
+        flags = self.global_flags(self._b_flags[:n_queries], self._b_gflags[:n_queries] if self._b_via_peer else None).copy()
         idx, sc, found = bi.cpu().numpy().copy(), bs.cpu().numpy().copy(), bf.cpu().numpy().copy()
         for q in range(n_queries):
             if flags[q] & 1:
@@ -199,11 +207,14 @@ class ShardedSearcher:
             self._b_score = torch.zeros(n_queries * req, dtype=torch.float64, device="cuda")
             self._b_found = torch.zeros(n_queries, dtype=torch.int32, device="cuda")
             self._b_flags = torch.zeros(n_queries, dtype=torch.int32, device="cuda")
+            self._b_gflags = torch.zeros(n_queries, dtype=torch.int32, device="cuda")
             self._b_cap = need
         stream = _current_stream_handle(torch)
         self.store.search_shard_batch_device(d_queries, n_queries, k, self._b_cand, self._b_flags, stream=stream)
-        if self.peer is not None and n_queries <= self.peer.max_queries and n_queries * req <= self.peer.max_records:
-            self.peer.merge(self._b_cand, n_queries, req, k, self._b_idx, self._b_score, self._b_found, self.d_status, stream=stream)
+        self._b_via_peer = self.peer is not None and n_queries <= self.peer.max_queries and n_queries * req <= self.peer.max_records
+        if self._b_via_peer:
+            self.peer.merge(self._b_cand, n_queries, req, k, self._b_idx, self._b_score, self._b_found, self.d_status, stream=stream,
+                            d_my_flags=self._b_flags, d_flags=self._b_gflags)
             return self._b_idx[: n_queries * req].view(n_queries, req), self._b_score[: n_queries * req].view(n_queries, req), self._b_found[:n_queries]
         if self.world > 1:
             self._all_gather(self._b_all[: self.world * need], self._b_cand[:need])
@@ -220,5 +231,5 @@ class ShardedSearcher:
         if self.peer is not None and int(self.d_status[0].item()) != 0:
             raise RuntimeError("peer exchange timed out: a rank did not publish its hits within 5 s")
         n = int(self.d_found.item())
-        self.last_flags = int(self.global_flags(self.d_flags)[0])
+        self.last_flags = int(self.global_flags(self.d_flags, self.d_gflags)[0])
         return self.d_idx[:n].cpu().numpy(), self.d_score[:n].cpu().numpy()
