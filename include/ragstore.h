@@ -56,7 +56,17 @@ enum { RAGSTORE_F32 = 0, RAGSTORE_BF16 = 1 };
  * (normalising changed it, or bf16 rounding did) can keep its original fp32 values in a sidecar that
  * only the rescoring stage reads, so returned scores are the reference's values for the row as added.
  * Default: sidecar on for fp32 stores, off for bf16 stores. */
-enum { RAGSTORE_CREATE_DEFAULT = 0, RAGSTORE_CREATE_SIDECAR_ON = 1, RAGSTORE_CREATE_SIDECAR_OFF = 2 };
+enum {
+    RAGSTORE_CREATE_DEFAULT = 0,
+    RAGSTORE_CREATE_SIDECAR_ON = 1,
+    RAGSTORE_CREATE_SIDECAR_OFF = 2,
+    /* fp32 stores only (rows a multiple of 8 elements): the upload kernel also writes a bf16 image of every stored row
+     * (+50 % device memory).  Batches of queries then NOMINATE their candidates from that image on the bf16 tensor-core
+     * path -- half the bytes and half the tensor-core work of tf32 -- from a wider candidate set (128 per query), and
+     * the returned hits are still rescored from the fp32 rows with the reference's arithmetic, so results do not change.
+     * Single queries never read the image. */
+    RAGSTORE_CREATE_BF16_SHADOW = 4
+};
 
 /* flags for ragstore_add */
 enum {

@@ -7,7 +7,7 @@ libragstore.so or a CUDA device is missing, calls raise.
 """
 from .native import (  # noqa: F401
     RAGSTORE_ADD_DEVICE, RAGSTORE_ADD_HOST, RAGSTORE_ADD_PRENORMALISED, RAGSTORE_BF16, RAGSTORE_F32,
-    RAGSTORE_CREATE_SIDECAR_OFF, RAGSTORE_CREATE_SIDECAR_ON,
+    RAGSTORE_CREATE_BF16_SHADOW, RAGSTORE_CREATE_SIDECAR_OFF, RAGSTORE_CREATE_SIDECAR_ON,
     RAGSTORE_HIT_CERTIFIED, RAGSTORE_HIT_EXACT_ROWS, RagStore, RagStoreError, lib, lib_path,
 )
 from .rag_index import RagChunk, RagHit, RagIndex  # noqa: F401

@@ -28,6 +28,7 @@
 // scan kernel (host side, ragstore_api.cu).
 #include <cuda.h>
 
+#include <algorithm>
 #include <cstdio>
 #include <cstdlib>
 #include <mutex>
@@ -820,7 +821,7 @@ struct BatchFinalizeArgs {
     const float* d_queries; // raw queries [nq][dim]
     const uint64_t* glists; // [nq][nlists][kp]
     const float* thr0;      // [nq] sampling-pass thresholds (null: single pass)
-    int nlists;
+    int nlists;             // lists per query, kBatchKp keys each; merged into scan.kp candidates
     int out_stride;         // hits per query in out_idx / out_score
     uint32_t ring_bytes, row_bytes, qpad;
 };
@@ -855,8 +856,9 @@ __global__ void __launch_bounds__(kScanThreads, 1) batch_finalize_kernel(const B
     f.lists = lists;
     f.misc = misc;
     f.qraw = qraw;
-    f.glists = b.glists + static_cast<size_t>(q) * b.nlists * a.kp;
+    f.glists = b.glists + static_cast<size_t>(q) * b.nlists * kBatchKp;
     f.nlists = b.nlists;
+    f.list_len = kBatchKp;
     f.bound_floor = b.thr0 ? b.thr0[q] : -CUDART_INF_F;
     finalize_candidates<T>(a, f);
 }
@@ -968,10 +970,26 @@ size_t batch_scratch_bytes(int sm_count) {
 
 int launch_batch_search(const BatchSearchArgs& b, cudaStream_t stream) {
     const ScanArgs& s = b.scan;
-    const bool bf = s.dtype == RAGSTORE_BF16;
-    if ((bf && s.ld % 8 != 0) || b.nq < 1 || b.nq > kBatchMaxQ || s.ld > kBatchMaxLd || s.kp != kBatchKp ||
-        s.n_rows < 1 || s.n_rows >= 0x7FFF0000ll)
+    const bool bf = s.dtype == RAGSTORE_BF16 || b.operand_bf16;     // element type of the tensor-core operands
+    const bool bf_rows = s.dtype == RAGSTORE_BF16;                   // element type of the rows the finalize step rescoring reads
+    const void* op_mat = b.operand_mat ? b.operand_mat : s.mat;
+    if ((bf && s.ld % 8 != 0) || b.nq < 1 || b.nq > kBatchMaxQ || s.ld > kBatchMaxLd || s.kp < kBatchKp || s.kp > kMaxKp ||
+        (s.kp & (s.kp - 1)) || s.n_rows < 1 || s.n_rows >= 0x7FFF0000ll)
         return static_cast<int>(cudaErrorInvalidValue);
+    {   // every TMA load of this path reads memory of the GPU the kernel runs on: the operands are the store's own
+        // matrix (or shadow) and its own scratch.  Refuse anything else outright.
+        int dev = -1;
+        cudaGetDevice(&dev);
+        cudaPointerAttributes pa{};
+        if (cudaPointerGetAttributes(&pa, b.scratch) != cudaSuccess || pa.type != cudaMemoryTypeDevice || pa.device != dev) {
+            cudaGetLastError();
+            return static_cast<int>(cudaErrorInvalidDevicePointer);
+        }
+        if (cudaPointerGetAttributes(&pa, op_mat) != cudaSuccess || pa.type != cudaMemoryTypeDevice || pa.device != dev) {
+            cudaGetLastError();
+            return static_cast<int>(cudaErrorInvalidDevicePointer);
+        }
+    }
     const int mblocks = b.nq > kBM ? 2 : 1;
     const int nq_pad = mblocks * kBM;
     uint64_t* glists = reinterpret_cast<uint64_t*>(b.scratch);
@@ -989,7 +1007,7 @@ int launch_batch_search(const BatchSearchArgs& b, cudaStream_t stream) {
     const BatchKnobs& kn = knobs();
     const bool pair_maps = mblocks == 2 && !kn.no_pair;
     if (!make_map(&map_q, qhat, static_cast<uint64_t>(nq_pad), static_cast<uint64_t>(s.ld), pair_maps ? kBM : nq_pad / kCluster, bf) ||
-        !make_map(&map_c, s.mat, static_cast<uint64_t>(s.n_rows), static_cast<uint64_t>(s.ld), pair_maps ? 128 : kBN, bf))
+        !make_map(&map_c, op_mat, static_cast<uint64_t>(s.n_rows), static_cast<uint64_t>(s.ld), pair_maps ? 128 : kBN, bf))
         return static_cast<int>(cudaErrorNotSupported);
 
     // 129..256 queries: the CTA-pair (cta_group::2) kernel by default -- half the shared-memory fill per corpus row and a
@@ -1057,14 +1075,18 @@ int launch_batch_search(const BatchSearchArgs& b, cudaStream_t stream) {
             // small corpora: stride 1, i.e. the "sample" is a full (cheap: 4 registers per thread, no lists) sweep --
             // still far cheaper than filling cold lists column by column (~200 us per CTA for 256 queries)
             int stride = static_cast<int>(n_tiles / (2ll * nlists));   // every CTA (pair) samples >= 2 tiles when it can
-            const int stride_max = kn.stride_max;   // experiments
+            // ~kp * stride rows per query beat the threshold in the whole corpus; a CTA keeps 32 of its share, so the
+            // stride is held where that share (kp * stride / nlists) stays around 16 and lists rarely overflow
+            const int stride_lists = std::max(1, 16 * nlists / s.kp);
+            const int stride_max = std::min(kn.stride_max, stride_lists);   // (knob: experiments)
             stride = stride > stride_max ? stride_max : (stride < 1 ? 1 : stride);
             a.tile_stride = stride;
             a.sample = 1;
             e = launch_main();
             if (e != cudaSuccess) return static_cast<int>(e);
             const int nvals = nlists * 4;
-            batch_thresholds_kernel<<<b.nq, 256, nvals * sizeof(float), stream>>>(reinterpret_cast<const float*>(glists), nvals, kBatchKp, thr0);
+            // threshold = the kp-th largest sampled score: at least kp real rows reach it (fewer samples than kp: no threshold)
+            batch_thresholds_kernel<<<b.nq, 256, nvals * sizeof(float), stream>>>(reinterpret_cast<const float*>(glists), nvals, s.kp, thr0);
             e = cudaGetLastError();
             if (e != cudaSuccess) return static_cast<int>(e);
             a.sample = 0;
@@ -1083,7 +1105,7 @@ int launch_batch_search(const BatchSearchArgs& b, cudaStream_t stream) {
     f.thr0 = thr_used;
     f.nlists = nlists;
     f.out_stride = b.out_stride;
-    f.row_bytes = static_cast<uint32_t>(s.ld) * (bf ? 2u : 4u);
+    f.row_bytes = static_cast<uint32_t>(s.ld) * (bf_rows ? 2u : 4u);
     f.qpad = static_cast<uint32_t>(s.ld);
     const uint32_t fixed = f.qpad * 4u + sizeof(uint64_t) * 2u * kConsumerWarps * s.kp + sizeof(ScanMisc) + 256u;
     uint32_t ring = 200u * 1024u - fixed;
@@ -1093,7 +1115,7 @@ int launch_batch_search(const BatchSearchArgs& b, cudaStream_t stream) {
     if (ring < lists_need && lists_need + fixed <= 200u * 1024u) ring = lists_need;
     f.ring_bytes = (ring + 127u) & ~127u;
     const size_t fin_smem = f.ring_bytes + fixed;
-    if (bf) {
+    if (bf_rows) {
         e = opt_in_smem(batch_finalize_kernel<uint16_t>);
         if (e != cudaSuccess) return static_cast<int>(e);
         batch_finalize_kernel<uint16_t><<<b.nq, kScanThreads, fin_smem, stream>>>(f);

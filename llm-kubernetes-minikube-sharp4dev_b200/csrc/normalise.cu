@@ -52,6 +52,7 @@ __global__ void __launch_bounds__(256) normalise_rows_kernel(const NormaliseArgs
             if constexpr (sizeof(T) == 4) {
                 dst[i] = y;
                 stored = y;
+                if (a.shadow) a.shadow[r * static_cast<int64_t>(a.ld) + i] = static_cast<uint16_t>(f32_to_bf16_bits(y));
             } else {
                 const uint32_t b = f32_to_bf16_bits(y);
                 dst[i] = static_cast<uint16_t>(b);
@@ -129,6 +130,10 @@ __global__ void __launch_bounds__(256) normalise_rows_vec_kernel(const Normalise
             float4 y = make_float4(__fmul_rn(x.x, scale), __fmul_rn(x.y, scale), __fmul_rn(x.z, scale), __fmul_rn(x.w, scale));
             if constexpr (sizeof(T) == 4) {
                 reinterpret_cast<float4*>(static_cast<float*>(a.dst) + r * static_cast<int64_t>(a.ld))[ch] = y;
+                if (a.shadow) {   // the same pass also writes the bf16 image the tensor cores nominate from
+                    const uint32_t b0 = f32_to_bf16_bits(y.x), b1 = f32_to_bf16_bits(y.y), b2 = f32_to_bf16_bits(y.z), b3 = f32_to_bf16_bits(y.w);
+                    reinterpret_cast<uint2*>(a.shadow + r * static_cast<int64_t>(a.ld))[ch] = make_uint2(b0 | (b1 << 16), b2 | (b3 << 16));
+                }
             } else {
                 const uint32_t b0 = f32_to_bf16_bits(y.x), b1 = f32_to_bf16_bits(y.y), b2 = f32_to_bf16_bits(y.z), b3 = f32_to_bf16_bits(y.w);
                 reinterpret_cast<uint2*>(static_cast<uint16_t*>(a.dst) + r * static_cast<int64_t>(a.ld))[ch] = make_uint2(b0 | (b1 << 16), b2 | (b3 << 16));

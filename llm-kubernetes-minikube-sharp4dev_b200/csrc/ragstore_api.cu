@@ -156,6 +156,9 @@ ScanArgs base_args(const ragstore* s, int64_t n, int take, int kp) {
 // (<= 2^-9 relative per element -> <= 2^-9 on a cosine, Cauchy-Schwarz) and the fp32 accumulation remain; when
 // exact scores come from fp32 originals (sidecar) the stored image itself is another 2^-8 away, as in base_args.
 float batch_eps(const ragstore* s) {
+    // fp32 store nominated from its bf16 shadow: both operands rounded to bf16 (2^-9 relative each, Cauchy-Schwarz on
+    // unit vectors -> 2^-8), fp32 accumulation, and the 1e-7 between a sidecar original and its normalised image
+    if (s->dtype == RAGSTORE_F32 && s->shadow) return 3.92e-3f + static_cast<float>(s->ld) * 2.4e-7f + 2e-5f;
     if (s->dtype == RAGSTORE_F32) return 2.1e-3f;
     float e = 1.953125e-3f + static_cast<float>(s->ld) * 2.4e-7f + 2e-5f;
     if (s->raw_used > 0) e += 3.90625e-3f;
@@ -168,7 +171,7 @@ float batch_eps(const ragstore* s) {
 // 2..15 queries; 4M x 768: 15 queries 27.2 ms as scans, 1.91 ms as one batch.  The batch wins from 2 queries on
 // corpora of ~1 GB up and from 3 on small ones.  RAGSTORE_BATCH_MINQ=<n> replaces the model by "at least n queries".
 bool batch_eligible(const ragstore* s, int64_t n, int nq, int kp) {
-    if (nq < kBatchMinQ || n < kBatchMinRows || kp != 32 || s->ld > kBatchMaxLd || (s->dtype != RAGSTORE_F32 && s->ld % 8 != 0))
+    if (nq < kBatchMinQ || n < kBatchMinRows || kp < 32 || kp > kMaxKp || s->ld > kBatchMaxLd || (s->dtype != RAGSTORE_F32 && s->ld % 8 != 0))
         return false;
     static const int forced_min = [] {
         const char* e = std::getenv("RAGSTORE_BATCH_MINQ");
@@ -181,6 +184,16 @@ bool batch_eligible(const ragstore* s, int64_t n, int nq, int kp) {
     const double stride = std::min(16.0, std::max(1.0, std::floor(tiles_per_cta / 2.0)));
     const double t_batch = 62e-6 + (1.0 + 1.0 / stride) * bytes / (nq <= 128 ? 6.2e12 : 4.5e12);
     return nq * t_scan > t_batch;
+}
+
+void fill_batch_args(const ragstore* s, int64_t n, int take, int kp, BatchSearchArgs& b) {
+    // A bf16-shadow nomination is coarser (eps ~4e-3): it merges the per-CTA lists into at least 128 candidates per query,
+    // whose margin (rank k against rank 129 instead of rank 33) the certificate can still prove.
+    const int kpm = (s->dtype == RAGSTORE_F32 && s->shadow) ? std::max(kp, 128) : kp;
+    b.scan = base_args(s, n, take, kpm);
+    b.scan.eps = batch_eps(s);
+    b.operand_mat = (s->dtype == RAGSTORE_F32 && s->shadow) ? s->shadow : nullptr;
+    b.operand_bf16 = b.operand_mat ? 1 : 0;
 }
 
 int acquire_ctx(ragstore* s) {
@@ -204,11 +217,10 @@ void release_ctx(ragstore* s, int ci) {
 namespace {
 
 // One tensor-core launch for up to kBatchMaxQ queries (outputs laid out with `stride` hits per query).
-int run_batch(const ragstore* s, int64_t n, int take, const float* d_q, int nq, int64_t* d_idx, double* d_score,
+int run_batch(const ragstore* s, int64_t n, int take, int kp, const float* d_q, int nq, int64_t* d_idx, double* d_score,
               int32_t* d_found, int32_t* d_flags, int stride, uint8_t* scratch, cudaStream_t st) {
     BatchSearchArgs b{};
-    b.scan = base_args(s, n, take, 32);
-    b.scan.eps = batch_eps(s);
+    fill_batch_args(s, n, take, kp, b);
     b.scan.out_idx = d_idx;
     b.scan.out_score = d_score;
     b.scan.out_found = d_found;
@@ -291,6 +303,10 @@ int ragstore_create(int dim, int dtype, int64_t capacity_rows, int device, uint3
     if ((vr = s->mat_buf.reserve(static_cast<size_t>(capacity_rows) * s->ld * s->elem_size(), device))) return bail(fail(RAGSTORE_ERR_CUDA, "reserve(matrix)", cudaGetErrorString(static_cast<cudaError_t>(vr))));
     if ((vr = s->rnorm_buf.reserve(cap4 * sizeof(float), device))) return bail(fail(RAGSTORE_ERR_CUDA, "reserve(rnorm)", cudaGetErrorString(static_cast<cudaError_t>(vr))));
     if ((vr = s->exact_buf.reserve(cap4, device))) return bail(fail(RAGSTORE_ERR_CUDA, "reserve(exact)", cudaGetErrorString(static_cast<cudaError_t>(vr))));
+    if ((flags & RAGSTORE_CREATE_BF16_SHADOW) && dtype == RAGSTORE_F32 && s->ld % 8 == 0) {
+        if ((vr = s->shadow_buf.reserve(static_cast<size_t>(capacity_rows) * s->ld * 2, device))) return bail(fail(RAGSTORE_ERR_CUDA, "reserve(shadow)", cudaGetErrorString(static_cast<cudaError_t>(vr))));
+        s->shadow = s->shadow_buf.ptr<uint16_t>();
+    }
     s->mat = s->mat_buf.ptr<void>();
     s->rnorm = s->rnorm_buf.ptr<float>();
     s->exact = s->exact_buf.ptr<uint8_t>();
@@ -342,6 +358,7 @@ int ragstore_destroy(ragstore_t* s) {
     }
     if (s->h_counters) cudaFreeHost(s->h_counters);
     cudaFree(s->d_inexact);
+    s->shadow_buf.release();
     s->raw_buf.release();
     s->slot_buf.release();
     s->exact_buf.release();
@@ -398,6 +415,7 @@ int ragstore_reserve_rows(ragstore_t* s, int64_t n_rows) {
     const size_t upto = static_cast<size_t>(n_rows);
     const size_t upto4 = ((upto + 3) & ~size_t(3)) + 64;
     int vr = s->mat_buf.ensure(upto * s->ld * s->elem_size(), false, s->ingest_stream);
+    if (!vr && s->shadow) vr = s->shadow_buf.ensure(upto * s->ld * 2, false, s->ingest_stream);
     if (!vr) vr = s->rnorm_buf.ensure(upto4 * sizeof(float), true, s->ingest_stream);
     if (!vr) vr = s->exact_buf.ensure(upto4, true, s->ingest_stream);
     if (!vr && s->raw_slot) vr = s->slot_buf.ensure(upto4 * sizeof(int32_t), true, s->ingest_stream);
@@ -477,6 +495,7 @@ int ragstore_add(ragstore_t* s, const float* rows, int64_t n_rows, int row_dim, 
             const size_t upto = static_cast<size_t>(first + r0 + n);
             const size_t upto4 = ((upto + 3) & ~size_t(3)) + 64;
             int vr = s->mat_buf.ensure(upto * s->ld * esz, false, s->ingest_stream);
+            if (!vr && s->shadow) vr = s->shadow_buf.ensure(upto * s->ld * 2, false, s->ingest_stream);
             if (!vr) vr = s->rnorm_buf.ensure(upto4 * sizeof(float), true, s->ingest_stream);
             if (!vr) vr = s->exact_buf.ensure(upto4, true, s->ingest_stream);
             if (!vr && s->raw_slot) vr = s->slot_buf.ensure(upto4 * sizeof(int32_t), true, s->ingest_stream);
@@ -504,6 +523,7 @@ int ragstore_add(ragstore_t* s, const float* rows, int64_t n_rows, int row_dim, 
         a.dtype = s->dtype;
         a.prenormalised = (flags & RAGSTORE_ADD_PRENORMALISED) ? 1 : 0;
         a.inexact_counter = s->d_inexact;
+        a.shadow = s->shadow ? s->shadow + static_cast<size_t>(first + r0) * s->ld : nullptr;
         const float* h2d_src = src;
         if (!on_device && !src_pinned) {  // stage through pinned memory so that the PCIe copy is truly asynchronous
             memcpy(s->h_stage[b], src, static_cast<size_t>(n) * s->dim * sizeof(float));
@@ -608,7 +628,7 @@ int ragstore_search_device(ragstore_t* s, const float* d_queries, int n_queries,
         // tensor-core path: the corpus is swept once per 256 queries instead of once per query
         for (int q0 = 0; q0 < n_queries; q0 += kBatchMaxQ) {
             const int nq = std::min(kBatchMaxQ, n_queries - q0);
-            const int rc = run_batch(s, n, take, d_queries + static_cast<size_t>(q0) * s->dim, nq,
+            const int rc = run_batch(s, n, take, kp, d_queries + static_cast<size_t>(q0) * s->dim, nq,
                                      d_idx + static_cast<size_t>(q0) * req, d_score + static_cast<size_t>(q0) * req,
                                      d_found ? d_found + q0 : nullptr, d_flags ? d_flags + q0 : nullptr, req,
                                      s->dev_batch_scratch, st);
@@ -697,8 +717,7 @@ int ragstore_search_shard_batch_device(ragstore_t* s, const float* d_queries, in
         for (int q0 = 0; q0 < n_queries; q0 += kBatchMaxQ) {
             const int nq = std::min(kBatchMaxQ, n_queries - q0);
             BatchSearchArgs b{};
-            b.scan = base_args(s, n, take, 32);
-            b.scan.eps = batch_eps(s);
+            fill_batch_args(s, n, take, kp, b);
             b.scan.out_flags = d_flags ? d_flags + q0 : nullptr;
             b.scan.out_cand = d_out + static_cast<size_t>(q0) * req;
             b.scan.cand_slots = req;
@@ -890,7 +909,7 @@ int rag::search_host_limited(ragstore* s, int64_t n_limit, const float* queries,
             if (batch_pass) {
                 // first pass on the tensor cores; queries whose margin the tf32 scores cannot certify are
                 // redone below by the fp32 scan kernel
-                const int rc = run_batch(s, n, take, c.d_q, nq, c.d_idx, c.d_score, c.d_found, c.d_flags, hs,
+                const int rc = run_batch(s, n, take, kp0, c.d_q, nq, c.d_idx, c.d_score, c.d_found, c.d_flags, hs,
                                          c.batch_scratch, c.st);
                 if (rc) return fail(RAGSTORE_ERR_CUDA, "batched search launch", cudaGetErrorString(static_cast<cudaError_t>(rc)));
             }

@@ -79,6 +79,7 @@ struct NormaliseArgs {
     int dim, ld, dtype;
     int prenormalised;
     unsigned long long* inexact_counter;  // device counter of rows stored inexactly
+    uint16_t* shadow;     // fp32 stores with a bf16 shadow: destination slice of the shadow rows (ld elements each), or null
 };
 int launch_normalise(const NormaliseArgs& a, cudaStream_t stream);
 
@@ -88,7 +89,11 @@ constexpr int kBatchMinQ = 2;      // one query always takes the scan kernel; fr
 constexpr int kBatchMaxLd = 4096;  // padded row length covered by the query operand buffer
 constexpr int64_t kBatchMinRows = 4096;
 struct BatchSearchArgs {
-    ScanArgs scan;           // store views, k_take, kp (must be 32), eps, outputs as per-launch bases
+    ScanArgs scan;           // store views, k_take, kp (size of the MERGED candidate set per query: 32..256; every CTA
+                             // keeps 32 keys per query), eps, outputs as per-launch bases
+    const void* operand_mat; // rows the tensor cores read: null = scan.mat; else a bf16 shadow of an fp32 store
+                             // (same row count and ld): nomination on bf16 operands, rescoring from the fp32 rows
+    int operand_bf16;        // 1 when operand_mat is bf16 although scan.dtype is fp32
     const float* d_queries;  // raw queries [nq][dim], device
     int nq;
     int out_stride;          // hits per query in scan.out_idx / scan.out_score

@@ -323,6 +323,7 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanAr
     f.qraw = qraw;
     f.glists = a.scratch.cta_lists;
     f.nlists = static_cast<int>(gridDim.x);
+    f.list_len = 0;
     f.bound_floor = -CUDART_INF_F;
     finalize_candidates<T>(a, f);
     if (tid == 0) atomicExch(a.scratch.ticket + 1, 0u);  // scratch free again

@@ -139,8 +139,7 @@ int launch_shard(ragstore* sh, SearchCtx& c, int64_t n, int req, const float* h_
         std::memcpy(c.h_q, h_queries, sizeof(float) * static_cast<size_t>(nq) * sh->dim);
         SH_TRY(cudaMemcpyAsync(c.d_q, c.h_q, sizeof(float) * static_cast<size_t>(nq) * sh->dim, cudaMemcpyHostToDevice, c.st));
         BatchSearchArgs b{};
-        b.scan = base_args(sh, n, take, 32);
-        b.scan.eps = batch_eps(sh);
+        fill_batch_args(sh, n, take, kp, b);
         b.scan.out_flags = out_flags;
         b.scan.out_cand = out_cand;
         b.scan.cand_slots = req;

@@ -72,7 +72,9 @@ struct ragstore {
     int64_t row_block = 0;
     int row_nshards = 1, row_shard = 0;
     mutable std::atomic<int64_t> n_scan_launches{0}, n_batch_launches{0};  // kernel launches issued by searches
-    VmmBuffer mat_buf, rnorm_buf, exact_buf, slot_buf, raw_buf;  // address-stable, grown on demand
+    VmmBuffer mat_buf, rnorm_buf, exact_buf, slot_buf, raw_buf, shadow_buf;  // address-stable, grown on demand
+    uint16_t* shadow = nullptr;    // fp32 store created with RAGSTORE_CREATE_BF16_SHADOW: bf16 image of the stored rows,
+                                   // [rows][ld], read by the batched (tensor-core) nomination pass only
     void* mat = nullptr;
     float* rnorm = nullptr;
     uint8_t* exact = nullptr;
@@ -131,6 +133,8 @@ namespace rag {
 ScanArgs base_args(const ragstore* s, int64_t n, int take, int kp);
 float batch_eps(const ragstore* s);
 bool batch_eligible(const ragstore* s, int64_t n, int nq, int kp);
+// store views, candidate-set size, error bound and tensor-core operand of one batched launch (outputs left to the caller)
+void fill_batch_args(const ragstore* s, int64_t n, int take, int kp, BatchSearchArgs& b);
 int acquire_ctx(ragstore* s);            // blocks until one of the store's search contexts is free
 void release_ctx(ragstore* s, int ci);
 

@@ -157,10 +157,11 @@ __device__ __forceinline__ int64_t global_row_id(const ScanArgs& a, uint32_t loc
     return a.row_base + (blk * a.row_nshards + a.row_shard) * a.row_block + off;
 }
 
-// Merges `nlists` sorted lists of kp keys (global memory) into lists[0..kp) (shared, 2*kConsumerWarps*kp keys of
-// scratch); `stage` is idle shared memory of stage_bytes.  Called by all kScanThreads threads of the CTA.
-__device__ __forceinline__ void merge_global_lists(const uint64_t* glists, int nlists, int kp, uint64_t* lists, uint64_t* stage,
-                                                   uint32_t stage_bytes) {
+// Merges `nlists` sorted lists of list_len keys (global memory) into lists[0..kp) (shared, 2*kConsumerWarps*kp keys of
+// scratch), kp >= list_len (a shorter list is staged padded with empty keys); `stage` is idle shared memory of
+// stage_bytes.  Called by all kScanThreads threads of the CTA.
+__device__ __forceinline__ void merge_global_lists(const uint64_t* glists, int nlists, int list_len, int kp, uint64_t* lists,
+                                                   uint64_t* stage, uint32_t stage_bytes) {
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int cap_lists = max(1, static_cast<int>(stage_bytes / (static_cast<uint32_t>(kp) * 8u)));
     if (warp < kConsumerWarps) {
@@ -168,10 +169,18 @@ __device__ __forceinline__ void merge_global_lists(const uint64_t* glists, int n
     }
     for (int l0 = 0; l0 < nlists; l0 += cap_lists) {
         const int nl = min(cap_lists, nlists - l0);
-        const uint64_t* src = glists + static_cast<size_t>(l0) * kp;
+        const uint64_t* src = glists + static_cast<size_t>(l0) * list_len;
         const int total = nl * kp;
+        if (list_len == kp) {
 #pragma unroll 8
-        for (int i = tid; i < total; i += kScanThreads) stage[i] = __ldcg(src + i);  // all loads in flight
+            for (int i = tid; i < total; i += kScanThreads) stage[i] = __ldcg(src + i);  // all loads in flight
+        } else {
+#pragma unroll 4
+            for (int i = tid; i < total; i += kScanThreads) {
+                const int l = i / kp, j = i - l * kp;
+                stage[i] = j < list_len ? __ldcg(src + static_cast<size_t>(l) * list_len + j) : 0ull;
+            }
+        }
         __syncthreads();
         if (warp < kConsumerWarps)
             for (int c = warp; c < nl; c += kConsumerWarps) warp_merge_desc(lists + warp * kp, stage + c * kp, kp, lane);
@@ -191,8 +200,10 @@ struct FinalizeCtx {
     uint64_t* lists;        // shared: 2 * kConsumerWarps * kp keys
     ScanMisc* misc;         // shared
     const float* qraw;      // shared: the raw query, dim floats (16-byte aligned)
-    const uint64_t* glists; // global: nlists * kp keys
+    const uint64_t* glists; // global: nlists * list_len keys
     int nlists;
+    int list_len;           // keys per global list (<= a.kp; 0 = a.kp).  Shorter than a.kp: the batched path keeps 32 keys
+                            // per CTA and query but merges them into a wider candidate set (a.kp)
     float bound_floor;      // every row that was never offered to a list scored <= this (-inf if none)
 };
 
@@ -209,7 +220,24 @@ __device__ __forceinline__ void finalize_candidates(const ScanArgs& a, const Fin
     const float* qraw = f.qraw;
     const uint8_t* mat = static_cast<const uint8_t*>(a.mat);
     const uint32_t ring_bytes = f.ring_bytes;
-    merge_global_lists(f.glists, f.nlists, kp, lists, reinterpret_cast<uint64_t*>(f.ring), ring_bytes);
+    const int list_len = f.list_len > 0 ? f.list_len : kp;
+    // Lists shorter than the merged set: a row can have been pushed out of ITS list by 32 better rows of the same CTA
+    // while still beating the merged set's last entry.  Every such row scored no higher than the last key of the (full)
+    // list that dropped it, so the largest of those keys joins the bound below.
+    if (tid == 0) misc->n_cand = 0;   // reused as the max of the full lists' last score bits until the count below
+    __syncthreads();
+    if (list_len < kp) {
+        unsigned int mx = 0u;
+        for (int l = tid; l < f.nlists; l += kScanThreads) {
+            const uint64_t last = __ldcg(f.glists + static_cast<size_t>(l) * list_len + (list_len - 1));
+            mx = max(mx, static_cast<unsigned int>(last >> 32));
+        }
+        if (mx) atomicMax(reinterpret_cast<unsigned int*>(&misc->n_cand), mx);
+    }
+    __syncthreads();
+    const unsigned int dropped_bits = static_cast<unsigned int>(misc->n_cand);
+    __syncthreads();
+    merge_global_lists(f.glists, f.nlists, list_len, kp, lists, reinterpret_cast<uint64_t*>(f.ring), ring_bytes);
     // lists[0..kp) : the kp best approximate keys of the whole shard, descending
     if (tid == 0) stamp(a, 2);
 
@@ -333,6 +361,7 @@ __device__ __forceinline__ void finalize_candidates(const ScanArgs& a, const Fin
             // 1e-9 / (|q| * smallest row norm) towards zero.
             double bound = lists[kp - 1] ? static_cast<double>(key_score(lists[kp - 1])) : -CUDART_INF;
             if (static_cast<double>(f.bound_floor) > bound) bound = static_cast<double>(f.bound_floor);
+            if (dropped_bits) bound = fmax(bound, static_cast<double>(unord_f32(dropped_bits)));
             double shrink = 0.0;
             if (a.min_norm_bits || a.min_norm_assumed > 0.f) {
                 const double mn = a.min_norm_bits ? static_cast<double>(__uint_as_float(*a.min_norm_bits)) : static_cast<double>(a.min_norm_assumed);
@@ -341,7 +370,7 @@ __device__ __forceinline__ void finalize_candidates(const ScanArgs& a, const Fin
             }
             bound_total = bound + static_cast<double>(a.eps) + shrink;
             // the list did not fill up and nothing was skipped by an initial threshold: no row was left out below it
-            const bool complete = n_cand < kp && !(f.bound_floor > -CUDART_INF_F);
+            const bool complete = n_cand < kp && !(f.bound_floor > -CUDART_INF_F) && dropped_bits == 0u;
             if (complete) bound_total = -CUDART_INF;
             cert = misc->ek > bound_total || complete;  // false if either side is NaN
             if (misc->na == 0.0) {

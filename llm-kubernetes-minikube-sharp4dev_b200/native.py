@@ -10,7 +10,7 @@ import numpy as np
 RAGSTORE_F32, RAGSTORE_BF16 = 0, 1
 RAGSTORE_ADD_HOST, RAGSTORE_ADD_DEVICE, RAGSTORE_ADD_PRENORMALISED = 0, 1, 2
 RAGSTORE_HIT_CERTIFIED, RAGSTORE_HIT_EXACT_ROWS = 1, 2
-RAGSTORE_CREATE_SIDECAR_ON, RAGSTORE_CREATE_SIDECAR_OFF = 1, 2
+RAGSTORE_CREATE_SIDECAR_ON, RAGSTORE_CREATE_SIDECAR_OFF, RAGSTORE_CREATE_BF16_SHADOW = 1, 2, 4
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB = None

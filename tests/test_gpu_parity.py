@@ -1005,3 +1005,51 @@ def test_sharded_handle_redoes_queries_a_shard_could_not_certify():
             assert flags[i] & rb.RAGSTORE_HIT_CERTIFIED, i
     finally:
         st.close()
+
+
+# ---------------------------------------------------------------- batched top-k beyond 32 candidates, bf16 shadow
+@pytest.mark.parametrize("n,d,nq,k,dtype", [(30000, 256, 64, 50, 0), (30000, 256, 200, 100, 0), (40000, 128, 130, 100, 1),
+                                            (300000, 64, 40, 200, 0), (20000, 768, 16, 30, 1)])
+def test_batched_queries_with_large_top_k_take_the_tensor_core_path(n, d, nq, k, dtype):
+    """QueryAsync takes any topK (RagIndex.cs:59,65).  A batch asking for 30..200 hits is still ONE sweep of the corpus on
+    the tensor cores: every CTA keeps 32 keys per query, the per-query finalize merges them into 64..256 candidates."""
+    bf = dtype == 1
+    rows = oc.synth_rows(0, n, d, 1234, round_bf16=bf)
+    rows[100:140] = rows[99]                   # 41 identical rows in ONE tile: they overflow a CTA's 32-key list
+    qs = oc.synth_rows(0, nq, d, 5678)
+    qs[1] = rows[99]                           # ... for the query that ranks them first
+    with rb.RagStore(d, n, rb.RAGSTORE_BF16 if bf else rb.RAGSTORE_F32) as st:
+        st.add(rows, prenormalised=bf)
+        idx, sc, found, flags = st.search(qs, k)
+        info = st.info()
+        assert info["batch_launches"] >= 1
+        assert info["scan_launches"] <= 8       # only what the batch could not certify went through the scan kernel
+    for i in list(range(0, nq, 9)) + [1]:
+        eidx, esc = oc.query(rows, qs[i], k, n_threads=4)
+        assert list(idx[i]) == list(eidx), i
+        assert np.array_equal(sc[i].view(np.uint64), esc.view(np.uint64)), i
+
+
+@pytest.mark.parametrize("n,d,nq,k", [(30000, 256, 64, 10), (50000, 1024, 256, 10), (30000, 128, 140, 100), (200000, 64, 33, 5)])
+def test_bf16_shadow_nominates_and_fp32_rows_decide(n, d, nq, k):
+    """RAGSTORE_CREATE_BF16_SHADOW: batches read the bf16 image (kind::f16 tensor-core path), hits are rescored from the
+    fp32 rows -- the same indices and bit-identical scores as without the shadow; single queries never touch it."""
+    rows = oc.synth_rows(0, n, d, 1234)
+    rows[::7] *= 2.5                           # unnormalised rows: stored normalised, originals in the sidecar
+    qs = oc.synth_rows(0, nq, d, 5678)
+    with rb.RagStore(d, n, rb.RAGSTORE_F32, 0, rb.RAGSTORE_CREATE_BF16_SHADOW) as st:
+        st.add(rows[: n // 2])
+        st.add(rows[n // 2:])
+        idx, sc, found, flags = st.search(qs, k)
+        info = st.info()
+        assert info["batch_launches"] >= 1
+        one = st.search(qs[3], k)
+    cert = 0
+    for i in range(0, nq, 5):
+        eidx, esc = oc.query(rows, qs[i], k, n_threads=4)
+        assert list(idx[i]) == list(eidx), i
+        assert np.array_equal(sc[i].view(np.uint64), esc.view(np.uint64)), i
+        assert flags[i] & rb.RAGSTORE_HIT_EXACT_ROWS
+        cert += int(flags[i] & rb.RAGSTORE_HIT_CERTIFIED != 0)
+    assert cert == len(range(0, nq, 5))
+    assert list(one[0][0]) == list(idx[3]) and np.array_equal(one[1][0].view(np.uint64), sc[3].view(np.uint64))
