@@ -40,11 +40,15 @@ WORKLOADS = {
     "target10m": (10_000_000, 768, "f32", 10, "10M x 768 fp32 corpus, single query, top-10 (north_star target)"),
     "config4": (12_500_000, 768, "bf16", 100, "100M x 768 bf16 row-sharded over 8 (12.5M rows per GPU), single query, top-100"),
     "config3": (10_000_000, 1024, "f32", 10, "10M x 1024 fp32 corpus, batched 256 queries, top-10 (tcgen05 tf32 GEMM + exact rescoring)"),
+    "config3_shadow": (10_000_000, 1024, "f32", 10, "10M x 1024 fp32 corpus + bf16 shadow image (RAGSTORE_CREATE_BF16_SHADOW), batched 256 queries, top-10 "
+                                                    "(tcgen05 bf16 GEMM nominates 128 candidates per query from the shadow, exact rescoring from the fp32 rows)"),
+    "config4_batch": (12_500_000, 768, "bf16", 100, "one config4 shard (12.5M x 768 bf16) answering 256 queries per sweep, top-100 (tensor-core path with 128-256 candidates per query)"),
 }
+STORE_FLAGS = {"config3_shadow": 4}    # RAGSTORE_CREATE_BF16_SHADOW
 STREAM = {"name": "config5", "total_rows": 10_000_000, "dim": 768, "top_k": 10, "batch_rows": 65536, "queries_per_batch": 1024,
           "desc": "streaming ingest + query: 10M x 768 fp32 appended in 64k-row host batches through the upload/normalise kernel "
                   "while 1k-query batches (top-10) are served; rows dealt block-cyclically over the GPUs"}
-BATCH_QUERIES = {"config3": 256}   # queries per step for the batched (tensor-core) workloads
+BATCH_QUERIES = {"config3": 256, "config3_shadow": 256, "config4_batch": 256}   # queries per step for the batched (tensor-core) workloads
 CORPUS_SEED, QUERY_SEED = 1234, 5678
 
 
@@ -308,7 +312,8 @@ def measure_workload(name, args, torch, dist, rb, native, rank, world, dev, do_e
     if args.rows:
         rows = args.rows
     esz = 4 if dtype == "f32" else 2
-    st = rb.RagStore(dim, rows, rb.RAGSTORE_F32 if dtype == "f32" else rb.RAGSTORE_BF16, dev)
+    st = rb.RagStore(dim, rows, rb.RAGSTORE_F32 if dtype == "f32" else rb.RAGSTORE_BF16, dev, STORE_FLAGS.get(name, 0))
+    shadow = bool(STORE_FLAGS.get(name, 0) & 4)
     st.set_row_base(rank * rows)
     ts = torch.cuda.Stream()
     with torch.cuda.stream(ts):
@@ -405,7 +410,10 @@ def measure_workload(name, args, torch, dist, rb, native, rank, world, dev, do_e
             lat = sorted(evs[i].elapsed_time(evs[i + 1]) for i in range(n_lat))
             res["latency_ms"] = {"n": n_lat, "min": lat[0], "median": lat[n_lat // 2],
                                  "p99": lat[min(n_lat - 1, int(n_lat * 0.99))], "max": lat[-1]}
-        res["achieved_gbs"] = rows * dim * esz / (kern_ms * 1e-3) / 1e9
+        # a shadowed store's batches read the bf16 image: 2 bytes per element are the algorithmic bytes of that sweep
+        res["achieved_gbs"] = rows * dim * (2 if shadow else esz) / (kern_ms * 1e-3) / 1e9
+        if shadow:
+            res["operands"] = "bf16"
         last_q_index = (qi[0] - 1) % n_q
         torch.cuda.synchronize()
         res["flags"] = int(d_flags.flatten()[0].item())
@@ -747,7 +755,7 @@ def main():
     extra = {}
     if world == 1 and not args.no_extra and not args.rows:
         peak, _ = measured_peaks()
-        for name in ("config2", "config1", "config3", "target10m"):
+        for name in ("config2", "config1", "config3", "config3_shadow", "target10m"):
             if name == args.workload:
                 continue
             try:
@@ -759,7 +767,8 @@ def main():
                 extra[name] = {"desc": r["desc"], "vectors_per_s": r["value"], "queries_per_s": r["queries_per_s"], "ms_per_step": r["ms_per_step"],
                                "achieved_gbs": r["achieved_gbs"], "frac_of_measured_hbm": r["achieved_gbs"] / peak,
                                "frac_of_8TBs_spec": r["achieved_gbs"] / 8000.0, "steps": sub.steps, "flags": r["flags"], "latency_ms": r.get("latency_ms"),
-                               "clocks": r["clocks"], "parity": r.get("parity"), "certified_fraction": r.get("certified_fraction")}
+                               "clocks": r["clocks"], "parity": r.get("parity"), "certified_fraction": r.get("certified_fraction"),
+                               "algorithmic_bytes_per_sweep": r["rows_per_gpu"] * r["dim"] * (4 if (r["storage"] == "f32" and r.get("operands") != "bf16") else 2)}
                 if "e2e" in r:
                     extra[name]["e2e"] = r["e2e"]
                 if "tensor_tflops" in r:
@@ -793,7 +802,7 @@ def main():
                          "traffic": traffic, "peak_source": peak_src, "frac_of_8TBs_spec": r["achieved_gbs"] / 8000.0,
                          "kernel": "batch_score_kernel_2sm (threshold pass + full pass; prep, thresholds and finalize included: whole step timed)" if batched else "scan_topk_kernel",
                          "kernel_ms": r["kernel_ms"],
-                         "algorithmic_bytes_per_launch": r["rows_per_gpu"] * r["dim"] * (4 if r["storage"] == "f32" else 2),
+                         "algorithmic_bytes_per_launch": r["rows_per_gpu"] * r["dim"] * (4 if (r["storage"] == "f32" and r.get("operands") != "bf16") else 2),
                          "note": "peak = measured read+write copy bandwidth; a read-only stream can exceed it, so both denominators are given"},
             "tensor": tensor_block(r) if "tensor_tflops" in r else None,
             "cpu_baseline": r.get("cpu_baseline"),
