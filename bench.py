@@ -398,6 +398,12 @@ def measure_workload(name, args, torch, dist, rb, native, rank, world, dev, do_e
             kern_ms = time_device_steps(torch, dist, 1, lambda: st.search_shard_device(d_q[0], k, d_cand, d_flags, stream=ts.cuda_stream),
                                         max(10, args.steps // 4), 3) / max(10, args.steps // 4)
         res["kernel_ms"] = kern_ms
+        if world > 1:
+            # every rank's own shard scan, timed alone on its GPU: the step is paced by the slowest of them plus the exchange
+            km = torch.tensor([kern_ms], dtype=torch.float64, device="cuda")
+            allk = torch.empty(world, dtype=torch.float64, device="cuda")
+            dist.all_gather_into_tensor(allk, km)
+            res["kernel_ms_per_rank"] = [float(x) for x in allk.cpu().tolist()]
         if world == 1:
             # per-step latency distribution (median and p99), a separate pass with an event between steps
             n_lat = min(max(args.steps, 20), 400)
@@ -463,8 +469,8 @@ def measure_workload(name, args, torch, dist, rb, native, rank, world, dev, do_e
                 hq_pin.copy_(torch.from_numpy(hq_rows[i % n_q]))
                 d_q1.copy_(hq_pin, non_blocking=True)
                 sh.search_device(d_q1, k)
-                h_idx.copy_(d_idx, non_blocking=True)
-                h_sc.copy_(d_score, non_blocking=True)
+                h_idx.copy_(d_idx[:k], non_blocking=True)
+                h_sc.copy_(d_score[:k], non_blocking=True)
                 ts.synchronize()
             for i in range(3):
                 e2e_step(i)
@@ -797,6 +803,7 @@ def main():
             "queries_per_s": r["queries_per_s"],
             "config": config_dict(args.workload, world, args.rows),
             "exchange": r.get("exchange"),
+            "shard_scan_ms_per_rank": r.get("kernel_ms_per_rank"),
             "rescoring": "exact fp64 (reference arithmetic) for k' >= k candidates inside the same launch",
             "roofline": {"bound": "hbm", "achieved": r["achieved_gbs"], "peak": peak, "unit": "GB/s", "frac": r["achieved_gbs"] / peak,
                          "traffic": traffic, "peak_source": peak_src, "frac_of_8TBs_spec": r["achieved_gbs"] / 8000.0,
