@@ -1075,9 +1075,10 @@ int launch_batch_search(const BatchSearchArgs& b, cudaStream_t stream) {
             // small corpora: stride 1, i.e. the "sample" is a full (cheap: 4 registers per thread, no lists) sweep --
             // still far cheaper than filling cold lists column by column (~200 us per CTA for 256 queries)
             int stride = static_cast<int>(n_tiles / (2ll * nlists));   // every CTA (pair) samples >= 2 tiles when it can
-            // ~kp * stride rows per query beat the threshold in the whole corpus; a CTA keeps 32 of its share, so the
-            // stride is held where that share (kp * stride / nlists) stays around 16 and lists rarely overflow
-            const int stride_lists = std::max(1, 16 * nlists / s.kp);
+            // ~thr_rank * stride rows per query beat the threshold in the whole corpus; a CTA keeps 32 of its share, so the
+            // stride is held where that share (thr_rank * stride / nlists) stays around 16 and lists rarely overflow
+            const int thr_rank = b.thr_rank > 0 ? std::min(b.thr_rank, s.kp) : s.kp;
+            const int stride_lists = std::max(1, 16 * nlists / thr_rank);
             const int stride_max = std::min(kn.stride_max, stride_lists);   // (knob: experiments)
             stride = stride > stride_max ? stride_max : (stride < 1 ? 1 : stride);
             a.tile_stride = stride;
@@ -1085,8 +1086,8 @@ int launch_batch_search(const BatchSearchArgs& b, cudaStream_t stream) {
             e = launch_main();
             if (e != cudaSuccess) return static_cast<int>(e);
             const int nvals = nlists * 4;
-            // threshold = the kp-th largest sampled score: at least kp real rows reach it (fewer samples than kp: no threshold)
-            batch_thresholds_kernel<<<b.nq, 256, nvals * sizeof(float), stream>>>(reinterpret_cast<const float*>(glists), nvals, s.kp, thr0);
+            // threshold = the thr_rank-th largest sampled score: at least that many real rows reach it (fewer samples: no threshold)
+            batch_thresholds_kernel<<<b.nq, 256, nvals * sizeof(float), stream>>>(reinterpret_cast<const float*>(glists), nvals, thr_rank, thr0);
             e = cudaGetLastError();
             if (e != cudaSuccess) return static_cast<int>(e);
             a.sample = 0;

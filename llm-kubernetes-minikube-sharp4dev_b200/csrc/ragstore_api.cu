@@ -194,6 +194,7 @@ void fill_batch_args(const ragstore* s, int64_t n, int take, int kp, BatchSearch
     b.scan.eps = batch_eps(s);
     b.operand_mat = (s->dtype == RAGSTORE_F32 && s->shadow) ? s->shadow : nullptr;
     b.operand_bf16 = b.operand_mat ? 1 : 0;
+    b.thr_rank = kp;   // the skip threshold follows what the request needs, not the widened candidate set
 }
 
 int acquire_ctx(ragstore* s) {

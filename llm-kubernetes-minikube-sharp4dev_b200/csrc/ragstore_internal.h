@@ -94,6 +94,9 @@ struct BatchSearchArgs {
     const void* operand_mat; // rows the tensor cores read: null = scan.mat; else a bf16 shadow of an fp32 store
                              // (same row count and ld): nomination on bf16 operands, rescoring from the fp32 rows
     int operand_bf16;        // 1 when operand_mat is bf16 although scan.dtype is fp32
+    int thr_rank;            // rank of the sampled score that becomes the skip threshold (0 = scan.kp).  Smaller than
+                             // scan.kp when the candidate set is wider than the request needs (shadow nomination): fewer
+                             // rows pass the threshold, so the sampling pass can stay sparse
     const float* d_queries;  // raw queries [nq][dim], device
     int nq;
     int out_stride;          // hits per query in scan.out_idx / scan.out_score
