@@ -373,7 +373,7 @@ def measure_workload(name, args, torch, dist, rb, native, rank, world, dev, do_e
                 q = d_q[qi[0] % n_q]
                 qi[0] += 1
                 sh.search_device(q, k)      # shard scan -> exchange (peer-memory kernel, or NCCL all-gather + merge kernel)
-            launches_per_step = 2
+            launches_per_step = 1 if (sh.peer is not None and sh.fused) else 2
 
         with ClockSampler(dev, enabled=(rank == 0)) as clk:
             ms = time_device_steps(torch, dist, world, step, args.steps, args.warmup)
@@ -381,7 +381,8 @@ def measure_workload(name, args, torch, dist, rb, native, rank, world, dev, do_e
         total_rows = rows * world
         exchange_used = None
         if world > 1:
-            exchange_used = "p2p: one kernel per rank over IPC-mapped peer memory (csrc/exchange.cu)" if sh.peer is not None else \
+            exchange_used = ("p2p, fused: the shard scan's last CTA publishes, waits and merges over IPC-mapped peer memory (one launch per rank)"
+                             if sh.fused and nqb == 1 else "p2p: one exchange kernel per rank over IPC-mapped peer memory (csrc/exchange.cu)") if sh.peer is not None else \
                 ("nccl all-gather + merge kernel" + (" (p2p requested but peers could not be mapped)" if args.exchange == "p2p" else ""))
         res = {"ms_per_step": ms / args.steps, "value": total_rows * args.steps / (ms * 1e-3), "clocks": clocks, "exchange": exchange_used,
                "ingest_vectors_per_s": rows / ingest_s, "launches_per_step": launches_per_step,
@@ -484,8 +485,10 @@ def measure_workload(name, args, torch, dist, rb, native, rank, world, dev, do_e
             dt = float(dt.item())
         res["e2e"] = {"value": rows * world * n_e2e / dt, "unit": "vectors/s", "h2d_bytes_per_step": dim * 4,
                       "d2h_bytes_per_step": k * 16, "ms_per_step": dt / n_e2e * 1e3, "steps": n_e2e,
-                      "api": ("ShardedSearcher.search_host: ragstore_search_shard_hostq (query in the kernel parameters) + ragstore_exchange_merge writing "
-                              "into page-locked host memory; two launches and one stream wait per rank") if host_path else
+                      "api": (("ShardedSearcher.search_host: ragstore_search_shard_exchange -- query in the kernel parameters, the scan's last CTA exchanges "
+                               "and merges over peer memory and writes the hits into page-locked host memory; ONE launch and one stream wait per rank") if sh.fused else
+                              ("ShardedSearcher.search_host: ragstore_search_shard_hostq (query in the kernel parameters) + ragstore_exchange_merge writing "
+                               "into page-locked host memory; two launches and one stream wait per rank")) if host_path else
                              "host query -> ShardedSearcher.search_device (shard scan + exchange + merge) -> host hits, per rank"}
 
     # CPU baseline (rank 0, N = 1 only): the oracle, one thread, on a bounded sample of the workload
@@ -711,8 +714,9 @@ def main():
     ap.add_argument("--workload", default=None, choices=sorted(WORKLOADS) + ["config5"],
                     help="default: target10m at N = 1, config4 at N > 1 (north_star's two stated targets)")
     ap.add_argument("--rows", type=int, default=0, help="override rows per GPU")
-    ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"],
-                    help="N > 1: how the per-shard hits meet -- one peer-memory kernel per rank (default) or NCCL all-gather + merge kernel")
+    ap.add_argument("--exchange", default="p2p", choices=["p2p", "p2p-2launch", "nccl"],
+                    help="N > 1: how the per-shard hits meet -- inside the shard scan's last CTA over peer memory (default: one launch per "
+                         "rank and query), the same exchange as a second launch, or NCCL all-gather + merge kernel")
     ap.add_argument("--no-reserve", action="store_true", help="config5: let appends map device memory on demand")
     ap.add_argument("--pinned", action="store_true", help="config5: the application's batches live in page-locked memory")
     ap.add_argument("--no-extra", action="store_true", help="skip the extra config1 / config2 / config3 measurements")

@@ -255,6 +255,17 @@ RAGSTORE_API int ragstore_exchange_merge(ragstore_exchange_t* x, const ragstore_
 RAGSTORE_API int ragstore_exchange_merge_flags(ragstore_exchange_t* x, const ragstore_cand* d_mine, const int32_t* d_my_flags,
                                                int n_queries, int per_shard, int top_k, int64_t* d_idx, double* d_score,
                                                int32_t* d_found, int32_t* d_flags, int32_t* d_status, void* stream);
+/* Steps 1, "all-gather" and 2 of the row-sharded search in ONE launch per rank: the shard's scan kernel, whose last CTA
+ * -- the one that rescored and ranked the shard's hits -- also stores them into every rank's inbox, waits for the other
+ * ranks' and ranks the G x k records.  Replaces, per rank, the whole of the sharded RagIndex.QueryAsync
+ * (RagIndex.cs:59-67).  Exactly one of d_query (device) / h_query (host memory, read before the call returns; it rides
+ * in the kernel parameters, dim <= 1024) is given.  d_mine: max(1,top_k) records of scratch on this device (receives
+ * this shard's own hits); d_idx / d_score: max(1,top_k) merged hits (device or page-locked host memory); d_flags: the
+ * RAGSTORE_HIT_* bits ANDed over all ranks; d_status as ragstore_exchange_merge.  Collective like
+ * ragstore_exchange_merge (same sequence of calls on every rank); top_k <= 256. */
+RAGSTORE_API int ragstore_search_shard_exchange(ragstore_t* s, ragstore_exchange_t* x, const float* d_query, const float* h_query,
+                                                int top_k, ragstore_cand* d_mine, int64_t* d_idx, double* d_score,
+                                                int32_t* d_found, int32_t* d_flags, int32_t* d_status, void* stream);
 RAGSTORE_API int ragstore_exchange_destroy(ragstore_exchange_t* x);
 
 /* No counterpart in the reference: an extra search entry point for hosts that are not allowed to

@@ -19,26 +19,9 @@
 #include <cstring>
 #include <new>
 
-#include "merge_device.cuh"
+#include "exchange_impl.h"
 
 namespace rag {
-
-constexpr int kMaxWorld = 16;
-
-struct ExchangeView {
-    ragstore_cand* rec[kMaxWorld];        // rank r's inbox records
-    unsigned long long* flag[kMaxWorld];  // rank r's inbox flags
-    int world, rank, max_records, max_queries;
-};
-
-__device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
-    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
-}
-__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
-    unsigned long long v;
-    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-    return v;
-}
 
 __global__ void __launch_bounds__(256) exchange_merge_kernel(const ExchangeView v, const ragstore_cand* __restrict__ mine, int n_queries,
                                                              int per_shard, int k_req, unsigned long long seq,
@@ -100,16 +83,6 @@ __global__ void __launch_bounds__(256) exchange_merge_kernel(const ExchangeView 
 }  // namespace rag
 
 using namespace rag;
-
-struct ragstore_exchange {
-    int device = 0, world = 0, rank = 0, max_records = 0, max_queries = 0, sm_count = 0;
-    void* base = nullptr;                 // this rank's inbox
-    size_t bytes = 0, flag_bytes = 0;
-    void* peer[kMaxWorld] = {};           // mapped inboxes (peer[rank] == base)
-    bool connected = false;
-    unsigned long long seq = 0;
-    ExchangeView view{};
-};
 
 namespace {
 struct DeviceScope {
@@ -196,6 +169,11 @@ int ragstore_exchange_connect(ragstore_exchange_t* x, const void* all_handles) {
         x->view.flag[r] = static_cast<unsigned long long*>(x->peer[r]);
         x->view.rec[r] = reinterpret_cast<ragstore_cand*>(static_cast<uint8_t*>(x->peer[r]) + x->flag_bytes);
     }
+    {
+        cudaError_t e = cudaMalloc(&x->d_view, sizeof(ExchangeView));
+        if (e == cudaSuccess) e = cudaMemcpy(x->d_view, &x->view, sizeof(ExchangeView), cudaMemcpyHostToDevice);
+        if (e != cudaSuccess) return api_fail(RAGSTORE_ERR_CUDA, "ragstore_exchange_connect: device copy of the view", cudaGetErrorString(e));
+    }
     x->connected = true;
     return RAGSTORE_OK;
 }
@@ -239,6 +217,7 @@ int ragstore_exchange_destroy(ragstore_exchange_t* x) {
         for (int r = 0; r < x->world; ++r)
             if (r != x->rank && x->peer[r]) cudaIpcCloseMemHandle(x->peer[r]);
         if (x->base) cudaFree(x->base);
+        if (x->d_view) cudaFree(x->d_view);
         cudaGetLastError();
     }
     delete x;

@@ -16,6 +16,7 @@
 #include <string>
 #include <vector>
 
+#include "exchange_impl.h"
 #include "store_impl.h"
 
 using namespace rag;
@@ -697,6 +698,52 @@ int ragstore_search_shard_hostq(ragstore_t* s, const float* h_query, int top_k, 
                                 int32_t* d_flags, void* stream) {
     if (!h_query) return fail(RAGSTORE_ERR_INVALID, "ragstore_search_shard_hostq: null argument");
     return search_shard_impl(s, nullptr, h_query, top_k, d_out, d_flags, stream);
+}
+
+// Row-sharded search in ONE launch per rank: the shard scan whose last CTA also publishes this shard's hits to every peer,
+// waits for theirs and merges (topk_device.cuh, "the exchange step, fused").
+int ragstore_search_shard_exchange(ragstore_t* s, ragstore_exchange_t* x, const float* d_query, const float* h_query, int top_k,
+                                   ragstore_cand* d_mine, int64_t* d_idx, double* d_score, int32_t* d_found, int32_t* d_flags,
+                                   int32_t* d_status, void* stream) {
+    if (!s || !x || (!d_query == !h_query) || !d_mine || !d_idx || !d_score || !d_found)
+        return fail(RAGSTORE_ERR_INVALID, "ragstore_search_shard_exchange: null argument (give exactly one of d_query / h_query)");
+    if (s->sharded) return fail(RAGSTORE_ERR_INVALID, "ragstore_search_shard_exchange: per-device entry point, not available on a multi-device handle");
+    if (!x->connected) return fail(RAGSTORE_ERR_INVALID, "ragstore_search_shard_exchange: call ragstore_exchange_connect first");
+    if (x->device != s->device) return fail(RAGSTORE_ERR_INVALID, "ragstore_search_shard_exchange: store and exchange live on different devices");
+    if (h_query && s->dim > kParamQueryMax)
+        return fail(RAGSTORE_ERR_UNSUPPORTED, "ragstore_search_shard_exchange: rows above 1024 elements need the query in device memory");
+    const int req = top_k < 1 ? 1 : top_k;
+    if (req > kMaxKp) return fail(RAGSTORE_ERR_UNSUPPORTED, "top_k above 256 is not covered by the one-launch form");
+    if (req > x->max_records || x->world * req > 4096)
+        return fail(RAGSTORE_ERR_INVALID, "ragstore_search_shard_exchange: top_k exceeds what the exchange was created for");
+    DeviceGuard g(s->device);
+    cudaStream_t st = stream ? static_cast<cudaStream_t>(stream) : s->dev_stream;
+    const int64_t n = s->count.load(std::memory_order_acquire);
+    if (n == 0) {
+        // an empty shard launches no scan: padding records, then the stand-alone exchange kernel (same collective call)
+        const float* q = d_query ? d_query : h_query;
+        int rc = d_query ? ragstore_search_shard_device(s, q, top_k, d_mine, d_flags, stream) : ragstore_search_shard_hostq(s, q, top_k, d_mine, d_flags, stream);
+        if (rc) return rc;
+        return ragstore_exchange_merge_flags(x, d_mine, d_flags, 1, req, top_k, d_idx, d_score, d_found, d_flags, d_status, st);
+    }
+    const int take = static_cast<int>(std::min<int64_t>(n, req));
+    ScanArgs a = base_args(s, n, take, choose_kp(take));
+    a.d_query = d_query;
+    a.scratch = s->dev_scratch;
+    a.out_flags = d_flags ? d_flags : reinterpret_cast<int32_t*>(s->dev_scratch.stamps + 7);   // the tail reads this shard's flags back
+    a.out_cand = d_mine;
+    a.cand_slots = req;
+    a.xch = x->d_view;
+    a.xseq = ++x->seq;
+    a.x_idx = d_idx;
+    a.x_score = d_score;
+    a.x_found = d_found;
+    a.x_flags = d_flags;
+    a.x_status = d_status;
+    s->n_scan_launches.fetch_add(1, std::memory_order_relaxed);
+    const int rc = launch_scan(a, st, h_query);
+    if (rc) return fail(RAGSTORE_ERR_CUDA, "scan kernel launch", cudaGetErrorString(static_cast<cudaError_t>(rc)));
+    return RAGSTORE_OK;
 }
 
 int ragstore_search_shard_batch_device(ragstore_t* s, const float* d_queries, int n_queries, int top_k, ragstore_cand* d_out,

@@ -7,6 +7,8 @@
 
 namespace rag {
 
+struct ExchangeView;   // exchange_device.cuh
+
 constexpr int kConsumerWarps = 8;                       // warps that score rows
 constexpr int kScanThreads = (kConsumerWarps + 1) * 32; // + one producer warp (bulk-copy issue)
 constexpr int kMaxKp = 256;                             // largest candidate list kept per warp/CTA
@@ -53,6 +55,16 @@ struct ScanArgs {
     int32_t* out_flags;     // [1] RAGSTORE_HIT_*
     ragstore_cand* out_cand;// [cand_slots] shard records, padded with {-inf,-1} (may be null)
     int cand_slots;
+    // Row-sharded corpora: when `xch` is set the launch's LAST CTA also does the exchange step of SURVEY 8(e) -- it stores
+    // the cand_slots records it has just written to out_cand into every rank's inbox over peer memory, waits for the
+    // other ranks' records of call `xseq` and ranks all of them: one launch per query per rank (exchange_device.cuh)
+    const ExchangeView* xch;           // device copy of the exchange view (null: no exchange)
+    unsigned long long xseq;          // sequence number of this collective call
+    int64_t* x_idx;                   // [cand_slots] merged global ids, best first
+    double* x_score;                  // [cand_slots]
+    int32_t* x_found;                 // [1]
+    int32_t* x_flags;                 // [1] RAGSTORE_HIT_* ANDed over all ranks (may be null)
+    int32_t* x_status;                // [1] 0, or 1 when a peer's records did not arrive in time (may be null)
     double* out_bound;      // [1] bound + eps + shrink: no row outside the collected candidates scores above it (may be null)
     uint64_t* out_last_key; // [1] approximate key of the worst collected candidate, 0 if none (may be null)
     int sm_count;

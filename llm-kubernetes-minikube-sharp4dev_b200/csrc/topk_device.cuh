@@ -5,6 +5,7 @@
 #include <math_constants.h>
 
 #include "common.cuh"
+#include "exchange_device.cuh"
 #include "ragstore_internal.h"
 
 namespace rag {
@@ -392,6 +393,56 @@ __device__ __forceinline__ void finalize_candidates(const ScanArgs& a, const Fin
         if (a.out_last_key) *a.out_last_key = n_cand > 0 ? lists[n_cand - 1] : 0ull;
         stamp(a, 5);
     }
+    if (a.xch == nullptr) return;
+
+    // ---- the exchange step, fused: this CTA is the only one of the launch still running.  Publish this shard's records to
+    // every rank (own inbox included), raise the arrival words, wait for everybody else's, rank the G x k records.
+    // Liveness and the two-slot argument are those of exchange.cu: every rank publishes BEFORE it waits for anything,
+    // and a rank can only reach call s+1 once every rank has published call s.
+    __syncthreads();   // out_cand / out_flags of this launch were written by threads of this CTA
+    const ExchangeView& v = *a.xch;
+    const int per = a.cand_slots;
+    const int slot = static_cast<int>(a.xseq & 1ull);
+    const size_t rec_base = (static_cast<size_t>(slot) * v.world + v.rank) * v.max_records;
+    const size_t flag_base = (static_cast<size_t>(slot) * v.world + v.rank) * v.max_queries;
+    {
+        const uint4* src = reinterpret_cast<const uint4*>(a.out_cand);
+        for (int i = tid; i < v.world * per; i += kScanThreads) {
+            const int r = i / per, j = i - r * per;
+            reinterpret_cast<uint4*>(v.rec[r] + rec_base)[j] = src[j];   // plain stores over NVLink into the peer's inbox
+        }
+    }
+    __threadfence_system();
+    if (tid == 0) {
+        misc->is_last = 0;   // reused: "a peer timed out"
+        misc->inexact = 3;   // reused: flags ANDed over the ranks
+    }
+    __syncthreads();
+    const int my_flags = a.out_flags ? *a.out_flags : 3;
+    if (tid < v.world)
+        st_release_sys(v.flag[tid] + flag_base, (a.xseq << 2) | static_cast<unsigned long long>(my_flags & 3));
+    if (tid < v.world) {
+        const unsigned long long* fw = v.flag[v.rank] + (static_cast<size_t>(slot) * v.world + tid) * v.max_queries;
+        const unsigned long long t0 = globaltimer_ns();
+        unsigned long long w;
+        while (((w = ld_acquire_sys(fw)) >> 2) != a.xseq) {
+            if (globaltimer_ns() - t0 > 5000000000ull) {   // 5 s: reported, never hung on
+                misc->is_last = 1;
+                w = 0;
+                break;
+            }
+            __nanosleep(64);
+        }
+        atomicAnd(&misc->inexact, static_cast<int>(w & 3ull));
+    }
+    __syncthreads();
+    if (tid == 0) {
+        if (a.x_status) *a.x_status = misc->is_last;
+        if (a.x_flags) *a.x_flags = misc->inexact;
+    }
+    const ragstore_cand* inbox = v.rec[v.rank] + static_cast<size_t>(slot) * v.world * v.max_records;
+    merge_query_block<true>(inbox, static_cast<size_t>(v.max_records), v.world, 0, per, per, a.x_idx, a.x_score, a.x_found, f.ring,
+                            &misc->n_cand);
 }
 
 }  // namespace rag

@@ -67,6 +67,7 @@ def lib():
             "ragstore_exchange_connect": (C.c_int, [vp, vp]),
             "ragstore_exchange_merge": (C.c_int, [vp, vp, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp, vp]),
             "ragstore_exchange_merge_flags": (C.c_int, [vp, vp, vp, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp, vp, vp]),
+            "ragstore_search_shard_exchange": (C.c_int, [vp, vp, vp, vp, C.c_int, vp, vp, vp, vp, vp, vp, vp]),
             "ragstore_exchange_destroy": (C.c_int, [vp]),
             "ragstore_info": (C.c_int, [vp, i64p, C.c_int]),
             "ragstore_debug_reload_env": (C.c_int, []),
@@ -281,6 +282,14 @@ class RagStore:
 
     def search_shard_device(self, d_query, top_k: int, d_cand, d_flags=None, stream: int = 0):
         check(lib().ragstore_search_shard_device(self._h, _ptr(d_query), int(top_k), _ptr(d_cand), _ptr(d_flags), C.c_void_p(stream)))
+
+    def search_shard_exchange(self, peer: "PeerExchange", top_k: int, d_mine, d_idx, d_score, d_found, d_flags=None, d_status=None,
+                              d_query=None, h_query: np.ndarray = None, stream: int = 0):
+        """One launch: shard scan + peer-memory exchange + merge (ragstore_search_shard_exchange).  Give d_query (device
+        tensor) or h_query (C-contiguous float32 host array, rides in the kernel parameters)."""
+        hq = C.c_void_p(h_query.ctypes.data) if h_query is not None else None
+        check(lib().ragstore_search_shard_exchange(self._h, peer._h, _ptr(d_query), hq, int(top_k), _ptr(d_mine), _ptr(d_idx), _ptr(d_score),
+                                                   _ptr(d_found), _ptr(d_flags), _ptr(d_status), C.c_void_p(stream)))
 
     def search_shard_hostq(self, h_query: np.ndarray, top_k: int, d_cand, d_flags=None, stream: int = 0):
         """Shard search with the query in host memory (C-contiguous float32 of `dim` values); it rides in the kernel parameters."""

@@ -5,8 +5,10 @@ The order (score desc, global id asc) is what a single RagIndex over the whole c
 (reference Helpers/RagIndex.cs:64-65).
 
 Two forms of the exchange:
-  * "p2p"  -- one kernel per rank stores its records into every peer's inbox over NVLink, waits for the peers' flags
-              and merges (csrc/exchange.cu): no NCCL call and one launch on the query path;
+  * "p2p"  -- ONE launch per rank and query: the shard scan's last CTA stores its records into every peer's inbox over
+              NVLink, waits for the peers' arrival words and merges (ragstore_search_shard_exchange); batches use the
+              stand-alone exchange kernel after the shard's batched search (csrc/exchange.cu).  No NCCL on the query path;
+  * "p2p-2launch" -- the same exchange as a second launch behind every shard scan (what "p2p" was before the fusion);
   * "nccl" -- torch.distributed.all_gather_into_tensor + the merge kernel (also what tests inject a fake into)."""
 from __future__ import annotations
 
@@ -66,10 +68,11 @@ class ShardedSearcher:
         self._all_gather = all_gather
         self.peer = None
         self.d_status = torch.zeros(max_queries, dtype=torch.int32, device="cuda")
-        if exchange == "p2p":
+        self.fused = exchange == "p2p"
+        if exchange in ("p2p", "p2p-2launch"):
             self.peer = self._connect_peers(max_k, max_queries)
         elif exchange != "nccl":
-            raise ValueError("exchange must be 'p2p' or 'nccl'")
+            raise ValueError("exchange must be 'p2p', 'p2p-2launch' or 'nccl'")
 
     def _connect_peers(self, max_k: int, max_queries: int):
         """Create this rank's inbox, swap the 64-byte IPC handles (one all-gather at set-up time), map the peers.
@@ -110,6 +113,10 @@ class ShardedSearcher:
             raise ValueError("k above max_k")
         stream = _current_stream_handle(self.torch)
         per, total = gather_layout(self.world, req)
+        if self.peer is not None and self.fused:
+            self.store.search_shard_exchange(self.peer, k, self.d_cand, self.d_idx, self.d_score, self.d_found, self.d_gflags, self.d_status,
+                                             d_query=d_query, stream=stream)
+            return
         self.store.search_shard_device(d_query, k, self.d_cand, self.d_flags, stream=stream)
         if self.peer is not None:
             self.peer.merge(self.d_cand, 1, req, k, self.d_idx, self.d_score, self.d_found, self.d_status, stream=stream,
@@ -143,9 +150,13 @@ class ShardedSearcher:
         cur = torch.cuda.current_stream()
         stream = cur.cuda_stream or 1
         p_idx, p_sc, p_found, p_status = self._h_ptr
-        self.store.search_shard_hostq(h_query, k, self.d_cand, self.d_flags, stream=stream)
-        self.peer.merge(self.d_cand, 1, req, k, p_idx, p_sc, p_found, p_status, stream=stream,
-                        d_my_flags=self.d_flags, d_flags=self._h_meta.data_ptr() + 8)
+        if self.fused and self.store.dim <= 1024:
+            self.store.search_shard_exchange(self.peer, k, self.d_cand, p_idx, p_sc, p_found, self._h_meta.data_ptr() + 8, p_status,
+                                             h_query=h_query, stream=stream)
+        else:
+            self.store.search_shard_hostq(h_query, k, self.d_cand, self.d_flags, stream=stream)
+            self.peer.merge(self.d_cand, 1, req, k, p_idx, p_sc, p_found, p_status, stream=stream,
+                            d_my_flags=self.d_flags, d_flags=self._h_meta.data_ptr() + 8)
         cur.synchronize()
         np_idx, np_sc, np_meta = self._h_np
         if np_meta[1] != 0:

@@ -70,21 +70,21 @@ def _worker(rank, world, port, name, out_dir):
     with rb.RagStore(d, max(1, len(ids)), rb.RAGSTORE_BF16 if bf else rb.RAGSTORE_F32, rank) as st:
         if len(ids):
             st.add(rows, prenormalised=bf)
-        for mode in ("p2p", "nccl"):
+        for mode in ("p2p", "p2p-2launch", "nccl"):     # fused into the scan's last CTA / separate exchange kernel / NCCL
             sh = rb.ShardedSearcher(st, rank, world, int(ids[0]) if (len(ids) and case["block"] == 0) else 0, max_k=k, device=rank,
                                     exchange=mode, max_queries=nq)
             if case["block"]:
                 st.set_row_blocking(case["block"], world, rank)
-            if mode == "p2p":
+            if mode != "nccl":
                 assert sh.peer is not None, "peer inboxes could not be mapped"
             single = []
-            n_calls = case["calls"] if mode == "p2p" else min(case["calls"], 6)
+            n_calls = case["calls"] if mode == "p2p" else min(case["calls"], 12)
             for i in range(n_calls):                # consecutive calls: both inbox slots, many times
                 if mode == "p2p" and case["delay_rank"] == rank and i == n_calls // 2:
                     time.sleep(0.05)                # this rank is late: the others wait for it inside their kernels
                 idx, sc = sh.search(qs[i % nq], k)
                 single.append((idx.copy(), sc.copy()))
-            if mode == "p2p" and d <= 1024:         # host query in (kernel parameters), host hits out (page-locked memory)
+            if mode != "nccl" and d <= 1024:        # host query in (kernel parameters), host hits out (page-locked memory)
                 hq = np.ascontiguousarray(qs.cpu().numpy())
                 for i in range(min(6, n_calls)):
                     hidx, hsc = sh.search_host(hq[i % nq], k)
@@ -103,11 +103,12 @@ def _worker(rank, world, port, name, out_dir):
     np.save(os.path.join(out_dir, f"r{rank}_p2p_sc.npy"), res["p2p"][2])
     np.save(os.path.join(out_dir, f"r{rank}_single_idx.npy"), np.stack([s[0] for s in res["p2p"][4]]))
     np.save(os.path.join(out_dir, f"r{rank}_single_sc.npy"), np.stack([s[1] for s in res["p2p"][4]]))
-    for a, b in zip(res["p2p"][0], res["nccl"][0]):
-        assert np.array_equal(a[0], b[0]) and np.array_equal(a[1].view(np.uint64), b[1].view(np.uint64))
-    assert np.array_equal(res["p2p"][1], res["nccl"][1])
-    assert np.array_equal(res["p2p"][2].view(np.uint64), res["nccl"][2].view(np.uint64))
-    assert np.array_equal(res["p2p"][3], res["nccl"][3])
+    for m in ("p2p", "p2p-2launch"):
+        for a, b in zip(res[m][0], res["nccl"][0]):
+            assert np.array_equal(a[0], b[0]) and np.array_equal(a[1].view(np.uint64), b[1].view(np.uint64)), m
+        assert np.array_equal(res[m][1], res["nccl"][1]), m
+        assert np.array_equal(res[m][2].view(np.uint64), res["nccl"][2].view(np.uint64)), m
+        assert np.array_equal(res[m][3], res["nccl"][3]), m
     dist.destroy_process_group()
 
 
