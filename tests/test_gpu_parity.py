@@ -1053,3 +1053,42 @@ def test_bf16_shadow_nominates_and_fp32_rows_decide(n, d, nq, k):
         cert += int(flags[i] & rb.RAGSTORE_HIT_CERTIFIED != 0)
     assert cert == len(range(0, nq, 5))
     assert list(one[0][0]) == list(idx[3]) and np.array_equal(one[1][0].view(np.uint64), sc[3].view(np.uint64))
+
+
+@pytest.mark.parametrize("n,d,k,dtype", [(20000, 768, 10, 0), (9000, 256, 100, 1), (7, 64, 5, 0)])
+def test_scan_with_fused_exchange_on_one_rank(n, d, k, dtype):
+    """ragstore_search_shard_exchange in a world of one: the scan's last CTA publishes into its own inbox, finds its own
+    arrival word and merges -- the whole protocol (both inbox slots, sequence numbers, flags riding in the arrival word,
+    hits written to page-locked host memory) against the plain search and the oracle; tests/test_gpu_multi.py runs it
+    between real peers."""
+    import torch
+    from ragstore_b200 import native
+    bf = dtype == 1
+    rows = oc.synth_rows(0, n, d, 61, round_bf16=bf)
+    qs = oc.synth_rows(0, 5, d, 62)
+    with rb.RagStore(d, n, rb.RAGSTORE_BF16 if bf else rb.RAGSTORE_F32) as st:
+        st.set_row_base(1000)
+        st.add(rows, prenormalised=bf)
+        px = native.PeerExchange(0, 1, 0, max_records=256, max_queries=1)
+        px.connect(px.handle)
+        d_mine = torch.zeros(max(1, k) * 16, dtype=torch.uint8, device="cuda")
+        h_idx = torch.full((k,), -7, dtype=torch.int64).pin_memory()
+        h_sc = torch.zeros(k, dtype=torch.float64).pin_memory()
+        h_meta = torch.full((4,), 9, dtype=torch.int32).pin_memory()     # found, flags, status
+        stream = torch.cuda.Stream()
+        for call in range(5):                       # consecutive collective calls: slots alternate
+            q = qs[call]
+            if call % 2:
+                st.search_shard_exchange(px, k, d_mine, h_idx.data_ptr(), h_sc.data_ptr(), h_meta.data_ptr(), h_meta.data_ptr() + 4,
+                                         h_meta.data_ptr() + 8, h_query=np.ascontiguousarray(q), stream=stream.cuda_stream)
+            else:
+                st.search_shard_exchange(px, k, d_mine, h_idx.data_ptr(), h_sc.data_ptr(), h_meta.data_ptr(), h_meta.data_ptr() + 4,
+                                         h_meta.data_ptr() + 8, d_query=torch.from_numpy(q).cuda(), stream=stream.cuda_stream)
+            stream.synchronize()
+            found, flags, status = (int(x) for x in h_meta[:3])
+            eidx, esc = oc.query(rows, q, k, n_threads=2)
+            assert status == 0 and found == len(eidx)
+            assert list(h_idx[:found].numpy()) == [int(i) + 1000 for i in eidx]
+            assert np.array_equal(h_sc[:found].numpy().view(np.uint64), esc.view(np.uint64))
+            assert flags & rb.RAGSTORE_HIT_EXACT_ROWS
+        px.close()
