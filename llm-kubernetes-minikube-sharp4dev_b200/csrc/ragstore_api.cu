@@ -1172,9 +1172,9 @@ int ragstore_load(const char* path, int device, int64_t capacity_rows, ragstore_
 
 int ragstore_set_coalescing(ragstore_t* s, int window_us, int max_batch) {
     if (!s || window_us < 0 || max_batch < 1) return fail(RAGSTORE_ERR_INVALID, "ragstore_set_coalescing: bad argument");
-    std::lock_guard<std::mutex> lk(s->co_mu);
-    s->co_window_us = window_us;
-    s->co_max_batch = std::min(max_batch, 1024);
+    std::lock_guard<std::mutex> lk(s->co.mu);
+    s->co.window_us = window_us;
+    s->co.max_batch = std::min(max_batch, 1024);
     return RAGSTORE_OK;
 }
 
@@ -1194,56 +1194,21 @@ int ragstore_search_coalesced(ragstore_t* s, const float* query, int query_dim, 
     // refused before it is queued: an unservable request must not reach (and fail) a batch it shares with others
     if (std::min<int64_t>(s->count.load(std::memory_order_acquire), req) > kMaxTake)
         return fail(RAGSTORE_ERR_UNSUPPORTED, "more than 8128 hits per query are not covered");
-    ragstore::Pending me{query, top_k, out_idx, out_score, out_found, out_flags};
-    std::unique_lock<std::mutex> lk(s->co_mu);
-    s->co_queue.push_back(&me);
-    s->co_cv.notify_all();  // lets a leader that waits for company see that its batch has grown
-    std::vector<float> qbuf;
-    std::vector<int64_t> ibuf;
-    std::vector<double> sbuf;
-    std::vector<int32_t> fbuf, gbuf;
-    // Leadership is held for ONE batch at a time.  Whoever finds no batch running while its own request is still pending
-    // runs the next batch (the oldest request's kind), then steps down and wakes the others: a caller whose hits are in
-    // returns at once, and under sustained load the queue is served by whoever is waiting -- nobody is kept past its own
-    // answer, however many clients keep re-entering.
-    while (!me.done) {
-        if (s->co_leader) {
-            s->co_cv.wait(lk, [&] { return me.done || !s->co_leader; });
-            continue;
-        }
-        s->co_leader = true;
-        // Batches form by themselves: whoever arrives while a batch is executing is queued and taken, all together, by
-        // the next one, so by default nobody waits (a lone caller on an idle store runs at once).  A window set with
-        // ragstore_set_coalescing makes every batch's first caller wait that long for company: larger batches, at the
-        // price of that much latency (measured with 16 closed-loop clients on 10k x 768: 2.9 -> 10.3 queries per sweep).
-        if (s->co_window_us > 0) {
-            const auto deadline = std::chrono::steady_clock::now() + std::chrono::microseconds(s->co_window_us);
-            s->co_cv.wait_until(lk, deadline, [&] { return static_cast<int>(s->co_queue.size()) >= s->co_max_batch; });
-        }
-        const int cls = coalesce_class(s->co_queue.front()->top_k < 1 ? 1 : s->co_queue.front()->top_k);
-        std::vector<ragstore::Pending*> batch, rest;
-        for (auto* p : s->co_queue) {
-            if (static_cast<int>(batch.size()) < s->co_max_batch && coalesce_class(p->top_k < 1 ? 1 : p->top_k) == cls)
-                batch.push_back(p);
-            else
-                rest.push_back(p);
-        }
-        s->co_queue.swap(rest);
+    CoPending me{query, top_k, out_idx, out_score, out_found, out_flags};
+    // one sweep of the corpus for a whole batch (tensor-core path from 2-3 queries up); runs without the queue's lock
+    auto run = [s](const std::vector<CoPending*>& batch) {
         const int nb = static_cast<int>(batch.size());
-        lk.unlock();
         int kmax = 1;
         for (auto* p : batch) kmax = std::max(kmax, p->top_k);
-        qbuf.resize(static_cast<size_t>(nb) * s->dim);
-        ibuf.resize(static_cast<size_t>(nb) * kmax);
-        sbuf.resize(static_cast<size_t>(nb) * kmax);
-        fbuf.resize(nb);
-        gbuf.resize(nb);
+        std::vector<float> qbuf(static_cast<size_t>(nb) * s->dim);
+        std::vector<int64_t> ibuf(static_cast<size_t>(nb) * kmax);
+        std::vector<double> sbuf(static_cast<size_t>(nb) * kmax);
+        std::vector<int32_t> fbuf(nb), gbuf(nb);
         for (int i = 0; i < nb; ++i) memcpy(qbuf.data() + static_cast<size_t>(i) * s->dim, batch[i]->q, sizeof(float) * s->dim);
-        // one sweep of the corpus for the whole batch (tensor-core path from 2-3 queries up)
         const int rc = ragstore_search(s, qbuf.data(), nb, s->dim, kmax, ibuf.data(), sbuf.data(), fbuf.data(), gbuf.data());
         const std::string err = rc ? g_err : std::string();
         for (int i = 0; i < nb; ++i) {
-            ragstore::Pending* p = batch[i];
+            CoPending* p = batch[i];
             if (!rc) {
                 // a hit list for k is the prefix of the hit list for any larger k (the order is total)
                 const int want = p->top_k < 1 ? 1 : p->top_k;
@@ -1256,14 +1221,10 @@ int ragstore_search_coalesced(ragstore_t* s, const float* query, int query_dim, 
             p->status = rc;
             p->err = err;
         }
-        lk.lock();
-        for (auto* p : batch) p->done = true;
-        s->co_leader = false;
-        s->co_cv.notify_all();
-    }
-    lk.unlock();
-    if (me.status) g_err = me.err;
-    return me.status;
+    };
+    const int status = s->co.submit(me, [](int k) { return coalesce_class(k < 1 ? 1 : k); }, run);
+    if (status) g_err = me.err;
+    return status;
 }
 
 int ragstore_synth_fill_device(float* d_out, int64_t row0, int64_t n_rows, int dim, int64_t ld, uint64_t seed,

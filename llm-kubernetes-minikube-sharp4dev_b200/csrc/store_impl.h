@@ -7,6 +7,7 @@
 #include <string>
 #include <vector>
 
+#include "coalesce.h"
 #include "ragstore_internal.h"
 #include "vmm_buffer.h"
 
@@ -96,23 +97,7 @@ struct ragstore {
     cudaEvent_t k1_ev0[2] = {nullptr, nullptr}, k1_ev1[2] = {nullptr, nullptr};  // bracket the K1 launches (profiling aid)
     double last_add_kernel_us = 0.0;
     unsigned long long* h_counters = nullptr; // pinned: per slot [inexact rows, sidecar rows]
-    // coalescing of concurrent single-query callers (ragstore_search_coalesced)
-    struct Pending {
-        const float* q;
-        int top_k;
-        int64_t* idx;
-        double* score;
-        int32_t* found;
-        int32_t* flags;
-        int status = 0;
-        bool done = false;
-        std::string err;
-    };
-    std::mutex co_mu;
-    std::condition_variable co_cv;
-    std::vector<Pending*> co_queue;
-    bool co_leader = false;
-    int co_window_us = 0, co_max_batch = 256;
+    rag::Coalescer co;   // coalescing of concurrent single-query callers (ragstore_search_coalesced)
     ScanScratch dev_scratch{};
     uint8_t* dev_batch_scratch = nullptr;
     std::vector<SearchCtx> ctxs;

@@ -1,0 +1,50 @@
+// coalesce_stress.cpp -- host-only stress of the coalescing queue (csrc/coalesce.h) with the GPU search stubbed out;
+// built with -fsanitize=thread by tests/test_sanitizers.py.  Closed-loop clients of mixed kinds hammer one queue; every
+// request must be answered exactly once, by a batch of its own kind, and no client may be kept past its own answer.
+#include <atomic>
+#include <cstdio>
+#include <thread>
+
+#include "../../llm-kubernetes-minikube-sharp4dev_b200/csrc/coalesce.h"
+
+int main() {
+    rag::Coalescer co;
+    co.max_batch = 8;
+    const int n_clients = 24, rounds = 400;
+    std::atomic<long> answered{0}, batches{0}, mixed{0}, oversize{0};
+    auto class_of = [](int k) { return k <= 24 ? 0 : (k <= 256 ? 1 : 2); };
+    auto run = [&](const std::vector<rag::CoPending*>& batch) {
+        batches.fetch_add(1);
+        if (static_cast<int>(batch.size()) > 8) oversize.fetch_add(1);
+        const int cls = class_of(batch[0]->top_k);
+        for (auto* p : batch) {
+            if (class_of(p->top_k) != cls) mixed.fetch_add(1);
+            p->idx[0] = static_cast<int64_t>(p->q[0]);      // the "search": echo the query's tag
+            p->score[0] = p->top_k;
+            *p->found = 1;
+            p->status = 0;
+        }
+        std::this_thread::sleep_for(std::chrono::microseconds(50));
+    };
+    std::vector<std::thread> th;
+    std::atomic<int> wrong{0};
+    for (int c = 0; c < n_clients; ++c)
+        th.emplace_back([&, c] {
+            const int k = c % 3 == 0 ? 300 : (c % 3 == 1 ? 100 : 5);
+            for (int r = 0; r < rounds; ++r) {
+                float tag = static_cast<float>(c * 1000 + r % 1000);
+                int64_t idx = -1;
+                double score = -1;
+                int32_t found = 0, flags = 0;
+                rag::CoPending me{&tag, k, &idx, &score, &found, &flags};
+                const int rc = co.submit(me, class_of, run);
+                if (rc != 0 || found != 1 || idx != static_cast<int64_t>(tag) || score != k) wrong.fetch_add(1);
+                answered.fetch_add(1);
+            }
+        });
+    for (auto& t : th) t.join();
+    const bool ok = wrong == 0 && mixed == 0 && oversize == 0 && answered == static_cast<long>(n_clients) * rounds && co.queue.empty() && !co.leader;
+    std::printf("coalesce_stress %s: %ld requests in %ld batches (%.1f per batch), wrong %d, mixed-kind batches %ld\n", ok ? "ok" : "FAILED",
+                answered.load(), batches.load(), double(answered.load()) / double(batches.load()), wrong.load(), mixed.load());
+    return ok ? 0 : 1;
+}
