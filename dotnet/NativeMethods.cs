@@ -13,8 +13,13 @@ namespace Minimal_RAG.Helpers
         public const int RAGSTORE_F32 = 0, RAGSTORE_BF16 = 1;
         public const uint RAGSTORE_ADD_HOST = 0;
         public const int RAGSTORE_HIT_CERTIFIED = 1, RAGSTORE_HIT_EXACT_ROWS = 2;
+        public const uint RAGSTORE_CREATE_BF16_SHADOW = 4;   // fp32 store + bf16 image for the batched tensor-core nomination
 
         [LibraryImport(Lib)] public static partial int ragstore_create(int dim, int dtype, long capacityRows, int device, uint flags, out IntPtr store);
+        // ONE handle over several GPUs of this process: same add / search / count calls (the singleton of Program.cs:35,43
+        // keeps its shape when the corpus outgrows one GPU)
+        [LibraryImport(Lib)] public static unsafe partial int ragstore_create_sharded(int dim, int dtype, long capacityRows, int* devices, int nDevices,
+                                                                                     long blockRows, uint flags, out IntPtr store);
         [LibraryImport(Lib)] public static partial int ragstore_destroy(IntPtr store);
         [LibraryImport(Lib)] public static unsafe partial int ragstore_add(IntPtr store, float* rows, long nRows, int rowDim, uint flags, out long firstRow);
         [LibraryImport(Lib)] public static partial int ragstore_count(IntPtr store, out long rows);
@@ -45,6 +50,12 @@ namespace Minimal_RAG.Helpers
         [LibraryImport(Lib)] public static unsafe partial int ragstore_exchange_connect(IntPtr exchange, byte* allHandles /* world x 64 bytes, rank order */);
         [LibraryImport(Lib)] public static partial int ragstore_exchange_merge(IntPtr exchange, IntPtr dMine, int nQueries, int perShard, int topK,
                                                                               IntPtr dIdx, IntPtr dScore, IntPtr dFound, IntPtr dStatus, IntPtr stream);
+        [LibraryImport(Lib)] public static partial int ragstore_exchange_merge_flags(IntPtr exchange, IntPtr dMine, IntPtr dMyFlags, int nQueries, int perShard, int topK,
+                                                                                    IntPtr dIdx, IntPtr dScore, IntPtr dFound, IntPtr dFlags, IntPtr dStatus, IntPtr stream);
+        // shard scan + exchange + merge in ONE launch per rank (give exactly one of dQuery / hostQuery)
+        [LibraryImport(Lib)] public static unsafe partial int ragstore_search_shard_exchange(IntPtr store, IntPtr exchange, IntPtr dQuery, float* hostQuery, int topK,
+                                                                                            IntPtr dMine, IntPtr dIdx, IntPtr dScore, IntPtr dFound, IntPtr dFlags,
+                                                                                            IntPtr dStatus, IntPtr stream);
         [LibraryImport(Lib)] public static partial int ragstore_exchange_destroy(IntPtr exchange);
 
         public static unsafe void Check(int rc)

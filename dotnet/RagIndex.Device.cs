@@ -16,8 +16,12 @@ namespace Minimal_RAG.Helpers
         IntPtr _store;
         int _dim;
         const long CapacityRows = 1L << 26;   // address space only; HBM is mapped as rows arrive
+        // GPUs the index is spread over.  One entry: a single-device store.  Several: ONE handle over all of them
+        // (ragstore_create_sharded) -- rows are dealt round-robin in blocks, ids stay insertion order, QueryAsync does not change.
+        readonly int[] _devices;
 
-        public RagIndex(string embedModel) => _embedModel = embedModel;
+        public RagIndex(string embedModel) : this(embedModel, new[] { 0 }) { }
+        public RagIndex(string embedModel, int[] devices) { _embedModel = embedModel; _devices = devices; }
 
         public async Task BuildFromFolderAsync(string folder, int chunkSize, int overlap, ILogger logger)
         {
@@ -34,7 +38,12 @@ namespace Minimal_RAG.Helpers
             if (_store == IntPtr.Zero)
             {
                 _dim = emb.Length;
-                NativeMethods.Check(NativeMethods.ragstore_create(_dim, NativeMethods.RAGSTORE_F32, CapacityRows, 0, 0, out _store));
+                if (_devices.Length == 1)
+                    NativeMethods.Check(NativeMethods.ragstore_create(_dim, NativeMethods.RAGSTORE_F32, CapacityRows, _devices[0], 0, out _store));
+                else
+                    fixed (int* pd = _devices)
+                        NativeMethods.Check(NativeMethods.ragstore_create_sharded(_dim, NativeMethods.RAGSTORE_F32, CapacityRows, pd, _devices.Length,
+                                                                                  0 /* 65536-row blocks */, 0, out _store));
             }
             fixed (float* p = emb)
                 NativeMethods.Check(NativeMethods.ragstore_add(_store, p, 1, emb.Length, NativeMethods.RAGSTORE_ADD_HOST, out long row));
