@@ -16,6 +16,8 @@
 // Liveness: a block publishes ALL of its queries before it waits for anything and the grid never exceeds the SM count
 // (every block is resident), so no wait depends on a block that cannot run; waits are bounded by a timeout that is
 // reported in d_status instead of hanging the GPU.
+#include <nvtx3/nvToolsExt.h>
+
 #include <cstring>
 #include <new>
 
@@ -192,6 +194,10 @@ int ragstore_exchange_merge_flags(ragstore_exchange_t* x, const ragstore_cand* d
     if (n_queries < 1 || per_shard < 1 || n_queries > x->max_queries || static_cast<int64_t>(n_queries) * per_shard > x->max_records ||
         x->world * per_shard > 8192)
         return api_fail(RAGSTORE_ERR_INVALID, "ragstore_exchange_merge: n_queries / per_shard exceed what the exchange was created for");
+    nvtxRangePushA("ragstore_exchange_merge: peer stores + flags + merge");
+    struct Pop {
+        ~Pop() { nvtxRangePop(); }
+    } pop;
     DeviceScope g(x->device);
     if (!g.ok) return api_fail(RAGSTORE_ERR_CUDA, "ragstore_exchange_merge: cudaSetDevice failed");
     const size_t smem = static_cast<size_t>(x->world) * per_shard * 24;

@@ -430,6 +430,7 @@ int ragstore_add(ragstore_t* s, const float* rows, int64_t n_rows, int row_dim, 
     if (!s || (!rows && n_rows > 0) || n_rows < 0) return fail(RAGSTORE_ERR_INVALID, "ragstore_add: null/negative argument");
     if (row_dim != s->dim) return fail(RAGSTORE_ERR_INVALID, "ragstore_add: row_dim differs from the store's dim");
     if (s->sharded) return sharded_add(s, rows, n_rows, flags, out_first_row);
+    NvtxRange nvtx("ragstore_add: upload + normalise (K1)");
     std::lock_guard<std::mutex> lk(s->add_mu);
     const int64_t first = s->count.load(std::memory_order_acquire);
     if (out_first_row) *out_first_row = first;
@@ -615,6 +616,7 @@ int ragstore_search_device(ragstore_t* s, const float* d_queries, int n_queries,
                            double* d_score, int32_t* d_found, int32_t* d_flags, void* stream) {
     if (!s || !d_queries || n_queries < 0 || !d_idx || !d_score) return fail(RAGSTORE_ERR_INVALID, "ragstore_search_device: null argument");
     if (s && s->sharded) return fail(RAGSTORE_ERR_INVALID, "ragstore_search_device: per-device entry point, not available on a multi-device handle (ragstore_create_sharded)");
+    NvtxRange nvtx("ragstore_search_device: scan + top-k + rescoring (K2/K3/K4/K5)");
     DeviceGuard g(s->device);
     cudaStream_t st = stream ? static_cast<cudaStream_t>(stream) : s->dev_stream;
     const int64_t n = s->count.load(std::memory_order_acquire);
@@ -716,6 +718,7 @@ int ragstore_search_shard_exchange(ragstore_t* s, ragstore_exchange_t* x, const 
     if (req > kMaxKp) return fail(RAGSTORE_ERR_UNSUPPORTED, "top_k above 256 is not covered by the one-launch form");
     if (req > x->max_records || x->world * req > 4096)
         return fail(RAGSTORE_ERR_INVALID, "ragstore_search_shard_exchange: top_k exceeds what the exchange was created for");
+    NvtxRange nvtx("ragstore_search_shard_exchange: shard scan + peer exchange + merge, one launch");
     DeviceGuard g(s->device);
     cudaStream_t st = stream ? static_cast<cudaStream_t>(stream) : s->dev_stream;
     const int64_t n = s->count.load(std::memory_order_acquire);
@@ -857,6 +860,7 @@ int rag::search_host_limited(ragstore* s, int64_t n_limit, const float* queries,
     }
     if (take > kMaxTake) return fail(RAGSTORE_ERR_UNSUPPORTED, "more than 8128 hits per query are not covered");
     if (s->sharded) return sharded_search(s, queries, n_queries, top_k, out_idx, out_score, out_found, out_flags);
+    NvtxRange nvtx("ragstore_search: host query -> scan/batch + top-k + rescoring -> host hits");
     DeviceGuard g(s->device);
     if (!g.ok) return fail(RAGSTORE_ERR_CUDA, "cudaSetDevice failed");
 

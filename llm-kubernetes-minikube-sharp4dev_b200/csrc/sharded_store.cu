@@ -200,6 +200,7 @@ int sharded_reserve_rows(ragstore* p, int64_t n_rows) {
 }
 
 int sharded_add(ragstore* p, const float* rows, int64_t n_rows, uint32_t flags, int64_t* out_first_row) {
+    NvtxRange nvtx("ragstore_add (multi-device handle): deal blocks, upload + normalise per shard");
     ShardedState* ss = p->sharded;
     std::lock_guard<std::mutex> lk(ss->add_mu);
     const int64_t first = p->count.load(std::memory_order_acquire);
@@ -265,6 +266,7 @@ int sharded_info(ragstore* p, int64_t* out, int n) {
 
 int sharded_search(ragstore* p, const float* queries, int n_queries, int top_k, int64_t* out_idx, double* out_score,
                    int32_t* out_found, int32_t* out_flags) {
+    NvtxRange nvtx("ragstore_search (multi-device handle): per-shard scans -> peer stores -> merge");
     ShardedState* ss = p->sharded;
     const int G = ss->n;
     const int64_t N = p->count.load(std::memory_order_acquire);   // the prefix this search works on

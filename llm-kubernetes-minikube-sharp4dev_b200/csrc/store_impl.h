@@ -7,6 +7,8 @@
 #include <string>
 #include <vector>
 
+#include <nvtx3/nvToolsExt.h>
+
 #include "coalesce.h"
 #include "ragstore_internal.h"
 #include "vmm_buffer.h"
@@ -28,6 +30,16 @@ struct DeviceGuard {
     ~DeviceGuard() {
         if (prev >= 0) cudaSetDevice(prev);
     }
+};
+
+// NVTX range around a host-side phase (upload/normalise, scan, batched search, exchange, merge): shows up on an nsys /
+// Nsight timeline when a tool is attached; a few nanoseconds of no-op otherwise (NVTX v3 is header-only and resolves the
+// tool's injection library lazily).
+struct NvtxRange {
+    explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+    ~NvtxRange() { nvtxRangePop(); }
+    NvtxRange(const NvtxRange&) = delete;
+    NvtxRange& operator=(const NvtxRange&) = delete;
 };
 
 constexpr int kCtxQueries = 256; // queries per host-search context batch (= one tensor-core launch)
