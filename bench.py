@@ -561,6 +561,64 @@ def measure_workload(name, args, torch, dist, rb, native, rank, world, dev, do_e
     return res
 
 
+def measure_single_process(name, args, torch, rb, native, devices, do_parity=True):
+    """The same sharded workload through ONE handle in ONE process (ragstore_create_sharded) -- the shape the reference's
+    singleton RagIndex has (Program.cs:35,43): host query in, host hits out, all GPUs of the box behind one call."""
+    import numpy as np
+    rows, dim, dtype, k, desc = WORKLOADS[name]
+    if args.rows:
+        rows = args.rows
+    G, bf = len(devices), dtype == "bf16"
+    total = rows * G
+    torch.cuda.set_device(devices[0])
+    st = rb.RagStore.create_sharded(dim, total, devices, dtype=rb.RAGSTORE_BF16 if bf else rb.RAGSTORE_F32, block_rows=65536)
+    try:
+        t0 = time.perf_counter()
+        chunk = 1 << 19
+        buf = torch.empty((chunk, dim), dtype=torch.float32, device="cuda")
+        for r0 in range(0, total, chunk):          # rows are generated on the first GPU; every shard's upload kernel reads its blocks over NVLink
+            m = min(chunk, total - r0)
+            native.synth_fill_device(buf, r0, m, dim, dim, CORPUS_SEED, round_bf16=bf, device=devices[0])
+            torch.cuda.synchronize()
+            st.add_device(buf, m, dim, prenormalised=bf)
+        del buf
+        ingest_s = time.perf_counter() - t0
+        n_q = 64
+        d_q = torch.empty((n_q, dim), dtype=torch.float32, device="cuda")
+        native.synth_fill_device(d_q, 0, n_q, dim, dim, QUERY_SEED, device=devices[0])
+        torch.cuda.synchronize()
+        hq = [np.ascontiguousarray(r) for r in d_q.cpu().numpy()]
+        call, idx, sc, found, flags = st.search_call(1, k)
+        for i in range(max(5, args.warmup)):
+            call(hq[i % n_q])
+        n_calls = max(100, args.steps)
+        per = []
+        t0 = time.perf_counter()
+        for i in range(n_calls):
+            tc = time.perf_counter()
+            call(hq[i % n_q])
+            per.append(time.perf_counter() - tc)
+        dt = time.perf_counter() - t0
+        per.sort()
+        out = {"desc": desc, "api": "ragstore_create_sharded + ragstore_search: one process, one handle, host query in / host hits out; the shards' last CTAs "
+                                    "store their hits into the first GPU's memory over NVLink peer access, one merge kernel writes to page-locked memory",
+               "devices": devices, "rows_total": total, "rows_per_gpu": rows, "dim": dim, "top_k": k, "storage": dtype,
+               "ms_per_query": dt / n_calls * 1e3, "median_ms": per[n_calls // 2] * 1e3, "p99_ms": per[min(n_calls - 1, int(n_calls * 0.99))] * 1e3,
+               "vectors_per_s": total * n_calls / dt, "queries_per_s": n_calls / dt, "calls": n_calls, "ingest_vectors_per_s": total / ingest_s,
+               "h2d_bytes_per_step": dim * 4, "d2h_bytes_per_step": k * 16 + 8}
+        if do_parity:
+            t_par = time.perf_counter()
+            call(hq[0])
+            g_idx, g_sc, g_flags = idx[0, :found[0]].copy(), sc[0, :found[0]].copy(), int(flags[0])
+            ora = oracle_topk_streamed(0, total, dim, bf, [hq[0]], k, os.cpu_count() or 1)[0]
+            ok = compare_hits(g_idx, g_sc, ora[0], ora[1])
+            out["parity"] = {"checked": f"1 query x all {total} rows vs the CPU oracle", "indices_bit_exact": ok[0], "scores_bit_exact": ok[1],
+                             "gpu_flags": g_flags, "seconds": time.perf_counter() - t_par}
+        return out
+    finally:
+        st.close()
+
+
 def measure_k1(torch, rb, native, dev, rows=1 << 20, dim=768, reps=8):
     """K1 alone: device-resident fp32 rows -> normalised store rows (+ reciprocal norms, flags), read + write = 2*d*4 B/row."""
     buf = torch.empty((rows, dim), dtype=torch.float32, device="cuda")
@@ -721,6 +779,9 @@ def main():
     ap.add_argument("--pinned", action="store_true", help="config5: the application's batches live in page-locked memory")
     ap.add_argument("--no-extra", action="store_true", help="skip the extra config1 / config2 / config3 measurements")
     ap.add_argument("--no-parity", action="store_true", help="skip the full-corpus oracle check (profiling runs)")
+    ap.add_argument("--single-process", action="store_true",
+                    help="run the sharded workload through ONE handle over --gpus devices in this process (ragstore_create_sharded); "
+                         "start with plain `python bench.py`, not torchrun")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     quiet_stdout()
@@ -748,6 +809,17 @@ def main():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
+    if args.single_process:
+        name = args.workload if args.workload in WORKLOADS else "config4"
+        r = measure_single_process(name, args, torch, rb, native, list(range(args.gpus)), do_parity=not args.no_parity)
+        emit({"metric": "corpus vectors scanned/sec (single query, top-k), one process over all GPUs", "value": r["vectors_per_s"], "unit": "vectors/s",
+              "n_gpus": args.gpus, "steps": r["calls"], "warmup": args.warmup, "ms_per_step": r["ms_per_query"], "higher_is_better": True,
+              "scaling": "weak", "vs_baseline": None, "dtype": "f32" if r["storage"] == "f32" else "bf16 storage, f32 accumulate", "data": "synthetic",
+              "config": config_dict(name, args.gpus, args.rows), "single_process": r,
+              "e2e": {"value": r["vectors_per_s"], "unit": "vectors/s", "h2d_bytes_per_step": r["h2d_bytes_per_step"],
+                      "d2h_bytes_per_step": r["d2h_bytes_per_step"], "ms_per_step": r["ms_per_query"], "steps": r["calls"], "api": r["api"]},
+              "gpu_launches": r["calls"] * (args.gpus + 1), "parity": r.get("parity")})
+        return
     if args.workload == "config5":
         out = run_streaming(args, torch, dist, rb, native, rank, world, local)
         if rank == 0:
@@ -785,6 +857,19 @@ def main():
                     extra[name]["tensor"] = tensor_block(r)
             except Exception as ex:  # an extra must never take the headline down
                 extra[name] = {"error": repr(ex)[:300]}
+
+    if world > 1 and not args.no_extra:
+        # The same corpus behind ONE handle in ONE process (rank 0; the other ranks wait): what a singleton RagIndex uses.
+        torch.cuda.synchronize()
+        dist.barrier()
+        if rank == 0:
+            try:
+                extra["single_process_sharded"] = measure_single_process(args.workload, args, torch, rb, native, list(range(world)),
+                                                                         do_parity=not args.no_parity)
+            except Exception as ex:
+                extra["single_process_sharded"] = {"error": repr(ex)[:300]}
+            torch.cuda.set_device(local)
+        dist.barrier()
 
     if rank == 0:
         peak, peak_src = measured_peaks()
