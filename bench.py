@@ -858,19 +858,6 @@ def main():
             except Exception as ex:  # an extra must never take the headline down
                 extra[name] = {"error": repr(ex)[:300]}
 
-    if world > 1 and not args.no_extra:
-        # The same corpus behind ONE handle in ONE process (rank 0; the other ranks wait): what a singleton RagIndex uses.
-        torch.cuda.synchronize()
-        dist.barrier()
-        if rank == 0:
-            try:
-                extra["single_process_sharded"] = measure_single_process(args.workload, args, torch, rb, native, list(range(world)),
-                                                                         do_parity=not args.no_parity)
-            except Exception as ex:
-                extra["single_process_sharded"] = {"error": repr(ex)[:300]}
-            torch.cuda.set_device(local)
-        dist.barrier()
-
     if rank == 0:
         peak, peak_src = measured_peaks()
         r = main_res
@@ -912,9 +899,21 @@ def main():
             "k1_upload_normalise": k1,
             "extra": extra,
         }
-        emit(out)
     if world > 1:
+        torch.cuda.synchronize()
+        dist.barrier()
         dist.destroy_process_group()
+    if rank == 0:
+        if world > 1 and not args.no_extra:
+            # The same corpus behind ONE handle in ONE process -- what a singleton RagIndex uses.  Measured by rank 0 after
+            # the process group is gone: the other ranks have left their GPUs (no collective kernel spins there).
+            time.sleep(2.0)
+            try:
+                out["extra"]["single_process_sharded"] = measure_single_process(args.workload, args, torch, rb, native, list(range(world)),
+                                                                                do_parity=not args.no_parity)
+            except Exception as ex:
+                out["extra"]["single_process_sharded"] = {"error": repr(ex)[:300]}
+        emit(out)
 
 
 if __name__ == "__main__":
