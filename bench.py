@@ -880,6 +880,10 @@ def main():
             "config": config_dict(args.workload, world, args.rows),
             "exchange": r.get("exchange"),
             "shard_scan_ms_per_rank": r.get("kernel_ms_per_rank"),
+            # what ONE GPU does on the same shard without any exchange (rank 0's scan, timed alone in this run): the N = 1 point
+            # of this workload's weak-scaling curve (the N = 1 default line is a different workload, 10M x 768 fp32)
+            "single_gpu_same_shard": ({"ms_per_step": r["kernel_ms"], "value": r["rows_per_gpu"] / (r["kernel_ms"] * 1e-3), "unit": "vectors/s"}
+                                      if world > 1 else None),
             "rescoring": "exact fp64 (reference arithmetic) for k' >= k candidates inside the same launch",
             "roofline": {"bound": "hbm", "achieved": r["achieved_gbs"], "peak": peak, "unit": "GB/s", "frac": r["achieved_gbs"] / peak,
                          "traffic": traffic, "peak_source": peak_src, "frac_of_8TBs_spec": r["achieved_gbs"] / 8000.0,
