@@ -619,6 +619,100 @@ def measure_single_process(name, args, torch, rb, native, devices, do_parity=Tru
         st.close()
 
 
+def run_streaming_single_process(args, torch, rb, native, devices):
+    """config5 through ONE handle in ONE process: a writer thread appends host batches (one 64k-row block per GPU per call, so
+    every GPU's upload pipeline runs at once) while the main thread serves 1k-query batches through the same handle."""
+    import threading
+    import numpy as np
+    c = STREAM
+    dim, k, B, QB = c["dim"], c["top_k"], c["batch_rows"], c["queries_per_batch"]
+    G = len(devices)
+    total = args.rows * G if args.rows else c["total_rows"]
+    group = B * G                                   # rows per append call: one block for every shard
+    n_groups = max(2, total // group)
+    torch.cuda.set_device(devices[0])
+    st = rb.RagStore.create_sharded(dim, n_groups * group, devices, block_rows=B)
+    try:
+        if not args.no_reserve:
+            st.reserve_rows(n_groups * group)
+        d_batch = torch.empty((group, dim), dtype=torch.float32, device="cuda")
+        native.synth_fill_device(d_batch, 0, group, dim, dim, CORPUS_SEED, device=devices[0])
+        torch.cuda.synchronize()
+        h_pin = d_batch.cpu().pin_memory() if args.pinned else None
+        h_batch = h_pin.numpy() if args.pinned else d_batch.cpu().numpy()
+        del d_batch
+        d_q = torch.empty((QB, dim), dtype=torch.float32, device="cuda")
+        native.synth_fill_device(d_q, 0, QB, dim, dim, QUERY_SEED, device=devices[0])
+        torch.cuda.synchronize()
+        hq = np.ascontiguousarray(d_q.cpu().numpy())
+        del d_q
+        call, idx, sc, found, flags = st.search_call(QB, k)
+        st.add(h_batch)                              # first group in before serving starts (also warms up)
+        for _ in range(3):
+            call(hq)
+        stop = threading.Event()
+        t_ingest = [0.0]
+
+        def writer():
+            torch.cuda.set_device(devices[0])
+            t0 = time.perf_counter()
+            for _ in range(n_groups - 1):
+                st.add(h_batch)
+            t_ingest[0] = time.perf_counter() - t0
+            stop.set()
+
+        w = threading.Thread(target=writer)
+        qbatches = 0
+        with ClockSampler(devices[0]) as clk:
+            t0 = time.perf_counter()
+            w.start()
+            while True:
+                done = stop.is_set()
+                call(hq)
+                qbatches += 1
+                if done:
+                    break
+            t_srv = time.perf_counter() - t0
+        w.join()
+        rows_streamed = (n_groups - 1) * group
+        # prefix consistency of the last answer: all rows are in now, so query 0 must equal the oracle over the whole stream
+        # (every appended group repeats the same 64k x G synthetic rows, so the oracle scores one group and the ties -- the
+        # same row in every group -- must come back lowest id first)
+        from oracle import oracle_c as oc
+        base = oc.synth_rows(0, group, dim, CORPUS_SEED)
+        eidx, esc = oc.query(base, hq[0], k, n_threads=os.cpu_count() or 1)
+        want_ids, want_sc = [], []
+        for j in range(len(eidx)):                   # row r of group g has id g * group + r; equal scores -> lower id first
+            for g in range(n_groups):
+                want_ids.append(int(eidx[j]) + g * group)
+                want_sc.append(float(esc[j]))
+                if len(want_ids) == k:
+                    break
+            if len(want_ids) == k:
+                break
+        ok_idx = [int(x) for x in idx[0, :found[0]]] == want_ids
+        ok_sc = np.array_equal(np.asarray(sc[0, :found[0]]).view(np.uint64), np.asarray(want_sc, dtype=np.float64).view(np.uint64))
+        info = st.info()
+        return {"metric": "streaming ingest vectors/sec while serving 1k-query batches (top-10), one process / one handle", "value": rows_streamed / t_ingest[0],
+                "unit": "vectors/s", "n_gpus": G, "steps": n_groups - 1, "warmup": 1, "ms_per_step": t_ingest[0] / (n_groups - 1) * 1e3,
+                "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "queries_per_s": qbatches * QB / t_srv, "query_batches_served": qbatches,
+                "config": {"workload": "config5", "desc": c["desc"], "rows_total": n_groups * group, "dim": dim, "top_k": k, "batch_rows": B,
+                           "rows_per_append_call": group, "queries_per_batch": QB, "parallelism": f"one handle over {G} GPUs (ragstore_create_sharded), block-cyclic",
+                           "host_batches": "page-locked (direct PCIe copy)" if args.pinned else "pageable (staged through the library's pinned ring)"},
+                "roofline": {"bound": "pcie (host->device copy of the appended rows)", "achieved": rows_streamed * dim * 4 / t_ingest[0] / 1e9 / G, "peak": 64.0,
+                             "unit": "GB/s per GPU", "frac": rows_streamed * dim * 4 / t_ingest[0] / 1e9 / G / 64.0, "traffic": None, "peak_source": "nominal PCIe Gen5 x16"},
+                "cpu_baseline": None,
+                "e2e": {"value": rows_streamed / t_ingest[0], "unit": "vectors/s", "h2d_bytes_per_step": group * dim * 4, "d2h_bytes_per_step": 0,
+                        "api": "ragstore_add + ragstore_search on one multi-device handle, from two threads of one process"},
+                "gpu_launches": int(info["batch_launches"]) * 5 + int(info["scan_launches"]) + (n_groups - 1) * G * 2, "clocks": clk.summary(),
+                "parity": {"checked": "query 0 of the last batch served (all rows resident) vs the oracle over the stream; ties across the repeated groups must come back lowest id first",
+                           "indices_bit_exact": bool(ok_idx), "scores_bit_exact": bool(ok_sc)},
+                "final_count": info["count"]}
+    finally:
+        st.close()
+
+
 def measure_k1(torch, rb, native, dev, rows=1 << 20, dim=768, reps=8):
     """K1 alone: device-resident fp32 rows -> normalised store rows (+ reciprocal norms, flags), read + write = 2*d*4 B/row."""
     buf = torch.empty((rows, dim), dtype=torch.float32, device="cuda")
@@ -809,6 +903,9 @@ def main():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
+    if args.single_process and args.workload == "config5":
+        emit(run_streaming_single_process(args, torch, rb, native, list(range(args.gpus))))
+        return
     if args.single_process:
         name = args.workload if args.workload in WORKLOADS else "config4"
         r = measure_single_process(name, args, torch, rb, native, list(range(args.gpus)), do_parity=not args.no_parity)
