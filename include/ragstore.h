@@ -111,7 +111,8 @@ RAGSTORE_API int ragstore_create(int dim, int dtype, int64_t capacity_rows, int 
  * (RagIndex.cs:64-65).  ragstore_add, ragstore_add_many, ragstore_reserve_rows, ragstore_count, ragstore_search (any
  * top_k up to 8128, batches on the tensor cores of every device), ragstore_search_coalesced, ragstore_info and
  * ragstore_destroy accept the handle; the per-device entry points (ragstore_search_device, ragstore_search_shard_*,
- * ragstore_device_views, ragstore_set_row_*) return RAGSTORE_ERR_INVALID and ragstore_save RAGSTORE_ERR_UNSUPPORTED.
+ * ragstore_device_views, ragstore_set_row_*) return RAGSTORE_ERR_INVALID.  ragstore_save writes all shards into one file;
+ * ragstore_load_sharded maps it back over the same NUMBER of devices (rows are dealt by shard count).
  * A device may be listed more than once (several shards on one GPU). */
 RAGSTORE_API int ragstore_create_sharded(int dim, int dtype, int64_t capacity_rows, const int* devices, int n_devices,
                                          int64_t block_rows, uint32_t flags, ragstore_t** out);
@@ -309,6 +310,10 @@ RAGSTORE_API int ragstore_hit_filters(const double* scores, int found, double ev
  * A loaded store answers exactly as the saved one did.  capacity_rows: 0 = just the saved rows. */
 RAGSTORE_API int ragstore_save(ragstore_t* s, const char* path);
 RAGSTORE_API int ragstore_load(const char* path, int device, int64_t capacity_rows, ragstore_t** out);
+/* The image of a multi-device handle (ragstore_save on a handle from ragstore_create_sharded) back over n_devices GPUs;
+ * n_devices must equal the number of shards it was saved with.  A store created with RAGSTORE_CREATE_BF16_SHADOW gets its
+ * bf16 image back on load (rebuilt from the fp32 rows; it is not part of the file). */
+RAGSTORE_API int ragstore_load_sharded(const char* path, const int* devices, int n_devices, int64_t capacity_rows, ragstore_t** out);
 
 /* ---- utilities ----------------------------------------------------------------------------- */
 

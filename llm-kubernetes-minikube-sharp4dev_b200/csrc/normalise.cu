@@ -172,6 +172,20 @@ __global__ void __launch_bounds__(256) normalise_rows_vec_kernel(const Normalise
     }
 }
 
+__global__ void __launch_bounds__(256) shadow_from_rows_kernel(const float4* __restrict__ src, uint2* __restrict__ dst, int64_t n4) {
+    for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n4; i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+        const float4 v = src[i];
+        dst[i] = make_uint2(f32_to_bf16_bits(v.x) | (f32_to_bf16_bits(v.y) << 16), f32_to_bf16_bits(v.z) | (f32_to_bf16_bits(v.w) << 16));
+    }
+}
+
+int launch_shadow_from_rows(const float* src, uint16_t* dst, int64_t n, cudaStream_t stream) {
+    if (n <= 0) return 0;
+    if (n % 4) return static_cast<int>(cudaErrorInvalidValue);   // rows are multiples of 8 elements
+    shadow_from_rows_kernel<<<148 * 8, 256, 0, stream>>>(reinterpret_cast<const float4*>(src), reinterpret_cast<uint2*>(dst), n / 4);
+    return static_cast<int>(cudaGetLastError());
+}
+
 int launch_normalise(const NormaliseArgs& a, cudaStream_t stream) {
     if (a.n_rows <= 0) return 0;
     const int threads = 256;

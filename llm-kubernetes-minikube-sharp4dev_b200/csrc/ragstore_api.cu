@@ -1063,19 +1063,12 @@ int copy_in(FILE* f, void* d_dst, size_t bytes, void* h_pin, size_t pin_bytes) {
 }
 }  // namespace
 
-int ragstore_save(ragstore_t* s, const char* path) {
-    if (!s || !path) return fail(RAGSTORE_ERR_INVALID, "ragstore_save: null argument");
-    if (s->sharded) return fail(RAGSTORE_ERR_UNSUPPORTED, "ragstore_save: a multi-device handle is not saved as one image yet");
-    std::lock_guard<std::mutex> lk(s->add_mu);  // no append while the image is written
+// one single-device store as a self-delimiting image at the current position of f (add_mu of the store is held by the caller)
+static int save_image(ragstore* s, FILE* f) {
     DeviceGuard g(s->device);
-    FILE* f = fopen(path, "wb");
-    if (!f) return fail(RAGSTORE_ERR_INVALID, "ragstore_save: cannot open file", path);
     const size_t pin_bytes = size_t(32) << 20;
     void* h_pin = nullptr;
-    if (cudaMallocHost(&h_pin, pin_bytes) != cudaSuccess) {
-        fclose(f);
-        return fail(RAGSTORE_ERR_CUDA, "ragstore_save: cudaMallocHost");
-    }
+    if (cudaMallocHost(&h_pin, pin_bytes) != cudaSuccess) return fail(RAGSTORE_ERR_CUDA, "ragstore_save: cudaMallocHost");
     SaveHeader h{};
     memcpy(h.magic, "RAGSTOR1", 8);
     h.version = 1;
@@ -1084,6 +1077,7 @@ int ragstore_save(ragstore_t* s, const char* path) {
     h.dtype = s->dtype;
     h.has_sidecar = s->raw_slot ? 1 : 0;
     h.raw_ld = s->raw_ld;
+    h.pad = s->shadow ? RAGSTORE_CREATE_BF16_SHADOW : 0;   // the shadow itself is not written: it is rebuilt from the rows on load
     h.count = s->count.load();
     h.inexact_rows = s->inexact_rows;
     h.sidecar_rows = s->raw_used;
@@ -1097,47 +1091,83 @@ int ragstore_save(ragstore_t* s, const char* path) {
     if (!rc && h.has_sidecar) rc = copy_out(f, s->raw_slot, n * sizeof(int32_t), h_pin, pin_bytes);
     if (!rc && h.has_sidecar) rc = copy_out(f, s->raw_rows, static_cast<size_t>(h.sidecar_rows) * s->raw_ld * sizeof(float), h_pin, pin_bytes);
     cudaFreeHost(h_pin);
+    return rc;
+}
+
+namespace {
+struct ShardedSaveHeader {
+    char magic[8];  // "RAGSHRD1"
+    int32_t version, n_shards, dim, dtype;
+    int64_t block_rows, count;
+};
+int64_t file_bytes_left(FILE* f) {
+    const long here = ftell(f);
+    if (here < 0 || fseek(f, 0, SEEK_END) != 0) return -1;
+    const long end = ftell(f);
+    if (fseek(f, here, SEEK_SET) != 0) return -1;
+    return static_cast<int64_t>(end) - here;
+}
+}  // namespace
+
+int ragstore_save(ragstore_t* s, const char* path) {
+    if (!s || !path) return fail(RAGSTORE_ERR_INVALID, "ragstore_save: null argument");
+    FILE* f = fopen(path, "wb");
+    if (!f) return fail(RAGSTORE_ERR_INVALID, "ragstore_save: cannot open file", path);
+    int rc = RAGSTORE_OK;
+    if (s->sharded) {
+        // a multi-device handle: a small header, then every shard's image in shard order.  No append runs meanwhile, so the
+        // shards hold exactly the published prefix.
+        int64_t block_rows = 0;
+        std::unique_lock<std::mutex> lk(*sharded_add_mutex(s, &block_rows));
+        ShardedSaveHeader h{};
+        memcpy(h.magic, "RAGSHRD1", 8);
+        h.version = 1;
+        h.n_shards = static_cast<int32_t>(s->shards.size());
+        h.dim = s->dim;
+        h.dtype = s->dtype;
+        h.block_rows = block_rows;
+        h.count = s->count.load();
+        if (fwrite(&h, sizeof(h), 1, f) != 1) rc = fail(RAGSTORE_ERR_INVALID, "ragstore_save: short write");
+        for (size_t i = 0; !rc && i < s->shards.size(); ++i) {
+            std::lock_guard<std::mutex> lk2(s->shards[i]->add_mu);
+            rc = save_image(s->shards[i], f);
+        }
+    } else {
+        std::lock_guard<std::mutex> lk(s->add_mu);  // no append while the image is written
+        rc = save_image(s, f);
+    }
     if (fclose(f) != 0 && !rc) rc = fail(RAGSTORE_ERR_INVALID, "ragstore_save: close failed");
     return rc;
 }
 
-int ragstore_load(const char* path, int device, int64_t capacity_rows, ragstore_t** out) {
-    if (!path || !out) return fail(RAGSTORE_ERR_INVALID, "ragstore_load: null argument");
+// Reads one image from the current position of f into a new store on `device`.  whole_file: the image must end where the
+// file ends (a stand-alone image); otherwise it must fit in what is left (an image inside a multi-device file).
+static int load_image(FILE* f, bool whole_file, int device, int64_t capacity_rows, ragstore_t** out) {
     *out = nullptr;
-    FILE* f = fopen(path, "rb");
-    if (!f) return fail(RAGSTORE_ERR_INVALID, "ragstore_load: cannot open file", path);
     SaveHeader h{};
-    if (fread(&h, sizeof(h), 1, f) != 1 || memcmp(h.magic, "RAGSTOR1", 8) != 0 || h.version != 1) {
-        fclose(f);
+    if (fread(&h, sizeof(h), 1, f) != 1 || memcmp(h.magic, "RAGSTOR1", 8) != 0 || h.version != 1)
         return fail(RAGSTORE_ERR_INVALID, "ragstore_load: not a ragstore image (version 1)");
-    }
     {   // nothing in the header is trusted before it is checked against itself and against the file's size
         const bool dt_ok = h.dtype == RAGSTORE_F32 || h.dtype == RAGSTORE_BF16;
         const int align = h.dtype == RAGSTORE_F32 ? 4 : 8;
         bool ok = dt_ok && h.dim > 0 && h.dim <= (1 << 20) && h.ld == (h.dim + align - 1) / align * align && h.raw_ld == (h.dim + 3) / 4 * 4 &&
                   h.count >= 0 && h.count < 0xFFFFFFFFll && (h.has_sidecar == 0 || h.has_sidecar == 1) && h.sidecar_rows >= 0 &&
-                  h.sidecar_rows <= h.count && h.inexact_rows >= 0 && h.inexact_rows <= h.count && (h.has_sidecar || h.sidecar_rows == 0);
+                  h.sidecar_rows <= h.count && h.inexact_rows >= 0 && h.inexact_rows <= h.count && (h.has_sidecar || h.sidecar_rows == 0) &&
+                  (h.pad == 0 || h.pad == RAGSTORE_CREATE_BF16_SHADOW);
         if (ok) {
             const uint64_t n = static_cast<uint64_t>(h.count), esz = h.dtype == RAGSTORE_F32 ? 4 : 2;
-            uint64_t want = sizeof(SaveHeader) + n * static_cast<uint64_t>(h.ld) * esz + n * 4 + n;
+            uint64_t want = n * static_cast<uint64_t>(h.ld) * esz + n * 4 + n;
             if (h.has_sidecar) want += n * 4 + static_cast<uint64_t>(h.sidecar_rows) * static_cast<uint64_t>(h.raw_ld) * 4;
-            long here = ftell(f);
-            ok = fseek(f, 0, SEEK_END) == 0 && static_cast<uint64_t>(ftell(f)) == want && fseek(f, here, SEEK_SET) == 0;
+            const int64_t left = file_bytes_left(f);
+            ok = left >= 0 && (whole_file ? static_cast<uint64_t>(left) == want : static_cast<uint64_t>(left) >= want);
         }
-        if (!ok) {
-            fclose(f);
-            return fail(RAGSTORE_ERR_INVALID, "ragstore_load: header is inconsistent (counts, layout or file size do not agree)");
-        }
+        if (!ok) return fail(RAGSTORE_ERR_INVALID, "ragstore_load: header is inconsistent (counts, layout or file size do not agree)");
     }
     const int64_t cap = std::max<int64_t>(std::max<int64_t>(capacity_rows, h.count), 1);
     ragstore_t* s = nullptr;
-    int rc = ragstore_create(h.dim, h.dtype, cap, device, h.has_sidecar ? RAGSTORE_CREATE_SIDECAR_ON : RAGSTORE_CREATE_SIDECAR_OFF, &s);
-    if (rc) {
-        fclose(f);
-        return rc;
-    }
+    int rc = ragstore_create(h.dim, h.dtype, cap, device, (h.has_sidecar ? RAGSTORE_CREATE_SIDECAR_ON : RAGSTORE_CREATE_SIDECAR_OFF) | h.pad, &s);
+    if (rc) return rc;
     if (s->ld != h.ld || s->raw_ld != h.raw_ld) {
-        fclose(f);
         ragstore_destroy(s);
         return fail(RAGSTORE_ERR_INVALID, "ragstore_load: image layout differs from this build");
     }
@@ -1148,6 +1178,7 @@ int ragstore_load(const char* path, int device, int64_t capacity_rows, ragstore_
     const size_t n = static_cast<size_t>(h.count), n4 = ((n + 3) & ~size_t(3)) + 64;
     if (!rc && n) {
         int vr = s->mat_buf.ensure(n * s->ld * s->elem_size(), false, s->ingest_stream);
+        if (!vr && s->shadow) vr = s->shadow_buf.ensure(n * s->ld * 2, false, s->ingest_stream);
         if (!vr) vr = s->rnorm_buf.ensure(n4 * sizeof(float), true, s->ingest_stream);
         if (!vr) vr = s->exact_buf.ensure(n4, true, s->ingest_stream);
         if (!vr && h.has_sidecar) vr = s->slot_buf.ensure(n4 * sizeof(int32_t), true, s->ingest_stream);
@@ -1159,6 +1190,10 @@ int ragstore_load(const char* path, int device, int64_t capacity_rows, ragstore_
         if (!rc) rc = copy_in(f, s->exact, n, h_pin, pin_bytes);
         if (!rc && h.has_sidecar) rc = copy_in(f, s->raw_slot, n * sizeof(int32_t), h_pin, pin_bytes);
         if (!rc && h.has_sidecar) rc = copy_in(f, s->raw_rows, static_cast<size_t>(h.sidecar_rows) * s->raw_ld * sizeof(float), h_pin, pin_bytes);
+        if (!rc && s->shadow) {   // the bf16 image the batched path nominates from, rebuilt from the loaded fp32 rows
+            const int lr = launch_shadow_from_rows(static_cast<const float*>(s->mat), s->shadow, static_cast<int64_t>(n) * s->ld, s->ingest_stream);
+            if (lr || cudaStreamSynchronize(s->ingest_stream) != cudaSuccess) rc = fail(RAGSTORE_ERR_CUDA, "ragstore_load: rebuilding the bf16 shadow");
+        }
     }
     if (!rc) {
         const unsigned long long counters[2] = {static_cast<unsigned long long>(h.inexact_rows), static_cast<unsigned long long>(h.sidecar_rows)};
@@ -1167,7 +1202,6 @@ int ragstore_load(const char* path, int device, int64_t capacity_rows, ragstore_
             rc = fail(RAGSTORE_ERR_CUDA, "ragstore_load: restoring counters");
     }
     if (h_pin) cudaFreeHost(h_pin);
-    fclose(f);
     if (rc) {
         ragstore_destroy(s);
         return rc;
@@ -1177,6 +1211,45 @@ int ragstore_load(const char* path, int device, int64_t capacity_rows, ragstore_
     s->count.store(h.count, std::memory_order_release);
     *out = s;
     return RAGSTORE_OK;
+}
+
+int ragstore_load(const char* path, int device, int64_t capacity_rows, ragstore_t** out) {
+    if (!path || !out) return fail(RAGSTORE_ERR_INVALID, "ragstore_load: null argument");
+    *out = nullptr;
+    FILE* f = fopen(path, "rb");
+    if (!f) return fail(RAGSTORE_ERR_INVALID, "ragstore_load: cannot open file", path);
+    const int rc = load_image(f, true, device, capacity_rows, out);
+    fclose(f);
+    return rc;
+}
+
+int ragstore_load_sharded(const char* path, const int* devices, int n_devices, int64_t capacity_rows, ragstore_t** out) {
+    if (!path || !out || !devices || n_devices < 1) return fail(RAGSTORE_ERR_INVALID, "ragstore_load_sharded: null argument");
+    *out = nullptr;
+    FILE* f = fopen(path, "rb");
+    if (!f) return fail(RAGSTORE_ERR_INVALID, "ragstore_load_sharded: cannot open file", path);
+    ShardedSaveHeader h{};
+    int rc = RAGSTORE_OK;
+    if (fread(&h, sizeof(h), 1, f) != 1 || memcmp(h.magic, "RAGSHRD1", 8) != 0 || h.version != 1)
+        rc = fail(RAGSTORE_ERR_INVALID, "ragstore_load_sharded: not a multi-device ragstore image (version 1)");
+    if (!rc && (h.n_shards != n_devices || h.n_shards < 1 || h.n_shards > 64 || h.block_rows < 1 || h.count < 0 || h.dim < 1))
+        rc = fail(RAGSTORE_ERR_INVALID, "ragstore_load_sharded: the image was saved over a different number of shards (rows are dealt by shard count), or its header is damaged");
+    std::vector<ragstore_t*> shards;
+    const int64_t cap_total = std::max<int64_t>(std::max<int64_t>(capacity_rows, h.count), 1);
+    for (int i = 0; !rc && i < n_devices; ++i) {
+        ragstore_t* sh = nullptr;
+        // per-shard capacity as ragstore_create_sharded would size it
+        const int64_t full = cap_total / h.block_rows, rem = cap_total % h.block_rows;
+        const int64_t cap = std::max<int64_t>((full / n_devices + (i < full % n_devices ? 1 : 0)) * h.block_rows + (i == full % n_devices ? rem : 0), h.block_rows);
+        rc = load_image(f, false, devices[i], cap, &sh);
+        if (!rc) shards.push_back(sh);
+    }
+    if (!rc && file_bytes_left(f) != 0) rc = fail(RAGSTORE_ERR_INVALID, "ragstore_load_sharded: trailing bytes after the last shard");
+    fclose(f);
+    if (!rc) rc = sharded_adopt(shards, devices, h.dim, h.dtype, cap_total, h.block_rows, h.count, out);
+    if (rc)
+        for (ragstore_t* sh : shards) ragstore_destroy(sh);
+    return rc;
 }
 
 int ragstore_set_coalescing(ragstore_t* s, int window_us, int max_batch) {

@@ -94,6 +94,8 @@ struct NormaliseArgs {
     uint16_t* shadow;     // fp32 stores with a bf16 shadow: destination slice of the shadow rows (ld elements each), or null
 };
 int launch_normalise(const NormaliseArgs& a, cudaStream_t stream);
+// bf16 image of n fp32 values (a loaded store's shadow is rebuilt from its rows)
+int launch_shadow_from_rows(const float* src, uint16_t* dst, int64_t n, cudaStream_t stream);
 
 // ---- batched (tensor-core) path, batch_gemm.cu
 constexpr int kBatchMaxQ = 256;    // queries per launch (two 128-row MMA blocks)

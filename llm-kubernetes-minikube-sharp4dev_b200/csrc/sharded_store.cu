@@ -408,42 +408,21 @@ int sharded_search(ragstore* p, const float* queries, int n_queries, int top_k, 
 
 }  // namespace rag
 
-using namespace rag;
+namespace rag {
 
-extern "C" int ragstore_create_sharded(int dim, int dtype, int64_t capacity_rows, const int* devices, int n_devices,
-                                       int64_t block_rows, uint32_t flags, ragstore_t** out) {
-    if (!out) return api_fail(RAGSTORE_ERR_INVALID, "ragstore_create_sharded: out is null");
-    *out = nullptr;
-    if (!devices || n_devices < 1 || n_devices > 64 || dim <= 0 || capacity_rows <= 0 || block_rows < 0)
-        return api_fail(RAGSTORE_ERR_INVALID, "ragstore_create_sharded: need 1..64 devices, positive dim and capacity, block_rows >= 0");
-    if (block_rows == 0) block_rows = 65536;
-    ragstore* p = new ragstore();
-    ShardedState* ss = new ShardedState();
-    p->sharded = ss;
+std::mutex* sharded_add_mutex(ragstore* p, int64_t* block_rows) {
+    if (block_rows) *block_rows = p->sharded->block_rows;
+    return &p->sharded->add_mu;
+}
+
+// the parent object around existing shard stores: peer access towards the first device, search contexts
+static int sharded_wrap(ragstore* p, const int* devices, int n_devices, int64_t block_rows) {
+    ShardedState* ss = p->sharded;
     ss->n = n_devices;
     ss->block_rows = block_rows;
     ss->devices.assign(devices, devices + n_devices);
     ss->direct.assign(n_devices, 1);
-    p->dim = dim;
-    p->dtype = dtype;
-    p->capacity = capacity_rows;
     p->device = devices[0];
-    auto bail = [&](int rc) {
-        char buf[512];
-        ragstore_last_error(buf, sizeof buf);   // keep the cause across the clean-up calls
-        const std::string why = buf;
-        sharded_destroy(p);
-        return api_fail(rc, why.c_str());
-    };
-    for (int s = 0; s < n_devices; ++s) {
-        ragstore* sh = nullptr;
-        const int64_t cap = std::max<int64_t>(shard_rows(capacity_rows, s, block_rows, n_devices), block_rows);
-        int rc = ragstore_create(dim, dtype, cap, devices[s], flags, &sh);
-        if (rc) return bail(rc);
-        p->shards.push_back(sh);
-        rc = ragstore_set_row_blocking(sh, block_rows, n_devices, s);
-        if (rc) return bail(rc);
-    }
     p->ld = p->shards[0]->ld;
     p->sm_count = p->shards[0]->sm_count;
     // a shard on another GPU stores its hit records straight into the first GPU's gather buffer when peer access exists
@@ -462,9 +441,77 @@ extern "C" int ragstore_create_sharded(int dim, int dtype, int64_t capacity_rows
     ss->ctxs.resize(kNumCtx);
     for (int i = 0; i < kNumCtx; ++i) {
         const int rc = alloc_sharded_ctx(p, ss->ctxs[i]);
-        if (rc) return bail(rc);
+        if (rc) return rc;
         ss->free_ctx.push_back(i);
     }
+    return RAGSTORE_OK;
+}
+
+int sharded_adopt(std::vector<ragstore*>& shards, const int* devices, int dim, int dtype, int64_t capacity_rows, int64_t block_rows,
+                  int64_t count, ragstore** out) {
+    const int G = static_cast<int>(shards.size());
+    for (int s = 0; s < G; ++s) {
+        if (shards[s]->dim != dim || shards[s]->dtype != dtype || shards[s]->count.load() != shard_rows(count, s, block_rows, G))
+            return api_fail(RAGSTORE_ERR_INVALID, "ragstore_load_sharded: a shard's image does not belong to this corpus (dim, dtype or row count)");
+        const int rc = ragstore_set_row_blocking(shards[s], block_rows, G, s);
+        if (rc) return rc;
+    }
+    ragstore* p = new ragstore();
+    p->sharded = new ShardedState();
+    p->dim = dim;
+    p->dtype = dtype;
+    p->capacity = capacity_rows;
+    p->shards = shards;
+    const int rc = sharded_wrap(p, devices, G, block_rows);
+    if (rc) {
+        char buf[512];
+        ragstore_last_error(buf, sizeof buf);
+        const std::string why = buf;
+        p->shards.clear();   // the caller keeps (and destroys) the shards
+        sharded_destroy(p);
+        return api_fail(rc, why.c_str());
+    }
+    p->count.store(count, std::memory_order_release);
+    *out = p;
+    return RAGSTORE_OK;
+}
+
+}  // namespace rag
+
+using namespace rag;
+
+extern "C" int ragstore_create_sharded(int dim, int dtype, int64_t capacity_rows, const int* devices, int n_devices,
+                                       int64_t block_rows, uint32_t flags, ragstore_t** out) {
+    if (!out) return api_fail(RAGSTORE_ERR_INVALID, "ragstore_create_sharded: out is null");
+    *out = nullptr;
+    if (!devices || n_devices < 1 || n_devices > 64 || dim <= 0 || capacity_rows <= 0 || block_rows < 0)
+        return api_fail(RAGSTORE_ERR_INVALID, "ragstore_create_sharded: need 1..64 devices, positive dim and capacity, block_rows >= 0");
+    if (block_rows == 0) block_rows = 65536;
+    ragstore* p = new ragstore();
+    p->sharded = new ShardedState();
+    p->sharded->n = n_devices;
+    p->sharded->devices.assign(devices, devices + n_devices);
+    p->dim = dim;
+    p->dtype = dtype;
+    p->capacity = capacity_rows;
+    auto bail = [&](int rc) {
+        char buf[512];
+        ragstore_last_error(buf, sizeof buf);   // keep the cause across the clean-up calls
+        const std::string why = buf;
+        sharded_destroy(p);
+        return api_fail(rc, why.c_str());
+    };
+    for (int s = 0; s < n_devices; ++s) {
+        ragstore* sh = nullptr;
+        const int64_t cap = std::max<int64_t>(shard_rows(capacity_rows, s, block_rows, n_devices), block_rows);
+        int rc = ragstore_create(dim, dtype, cap, devices[s], flags, &sh);
+        if (rc) return bail(rc);
+        p->shards.push_back(sh);
+        rc = ragstore_set_row_blocking(sh, block_rows, n_devices, s);
+        if (rc) return bail(rc);
+    }
+    const int rc = sharded_wrap(p, devices, n_devices, block_rows);
+    if (rc) return bail(rc);
     *out = p;
     return RAGSTORE_OK;
 }

@@ -146,5 +146,10 @@ int sharded_reserve_rows(ragstore* p, int64_t n_rows);
 int sharded_search(ragstore* p, const float* queries, int n_queries, int top_k, int64_t* out_idx, double* out_score,
                    int32_t* out_found, int32_t* out_flags);
 int sharded_info(ragstore* p, int64_t* out, int n);
+std::mutex* sharded_add_mutex(ragstore* p, int64_t* block_rows);   // the handle's append lock (held while it is saved)
+// wraps already loaded shard stores (one per device, dealt with block_rows) into a multi-device handle; checks that their
+// row counts are those of a corpus of `count` rows.  On failure the shards stay the caller's.
+int sharded_adopt(std::vector<ragstore*>& shards, const int* devices, int dim, int dtype, int64_t capacity_rows, int64_t block_rows,
+                  int64_t count, ragstore** out);
 
 }  // namespace rag

@@ -54,6 +54,7 @@ def lib():
             "ragstore_hit_filters": (C.c_int, [f64p, C.c_int, C.c_double, C.c_double, C.c_double, C.POINTER(C.c_uint8), f64p, i32p]),
             "ragstore_save": (C.c_int, [vp, C.c_char_p]),
             "ragstore_load": (C.c_int, [C.c_char_p, C.c_int, C.c_int64, C.POINTER(vp)]),
+            "ragstore_load_sharded": (C.c_int, [C.c_char_p, C.POINTER(C.c_int), C.c_int, C.c_int64, C.POINTER(vp)]),
             "ragstore_search_coalesced": (C.c_int, [vp, f32p, C.c_int, C.c_int, i64p, f64p, i32p, i32p]),
             "ragstore_set_coalescing": (C.c_int, [vp, C.c_int, C.c_int]),
             "ragstore_search_device": (C.c_int, [vp, vp, C.c_int, C.c_int, vp, vp, vp, vp, vp]),
@@ -155,6 +156,17 @@ class RagStore:
         st = cls(0, 0, 0, device, _handle=h)
         i = st.info()
         st.dim, st.dtype, st.capacity = i["dim"], i["dtype"], i["capacity"]
+        return st
+
+    @classmethod
+    def load_sharded(cls, path: str, devices, capacity_rows: int = 0) -> "RagStore":
+        devs = (C.c_int * len(devices))(*[int(d) for d in devices])
+        h = C.c_void_p()
+        check(lib().ragstore_load_sharded(path.encode(), devs, len(devices), capacity_rows, C.byref(h)))
+        st = cls(0, 0, 0, int(devices[0]), _handle=h)
+        i = st.info()
+        st.dim, st.dtype, st.capacity = i["dim"], i["dtype"], i["capacity"]
+        st.devices = [int(d) for d in devices]
         return st
 
     def close(self):

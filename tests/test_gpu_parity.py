@@ -1092,3 +1092,50 @@ def test_scan_with_fused_exchange_on_one_rank(n, d, k, dtype):
             assert np.array_equal(h_sc[:found].numpy().view(np.uint64), esc.view(np.uint64))
             assert flags & rb.RAGSTORE_HIT_EXACT_ROWS
         px.close()
+
+
+def test_save_and_load_of_a_multi_device_handle_and_of_a_shadowed_store(tmp_path):
+    """N3 on the round-2 stores: a handle over several shards is saved as one file and mapped back over the same number
+    of devices (answers unchanged, appends continue in the same dealing order); a store with a bf16 shadow gets its
+    shadow back on load (batches keep taking the bf16 tensor-core path)."""
+    n, d, k = 7000, 128, 10
+    rows = oc.synth_rows(0, n, d, 91)
+    rows[::9] *= 1.7                                  # sidecar rows on every shard
+    qs = oc.synth_rows(0, 40, d, 92)
+    path = str(tmp_path / "sharded.rag")
+    st = rb.RagStore.create_sharded(d, n, _sharded_devices(3), block_rows=200)
+    try:
+        st.add(rows[:5000])
+        before = st.search(qs, k)
+        st.save(path)
+    finally:
+        st.close()
+    with pytest.raises(rb.RagStoreError):
+        rb.RagStore.load_sharded(path, _sharded_devices(2))           # dealt over 3 shards: cannot be mapped over 2
+    with pytest.raises(rb.RagStoreError):
+        rb.RagStore.load(path)                                        # not a single-device image
+    st2 = rb.RagStore.load_sharded(path, _sharded_devices(3), capacity_rows=n)
+    try:
+        assert st2.count() == 5000
+        after = st2.search(qs, k)
+        assert np.array_equal(before[0], after[0]) and np.array_equal(before[1].view(np.uint64), after[1].view(np.uint64))
+        assert st2.add(rows[5000:]) == 5000
+        idx, sc, found, _ = st2.search(qs[0], k)
+        eidx, esc = oc.query(rows, qs[0], k, n_threads=4)
+        assert list(idx[0]) == list(eidx) and np.array_equal(sc[0].view(np.uint64), esc.view(np.uint64))
+    finally:
+        st2.close()
+    p2 = str(tmp_path / "shadow.rag")
+    n2, d2 = 30000, 256
+    rows2 = oc.synth_rows(0, n2, d2, 93)
+    with rb.RagStore(d2, n2, rb.RAGSTORE_F32, 0, rb.RAGSTORE_CREATE_BF16_SHADOW) as s1:
+        s1.add(rows2)
+        b1 = s1.search(oc.synth_rows(0, 64, d2, 94), k)
+        s1.save(p2)
+    s2 = rb.RagStore.load(p2)
+    try:
+        b2 = s2.search(oc.synth_rows(0, 64, d2, 94), k)
+        assert s2.info()["batch_launches"] >= 1
+        assert np.array_equal(b1[0], b2[0]) and np.array_equal(b1[1].view(np.uint64), b2[1].view(np.uint64)) and (b2[3] & 1).all()
+    finally:
+        s2.close()
