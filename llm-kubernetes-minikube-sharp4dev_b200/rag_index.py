@@ -40,12 +40,16 @@ class RagIndex:
 
     def __init__(self, embedModel: str, embedder: Optional[Callable] = None, *, dim: Optional[int] = None,
                  capacity_rows: int = 1 << 20, dtype: int = RAGSTORE_F32, device: int = 0, coalesce: bool = False,
-                 batch_embedder: Optional[Callable] = None, embed_batch: int = 64):
+                 batch_embedder: Optional[Callable] = None, embed_batch: int = 64, devices: Optional[Sequence[int]] = None,
+                 block_rows: int = 0, store_flags: int = 0):
         self._embedModel = embedModel                       # RagIndex.cs:9,11
         self._embedder = embedder
         self._meta: List[tuple] = []                        # (Id, Source, Text) per row, insertion order
         self._store: Optional[RagStore] = None
         self._dim, self._cap, self._dtype, self._device = dim, capacity_rows, dtype, device
+        # `devices`: the same index spread over several GPUs of this process behind ONE handle (ragstore_create_sharded);
+        # the object keeps its shape -- one RagIndex, as the reference's DI singleton (Program.cs:35,43)
+        self._devices, self._block_rows, self._store_flags = (list(devices) if devices else None), block_rows, store_flags
         self._coalesce = coalesce          # concurrent QueryAsync callers share one corpus sweep
         # `batch_embedder(model, [texts]) -> [embeddings]` -- the array form of the embed endpoint that
         # Embedder.cs:19 already sends for one text -- turns one HTTP round trip per chunk (RagIndex.cs:42-50) into one
@@ -57,7 +61,11 @@ class RagIndex:
     def _ensure(self, dim: int):
         if self._store is None:
             self._dim = self._dim or dim
-            self._store = RagStore(self._dim, self._cap, self._dtype, self._device)
+            if self._devices and len(self._devices) > 1:
+                self._store = RagStore.create_sharded(self._dim, self._cap, self._devices, dtype=self._dtype, block_rows=self._block_rows,
+                                                      flags=self._store_flags)
+            else:
+                self._store = RagStore(self._dim, self._cap, self._dtype, self._devices[0] if self._devices else self._device, self._store_flags)
 
     def Add(self, chunk: RagChunk):
         """`_chunks.Add(new RagChunk(..))` (RagIndex.cs:48)."""
