@@ -151,7 +151,7 @@ class ClockSampler:
                 self.power.append(nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0)
             except Exception:
                 pass
-            time.sleep(0.02)
+            time.sleep(0.005)     # short timed regions (20 steps of a few ms) still get a handful of samples
 
     def __enter__(self):
         if self.nv:
