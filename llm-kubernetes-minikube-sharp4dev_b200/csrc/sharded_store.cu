@@ -219,6 +219,20 @@ int sharded_add(ragstore* p, const float* rows, int64_t n_rows, uint32_t flags, 
         seg_rows[s].push_back(upto - g);
         g = upto;
     }
+    if (flags & RAGSTORE_ADD_DEVICE) {
+        // a device-resident source is read in place by every shard's upload kernel: that needs the source on the shard's own
+        // GPU, or on the first GPU with peer access from the shard's (what the handle set up at create)
+        cudaPointerAttributes pa{};
+        const bool known = cudaPointerGetAttributes(&pa, rows) == cudaSuccess && pa.type == cudaMemoryTypeDevice;
+        cudaGetLastError();
+        for (int s = 0; s < G; ++s) {
+            if (seg_ptr[s].empty()) continue;
+            const bool reachable = known && (pa.device == ss->devices[s] || (pa.device == ss->devices[0] && ss->direct[s]));
+            if (!reachable)
+                return api_fail(RAGSTORE_ERR_UNSUPPORTED, "ragstore_add: device-resident rows must live on the handle's first GPU (with peer access from every shard's GPU) "
+                                                          "or on the GPU of the shard that receives them; pass host rows otherwise");
+        }
+    }
     std::vector<int> rcs(G, RAGSTORE_OK);
     std::vector<std::string> errs(G);
     auto feed = [&](int s) {
