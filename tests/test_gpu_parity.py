@@ -1139,3 +1139,75 @@ def test_save_and_load_of_a_multi_device_handle_and_of_a_shadowed_store(tmp_path
         assert np.array_equal(b1[0], b2[0]) and np.array_equal(b1[1].view(np.uint64), b2[1].view(np.uint64)) and (b2[3] & 1).all()
     finally:
         s2.close()
+
+
+def test_multi_device_handle_streaming_appends_concurrent_with_searches():
+    """config 5 on ONE handle: a writer appends batches that straddle shard blocks while readers search.  Every answer
+    must equal the oracle on a whole-batch prefix of the insertion order -- never a mix of one shard's new rows with
+    another shard's old ones (the handle publishes its row count after every shard is done and turns it into per-shard
+    limits for each search)."""
+    import threading
+    d, batch, nb, k = 96, 1500, 16, 10
+    rows = oc.synth_rows(0, batch * nb, d, 41)
+    qs = oc.synth_rows(0, 6, d, 42)
+    results, errors = [], []
+    st = rb.RagStore.create_sharded(d, batch * nb, _sharded_devices(3), block_rows=400)     # a batch spans ~4 blocks: all shards
+    try:
+        st.add(rows[:batch])
+        done = threading.Event()
+
+        def writer():
+            try:
+                for b in range(1, nb):
+                    st.add(rows[b * batch:(b + 1) * batch])
+            except Exception as e:   # pragma: no cover
+                errors.append(e)
+
+        def reader(seed):
+            try:
+                i = seed
+                while not done.is_set() or i < seed + 4:
+                    before = st.count()
+                    if i % 3 == 0:
+                        idx, sc, found, flags = st.search(qs[:4], k)          # small batch
+                        res = [(j, idx[j].copy(), sc[j].copy()) for j in range(4)]
+                    else:
+                        idx, sc, found, flags = st.search(qs[i % 6], k)
+                        res = [(i % 6, idx[0].copy(), sc[0].copy())]
+                    after = st.count()
+                    results.append((before, after, res))
+                    i += 1
+            except Exception as e:   # pragma: no cover
+                errors.append(e)
+
+        readers = [threading.Thread(target=reader, args=(s,)) for s in (0, 1, 2)]
+        w = threading.Thread(target=writer)
+        for t in readers:
+            t.start()
+        w.start()
+        w.join()
+        done.set()
+        for t in readers:
+            t.join()
+        assert not errors, errors
+        assert st.count() == batch * nb and st.info()["scratch_overlaps"] == 0
+    finally:
+        st.close()
+    assert len(results) >= 9
+    cache = {}
+    for before, after, res in results:
+        ok_n = None
+        for n in range(before, after + 1):
+            if n % batch:
+                continue
+            good = True
+            for qi, idx, sc in res:                     # all queries of one call saw the SAME prefix
+                key = (qi, n)
+                if key not in cache:
+                    cache[key] = oc.query(rows[:n], qs[qi], k, n_threads=4)
+                eidx, esc = cache[key]
+                good = good and list(idx) == list(eidx) and np.array_equal(sc.view(np.uint64), esc.view(np.uint64))
+            if good:
+                ok_n = n
+                break
+        assert ok_n is not None, (before, after)
