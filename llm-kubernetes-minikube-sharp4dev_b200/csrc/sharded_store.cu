@@ -122,7 +122,8 @@ int alloc_sharded_ctx(ragstore* p, ShardedCtx& c) {
 // Enqueue shard s's part of a query block on its own stream: records for queries `which` (all nq when null) into
 // out_cand[q * req ...], flags into out_flags[q].  kp_force > 0: fp32 scans with that list length (the redo of queries the
 // first pass could not certify).
-int launch_shard(ragstore* sh, SearchCtx& c, int64_t n, int req, const float* h_queries, int nq, int kp_force,
+// h_pinned: the same queries in page-locked memory every device can read (the source of host->device copies), or null.
+int launch_shard(ragstore* sh, SearchCtx& c, int64_t n, int req, const float* h_queries, const float* h_pinned, int nq, int kp_force,
                  const std::vector<int>* which, ragstore_cand* out_cand, int32_t* out_flags) {
     const int take = static_cast<int>(std::min<int64_t>(n, req));
     if (n == 0) {
@@ -135,9 +136,15 @@ int launch_shard(ragstore* sh, SearchCtx& c, int64_t n, int req, const float* h_
         return RAGSTORE_OK;
     }
     const int kp = kp_force > 0 ? kp_force : choose_kp(take);
-    if (kp_force <= 0 && !which && batch_eligible(sh, n, nq, kp)) {
+    const float* h2d_src = h_pinned;
+    auto stage_queries = [&]() {   // without a shared page-locked copy, stage through this context's own
+        if (h2d_src) return;
         std::memcpy(c.h_q, h_queries, sizeof(float) * static_cast<size_t>(nq) * sh->dim);
-        SH_TRY(cudaMemcpyAsync(c.d_q, c.h_q, sizeof(float) * static_cast<size_t>(nq) * sh->dim, cudaMemcpyHostToDevice, c.st));
+        h2d_src = c.h_q;
+    };
+    if (kp_force <= 0 && !which && batch_eligible(sh, n, nq, kp)) {
+        stage_queries();
+        SH_TRY(cudaMemcpyAsync(c.d_q, h2d_src, sizeof(float) * static_cast<size_t>(nq) * sh->dim, cudaMemcpyHostToDevice, c.st));
         BatchSearchArgs b{};
         fill_batch_args(sh, n, take, kp, b);
         b.scan.out_flags = out_flags;
@@ -155,8 +162,8 @@ int launch_shard(ragstore* sh, SearchCtx& c, int64_t n, int req, const float* h_
     const bool in_params = sh->dim <= kParamQueryMax;
     const int count = which ? static_cast<int>(which->size()) : nq;
     if (!in_params) {
-        std::memcpy(c.h_q, h_queries, sizeof(float) * static_cast<size_t>(nq) * sh->dim);
-        SH_TRY(cudaMemcpyAsync(c.d_q, c.h_q, sizeof(float) * static_cast<size_t>(nq) * sh->dim, cudaMemcpyHostToDevice, c.st));
+        stage_queries();
+        SH_TRY(cudaMemcpyAsync(c.d_q, h2d_src, sizeof(float) * static_cast<size_t>(nq) * sh->dim, cudaMemcpyHostToDevice, c.st));
     }
     for (int i = 0; i < count; ++i) {
         const int q = which ? (*which)[i] : i;
@@ -367,6 +374,13 @@ int sharded_search(ragstore* p, const float* queries, int n_queries, int top_k, 
         int64_t* h_idx = reinterpret_cast<int64_t*>(pc.h_out);
         double* h_score = reinterpret_cast<double*>(h_idx + nh);
         int32_t* h_found = reinterpret_cast<int32_t*>(h_score + nh);
+        // Several queries: ONE page-locked copy of the block that every shard's host->device copy reads (a copy per shard
+        // cost 8 x 0.8 MB of memcpy per 256-query block on 8 GPUs -- more host time than the sweep takes on the devices)
+        const float* h_pinned = nullptr;
+        if (nq > 1 || p->dim > kParamQueryMax) {
+            std::memcpy(pc.h_q, hq, sizeof(float) * static_cast<size_t>(nq) * p->dim);
+            h_pinned = pc.h_q;
+        }
         std::vector<std::vector<int>> redo(G);   // per shard: queries to run again with the widest candidate lists
         for (int pass = 0; pass < 2; ++pass) {
             for (int s = 0; s < G; ++s) {
@@ -378,7 +392,7 @@ int sharded_search(ragstore* p, const float* queries, int n_queries, int top_k, 
                 int32_t* fdst = pc.d_flags + static_cast<size_t>(s) * nq;
                 ragstore_cand* oc = ss->direct[s] ? dst : pc.d_local[s];
                 int32_t* of = ss->direct[s] ? fdst : pc.d_lflags[s];
-                const int rc = launch_shard(sh, c, n_s[s], req, hq, nq, pass == 1 ? kMaxKp : 0, pass == 1 ? &redo[s] : nullptr, oc, of);
+                const int rc = launch_shard(sh, c, n_s[s], req, hq, h_pinned, nq, pass == 1 ? kMaxKp : 0, pass == 1 ? &redo[s] : nullptr, oc, of);
                 if (rc) return rc;
                 if (!ss->direct[s]) {   // no peer access from this device: the copy engine carries the records over
                     SH_TRY(cudaMemcpyPeerAsync(dst, ss->devices[0], oc, ss->devices[s], sizeof(ragstore_cand) * nh, c.st));
