@@ -18,6 +18,9 @@
 #include <algorithm>
 #include <cmath>
 #include <cstring>
+#include <deque>
+#include <functional>
+#include <memory>
 #include <thread>
 
 #include "store_impl.h"
@@ -36,7 +39,19 @@ struct ShardedCtx {
     float* h_q = nullptr;                  // page-locked copy of the query block (source of the H2D copies of a batch)
 };
 
+// One host thread per shard, parked on its device: a batch of queries costs every shard a query upload, two tensor-map
+// encodings and five launches (~0.1 ms of host time), which one caller thread would pay G times in a row per 256-query
+// block; the workers pay it side by side.  Single queries stay on the caller's thread (one launch per shard).
+struct ShardWorker {
+    std::thread th;
+    std::mutex mu;
+    std::condition_variable cv;
+    std::deque<std::function<void()>> jobs;
+    bool stop = false;
+};
+
 struct ShardedState {
+    std::vector<std::unique_ptr<ShardWorker>> workers;
     int n = 0;
     int64_t block_rows = 0;
     std::vector<int> devices;
@@ -71,6 +86,41 @@ uint64_t ord_key(double s) {
     uint64_t u;
     std::memcpy(&u, &s, 8);
     return (u & 0x8000000000000000ull) ? ~u : (u | 0x8000000000000000ull);
+}
+
+void worker_loop(ShardWorker* w, int device) {
+    cudaSetDevice(device);
+    for (;;) {
+        std::function<void()> job;
+        {
+            std::unique_lock<std::mutex> lk(w->mu);
+            w->cv.wait(lk, [&] { return w->stop || !w->jobs.empty(); });
+            if (w->jobs.empty()) return;   // stop requested and nothing left to do
+            job = std::move(w->jobs.front());
+            w->jobs.pop_front();
+        }
+        job();
+    }
+}
+
+void post(ShardWorker* w, std::function<void()> job) {
+    {
+        std::lock_guard<std::mutex> lk(w->mu);
+        w->jobs.push_back(std::move(job));
+    }
+    w->cv.notify_one();
+}
+
+void stop_workers(ShardedState* ss) {
+    for (auto& w : ss->workers) {
+        {
+            std::lock_guard<std::mutex> lk(w->mu);
+            w->stop = true;
+        }
+        w->cv.notify_one();
+        if (w->th.joinable()) w->th.join();
+    }
+    ss->workers.clear();
 }
 
 void free_sharded_ctx(ShardedState* ss, ShardedCtx& c) {
@@ -185,6 +235,7 @@ int launch_shard(ragstore* sh, SearchCtx& c, int64_t n, int req, const float* h_
 int sharded_destroy(ragstore* p) {
     ShardedState* ss = p->sharded;
     if (ss) {
+        stop_workers(ss);
         for (int s = 0; s < ss->n; ++s) {
             DeviceGuard g(ss->devices[s]);
             cudaDeviceSynchronize();
@@ -383,8 +434,8 @@ int sharded_search(ragstore* p, const float* queries, int n_queries, int top_k, 
         }
         std::vector<std::vector<int>> redo(G);   // per shard: queries to run again with the widest candidate lists
         for (int pass = 0; pass < 2; ++pass) {
-            for (int s = 0; s < G; ++s) {
-                if (pass == 1 && redo[s].empty()) continue;
+            // shard s's part of this block: launches on its own stream, records (and flags) into the first GPU's memory
+            auto shard_part = [&](int s) -> int {
                 ragstore* sh = p->shards[s];
                 SearchCtx& c = sh->ctxs[cis[s]];
                 SH_TRY(cudaSetDevice(ss->devices[s]));
@@ -399,6 +450,38 @@ int sharded_search(ragstore* p, const float* queries, int n_queries, int top_k, 
                     SH_TRY(cudaMemcpyPeerAsync(fdst, ss->devices[0], of, ss->devices[s], sizeof(int32_t) * nq, c.st));
                 }
                 SH_TRY(cudaEventRecord(pc.done[s], c.st));
+                return RAGSTORE_OK;
+            };
+            if (pass == 0 && nq > 1 && G > 1 && !ss->workers.empty()) {
+                // a block of queries: every shard's worker thread issues its part at the same time
+                std::mutex mu;
+                std::condition_variable cv;
+                int left = G, first_rc = RAGSTORE_OK;
+                std::string first_err;
+                for (int s = 0; s < G; ++s)
+                    post(ss->workers[s].get(), [&, s] {
+                        const int rc = shard_part(s);
+                        std::string err;
+                        if (rc) {
+                            char buf[512];
+                            ragstore_last_error(buf, sizeof buf);   // the worker thread's own error text
+                            err = buf;
+                        }
+                        std::lock_guard<std::mutex> lk(mu);
+                        if (rc && !first_rc) first_rc = rc, first_err = err;
+                        if (--left == 0) cv.notify_one();
+                    });
+                {
+                    std::unique_lock<std::mutex> lk(mu);
+                    cv.wait(lk, [&] { return left == 0; });
+                }
+                if (first_rc) return api_fail(first_rc, "ragstore_search (shard)", first_err.c_str());
+            } else {
+                for (int s = 0; s < G; ++s) {
+                    if (pass == 1 && redo[s].empty()) continue;
+                    const int rc = shard_part(s);
+                    if (rc) return rc;
+                }
             }
             SH_TRY(cudaSetDevice(ss->devices[0]));
             for (int s = 0; s < G; ++s)
@@ -472,6 +555,12 @@ static int sharded_wrap(ragstore* p, const int* devices, int n_devices, int64_t 
         if (rc) return rc;
         ss->free_ctx.push_back(i);
     }
+    if (n_devices > 1)
+        for (int s = 0; s < n_devices; ++s) {
+            ss->workers.emplace_back(new ShardWorker());
+            ShardWorker* w = ss->workers.back().get();
+            w->th = std::thread(worker_loop, w, devices[s]);
+        }
     return RAGSTORE_OK;
 }
 
