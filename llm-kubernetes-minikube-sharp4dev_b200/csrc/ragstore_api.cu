@@ -956,17 +956,16 @@ int rag::search_host_limited(ragstore* s, int64_t n_limit, const float* queries,
         // no staging copy, no host->device copy command in front of the kernel.  The tensor-core pass reads all
         // queries from device memory, so a batch is uploaded as before.
         const bool q_in_params = !batch_pass && s->dim <= kParamQueryMax;
-        if (!q_in_params) {
-            memcpy(c.h_q, queries + static_cast<size_t>(q0) * s->dim, static_cast<size_t>(nq) * s->dim * sizeof(float));
-            CU_TRY(cudaMemcpyAsync(c.d_q, c.h_q, static_cast<size_t>(nq) * s->dim * sizeof(float), cudaMemcpyHostToDevice, c.st));
-        }
+        // ... from the context's page-locked block, which the kernels read in place (it is device-addressable): no copy
+        // command that would wait behind an ingest chunk on the copy engine while rows are being appended
+        if (!q_in_params) memcpy(c.h_q, queries + static_cast<size_t>(q0) * s->dim, static_cast<size_t>(nq) * s->dim * sizeof(float));
         std::vector<int> todo(nq);
         for (int i = 0; i < nq; ++i) todo[i] = i;
         while (!todo.empty()) {
             if (batch_pass) {
                 // first pass on the tensor cores; queries whose margin the tf32 scores cannot certify are
                 // redone below by the fp32 scan kernel
-                const int rc = run_batch(s, n, take, kp0, c.d_q, nq, c.d_idx, c.d_score, c.d_found, c.d_flags, hs,
+                const int rc = run_batch(s, n, take, kp0, c.h_q, nq, c.d_idx, c.d_score, c.d_found, c.d_flags, hs,
                                          c.batch_scratch, c.st);
                 if (rc) return fail(RAGSTORE_ERR_CUDA, "batched search launch", cudaGetErrorString(static_cast<cudaError_t>(rc)));
             }
@@ -977,7 +976,7 @@ int rag::search_host_limited(ragstore* s, int64_t n_limit, const float* queries,
             for (int i : todo) {
                 if (batch_pass) break;
                 ScanArgs a = base_args(s, n, take, kp);
-                a.d_query = q_in_params ? nullptr : c.d_q + static_cast<size_t>(i) * s->dim;
+                a.d_query = q_in_params ? nullptr : c.h_q + static_cast<size_t>(i) * s->dim;
                 a.scratch = c.scratch;
                 a.out_idx = c.h_idx + static_cast<size_t>(i) * hs;
                 a.out_score = c.h_score + static_cast<size_t>(i) * hs;

@@ -192,15 +192,17 @@ int launch_shard(ragstore* sh, SearchCtx& c, int64_t n, int req, const float* h_
         std::memcpy(c.h_q, h_queries, sizeof(float) * static_cast<size_t>(nq) * sh->dim);
         h2d_src = c.h_q;
     };
+    // The kernels read the queries STRAIGHT from page-locked host memory (device-addressable under unified addressing):
+    // a few hundred KB of loads over PCIe instead of a copy command that would queue behind a 32 MB ingest chunk on the
+    // copy engine while rows are being appended.
     if (kp_force <= 0 && !which && batch_eligible(sh, n, nq, kp)) {
         stage_queries();
-        SH_TRY(cudaMemcpyAsync(c.d_q, h2d_src, sizeof(float) * static_cast<size_t>(nq) * sh->dim, cudaMemcpyHostToDevice, c.st));
         BatchSearchArgs b{};
         fill_batch_args(sh, n, take, kp, b);
         b.scan.out_flags = out_flags;
         b.scan.out_cand = out_cand;
         b.scan.cand_slots = req;
-        b.d_queries = c.d_q;
+        b.d_queries = h2d_src;
         b.nq = nq;
         b.out_stride = req;
         b.scratch = c.batch_scratch;
@@ -211,14 +213,11 @@ int launch_shard(ragstore* sh, SearchCtx& c, int64_t n, int req, const float* h_
     }
     const bool in_params = sh->dim <= kParamQueryMax;
     const int count = which ? static_cast<int>(which->size()) : nq;
-    if (!in_params) {
-        stage_queries();
-        SH_TRY(cudaMemcpyAsync(c.d_q, h2d_src, sizeof(float) * static_cast<size_t>(nq) * sh->dim, cudaMemcpyHostToDevice, c.st));
-    }
+    if (!in_params) stage_queries();
     for (int i = 0; i < count; ++i) {
         const int q = which ? (*which)[i] : i;
         ScanArgs a = base_args(sh, n, take, kp);
-        a.d_query = in_params ? nullptr : c.d_q + static_cast<size_t>(q) * sh->dim;
+        a.d_query = in_params ? nullptr : h2d_src + static_cast<size_t>(q) * sh->dim;
         a.scratch = c.scratch;
         a.out_flags = out_flags + q;
         a.out_cand = out_cand + static_cast<size_t>(q) * req;
