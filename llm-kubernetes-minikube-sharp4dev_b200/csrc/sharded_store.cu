@@ -36,7 +36,7 @@ struct ShardedCtx {
     std::vector<cudaEvent_t> done;         // per shard: its launches of this call have been issued and will complete
     uint8_t* h_out = nullptr;              // page-locked: [idx][score][found] of a query block, written by the merge kernel
     int32_t* h_flags = nullptr;            // page-locked: [shard][query]
-    float* h_q = nullptr;                  // page-locked copy of the query block (source of the H2D copies of a batch)
+    float* h_q = nullptr;                  // page-locked copy of the query block, read in place by every shard's kernels
 };
 
 // One host thread per shard, parked on its device: a batch of queries costs every shard a query upload, two tensor-map
@@ -162,7 +162,7 @@ int alloc_sharded_ctx(ragstore* p, ShardedCtx& c) {
             SH_TRY(cudaMalloc(&c.d_lflags[s], sizeof(int32_t) * kCtxQueries));
         }
     }
-    // portable: every device may write into it (the merge kernel does) and read from it (the query copies)
+    // portable: every device may write into it (the merge kernel does) and read from it (the kernels read query blocks in place)
     SH_TRY(cudaHostAlloc(reinterpret_cast<void**>(&c.h_out), kGatherRecords * 16 + kCtxQueries * 8, cudaHostAllocPortable));
     SH_TRY(cudaHostAlloc(reinterpret_cast<void**>(&c.h_flags), sizeof(int32_t) * kCtxQueries * G, cudaHostAllocPortable));
     SH_TRY(cudaHostAlloc(reinterpret_cast<void**>(&c.h_q), sizeof(float) * size_t(kCtxQueries) * p->ld, cudaHostAllocPortable));
@@ -172,7 +172,7 @@ int alloc_sharded_ctx(ragstore* p, ShardedCtx& c) {
 // Enqueue shard s's part of a query block on its own stream: records for queries `which` (all nq when null) into
 // out_cand[q * req ...], flags into out_flags[q].  kp_force > 0: fp32 scans with that list length (the redo of queries the
 // first pass could not certify).
-// h_pinned: the same queries in page-locked memory every device can read (the source of host->device copies), or null.
+// h_pinned: the same queries in page-locked memory that every device can read in place, or null.
 int launch_shard(ragstore* sh, SearchCtx& c, int64_t n, int req, const float* h_queries, const float* h_pinned, int nq, int kp_force,
                  const std::vector<int>* which, ragstore_cand* out_cand, int32_t* out_flags) {
     const int take = static_cast<int>(std::min<int64_t>(n, req));
@@ -187,7 +187,7 @@ int launch_shard(ragstore* sh, SearchCtx& c, int64_t n, int req, const float* h_
     }
     const int kp = kp_force > 0 ? kp_force : choose_kp(take);
     const float* h2d_src = h_pinned;
-    auto stage_queries = [&]() {   // without a shared page-locked copy, stage through this context's own
+    auto stage_queries = [&]() {   // without a shared page-locked copy, use this context's own
         if (h2d_src) return;
         std::memcpy(c.h_q, h_queries, sizeof(float) * static_cast<size_t>(nq) * sh->dim);
         h2d_src = c.h_q;
