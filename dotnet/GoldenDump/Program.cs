@@ -15,7 +15,8 @@
 //   * RagIndex.QueryAsync(query, topK)   (RagIndex.cs:59-67)  -- through the reference's own Embedder: QueryAsync asks
 //     http://localhost:11434/api/embeddings for the query vector (Embedder.cs:9,34), so the tool answers on that port
 //     with the test's query vector, every float printed as a round-trippable double ((float)GetDouble() gives it back
-//     exactly, Embedder.cs:44).  Stop a real Ollama on that port first.
+//     exactly, Embedder.cs:44).  Stop a real Ollama on that port first; on Windows HttpListener needs the URL reserved
+//     (netsh http add urlacl url=http://localhost:11434/ user=<you>) or an elevated prompt.
 //   * RagIndex.Cosine(float[], float[])  (RagIndex.cs:124-135) -- directly, by reflection, for every (query, row).
 // Rows go straight into the private `_chunks` list (RagIndex.cs:8) as RagChunk records (Program.cs:326), which is
 // what BuildFromFolderAsync does at :48; ids are the row numbers.
@@ -139,7 +140,7 @@ static class GoldenDump
         var gold = args[1];
         const BindingFlags any = BindingFlags.Public | BindingFlags.NonPublic | BindingFlags.Static | BindingFlags.Instance;
         ragIndexT = asm.GetType("Minimal_RAG.Helpers.RagIndex", true)!;
-        ragChunkT = asm.GetTypes().First(t => t.Name == "RagChunk");
+        ragChunkT = asm.GetType("RagChunk", true)!;            // a record of the top-level program: global namespace (Program.cs:326)
         cosine = ragIndexT.GetMethod("Cosine", any)!;
         queryAsync = ragIndexT.GetMethod("QueryAsync", any)!;
         chunksF = ragIndexT.GetField("_chunks", any)!;
