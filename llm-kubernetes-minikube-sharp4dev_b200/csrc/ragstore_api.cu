@@ -104,6 +104,8 @@ int alloc_ctx(SearchCtx& c, int ld, int sm_count) {
     CU_TRY(cudaMalloc(&c.d_idx, nq * kMaxKp * 16 + nq * 8));
     CU_TRY(cudaMallocHost(&c.h_q, nq * ld * sizeof(float)));
     CU_TRY(cudaMallocHost(&c.h_idx, nq * kMaxKp * 16 + nq * 8));
+    CU_TRY(cudaMallocHost(&c.h_done, 64));
+    *c.h_done = 0;
     return RAGSTORE_OK;
 }
 
@@ -117,6 +119,7 @@ void free_ctx(SearchCtx& c) {
     cudaFree(c.d_idx);
     cudaFreeHost(c.h_q);
     cudaFreeHost(c.h_idx);
+    cudaFreeHost(c.h_done);
     c = SearchCtx{};
 }
 
@@ -201,6 +204,25 @@ void fill_batch_args(const ragstore* s, int64_t n, int take, int kp, BatchSearch
     b.operand_mat = (s->dtype == RAGSTORE_F32 && s->shadow) ? s->shadow : nullptr;
     b.operand_bf16 = b.operand_mat ? 1 : 0;
     b.thr_rank = kp;   // the skip threshold follows what the request needs, not the widened candidate set
+}
+
+// Waits until the launch that carries (c.h_done, seq) has made its outputs visible to the host.  A short search (the
+// reference's own case is a 30 us kernel) is polled for in page-locked memory: the word arrives when the last CTA is done,
+// a few microseconds before the stream reports the kernel retired.  Anything long, or late, takes the ordinary stream wait.
+static int wait_done(SearchCtx& c, unsigned int seq, double expected_us) {
+    if (expected_us < 150.0) {
+        const auto t0 = std::chrono::steady_clock::now();
+        volatile unsigned int* w = c.h_done;
+        for (int spins = 0;; ++spins) {
+            if (*w == seq) return RAGSTORE_OK;
+            if ((spins & 255) == 255 && std::chrono::steady_clock::now() - t0 > std::chrono::microseconds(400)) break;
+#if defined(__x86_64__)
+            __builtin_ia32_pause();
+#endif
+        }
+    }
+    CU_TRY(cudaStreamSynchronize(c.st));
+    return RAGSTORE_OK;
 }
 
 int acquire_ctx(ragstore* s) {
@@ -973,9 +995,14 @@ int rag::search_host_limited(ragstore* s, int64_t n_limit, const float* queries,
             // unified addressing): k * 16 bytes of posted PCIe writes by the kernel's last CTA instead of a
             // device->host copy command behind the kernel -- one driver call and one DMA round trip less per search.
             const bool direct = !batch_pass;
+            unsigned int done_seq = 0;
             for (int i : todo) {
                 if (batch_pass) break;
                 ScanArgs a = base_args(s, n, take, kp);
+                if (i == todo.back()) {   // launches of one stream finish in order: the last one's word covers them all
+                    a.out_done = c.h_done;
+                    a.done_seq = done_seq = ++c.done_seq;
+                }
                 a.d_query = q_in_params ? nullptr : c.h_q + static_cast<size_t>(i) * s->dim;
                 a.scratch = c.scratch;
                 a.out_idx = c.h_idx + static_cast<size_t>(i) * hs;
@@ -986,9 +1013,14 @@ int rag::search_host_limited(ragstore* s, int64_t n_limit, const float* queries,
                 const int rc = launch_scan(a, c.st, q_in_params ? queries + static_cast<size_t>(q0 + i) * s->dim : nullptr);
                 if (rc) return fail(RAGSTORE_ERR_CUDA, "scan kernel launch", cudaGetErrorString(static_cast<cudaError_t>(rc)));
             }
-            if (!direct)
+            if (!direct) {
                 CU_TRY(cudaMemcpyAsync(c.h_idx, c.d_idx, static_cast<size_t>(nq) * hs * 16 + static_cast<size_t>(nq) * 8, cudaMemcpyDeviceToHost, c.st));
-            CU_TRY(cudaStreamSynchronize(c.st));
+                CU_TRY(cudaStreamSynchronize(c.st));
+            } else {
+                const double bytes = static_cast<double>(n) * s->ld * (s->dtype == RAGSTORE_F32 ? 4.0 : 2.0);
+                const int rcw = wait_done(c, done_seq, static_cast<double>(todo.size()) * (30.0 + bytes / 6.5e6));
+                if (rcw) return rcw;
+            }
             std::vector<int> again;
             for (int i : todo) {
                 const bool cert = (c.h_flags[i] & RAGSTORE_HIT_CERTIFIED) != 0;

@@ -65,6 +65,8 @@ struct ScanArgs {
     int32_t* x_found;                 // [1]
     int32_t* x_flags;                 // [1] RAGSTORE_HIT_* ANDed over all ranks (may be null)
     int32_t* x_status;                // [1] 0, or 1 when a peer's records did not arrive in time (may be null)
+    unsigned int* out_done; // [1] page-locked host word: receives done_seq once every output of this launch is visible to the
+    unsigned int done_seq;  // host (system-scope fence first).  A host thread may poll it instead of waiting for the stream.
     double* out_bound;      // [1] bound + eps + shrink: no row outside the collected candidates scores above it (may be null)
     uint64_t* out_last_key; // [1] approximate key of the worst collected candidate, 0 if none (may be null)
     int sm_count;

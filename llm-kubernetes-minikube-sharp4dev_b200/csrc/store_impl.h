@@ -63,6 +63,8 @@ struct SearchCtx {
     double* h_score = nullptr;
     int32_t* h_found = nullptr;
     int32_t* h_flags = nullptr;
+    unsigned int* h_done = nullptr;   // page-locked completion word the scan's last CTA writes (see wait_done)
+    unsigned int done_seq = 0;
 };
 
 int choose_kp(int take);

@@ -392,6 +392,12 @@ __device__ __forceinline__ void finalize_candidates(const ScanArgs& a, const Fin
         if (a.out_bound) *a.out_bound = bound_total;
         if (a.out_last_key) *a.out_last_key = n_cand > 0 ? lists[n_cand - 1] : 0ull;
         stamp(a, 5);
+        if (a.out_done) {
+            // Hits, found and flags were stored by threads of this CTA before the barrier above (or by this thread just now):
+            // the system-scope fence orders all of them before the word the host polls.
+            __threadfence_system();
+            *reinterpret_cast<volatile unsigned int*>(a.out_done) = a.done_seq;
+        }
     }
     if (a.xch == nullptr) return;
 
