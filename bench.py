@@ -744,16 +744,26 @@ def run_streaming(args, torch, dist, rb, native, rank, world, dev):
         st.reserve_rows(n_batches * B)      # HBM for the announced capacity mapped at start-up, not inside the stream
     ts = torch.cuda.Stream()
     with torch.cuda.stream(ts):
+        # This rank's part of the stream as DISTINCT rows in host memory: batch b of rank r is block b * world + r of the global
+        # insertion order (rows [g*B, (g+1)*B) of the synthetic corpus), generated on the device and copied back once.  Repeating
+        # one batch would fill the corpus with exact duplicates -- ties at every top-k boundary, which no margin can certify --
+        # and would leave nothing to check the final answer against.
+        h_all = torch.empty((n_batches * B, dim), dtype=torch.float32)
+        if args.pinned:
+            h_all = h_all.pin_memory()
         d_batch = torch.empty((B, dim), dtype=torch.float32, device="cuda")
-        native.synth_fill_device(d_batch, rank * B, B, dim, dim, CORPUS_SEED, device=dev, stream=ts.cuda_stream)
-        h_pin = d_batch.cpu().pin_memory() if args.pinned else None
-        h_batch = h_pin.numpy() if args.pinned else d_batch.cpu().numpy()   # the host-side batch the "application" appends
+        for b in range(n_batches):
+            native.synth_fill_device(d_batch, (b * world + rank) * B, B, dim, dim, CORPUS_SEED, device=dev, stream=ts.cuda_stream)
+            ts.synchronize()
+            h_all[b * B:(b + 1) * B].copy_(d_batch)
         del d_batch
+        h_np = h_all.numpy()
+        h_batches = [h_np[b * B:(b + 1) * B] for b in range(n_batches)]   # the host-side batches the "application" appends
         d_q = torch.empty((QB, dim), dtype=torch.float32, device="cuda")
         native.synth_fill_device(d_q, 0, QB, dim, dim, QUERY_SEED, device=dev, stream=ts.cuda_stream)
         local_only = bool(os.environ.get("BENCH_STREAM_LOCAL"))    # experiment: no exchange between the ranks
         sh = rb.ShardedSearcher(st, rank, 1 if local_only else world, 0, max_k=k, device=dev)
-        st.add(h_batch)                                      # first batch in before serving starts (also warms up)
+        st.add(h_batches[0])                                 # first batch in before serving starts (also warms up)
         for _ in range(3):
             # the serving loop below, once, outside the timed region: NCCL sets its connections up lazily per collective
             # (device-wide allocations and mappings that stall the ingest stream as well)
@@ -774,7 +784,7 @@ def run_streaming(args, torch, dist, rb, native, rank, world, dev):
             # one native call for the whole stream of batches (ragstore_add_many): every batch is still uploaded,
             # normalised and published on its own, but the producer loop does not compete for the Python GIL with the
             # serving loop of this process -- that contention, not the device, bounded earlier multi-GPU runs
-            st.add_many([h_batch] * (n_batches - 1))
+            st.add_many(h_batches[1:])
             t_ingest[0] = time.perf_counter() - t0
             stop.set()
 
@@ -812,6 +822,39 @@ def run_streaming(args, torch, dist, rb, native, rank, world, dev):
         if world > 1:
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         t_ing, t_srv = float(tt[0].item()), float(tt[1].item())
+        # all rows are resident now: query 0 against the oracle over the whole stream, every rank scoring its own blocks
+        parity = None
+        if not args.no_parity and not local_only:
+            import numpy as np
+            from oracle import oracle_c as oc
+            bi, bs, bf = sh.search_batch_device(d_q, QB, k)
+            ts.synchronize()
+            g_idx, g_sc = bi[0].cpu().numpy(), bs[0].cpu().numpy()
+            q0 = np.ascontiguousarray(d_q[0].cpu().numpy())
+            threads = max(1, (os.cpu_count() or 1) // world)
+            lists = []
+            for b in range(n_batches):
+                g = b * world + rank
+                rows_b = oc.synth_rows(g * B, B, dim, CORPUS_SEED, n_threads=threads)
+                li, ls = oc.query(rows_b, q0, k, n_threads=threads)
+                lists.append((li + g * B, ls))
+            mi, ms_ = merge_hit_lists(lists, k)
+            o_ids = torch.full((k,), -1, dtype=torch.int64, device="cuda")
+            o_scs = torch.full((k,), float("-inf"), dtype=torch.float64, device="cuda")
+            o_ids[:len(mi)] = torch.from_numpy(mi).cuda()
+            o_scs[:len(mi)] = torch.from_numpy(ms_).cuda()
+            if world > 1:
+                all_ids = torch.empty(world * k, dtype=torch.int64, device="cuda")
+                all_scs = torch.empty(world * k, dtype=torch.float64, device="cuda")
+                dist.all_gather_into_tensor(all_ids, o_ids)
+                dist.all_gather_into_tensor(all_scs, o_scs)
+            else:
+                all_ids, all_scs = o_ids, o_scs
+            ai, asc = all_ids.cpu().numpy(), all_scs.cpu().numpy()
+            oi, osc = merge_hit_lists([(ai[ai >= 0], asc[ai >= 0])], k)
+            ok_idx, ok_sc, _ = compare_hits(g_idx, g_sc, oi, osc)
+            parity = {"checked": f"query 0 after the stream (all {n_batches * B * world} rows resident) vs the CPU oracle over the whole stream, every rank its own blocks",
+                      "indices_bit_exact": ok_idx, "scores_bit_exact": ok_sc}
     rows_streamed = (n_batches - 1) * B * world
     info = st.info()
     out = None
@@ -833,7 +876,7 @@ def run_streaming(args, torch, dist, rb, native, rank, world, dev):
                "e2e": {"value": rows_streamed / t_ing, "unit": "vectors/s", "h2d_bytes_per_step": B * dim * 4 * world, "d2h_bytes_per_step": 0,
                        "api": "ragstore_add (host rows) concurrent with ragstore_search_shard_batch_device + all-gather + merge"},
                "gpu_launches": int(info["batch_launches"]) * 3 + (n_batches - 1) * 2, "clocks": clk.summary(),
-               "final_count_rank0": info["count"], "sidecar_rows": info["sidecar_rows"]}
+               "parity": parity, "final_count_rank0": info["count"], "sidecar_rows": info["sidecar_rows"]}
     st.close()
     return out
 
