@@ -16,6 +16,7 @@
 #include <string>
 #include <vector>
 
+#include "dealing.h"
 #include "exchange_impl.h"
 #include "store_impl.h"
 
@@ -71,9 +72,7 @@ namespace {
 
 // host mirror of global_row_id() (topk_device.cuh)
 int64_t host_global_row_id(const ragstore* s, int64_t local) {
-    if (s->row_block <= 0) return s->row_base + local;
-    const int64_t blk = local / s->row_block, off = local % s->row_block;
-    return s->row_base + (blk * s->row_nshards + s->row_shard) * s->row_block + off;
+    return dealt_global_id(local, s->row_block, s->row_nshards, s->row_shard, s->row_base);
 }
 
 int alloc_scratch(ScanScratch& s) {
@@ -1269,9 +1268,8 @@ int ragstore_load_sharded(const char* path, const int* devices, int n_devices, i
     const int64_t cap_total = std::max<int64_t>(std::max<int64_t>(capacity_rows, h.count), 1);
     for (int i = 0; !rc && i < n_devices; ++i) {
         ragstore_t* sh = nullptr;
-        // per-shard capacity as ragstore_create_sharded would size it
-        const int64_t full = cap_total / h.block_rows, rem = cap_total % h.block_rows;
-        const int64_t cap = std::max<int64_t>((full / n_devices + (i < full % n_devices ? 1 : 0)) * h.block_rows + (i == full % n_devices ? rem : 0), h.block_rows);
+        // per-shard capacity as ragstore_create_sharded sizes it
+        const int64_t cap = std::max<int64_t>(shard_rows(cap_total, i, h.block_rows, n_devices), h.block_rows);
         rc = load_image(f, false, devices[i], cap, &sh);
         if (!rc) shards.push_back(sh);
     }

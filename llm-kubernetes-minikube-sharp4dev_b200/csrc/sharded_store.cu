@@ -23,6 +23,7 @@
 #include <memory>
 #include <thread>
 
+#include "dealing.h"
 #include "store_impl.h"
 
 namespace rag {
@@ -66,12 +67,6 @@ struct ShardedState {
 namespace {
 
 constexpr size_t kGatherRecords = size_t(kCtxQueries) * kMaxKp;   // per shard and context
-
-// rows of shard s among the first `total` rows of the global insertion order
-int64_t shard_rows(int64_t total, int s, int64_t B, int G) {
-    const int64_t full = total / B, rem = total % B;
-    return (full / G + (s < full % G ? 1 : 0)) * B + (s == full % G ? rem : 0);
-}
 
 #define SH_TRY(expr)                                                                             \
     do {                                                                                         \
@@ -269,13 +264,10 @@ int sharded_add(ragstore* p, const float* rows, int64_t n_rows, uint32_t flags, 
     // cut [first, first + n_rows) at block boundaries; block b belongs to shard b % G and lands at that shard's tail
     std::vector<std::vector<const float*>> seg_ptr(G);
     std::vector<std::vector<int64_t>> seg_rows(G);
-    for (int64_t g = first; g < first + n_rows;) {
-        const int64_t blk = g / B, upto = std::min((blk + 1) * B, first + n_rows);
-        const int s = static_cast<int>(blk % G);
-        seg_ptr[s].push_back(rows + (g - first) * p->dim);
-        seg_rows[s].push_back(upto - g);
-        g = upto;
-    }
+    deal_append(first, n_rows, B, G, [&](int s, int64_t off, int64_t n) {
+        seg_ptr[s].push_back(rows + off * p->dim);
+        seg_rows[s].push_back(n);
+    });
     if (flags & RAGSTORE_ADD_DEVICE) {
         // a device-resident source is read in place by every shard's upload kernel: that needs the source on the shard's own
         // GPU, or on the first GPU with peer access from the shard's (what the handle set up at create)

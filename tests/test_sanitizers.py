@@ -58,6 +58,13 @@ def test_coalescing_queue_plain():
     assert "coalesce_stress ok" in _run(exe).stdout
 
 
+def test_dealing_arithmetic_under_ubsan():
+    """csrc/dealing.h: how a multi-device handle deals rows to shards (ids = insertion order, prefixes stay prefixes)."""
+    exe = _cc(["g++", "-std=c++17", "-O1", "-g", "-fsanitize=address,undefined", os.path.join(ROOT, "tests", "c", "dealing_selftest.cpp")],
+              "dealing_selftest_ubsan")
+    assert "dealing_selftest ok" in _run(exe).stdout
+
+
 def _abi_smoke_asan():
     so_dir = os.path.join(ROOT, "llm-kubernetes-minikube-sharp4dev_b200")
     return _cc(["gcc", "-std=c11", "-O1", "-g", "-fsanitize=address,undefined", os.path.join(ROOT, "tests", "c", "abi_smoke.c"),
