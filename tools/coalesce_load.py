@@ -18,7 +18,7 @@ def run(n, d, threads, seconds=1.0, window=None):
     qs = qd.cpu().numpy()
     st.search_coalesced(qs[0], 10)
     i0 = st.info()
-    counts, lat = [0] * threads, [0.0] * threads
+    counts, lat, worst = [0] * threads, [0.0] * threads, [0.0] * threads
     stop = time.perf_counter() + seconds
     def worker(t):
         torch.cuda.set_device(0)
@@ -28,7 +28,9 @@ def run(n, d, threads, seconds=1.0, window=None):
             if t0 >= stop:
                 break
             st.search_coalesced(qs[i % 256], 10)
-            lat[t] += time.perf_counter() - t0
+            dt1 = time.perf_counter() - t0
+            lat[t] += dt1
+            worst[t] = max(worst[t], dt1)
             counts[t] += 1
             i += threads
     ths = [threading.Thread(target=worker, args=(t,)) for t in range(threads)]
@@ -40,11 +42,11 @@ def run(n, d, threads, seconds=1.0, window=None):
     total = sum(counts)
     sweeps = (i1["batch_launches"] - i0["batch_launches"]) + (i1["scan_launches"] - i0["scan_launches"])
     print(f"n={n} d={d} threads={threads} window={'default (0)' if window is None else window}: {total/dt:.0f} queries/s, "
-          f"mean latency {sum(lat)/max(total,1)*1e3:.3f} ms, {total/max(sweeps,1):.1f} queries per corpus sweep", flush=True)
+          f"mean latency {sum(lat)/max(total,1)*1e3:.3f} ms, worst single call {max(worst)*1e3:.3f} ms, {total/max(sweeps,1):.1f} queries per corpus sweep", flush=True)
     st.close()
 
 if __name__ == "__main__":
-    for n in (10000, 1000000):
+    for n in (10000, 1000000, 4000000):
         for th in (1, 4, 16, 64):
             run(n, 768, th)
         run(n, 768, 16, window=0)
