@@ -19,6 +19,7 @@ namespace Minimal_RAG.Helpers
         // GPUs the index is spread over.  One entry: a single-device store.  Several: ONE handle over all of them
         // (ragstore_create_sharded) -- rows are dealt round-robin in blocks, ids stay insertion order, QueryAsync does not change.
         readonly int[] _devices;
+        public bool Coalesce { get; set; } = true;
 
         public RagIndex(string embedModel) : this(embedModel, new[] { 0 }) { }
         public RagIndex(string embedModel, int[] devices) { _embedModel = embedModel; _devices = devices; }
@@ -63,8 +64,12 @@ namespace Minimal_RAG.Helpers
             int want = Math.Max(1, topK);
             var idx = new long[want]; var score = new double[want];
             int found, flags;
+            // Under load the ASP.NET handlers (Program.cs:62,106) call QueryAsync concurrently: with Coalesce set, callers that
+            // arrive together are answered by ONE sweep of the corpus on the tensor cores (same hits, same order).
             fixed (float* pq = q) fixed (long* pi = idx) fixed (double* ps = score)
-                NativeMethods.Check(NativeMethods.ragstore_search(_store, pq, 1, q.Length, topK, pi, ps, &found, &flags));
+                NativeMethods.Check(Coalesce
+                    ? NativeMethods.ragstore_search_coalesced(_store, pq, q.Length, topK, pi, ps, &found, &flags)
+                    : NativeMethods.ragstore_search(_store, pq, 1, q.Length, topK, pi, ps, &found, &flags));
             for (int j = 0; j < found; j++)
             {
                 var m = _meta[(int)idx[j]];
