@@ -1211,3 +1211,24 @@ def test_multi_device_handle_streaming_appends_concurrent_with_searches():
                 ok_n = n
                 break
         assert ok_n is not None, (before, after)
+
+
+def test_rag_index_mirror_over_several_shards():
+    """The RagIndex mirror with a device list: one object, one handle over several shards (Program.cs:35,43 stays a
+    singleton) -- the same hits, ids, order and scores as the single-device index, coalesced callers included."""
+    emb = {f"t{i}": oc.synth_rows(i, 1, 64, 42)[0] for i in range(300)}
+    chunks = [rb.RagChunk(f"doc.md#{i}", "doc.md", f"t{i}", emb[f"t{i}"]) for i in range(300)]
+    one = rb.RagIndex("m", embedder=lambda model, text: emb[text], capacity_rows=512)
+    many = rb.RagIndex("m", embedder=lambda model, text: emb[text], capacity_rows=512, devices=_sharded_devices(3), block_rows=32,
+                       coalesce=True)
+    try:
+        for lo in range(0, 300, 70):                # appends in pieces, like a folder indexed file by file
+            one.AddRange(chunks[lo:lo + 70])
+            many.AddRange(chunks[lo:lo + 70])
+        assert one.Count == many.Count == 300
+        for t in ("t7", "t131", "t299"):
+            a, b = one.Query(t, 6), many.Query(t, 6)
+            assert [(h.Id, h.Source, h.Text, h.Score) for h in a] == [(h.Id, h.Source, h.Text, h.Score) for h in b]
+            assert b[0].Text == t
+    finally:
+        one.close(), many.close()
