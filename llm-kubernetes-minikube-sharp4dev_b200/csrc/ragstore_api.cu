@@ -170,7 +170,7 @@ float batch_eps(const ragstore* s) {
 
 // nq scans (one corpus sweep each + ~28 us of fixed cost) against one tensor-core batch (~62 us of fixed cost in its
 // five launches, one sweep, and the threshold pass over 1/stride of the corpus -- a whole second sweep on corpora too
-// small to sample).  Measured on B200 (tools/quick_smallbatch.py): 10k x 768: scans 29 us per query, batch 67-77 us for
+// small to sample).  Measured on B200 (tools/probe.py few): 10k x 768: scans 29 us per query, batch 67-77 us for
 // 2..15 queries; 4M x 768: 15 queries 27.2 ms as scans, 1.91 ms as one batch.  The batch wins from 2 queries on
 // corpora of ~1 GB up and from 3 on small ones.  RAGSTORE_BATCH_MINQ=<n> replaces the model by "at least n queries".
 bool batch_eligible(const ragstore* s, int64_t n, int nq, int kp) {
