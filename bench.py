@@ -707,6 +707,47 @@ def run_streaming_single_process(args, torch, rb, native, devices):
         st.close()
 
 
+def measure_shadow_single(args, torch, rb, native, dev, rows=10_000_000, dim=768, k=10, do_parity=True):
+    """Single queries on an fp32 store WITH the opt-in bf16 shadow (RAGSTORE_CREATE_BF16_SHADOW): ragstore_search scans the bf16
+    image (d * 2 bytes per row) and rescoring reads the fp32 rows, so hits and scores are those of the plain store.  Host query in,
+    host hits out (the device-only entry point keeps scanning the fp32 rows: it cannot retry what the image cannot certify)."""
+    import numpy as np
+    st = rb.RagStore(dim, rows, rb.RAGSTORE_F32, dev, 4)
+    try:
+        fill_store(st, native, torch, rows, dim, "f32", 0)
+        d_q = torch.empty((64, dim), dtype=torch.float32, device="cuda")
+        native.synth_fill_device(d_q, 0, 64, dim, dim, QUERY_SEED, device=dev)
+        torch.cuda.synchronize()
+        hq = [np.ascontiguousarray(r) for r in d_q.cpu().numpy()]
+        call, idx, sc, found, flags = st.search_call(1, k)
+        for i in range(10):
+            call(hq[i])
+        n_calls, per, cert = max(100, args.steps // 4), [], 0
+        i0 = st.info()
+        t0 = time.perf_counter()
+        for i in range(n_calls):
+            tc = time.perf_counter()
+            call(hq[i % 64])
+            per.append(time.perf_counter() - tc)
+            cert += int(flags[0] & 1)
+        dt = time.perf_counter() - t0
+        per.sort()
+        i1 = st.info()
+        out = {"desc": f"{rows} x {dim} fp32 store + bf16 shadow, single query, top-{k}: scan of the bf16 image, exact rescoring from the fp32 rows",
+               "api": "ragstore_search (host buffers)", "ms_per_query": dt / n_calls * 1e3, "median_ms": per[n_calls // 2] * 1e3,
+               "p99_ms": per[min(n_calls - 1, int(n_calls * 0.99))] * 1e3, "calls": n_calls, "vectors_per_s": rows * n_calls / dt,
+               "image_gbs": rows * dim * 2 / (per[n_calls // 2]) / 1e9, "algorithmic_bytes_per_query": rows * dim * 2,
+               "scan_launches_per_query": (i1["scan_launches"] - i0["scan_launches"]) / n_calls, "certified_fraction": cert / n_calls}
+        if do_parity:
+            call(hq[0])
+            ora = oracle_topk_streamed(0, rows, dim, False, [hq[0]], k, os.cpu_count() or 1)[0]
+            ok = compare_hits(idx[0, :found[0]], sc[0, :found[0]], ora[0], ora[1])
+            out["parity"] = {"checked": f"1 query x all {rows} rows vs the CPU oracle", "indices_bit_exact": ok[0], "scores_bit_exact": ok[1], "gpu_flags": int(flags[0])}
+        return out
+    finally:
+        st.close()
+
+
 def measure_k1(torch, rb, native, dev, rows=1 << 20, dim=768, reps=8):
     """K1 alone: device-resident fp32 rows -> normalised store rows (+ reciprocal norms, flags), read + write = 2*d*4 B/row."""
     buf = torch.empty((rows, dim), dtype=torch.float32, device="cuda")
@@ -991,6 +1032,10 @@ def main():
                     extra[name]["tensor"] = tensor_block(r)
             except Exception as ex:  # an extra must never take the headline down
                 extra[name] = {"error": repr(ex)[:300]}
+        try:
+            extra["target10m_shadow_single_query"] = measure_shadow_single(args, torch, rb, native, local, do_parity=not args.no_parity)
+        except Exception as ex:
+            extra["target10m_shadow_single_query"] = {"error": repr(ex)[:300]}
 
     if rank == 0:
         peak, peak_src = measured_peaks()

@@ -154,6 +154,23 @@ ScanArgs base_args(const ragstore* s, int64_t n, int take, int kp) {
     return a;
 }
 
+// Single queries on a store with a bf16 shadow: the scan streams the shadow (d * 2 bytes per row instead of d * 4) with the
+// fp32 query, so only the rows' rounding to bf16 separates its scores from the fp32 scan's: <= 2^-9 relative per element ->
+// <= 2^-9 on a cosine of unit vectors (Cauchy-Schwarz), on top of the bf16 scan's own accumulation bound.  Candidates are
+// rescored from the fp32 rows, so hits and scores are those of the fp32 scan whenever the certificate holds; it uses
+// candidate lists of at least 64 keys, and callers redo what it cannot certify with the fp32 scan.
+int shadow_scan_kp(int take) { return std::max(64, choose_kp(take)); }
+
+ScanArgs shadow_scan_args(const ragstore* s, int64_t n, int take, int kp) {
+    ScanArgs a = base_args(s, n, take, kp);
+    a.mat = s->shadow;
+    a.dtype = RAGSTORE_BF16;
+    a.rescore_rows = static_cast<const float*>(s->mat);
+    a.rescore_ld = s->ld;
+    a.eps = scan_eps(s->ld, RAGSTORE_BF16) + 1.953125e-3f + 2e-5f;
+    return a;
+}
+
 // fp32 store: tf32 products (10-bit mantissas, both operands) + fp32 accumulation vs the reference's score.
 // bf16 store: the stored rows enter exactly and the row norm is applied, so only the query's rounding to bf16
 // (<= 2^-9 relative per element -> <= 2^-9 on a cosine, Cauchy-Schwarz) and the fp32 accumulation remain; when
@@ -973,6 +990,9 @@ int rag::search_host_limited(ragstore* s, int64_t n_limit, const float* queries,
         }
         int kp = kp0;
         bool batch_pass = batch_eligible(s, n, nq, kp0);
+        // A shadowed fp32 store answers single queries from the bf16 image first (half the bytes); what that cannot certify
+        // goes through the fp32 scan below as before.
+        bool shadow_pass = !batch_pass && s->shadow != nullptr && s->dtype == RAGSTORE_F32;
         // Scan launches carry their query inside the kernel's parameter block (rows of up to kParamQueryMax elements):
         // no staging copy, no host->device copy command in front of the kernel.  The tensor-core pass reads all
         // queries from device memory, so a batch is uploaded as before.
@@ -997,7 +1017,7 @@ int rag::search_host_limited(ragstore* s, int64_t n_limit, const float* queries,
             unsigned int done_seq = 0;
             for (int i : todo) {
                 if (batch_pass) break;
-                ScanArgs a = base_args(s, n, take, kp);
+                ScanArgs a = shadow_pass ? shadow_scan_args(s, n, take, shadow_scan_kp(take)) : base_args(s, n, take, kp);
                 if (i == todo.back()) {   // launches of one stream finish in order: the last one's word covers them all
                     a.out_done = c.h_done;
                     a.done_seq = done_seq = ++c.done_seq;
@@ -1016,14 +1036,14 @@ int rag::search_host_limited(ragstore* s, int64_t n_limit, const float* queries,
                 CU_TRY(cudaMemcpyAsync(c.h_idx, c.d_idx, static_cast<size_t>(nq) * hs * 16 + static_cast<size_t>(nq) * 8, cudaMemcpyDeviceToHost, c.st));
                 CU_TRY(cudaStreamSynchronize(c.st));
             } else {
-                const double bytes = static_cast<double>(n) * s->ld * (s->dtype == RAGSTORE_F32 ? 4.0 : 2.0);
+                const double bytes = static_cast<double>(n) * s->ld * ((s->dtype == RAGSTORE_F32 && !shadow_pass) ? 4.0 : 2.0);
                 const int rcw = wait_done(c, done_seq, static_cast<double>(todo.size()) * (30.0 + bytes / 6.5e6));
                 if (rcw) return rcw;
             }
             std::vector<int> again;
             for (int i : todo) {
                 const bool cert = (c.h_flags[i] & RAGSTORE_HIT_CERTIFIED) != 0;
-                if (!cert && (batch_pass || kp < kMaxKp)) {
+                if (!cert && (batch_pass || shadow_pass || kp < kMaxKp)) {
                     again.push_back(i);  // rescan this query (fp32 scan after a tf32 pass; else a wider list)
                     continue;
                 }
@@ -1036,6 +1056,8 @@ int rag::search_host_limited(ragstore* s, int64_t n_limit, const float* queries,
             todo.swap(again);
             if (batch_pass)
                 batch_pass = false;  // next pass: fp32 scan with the same list length
+            else if (shadow_pass)
+                shadow_pass = false; // next pass: fp32 scan with the request's own list length
             else
                 kp = kMaxKp;
         }

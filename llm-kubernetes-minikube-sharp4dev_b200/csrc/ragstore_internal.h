@@ -31,6 +31,8 @@ struct ScanArgs {
     const int32_t* raw_slot;// [n_rows] slot of the row's original fp32 values in raw_rows, -1 = stored exactly (may be null)
     const float* raw_rows;  // [n_slots][raw_ld] original fp32 rows of the inexactly stored ones (sidecar)
     int raw_ld;
+    const float* rescore_rows;      // not null: `mat` is only a bf16 IMAGE of an fp32 store (the shadow); candidates are rescored
+    int rescore_ld;                 // from these fp32 rows [n_rows][rescore_ld] (a sidecar original still takes precedence)
     const uint32_t* min_norm_bits;  // fp32 bits of the smallest non-zero original row norm (may be null)
     float min_norm_assumed;         // used when min_norm_bits is null: the caller's promise about the smallest row norm
                                     // (0 = no promise: the certificate then ignores the reference's +1e-9 term)

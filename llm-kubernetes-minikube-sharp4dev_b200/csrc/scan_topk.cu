@@ -346,6 +346,7 @@ static bool make_layout(const ScanArgs& a, int dv, ScanLayout& L) {
     const uint32_t fixed = bars_bytes + 2u * L.qpad * 4u + lists_bytes + buf_bytes + sizeof(ScanMisc) + 512u;
     if (fixed + 2u * (4u * L.row_bytes + 128u) > kSmemBudget) return false;
     if (a.raw_slot && static_cast<uint32_t>(a.raw_ld) * 4u + 16u > 2u * (4u * L.row_bytes + 128u)) return false;
+    if (a.rescore_rows && static_cast<uint32_t>(a.rescore_ld) * 4u + 16u > 2u * (4u * L.row_bytes + 128u)) return false;
     const uint32_t ring = kSmemBudget - fixed;
     // Rows per tile R: a multiple of 4 (row group of a warp; 16-byte granularity of the reciprocal-norm
     // slice).  Stages: 16, 8 or fewer, with min(8, stages) consumer warps so that each warp owns

@@ -130,6 +130,11 @@ namespace rag {
 
 // ---- helpers implemented in ragstore_api.cu
 ScanArgs base_args(const ragstore* s, int64_t n, int take, int kp);
+// the same search as a scan over the store's bf16 shadow (half the bytes), candidates rescored from the fp32 rows; only for
+// stores created with RAGSTORE_CREATE_BF16_SHADOW (s->shadow != null).  Wider error bound: callers retry uncertified
+// queries with base_args().
+ScanArgs shadow_scan_args(const ragstore* s, int64_t n, int take, int kp);
+int shadow_scan_kp(int take);
 float batch_eps(const ragstore* s);
 bool batch_eligible(const ragstore* s, int64_t n, int nq, int kp);
 // store views, candidate-set size, error bound and tensor-core operand of one batched launch (outputs left to the caller)

@@ -257,8 +257,10 @@ __device__ __forceinline__ void finalize_candidates(const ScanArgs& a, const Fin
     // Rows are staged in the (now idle) tile ring.  A row that was stored inexactly (normalised with
     // scale != 1, or rounded to bf16) is rescored from its ORIGINAL fp32 values kept in the sidecar,
     // so the fp64 score below is the reference's value for the row as it was added.
+    // A scan over the bf16 shadow of an fp32 store (a.rescore_rows) rescoring from the fp32 rows themselves: same mechanism.
     const uint32_t raw_bytes = a.raw_slot ? static_cast<uint32_t>(a.raw_ld) * 4u : 0u;
-    const uint32_t rs = max(f.row_bytes, raw_bytes) + 16;  // padded smem row stride: spreads rows over banks
+    const uint32_t res_bytes = a.rescore_rows ? static_cast<uint32_t>(a.rescore_ld) * 4u : 0u;
+    const uint32_t rs = max(max(f.row_bytes, raw_bytes), res_bytes) + 16;  // padded smem row stride: spreads rows over banks
     const int cap = max(1, static_cast<int>(ring_bytes / rs));
     uint8_t* rowbuf = f.ring;
 
@@ -272,7 +274,7 @@ __device__ __forceinline__ void finalize_candidates(const ScanArgs& a, const Fin
             for (int c = lane; c < nb; c += 32) {
                 const uint32_t row = key_row(lists[b0 + c]);
                 const int32_t slot = a.raw_slot ? a.raw_slot[row] : -1;
-                my_bytes += slot >= 0 ? raw_bytes : f.row_bytes;
+                my_bytes += slot >= 0 ? raw_bytes : (a.rescore_rows ? res_bytes : f.row_bytes);
             }
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) my_bytes += __shfl_xor_sync(0xffffffffu, my_bytes, o);
@@ -282,9 +284,10 @@ __device__ __forceinline__ void finalize_candidates(const ScanArgs& a, const Fin
                 const uint32_t row = key_row(lists[b0 + c]);
                 const int32_t slot = a.raw_slot ? a.raw_slot[row] : -1;
                 const void* src = slot >= 0 ? static_cast<const void*>(a.raw_rows + static_cast<size_t>(slot) * a.raw_ld)
-                                            : static_cast<const void*>(mat + static_cast<size_t>(row) * f.row_bytes);
-                bulk_g2s(rowbuf + static_cast<size_t>(c) * rs, src, slot >= 0 ? raw_bytes : f.row_bytes, sbar);
-                misc->raw_fmt[c] = slot >= 0 ? 1 : 0;
+                                  : a.rescore_rows ? static_cast<const void*>(a.rescore_rows + static_cast<size_t>(row) * a.rescore_ld)
+                                                   : static_cast<const void*>(mat + static_cast<size_t>(row) * f.row_bytes);
+                bulk_g2s(rowbuf + static_cast<size_t>(c) * rs, src, slot >= 0 ? raw_bytes : (a.rescore_rows ? res_bytes : f.row_bytes), sbar);
+                misc->raw_fmt[c] = (slot >= 0 || a.rescore_rows) ? 1 : 0;
             }
         }
         mbar_wait(reinterpret_cast<uint64_t*>(&misc->stage_bar), static_cast<uint32_t>(b0 / cap) & 1u);

@@ -1043,7 +1043,12 @@ def test_bf16_shadow_nominates_and_fp32_rows_decide(n, d, nq, k):
         idx, sc, found, flags = st.search(qs, k)
         info = st.info()
         assert info["batch_launches"] >= 1
-        one = st.search(qs[3], k)
+        before = st.info()["scan_launches"]
+        one = st.search(qs[3], k)          # a single query: scanned from the bf16 image, rescored from the fp32 rows
+        assert st.info()["scan_launches"] > before
+        eidx3, esc3 = oc.query(rows, qs[3], k, n_threads=4)
+        assert list(one[0][0]) == list(eidx3) and np.array_equal(one[1][0].view(np.uint64), esc3.view(np.uint64))
+        assert one[3][0] & rb.RAGSTORE_HIT_CERTIFIED and one[3][0] & rb.RAGSTORE_HIT_EXACT_ROWS
     cert = 0
     for i in range(0, nq, 5):
         eidx, esc = oc.query(rows, qs[i], k, n_threads=4)
@@ -1232,3 +1237,26 @@ def test_rag_index_mirror_over_several_shards():
             assert b[0].Text == t
     finally:
         one.close(), many.close()
+
+
+@pytest.mark.parametrize("n,d,k", [(40000, 768, 10), (20000, 1024, 100), (9000, 64, 5), (3000, 256, 300)])
+def test_single_queries_on_a_shadowed_store_scan_the_bf16_image(n, d, k):
+    """With RAGSTORE_CREATE_BF16_SHADOW a single query streams the bf16 image (half the bytes) and rescoring reads the fp32
+    rows: hits and scores must be exactly those of the plain fp32 store -- including rows crowded closer than the bf16
+    rounding can separate (the certificate fails there and the fp32 scan takes over) and unnormalised rows (sidecar)."""
+    rows = oc.synth_rows(0, n, d, 71)
+    rows[::11] *= 4.0
+    q = oc.synth_rows(0, 3, d, 72)
+    base = q[0].astype(np.float64)
+    for j in range(60):                                  # 60 rows within ~1e-4 of each other around query 0
+        r = 37 * j + 5
+        v = base + 0.01 * rows[r].astype(np.float64) / max(np.linalg.norm(rows[r]), 1e-9)
+        rows[r] = (v / np.linalg.norm(v)).astype(np.float32)
+    with rb.RagStore(d, n, rb.RAGSTORE_F32, 0, rb.RAGSTORE_CREATE_BF16_SHADOW) as st:
+        st.add(rows)
+        for i in range(3):
+            idx, sc, found, flags = st.search(q[i], k)
+            eidx, esc = oc.query(rows, q[i], k, n_threads=4)
+            assert found[0] == len(eidx) and list(idx[0, :found[0]]) == list(eidx), i
+            assert np.array_equal(sc[0, :found[0]].view(np.uint64), esc.view(np.uint64)), i
+            assert flags[0] & rb.RAGSTORE_HIT_EXACT_ROWS
