@@ -161,6 +161,12 @@ ScanArgs base_args(const ragstore* s, int64_t n, int take, int kp) {
 // candidate lists of at least 64 keys, and callers redo what it cannot certify with the fp32 scan.
 int shadow_scan_kp(int take) { return std::max(64, choose_kp(take)); }
 
+// Worth it only when the bytes saved outweigh the longer tail (64-key lists, fp32 rows staged for rescoring): from ~64 MB of
+// image up (10k x 768 answers in 44 us from the fp32 rows and in 53 us from the image; 1M x 768 in 0.49 against 0.26 ms).
+bool shadow_scan_pays(const ragstore* s, int64_t n) {
+    return s->shadow != nullptr && s->dtype == RAGSTORE_F32 && static_cast<double>(n) * s->ld * 2.0 >= 64e6;
+}
+
 ScanArgs shadow_scan_args(const ragstore* s, int64_t n, int take, int kp) {
     ScanArgs a = base_args(s, n, take, kp);
     a.mat = s->shadow;
@@ -992,7 +998,7 @@ int rag::search_host_limited(ragstore* s, int64_t n_limit, const float* queries,
         bool batch_pass = batch_eligible(s, n, nq, kp0);
         // A shadowed fp32 store answers single queries from the bf16 image first (half the bytes); what that cannot certify
         // goes through the fp32 scan below as before.
-        bool shadow_pass = !batch_pass && s->shadow != nullptr && s->dtype == RAGSTORE_F32;
+        bool shadow_pass = !batch_pass && shadow_scan_pays(s, n);
         // Scan launches carry their query inside the kernel's parameter block (rows of up to kParamQueryMax elements):
         // no staging copy, no host->device copy command in front of the kernel.  The tensor-core pass reads all
         // queries from device memory, so a batch is uploaded as before.

@@ -212,7 +212,7 @@ int launch_shard(ragstore* sh, SearchCtx& c, int64_t n, int req, const float* h_
     for (int i = 0; i < count; ++i) {
         const int q = which ? (*which)[i] : i;
         // a shadowed fp32 shard answers from its bf16 image first; the redo pass (kp_force) is the fp32 scan
-        const bool from_shadow = kp_force <= 0 && sh->shadow != nullptr && sh->dtype == RAGSTORE_F32;
+        const bool from_shadow = kp_force <= 0 && shadow_scan_pays(sh, n);
         ScanArgs a = from_shadow ? shadow_scan_args(sh, n, take, shadow_scan_kp(take)) : base_args(sh, n, take, kp);
         a.d_query = in_params ? nullptr : h2d_src + static_cast<size_t>(q) * sh->dim;
         a.scratch = c.scratch;

@@ -135,6 +135,7 @@ ScanArgs base_args(const ragstore* s, int64_t n, int take, int kp);
 // queries with base_args().
 ScanArgs shadow_scan_args(const ragstore* s, int64_t n, int take, int kp);
 int shadow_scan_kp(int take);
+bool shadow_scan_pays(const ragstore* s, int64_t n);
 float batch_eps(const ragstore* s);
 bool batch_eligible(const ragstore* s, int64_t n, int nq, int kp);
 // store views, candidate-set size, error bound and tensor-core operand of one batched launch (outputs left to the caller)

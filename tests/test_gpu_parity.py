@@ -1239,7 +1239,7 @@ def test_rag_index_mirror_over_several_shards():
         one.close(), many.close()
 
 
-@pytest.mark.parametrize("n,d,k", [(40000, 768, 10), (20000, 1024, 100), (9000, 64, 5), (3000, 256, 300)])
+@pytest.mark.parametrize("n,d,k", [(60000, 768, 10), (40000, 1024, 100), (9000, 64, 5), (3000, 256, 300)])
 def test_single_queries_on_a_shadowed_store_scan_the_bf16_image(n, d, k):
     """With RAGSTORE_CREATE_BF16_SHADOW a single query streams the bf16 image (half the bytes) and rescoring reads the fp32
     rows: hits and scores must be exactly those of the plain fp32 store -- including rows crowded closer than the bf16
