@@ -1260,3 +1260,32 @@ def test_single_queries_on_a_shadowed_store_scan_the_bf16_image(n, d, k):
             assert found[0] == len(eidx) and list(idx[0, :found[0]]) == list(eidx), i
             assert np.array_equal(sc[0, :found[0]].view(np.uint64), esc.view(np.uint64)), i
             assert flags[0] & rb.RAGSTORE_HIT_EXACT_ROWS
+
+
+@pytest.mark.parametrize("k", [10, 60])
+def test_wild_values_on_a_shadowed_store(k):
+    """Rows of wildly different lengths (1e-12 .. 1e12), zero rows, duplicates, a few non-finite rows, queries of any
+    length -- through every path a shadowed store has: batches on the bf16 image, single queries on the bf16 image
+    (large enough corpus), both rescored from the originals.  Everything must equal the oracle, NaN scores last."""
+    rng = np.random.default_rng(1234 + k)
+    n, d, nq = 300000, 128, 24           # 300k x 128 x 2 B = 77 MB of image: single queries take the image scan
+    rows = rng.standard_normal((n, d)).astype(np.float32)
+    rows *= (10.0 ** rng.uniform(-12, 12, size=(n, 1))).astype(np.float32)
+    rows[rng.integers(0, n, 50)] = 0.0
+    rows[100] = rows[7]
+    rows[5, 3] = np.inf
+    rows[6, 0] = np.nan
+    qs = (rng.standard_normal((nq, d)) * 10.0 ** rng.uniform(-5, 5, size=(nq, 1))).astype(np.float32)
+    qs[3] = rows[7] / np.float32(np.linalg.norm(rows[7].astype(np.float64)))     # ranks the duplicated pair first: tie -> lower id
+    with rb.RagStore(d, n, rb.RAGSTORE_F32, 0, rb.RAGSTORE_CREATE_BF16_SHADOW) as st:
+        st.add(rows)
+        idx, sc, found, flags = st.search(qs, k)
+        assert st.info()["batch_launches"] >= 1
+        singles = [st.search(qs[i], k) for i in (0, 3, 11)]
+    for j, i in enumerate((0, 3, 11)):
+        with np.errstate(all="ignore"):
+            eidx, esc = oc.query(rows, qs[i], k, n_threads=8)
+        for got_i, got_s in ((idx[i], sc[i]), (singles[j][0][0], singles[j][1][0])):
+            assert list(got_i) == list(eidx), i
+            assert np.array_equal(got_s.view(np.uint64), esc.view(np.uint64)), i
+    assert list(idx[3][:2]) == [7, 100]
